@@ -157,3 +157,343 @@ static void build_world(World& w, uint64_t seed, int nGenes) {
   double acc = 0;
   for (auto& G : w.genes) { acc += G.expr; w.cumExpr.push_back(acc); }
 }
+
+// ---------------------------------------------------------------- annotation files
+static std::string exon_key(const World& w, const Gene& G, int k) {     // map key (no gene prefix)
+  return fmt("%s/%d/%d/%c", w.chrs[G.chr].c_str(), G.ex[k].s, G.ex[k].e, G.strand);
+}
+static FILE* xopen(const std::string& p, const char* m) {
+  FILE* f = fopen(p.c_str(), m);
+  if (!f) { fprintf(stderr, "worldgen: cannot open %s\n", p.c_str()); exit(1); }
+  return f;
+}
+
+static void write_annotation(const World& w, const std::string& dir, uint64_t seed, int nGenes) {
+  const std::string base = dir + "/ensembl_rna_hs";
+  FILE* fs = xopen(dir + "/world.seed", "w"); fprintf(fs, "%llu %d\n", (unsigned long long)seed, nGenes); fclose(fs);
+  FILE* fai = xopen(dir + "/genome.fa.fai", "w");
+  for (int c = 0; c < w.nWhite; c++) fprintf(fai, "%s\t%d\t0\t60\t61\n", w.chrs[c].c_str(), w.chrLen[c]);
+  fclose(fai);
+  FILE* bed = xopen(base + fmt("_%d_combined_exons.bed", RADIUS), "w");
+  FILE* tbed = xopen(base + "_transcript_exons.bed", "w");
+  // transcript rows: exons in transcript (5'->3') order, transcript coordinates, 0-based half-open
+  for (auto& T : w.trs) {
+    const Gene& G = w.genes[T.gene]; int off = 0; int n = (int)T.ex.size();
+    for (int i = 0; i < n; i++) {
+      int k = G.strand == '+' ? T.ex[i] : T.ex[n - 1 - i];
+      int len = G.ex[k].e - G.ex[k].s + 1;
+      fprintf(bed, "%s\t%d\t%d\t%s/%s\t0\t%c\n", T.id.c_str(), off, off + len, G.id.c_str(), exon_key(w, G, k).c_str(), G.strand);
+      fprintf(tbed, "%s\t%d\t%d\t%s/%s\t0\t%c\n", T.id.c_str(), off, off + len, G.id.c_str(), exon_key(w, G, k).c_str(), G.strand);
+      off += len;
+    }
+  }
+  // junction rows: pieces in genome order, junction coordinates
+  for (auto& J : w.jrs) {
+    const Gene& G = w.genes[J.gene]; int off = 0;
+    for (size_t p = 0; p < J.pex.size(); p++) {
+      int len = J.pe[p] - J.ps[p] + 1;
+      fprintf(bed, "%s\t%d\t%d\t%s/%s\t0\t+\n", J.id.c_str(), off, off + len, G.id.c_str(), exon_key(w, G, J.pex[p]).c_str());
+      off += len;
+    }
+  }
+  // genome rows: one per distinct (chr,start,end,strand); first gene wins (avoids SURVEY H5 corner)
+  {
+    std::vector<std::string> seen;
+    std::vector<std::pair<std::string, std::string>> rows;
+    for (auto& G : w.genes) for (size_t k = 0; k < G.ex.size(); k++) {
+      std::string key = exon_key(w, G, (int)k);
+      rows.push_back({key, fmt("%s\t%d\t%d\t%s/%s\t0\t%c\n", w.chrs[G.chr].c_str(), G.ex[k].s - 1, G.ex[k].e, G.id.c_str(), key.c_str(), G.strand)});
+    }
+    std::stable_sort(rows.begin(), rows.end(), [](auto& a, auto& b) { return a.first < b.first; });
+    for (size_t i = 0; i < rows.size(); i++)
+      if (i == 0 || rows[i].first != rows[i - 1].first) fputs(rows[i].second.c_str(), bed);
+  }
+  fclose(bed); fclose(tbed);
+  FILE* eg = xopen(base + "_exon_gene.map", "w"); FILE* ee = xopen(base + "_exon_exon.map", "w");
+  fprintf(eg, "Exon Id\tGene Id\n"); fprintf(ee, "Exon Id\tExon Id\n");
+  int exonNo = 0;
+  for (auto& G : w.genes) for (size_t k = 0; k < G.ex.size(); k++) {
+    std::string key = exon_key(w, G, (int)k);
+    fprintf(eg, "%s\t%s\n", key.c_str(), G.id.c_str());
+    fprintf(ee, "%s\tENSE%011d\n", key.c_str(), ++exonNo);
+  }
+  fclose(eg); fclose(ee);
+  FILE* ej = xopen(base + "_exon_junction.map", "w"); FILE* ejt = xopen(base + "_exon_junction_transcript.map", "w");
+  FILE* jj = xopen(base + fmt("_%d_junction_junction_coordinate.map", RADIUS), "w");
+  FILE* eq = xopen(base + "_equivalent_junctions.map", "w");
+  std::vector<std::pair<std::string, std::string>> extByCoord;         // (coord w/o strand, ext id)
+  for (auto& J : w.jrs) {
+    const Gene& G = w.genes[J.gene];
+    for (int k : {J.a, J.b}) {
+      fprintf(ej, "%s\t%s\n", exon_key(w, G, k).c_str(), J.ext.c_str());
+      if (J.annotated) fprintf(ejt, "%s\t%s\n", exon_key(w, G, k).c_str(), J.ext.c_str());
+    }
+    fprintf(jj, "%s-junction-%02d-%02d:%s:%d:%d\t%s\n", G.id.c_str(), J.a + 1, J.b + 1, w.chrs[G.chr].c_str(), G.ex[J.a].e, G.ex[J.b].s, J.ext.c_str());
+    extByCoord.push_back({fmt("%s_%d_%d", w.chrs[G.chr].c_str(), G.ex[J.a].e, G.ex[J.b].s), J.ext});
+  }
+  std::sort(extByCoord.begin(), extByCoord.end());
+  for (size_t i = 0; i + 1 < extByCoord.size(); i++)
+    if (extByCoord[i].first == extByCoord[i + 1].first && extByCoord[i].second != extByCoord[i + 1].second) {
+      fprintf(eq, "%s\t%s\n", extByCoord[i].second.c_str(), extByCoord[i + 1].second.c_str());
+      fprintf(eq, "%s\t%s\n", extByCoord[i + 1].second.c_str(), extByCoord[i].second.c_str());
+    }
+  fclose(ej); fclose(ejt); fclose(jj); fclose(eq);
+}
+
+// ---------------------------------------------------------------- read placement
+struct Blk { int ex, gs, ge; };                       // exon idx, genome start/end (1-based closed)
+struct Place { int gene, tr, go; std::vector<Blk> b; };   // go: offset in genomic-order transcript coords
+
+// Footprint of `span` reference bases at genomic-order offset `go` of transcript T.
+static bool place(const World& w, int ti, int go, int span, Place& P) {
+  const Transcript& T = w.trs[ti]; const Gene& G = w.genes[T.gene];
+  if (go < 0 || go + span > T.len) return false;
+  P.gene = T.gene; P.tr = ti; P.go = go; P.b.clear();
+  int off = 0, need = span;
+  for (int k : T.ex) {
+    int len = G.ex[k].e - G.ex[k].s + 1;
+    if (go < off + len && need > 0) {
+      int s = G.ex[k].s + std::max(0, go - off);
+      int e = std::min(G.ex[k].e, s + need - 1);
+      P.b.push_back({k, s, e}); need -= e - s + 1;
+    }
+    off += len;
+  }
+  return need == 0;
+}
+// Offset of the same genomic footprint in another transcript of the gene, or -1.
+static int iso_offset(const World& w, int ti, const Place& P) {
+  const Transcript& T = w.trs[ti]; const Gene& G = w.genes[T.gene];
+  int off = 0; size_t j = 0; int res = -1;
+  for (size_t i = 0; i < T.ex.size(); i++) {
+    int k = T.ex[i]; int len = G.ex[k].e - G.ex[k].s + 1;
+    if (j < P.b.size() && k == P.b[j].ex) {
+      if (j == 0) res = off + (P.b[0].gs - G.ex[k].s);
+      j++;
+      if (j == P.b.size()) return res;
+    } else if (j > 0) return -1;                       // blocks must sit in consecutive exons
+    off += len;
+  }
+  return -1;
+}
+// Offset of the footprint inside junction reference J, or -1.
+static int jref_offset(const JRef& J, const Place& P) {
+  int off = 0;
+  for (size_t p = 0; p < J.pex.size(); p++) {
+    if (J.pex[p] == P.b[0].ex && P.b[0].gs >= J.ps[p] && P.b[0].ge <= J.pe[p]) {
+      int res = off + (P.b[0].gs - J.ps[p]);
+      for (size_t j = 1; j < P.b.size(); j++) {
+        size_t q = p + j;
+        if (q >= J.pex.size() || J.pex[q] != P.b[j].ex || P.b[j].gs != J.ps[q] || P.b[j].ge > J.pe[q]) return -1;
+        if (P.b[j - 1].ge != J.pe[q - 1]) return -1;
+      }
+      return res;
+    }
+    off += J.pe[p] - J.ps[p] + 1;
+  }
+  return -1;
+}
+
+// ---------------------------------------------------------------- SAM emission
+struct Out {
+  std::string buf; FILE* f;
+  void flush() { if (!buf.empty()) { fwrite(buf.data(), 1, buf.size(), f); buf.clear(); } }
+};
+static char g_seq[1 << 16], g_qual[1 << 16];
+struct ReadShape { const char* cigar; int span; int nmExtra; };
+static const ReadShape SHAPES[4] = {{"101M", 101, 0}, {"50M1I50M", 100, 1}, {"50M1D51M", 102, 1}, {"98M3S", 98, 0}};
+
+static void emit(Out& o, int frag, int flag, const char* rname, int pos, const char* cigar,
+                 const char* rnext, int pnext, int tlen, int nm, int seqOff) {
+  char line[700];
+  int n;
+  if (flag & 4)
+    n = snprintf(line, sizeof line, "F%09d\t%d\t*\t0\t0\t*\t*\t0\t0\t%.*s\t%.*s\tYT:Z:U%c\n", frag, flag,
+                 READ_LEN, g_seq + seqOff, READ_LEN, g_qual + seqOff, (flag & 1) ? 'P' : 'U');
+  else
+    n = snprintf(line, sizeof line, "F%09d\t%d\t%s\t%d\t%d\t%s\t%s\t%d\t%d\t%.*s\t%.*s\tAS:i:%d\tXN:i:0\tXM:i:%d\tXO:i:0\tXG:i:0\tNM:i:%d\tMD:Z:%d\tYT:Z:U%c\n",
+                 frag, flag, rname, pos, nm == 0 ? 42 : 1, cigar, rnext, pnext, tlen,
+                 READ_LEN, g_seq + seqOff, READ_LEN, g_qual + seqOff, -6 * nm, nm, nm, READ_LEN, (flag & 1) ? 'P' : 'U');
+  o.buf.append(line, n);
+  if (o.buf.size() > (1u << 22)) o.flush();
+}
+
+static int pick_gene(const World& w, Rng& r) {
+  double x = r.uni() * w.cumExpr.back();
+  return (int)(std::lower_bound(w.cumExpr.begin(), w.cumExpr.end(), x) - w.cumExpr.begin());
+}
+static int draw_nm(Rng& r) { double u = r.uni(); return u < 0.67 ? 0 : u < 0.94 ? 1 : u < 0.99 ? 2 : 3; }
+
+struct Aln { std::string ref; int pos, rev, nm; };
+struct MateAlns { std::vector<Aln> t, j, g; };
+
+// All alignments a bowtie2 -k run would report for footprint P of one locus.
+static void locus_alns(const World& w, const Place& P, int span, int rv, bool boundaryJ, int nm, MateAlns& M) {
+  const Gene& G = w.genes[P.gene]; int gflip = (G.strand == '-');
+  for (int ti : G.tr) {
+    int off = iso_offset(w, ti, P);
+    if (off < 0) continue;
+    int o = gflip ? w.trs[ti].len - off - span : off;
+    M.t.push_back({w.trs[ti].id, o + 1, rv, nm});
+  }
+  if (P.b.size() == 1) M.g.push_back({w.chrs[G.chr], P.b[0].gs, rv ^ gflip, nm});
+  int nb = 0;
+  for (int ji : G.jr) {
+    const JRef& J = w.jrs[ji];
+    if (P.b.size() == 1 && (!boundaryJ || nb >= 4)) continue;
+    int off = jref_offset(J, P);
+    if (off < 0 || off + span > J.len) continue;
+    M.j.push_back({J.id, off + 1, rv ^ gflip, nm});
+    if (P.b.size() == 1) nb++;
+  }
+}
+
+static bool random_place(const World& w, Rng& r, int span, Place& P, int gene = -1) {
+  for (int attempt = 0; attempt < 50; attempt++) {
+    int g = gene >= 0 ? gene : pick_gene(w, r);
+    const Gene& G = w.genes[g];
+    int ti = G.tr[r.below((int)G.tr.size())];
+    if (w.trs[ti].len < span) { if (gene >= 0 && attempt > 10) return false; continue; }
+    if (place(w, ti, r.below(w.trs[ti].len - span + 1), span, P)) return true;
+  }
+  return false;
+}
+
+static void emit_file(Out& o, int frag, bool pe, std::vector<Aln>* a, size_t cap, const char* cigar[2], int seqOff[2]) {
+  if (!pe) {
+    if (a[0].empty()) { emit(o, frag, 4, "*", 0, "*", "*", 0, 0, 0, seqOff[0]); return; }
+    for (size_t i = 0; i < a[0].size() && i < cap; i++)
+      emit(o, frag, a[0][i].rev ? 16 : 0, a[0][i].ref.c_str(), a[0][i].pos, cigar[0], "*", 0, 0, a[0][i].nm, seqOff[0]);
+    return;
+  }
+  std::vector<char> used0(a[0].size(), 0), used1(a[1].size(), 0);
+  size_t n = 0;
+  for (size_t i = 0; i < a[0].size() && n < cap; i++)
+    for (size_t k = 0; k < a[1].size(); k++) {
+      if (used1[k] || a[1][k].ref != a[0][i].ref) continue;
+      int d = a[1][k].pos - a[0][i].pos;
+      if (d < -500 || d > 500) continue;
+      const Aln &x = a[0][i], &y = a[1][k];
+      int tl = d >= 0 ? d + READ_LEN : d - READ_LEN;
+      emit(o, frag, 1 + 2 + 64 + (x.rev ? 16 : 0) + (y.rev ? 32 : 0), x.ref.c_str(), x.pos, cigar[0], "=", y.pos, tl, x.nm, seqOff[0]);
+      emit(o, frag, 1 + 2 + 128 + (y.rev ? 16 : 0) + (x.rev ? 32 : 0), y.ref.c_str(), y.pos, cigar[1], "=", x.pos, -tl, y.nm, seqOff[1]);
+      used0[i] = used1[k] = 1; n++;
+      break;
+    }
+  bool any[2] = {n > 0, n > 0};
+  for (int m = 0; m < 2; m++) {
+    std::vector<char>& used = m ? used1 : used0; size_t c = 0;
+    for (size_t i = 0; i < a[m].size() && c < cap && n == 0; i++) {     // bowtie2 reports unpaired hits only without a concordant pair
+      if (used[i]) continue;
+      emit(o, frag, 1 + 8 + (m ? 128 : 64) + (a[m][i].rev ? 16 : 0), a[m][i].ref.c_str(), a[m][i].pos, cigar[m], "*", 0, 0, a[m][i].nm, seqOff[m]);
+      any[m] = true; c++;
+    }
+  }
+  for (int m = 0; m < 2; m++)
+    if (!any[m]) emit(o, frag, 1 + 4 + (m ? 128 : 64) + (any[1 - m] ? 0 : 8), "*", 0, "*", "*", 0, 0, 0, seqOff[m]);
+}
+
+static void gen_reads(const World& w, const std::string& dir, uint64_t seed, int first, int n, bool pe, double splicedBoost) {
+  Rng init(seed ^ 0xABCDEFULL);
+  for (size_t i = 0; i < sizeof g_seq; i++) { g_seq[i] = "ACGT"[init.below(4)]; g_qual[i] = (char)(35 + init.below(38)); }
+  const char* sfx = pe ? "pe" : "sr";
+  Out T{"", xopen(dir + "/transcript-" + sfx + ".sam", "w")};
+  Out J{"", xopen(dir + "/junction-" + sfx + ".sam", "w")};
+  Out Gn{"", xopen(dir + "/genome-" + sfx + ".sam", "w")};
+  if (first == 1) {                                    // header only in chunk C001 (bowtie2-align.sh:462-467)
+    T.buf += "@HD\tVN:1.0\tSO:unsorted\n@PG\tID:bowtie2\tPN:bowtie2\tVN:2.0.5\n";
+    J.buf += "@HD\tVN:1.0\tSO:unsorted\n@PG\tID:bowtie2\tPN:bowtie2\tVN:2.0.5\n";
+  }
+  std::vector<int> novel;                              // junction refs that no transcript contains
+  for (size_t i = 0; i < w.jrs.size(); i++) if (!w.jrs[i].annotated) novel.push_back((int)i);
+  for (int f = 0; f < n; f++) {
+    int frag = first + f;
+    Rng r(seed * 1000003ULL + (uint64_t)frag);          // per-fragment stream: chunks are independent
+    MateAlns M[2];
+    int shape[2] = {0, 0};
+    for (int m = 0; m < 2; m++) { double u = r.uni(); shape[m] = u < 0.96 ? 0 : u < 0.97 ? 1 : u < 0.98 ? 2 : 3; }
+    const char* cigar[2] = {SHAPES[shape[0]].cigar, SHAPES[shape[1]].cigar};
+    int span[2] = {SHAPES[shape[0]].span, SHAPES[shape[1]].span};
+    int seqOff[2] = {r.below(60000), r.below(60000)};
+    int nMates = pe ? 2 : 1;
+    double cat = r.uni();
+    if (cat < 0.03) {
+      // unaligned everywhere
+    } else if (cat < 0.08) {                           // intronic / intergenic: genome only
+      const Gene& G = w.genes[pick_gene(w, r)];
+      int lo = std::max(1, G.ex.front().s - 300), hi = G.ex.back().e + 300;
+      int p = lo + r.below(hi - lo + 1), rv = r.below(2);
+      M[0].g.push_back({w.chrs[G.chr], p, rv, draw_nm(r)});
+      if (pe && r.uni() < 0.8) M[1].g.push_back({w.chrs[G.chr], p + 100 + r.below(250), 1 - rv, draw_nm(r)});
+    } else if (cat < 0.12 && !novel.empty()) {         // novel junction: junction reference only
+      const JRef& Jr = w.jrs[novel[r.below((int)novel.size())]];
+      int joint = 0; for (size_t p = 0; p < Jr.pex.size() && Jr.pex[p] != Jr.b; p++) joint += Jr.pe[p] - Jr.ps[p] + 1;
+      int lo = std::max(0, joint - span[0] + 8), hi = std::min(joint - 8, Jr.len - span[0]);
+      if (hi >= lo) M[0].j.push_back({Jr.id, lo + r.below(hi - lo + 1) + 1, r.below(2), draw_nm(r)});
+      if (pe && r.uni() < 0.5) {                       // mate 2 from a transcript of the same gene
+        Place P; if (random_place(w, r, span[1], P, Jr.gene)) locus_alns(w, P, span[1], r.below(2), false, draw_nm(r), M[1]);
+      }
+    } else {                                           // transcript-derived, maybe multi-mapped
+      int nLoci = 1; double u = r.uni();
+      if (u < 0.10) nLoci = 2 + r.below(4); else if (u < 0.115) nLoci = 6 + r.below(15);
+      bool wantSpliced = r.uni() < splicedBoost;
+      for (int l = 0; l < nLoci; l++) {
+        Place P[2]; int rv = r.below(2); int nm0 = draw_nm(r) + (l > 0 ? r.below(2) : 0);
+        bool ok = false;
+        for (int attempt = 0; attempt < 8 && !ok; attempt++) {
+          if (!random_place(w, r, span[0], P[0])) continue;
+          ok = !wantSpliced || P[0].b.size() > 1 || attempt == 7;
+        }
+        if (!ok) continue;
+        bool boundaryJ = r.uni() < 0.5;
+        locus_alns(w, P[0], span[0], rv, boundaryJ, nm0 + SHAPES[shape[0]].nmExtra, M[0]);
+        if (pe && r.uni() > 0.06) {                    // 6%: only one mate aligns
+          const Transcript& Tr = w.trs[P[0].tr];
+          int ins = std::max(READ_LEN, std::min(500, (int)(300 + 50 * r.normal())));
+          int go2 = rv ^ (w.genes[P[0].gene].strand == '-') ? P[0].go - (ins - span[0]) : P[0].go + ins - span[1];
+          go2 = std::max(0, std::min(Tr.len - span[1], go2));
+          if (place(w, P[0].tr, go2, span[1], P[1]))
+            locus_alns(w, P[1], span[1], 1 - rv, boundaryJ, draw_nm(r) + SHAPES[shape[1]].nmExtra, M[1]);
+        }
+      }
+      if (r.uni() < 0.01) {                            // highly repetitive: many genome-only copies
+        int extra = 21 + r.below(100);
+        for (int e = 0; e < extra; e++) {
+          Place P; if (!random_place(w, r, span[0], P) || P.b.size() != 1) continue;
+          M[0].g.push_back({w.chrs[w.genes[P.gene].chr], P.b[0].gs, r.below(2), 1 + r.below(2)});
+        }
+      }
+      if (pe && r.uni() < 0.03) {                      // mates best in different files (CombineSamFiles.java:312-349)
+        M[1] = MateAlns(); M[0].g.clear(); M[0].j.clear();
+        const Gene& G = w.genes[pick_gene(w, r)];
+        M[1].g.push_back({w.chrs[G.chr], std::max(1, G.ex.front().s - 200 + r.below(400)), r.below(2), 0});
+      }
+    }
+    std::vector<Aln> a[2];
+    a[0] = M[0].t; a[1] = M[1].t; emit_file(T, frag, pe, a, 2000, cigar, seqOff);
+    a[0] = M[0].j; a[1] = M[1].j; emit_file(J, frag, pe, a, 400, cigar, seqOff);
+    a[0] = M[0].g; a[1] = M[1].g; emit_file(Gn, frag, pe, a, 100, cigar, seqOff);
+    (void)nMates;
+  }
+  T.flush(); J.flush(); Gn.flush(); fclose(T.f); fclose(J.f); fclose(Gn.f);
+}
+
+int main(int argc, char** argv) {
+  if (argc >= 5 && !strcmp(argv[1], "anno")) {
+    World w; uint64_t seed = strtoull(argv[3], 0, 10); int ng = atoi(argv[4]);
+    build_world(w, seed, ng); write_annotation(w, argv[2], seed, ng);
+    fprintf(stderr, "worldgen: %zu genes, %zu transcripts, %zu junction references\n", w.genes.size(), w.trs.size(), w.jrs.size());
+    return 0;
+  }
+  if (argc >= 8 && !strcmp(argv[1], "reads")) {
+    unsigned long long seed; int ng;
+    FILE* fs = xopen(std::string(argv[2]) + "/world.seed", "r");
+    if (fscanf(fs, "%llu %d", &seed, &ng) != 2) return 1;
+    fclose(fs);
+    World w; build_world(w, seed, ng);
+    gen_reads(w, argv[3], strtoull(argv[4], 0, 10), atoi(argv[5]), atoi(argv[6]), !strcmp(argv[7], "pe"), argc > 8 ? atof(argv[8]) : 0.0);
+    return 0;
+  }
+  fprintf(stderr, "usage: worldgen anno <outdir> <seed> <n_genes> | reads <annodir> <outdir> <seed> <first_frag> <n_frags> <se|pe> [spliced_frac]\n");
+  return 2;
+}
