@@ -82,8 +82,8 @@ static void build_world(World& w, uint64_t seed, int nGenes) {
     w.chrs.push_back(c < 22 ? fmt("chr%d", c + 1) : c == 22 ? "chrX" : c == 23 ? "chrY" : "chrM");
     w.chrLen.push_back(0);
   }
-  w.nWhite = nChr;                                    // scaffolds below are NOT in genome.fa.fai
   w.chrs.push_back("GL000191.1"); w.chrLen.push_back(0);
+  w.nWhite = nChr + 1;                                // the decoy used for repeat copies is NOT in genome.fa.fai
   std::vector<int> cursor(w.chrs.size(), 10000), lastOnChr(w.chrs.size(), -1);
   for (int g = 0; g < nGenes; g++) {
     Gene G; G.id = fmt("ENSG%011d", g + 1);
@@ -460,7 +460,8 @@ static void gen_reads(const World& w, const std::string& dir, uint64_t seed, int
         int extra = 21 + r.below(100);
         for (int e = 0; e < extra; e++) {
           Place P; if (!random_place(w, r, span[0], P) || P.b.size() != 1) continue;
-          M[0].g.push_back({w.chrs[w.genes[P.gene].chr], P.b[0].gs, r.below(2), 1 + r.below(2)});
+          bool decoy = r.uni() < 0.1;                    // exercises the -c whitelist (ComputeReadWeightsSam.java:168-172)
+          M[0].g.push_back({decoy ? std::string("GL000999.1_decoy") : w.chrs[w.genes[P.gene].chr], P.b[0].gs, r.below(2), 1 + r.below(2)});
         }
       }
       if (pe && r.uni() < 0.03) {                      // mates best in different files (CombineSamFiles.java:312-349)
