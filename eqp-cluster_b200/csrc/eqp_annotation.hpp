@@ -1,0 +1,234 @@
+// Host-side annotation loader: parses the files compute-counts.sh reads and builds the device index
+// (reference-name hash table, bucketed sorted interval index, exon -> feature CSR lists, a27 activation lists).
+// Mirrors: ConvertSamBed.loadBedFile (J/sam-source/ConvertSamBed.java:47-98), Exon.loadCountObjectFile
+// (J/bed-source/Exon.java:70-152), Exon(String,String) (:230-301), ComputeReadWeightsSam.readChromosomeNames (:44-58),
+// filter-junction-map-files.sh:254-304 + createExtendedJunctionIds.py:93-114 + filterFile.py:131-194.
+#pragma once
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <set>
+#include <stdexcept>
+#include <string>
+#include <unordered_map>
+#include <unordered_set>
+#include <vector>
+#include "eqp_types.h"
+
+namespace eqpb {
+
+EQP_HD uint64_t fnv1a(const char* p, int n) {
+  uint64_t h = 1469598103934665603ULL;
+  for (int i = 0; i < n; i++) { h ^= (uint8_t)p[i]; h *= 1099511628211ULL; }
+  return h ? h : 1;                                   // 0 marks an empty slot
+}
+
+struct AnnoError : std::runtime_error { int code; AnnoError(int c, const std::string& m) : std::runtime_error(m), code(c) {} };
+
+struct AnnoHost {
+  std::vector<uint64_t> dictHash; std::vector<int32_t> dictVal; uint32_t dictMask = 0;
+  std::string strPool; std::vector<uint32_t> refStrOff; std::vector<uint16_t> refStrLen; std::vector<uint8_t> refFlags;
+  std::vector<uint32_t> refVerOff; std::vector<int32_t> refVerBucket;
+  std::vector<uint32_t> refActOff; std::vector<int32_t> refAct;
+  std::vector<uint32_t> bktRowOff; std::vector<uint8_t> bktFlags;
+  std::vector<int32_t> rowStart, rowEnd, rowMaxEnd, rowExon; std::vector<uint8_t> rowFlags;
+  std::vector<int32_t> exChr, exStart, exEnd; std::vector<uint8_t> exStrand;
+  std::vector<uint32_t> featOff[3], feat[3]; std::vector<std::string> featIds[3];
+  std::vector<std::string> chrNames, bucketNames;
+
+  static std::string slurp(const char* path) {
+    if (!path) throw AnnoError(-1, "annotation path is null");
+    FILE* f = fopen(path, "rb");
+    if (!f) throw AnnoError(-3, std::string("Warning: file ") + path + " not found.");
+    std::string s; char buf[1 << 16]; size_t n;
+    while ((n = fread(buf, 1, sizeof buf, f)) > 0) s.append(buf, n);
+    fclose(f); return s;
+  }
+  template <class F> static void lines(const std::string& s, F&& fn) {
+    size_t p = 0;
+    while (p < s.size()) {
+      size_t e = s.find('\n', p); if (e == std::string::npos) e = s.size();
+      size_t l = e; if (l > p && s[l - 1] == '\r') l--;
+      fn(s.substr(p, l - p)); p = e + 1;
+    }
+  }
+  static std::vector<std::string> splitc(const std::string& s, char c) {
+    std::vector<std::string> o; size_t p = 0;
+    while (true) { size_t e = s.find(c, p); if (e == std::string::npos) { o.push_back(s.substr(p)); break; } o.push_back(s.substr(p, e - p)); p = e + 1; }
+    return o;
+  }
+  static std::vector<std::string> tok(const std::string& s, char c) {   // StringTokenizer
+    std::vector<std::string> o; for (auto& t : splitc(s, c)) if (!t.empty()) o.push_back(t); return o;
+  }
+  static std::string stripVersion(const std::string& s) {               // Pattern "[.][0-9]+$"
+    size_t d = s.rfind('.'); if (d == std::string::npos || d + 1 >= s.size()) return s;
+    for (size_t i = d + 1; i < s.size(); i++) if (s[i] < '0' || s[i] > '9') return s;
+    return s.substr(0, d);
+  }
+  struct ExonKey { std::string chr; int s, e; char strand; bool tr; };
+  static ExonKey parseExon(const std::string& id) {                     // Exon.java:230-301
+    auto t = tok(id, '/');
+    if (t.size() < 3 || t.size() > 5) throw AnnoError(-3, "Less than three fields are separated by / in exon: " + id);
+    size_t o = t.size() == 5 ? 1 : 0; ExonKey k;
+    k.chr = t[o]; k.s = atoi(t[o + 1].c_str()); k.e = atoi(t[o + 2].c_str()); k.strand = t.size() >= 4 ? t[o + 3][0] : '+';
+    if (k.s == 0) k.s = 1;
+    k.tr = k.chr.compare(0, 3, "tr-") == 0;
+    if (k.tr) k.chr = stripVersion(k.chr);
+    return k;
+  }
+  static std::string keyStr(const ExonKey& k) { return k.chr + "/" + std::to_string(k.s) + "/" + std::to_string(k.e) + "/" + k.strand; }
+
+  int32_t addRef(std::unordered_map<std::string, int32_t>& idx, const std::string& name) {
+    auto it = idx.find(name); if (it != idx.end()) return it->second;
+    int32_t r = (int32_t)refStrOff.size(); idx[name] = r;
+    refStrOff.push_back((uint32_t)strPool.size()); refStrLen.push_back((uint16_t)name.size()); strPool += name; refFlags.push_back(0);
+    return r;
+  }
+
+  void load(const char* combinedBed, const char* transcriptBed, const char* geneMap, const char* exonMap, const char* junctionMap,
+            const char* junctionTranscriptMap, const char* jjCoordinateMap, const char* equivalentsMap, const char* fai) {
+    // ---- B file: buckets, rows, distinct exons.  Rows equal in (start,end,strand) keep file order, so the device-side
+    // first-wins dedupe (TreeSet<BedRecord>, BedRecord.java:351-387) can pick the lowest row index.
+    std::unordered_map<std::string, int32_t> bucketIdx, exonIdx, chrIdxTmp;
+    struct Row { int s, e, exon; char strand; size_t file; };
+    std::vector<std::vector<Row>> rows; std::vector<ExonKey> exons;
+    { std::string b = slurp(combinedBed); size_t fileIdx = 0;
+      lines(b, [&](const std::string& l) {
+        if (l.empty()) return;
+        auto t = splitc(l, '\t'); if (t.size() < 6) throw AnnoError(-3, "Too few BED entries in " + std::string(combinedBed));
+        auto bi = bucketIdx.find(t[0]);
+        if (bi == bucketIdx.end()) { bi = bucketIdx.emplace(t[0], (int32_t)rows.size()).first; rows.emplace_back(); bucketNames.push_back(t[0]); }
+        ExonKey k = parseExon(t[3]);
+        std::string ks = keyStr(k);
+        auto ei = exonIdx.find(ks);
+        if (ei == exonIdx.end()) { ei = exonIdx.emplace(ks, (int32_t)exons.size()).first; exons.push_back(k); }
+        rows[bi->second].push_back({atoi(t[1].c_str()), atoi(t[2].c_str()), ei->second, t[5].empty() ? '.' : t[5][0], fileIdx++});
+      }); }
+    { std::set<std::string> chrs; for (auto& k : exons) if (!k.tr) chrs.insert(k.chr);
+      for (auto& c : chrs) { chrIdxTmp[c] = (int32_t)chrNames.size(); chrNames.push_back(c); } }
+    for (auto& k : exons) { exChr.push_back(k.tr ? -2 : chrIdxTmp[k.chr]); exStart.push_back(k.s); exEnd.push_back(k.e); exStrand.push_back((uint8_t)k.strand); }
+    bktRowOff.push_back(0);
+    for (size_t b = 0; b < rows.size(); b++) {
+      auto& v = rows[b];
+      std::stable_sort(v.begin(), v.end(), [](const Row& x, const Row& y) { return x.s != y.s ? x.s < y.s : x.e != y.e ? x.e < y.e : x.strand != y.strand ? x.strand < y.strand : x.file < y.file; });
+      const std::string& name = bucketNames[b];
+      bool inv = name.size() > 11 && name.compare(name.size() - 11, 11, ".inv-strand") == 0;
+      bktFlags.push_back((name.find("junction") != std::string::npos ? 1 : 0) | (inv ? 2 : 0));
+      int maxEnd = 0;
+      for (size_t i = 0; i < v.size(); i++) {
+        maxEnd = std::max(maxEnd, v[i].e);
+        rowStart.push_back(v[i].s); rowEnd.push_back(v[i].e); rowMaxEnd.push_back(maxEnd); rowExon.push_back(v[i].exon);
+        rowFlags.push_back((!exons[v[i].exon].tr && exons[v[i].exon].chr == name ? 1 : 0) | (v[i].strand == '+' ? 0 : v[i].strand == '-' ? 2 : 4));
+      }
+      bktRowOff.push_back((uint32_t)rowStart.size());
+    }
+    // ---- reference-name dictionary: bucket names, base ids of transcript_exons.bed, genome.fa.fai names
+    std::unordered_map<std::string, int32_t> refIdx;
+    std::map<std::string, std::vector<std::string>> versions;           // base id -> versioned ids, first-seen order
+    { std::string t = slurp(transcriptBed);
+      lines(t, [&](const std::string& l) {
+        auto f = tok(l, '\t'); if (f.empty()) return;
+        std::string ver = f[0], base = ver;
+        if (base.size() > 11 && base.compare(base.size() - 11, 11, ".inv-strand") == 0) base.resize(base.size() - 11);
+        size_t dot = base.rfind('.'); if (dot != std::string::npos && base.size() - dot <= 4) base.resize(dot);
+        auto& v = versions[base]; if (std::find(v.begin(), v.end(), ver) == v.end()) v.push_back(ver);
+      }); }
+    for (auto& n : bucketNames) addRef(refIdx, n);
+    for (auto& kv : versions) addRef(refIdx, kv.first);
+    { std::string f = slurp(fai); lines(f, [&](const std::string& l) { auto t = tok(l, '\t'); if (!t.empty()) refFlags[addRef(refIdx, t[0])] |= 1; }); }
+    int32_t nRef = (int32_t)refStrOff.size();
+    std::vector<std::string> refNames(nRef); for (auto& kv : refIdx) refNames[kv.second] = kv.first;
+    refVerOff.push_back(0);
+    for (int32_t r = 0; r < nRef; r++) {
+      auto vi = versions.find(refNames[r]);
+      if (vi != versions.end()) { for (auto& v : vi->second) { auto b = bucketIdx.find(v); if (b != bucketIdx.end()) refVerBucket.push_back(b->second); } }
+      else { auto b = bucketIdx.find(refNames[r]); if (b != bucketIdx.end()) refVerBucket.push_back(b->second); }
+      refVerOff.push_back((uint32_t)refVerBucket.size());
+    }
+    uint32_t cap = 16; while (cap < (uint32_t)nRef * 2u) cap <<= 1;
+    dictHash.assign(cap, 0); dictVal.assign(cap, -1); dictMask = cap - 1;
+    for (int32_t r = 0; r < nRef; r++) {
+      uint64_t h = fnv1a(refNames[r].data(), (int)refNames[r].size()); uint32_t s = (uint32_t)h & dictMask;
+      while (dictHash[s]) s = (s + 1) & dictMask;
+      dictHash[s] = h; dictVal[s] = r;
+    }
+    // ---- exon -> feature lists (2- or 3-column maps; 3-column maps are rejected for now)
+    const char* maps[3] = {geneMap, exonMap, junctionMap};
+    std::unordered_map<std::string, uint32_t> jFeatIdx;
+    for (int m = 0; m < 3; m++) {
+      std::string text = slurp(maps[m]); std::set<std::string> ids; std::vector<std::pair<std::string, std::string>> pairs;
+      std::set<std::pair<std::string, std::string>> always;
+      auto readMap = [&](const std::string& txt, bool isAlways) {
+        lines(txt, [&](const std::string& l) {
+          auto t = tok(l, '\t'); if (t.empty()) throw AnnoError(-3, "No exon id found.");
+          if (t[0] == "Exon Id") return;
+          if (t.size() < 2) throw AnnoError(-3, "No count object for exon " + t[0] + " found on loading.");
+          if (t.size() > 2) throw AnnoError(-5, "3-column count object maps are not supported yet");
+          std::string k = keyStr(parseExon(t[0]));
+          ids.insert(t[1]); pairs.push_back({k, t[1]}); if (isAlways) always.insert({k, t[1]});
+        });
+      };
+      readMap(text, false);
+      if (m == 2) readMap(slurp(junctionTranscriptMap), true);
+      featIds[m].assign(ids.begin(), ids.end());
+      std::unordered_map<std::string, uint32_t> fidx; for (size_t i = 0; i < featIds[m].size(); i++) fidx[featIds[m][i]] = (uint32_t)i;
+      if (m == 2) jFeatIdx = fidx;
+      std::vector<std::vector<uint32_t>> per(exons.size());
+      for (auto& pr : pairs) {
+        auto ei = exonIdx.find(pr.first); if (ei == exonIdx.end()) continue;   // exon never reachable through the B file
+        uint32_t f = fidx[pr.second] | (m == 2 && always.count(pr) ? 0x80000000u : 0u);
+        auto& v = per[ei->second]; bool have = false;
+        for (auto& x : v) if ((x & 0x7fffffffu) == (f & 0x7fffffffu)) { x |= f; have = true; }
+        if (!have) v.push_back(f);
+      }
+      featOff[m].push_back(0);
+      for (auto& v : per) { for (auto x : v) feat[m].push_back(x); featOff[m].push_back((uint32_t)feat[m].size()); }
+    }
+    // ---- a27: which junction features does a reference id seen in the chunk keep alive?
+    std::unordered_map<std::string, std::vector<std::string>> jjExt;    // internal junction id -> external ids
+    { std::string t = slurp(jjCoordinateMap);
+      lines(t, [&](const std::string& l) { auto c = splitc(l, ':'); auto f = splitc(l, '\t'); if (f.size() >= 2) jjExt[c[0]].push_back(f[1]); }); }
+    std::unordered_map<std::string, std::vector<std::string>> equiv;
+    { std::string t = slurp(equivalentsMap);
+      lines(t, [&](const std::string& l) { auto f = splitc(l, '\t'); if (f.size() >= 2) equiv[f[0]].push_back(f[1]); }); }
+    refActOff.push_back(0);
+    for (int32_t r = 0; r < nRef; r++) {
+      const std::string& name = refNames[r];
+      if (name.find('-') != std::string::npos) {
+        auto c = splitc(name, ':'); std::vector<std::string> j; if (c.size() == 3) j = splitc(c[0], '-');
+        if (c.size() != 3 || j.size() != 4) refFlags[r] |= 2;          // createExtendedJunctionIds.py would raise
+        else {
+          std::vector<std::string> idx;
+          if (!c[1].empty()) for (auto& x : splitc(c[1], '-')) idx.push_back(x);
+          idx.push_back(j[2]); idx.push_back(j[3]);
+          if (!c[2].empty()) for (auto& x : splitc(c[2], '-')) idx.push_back(x);
+          std::set<std::string> ext;
+          for (size_t i = 0; i + 1 < idx.size(); i++) {
+            auto e = jjExt.find(j[0] + "-" + j[1] + "-" + idx[i] + "-" + idx[i + 1]);
+            if (e != jjExt.end()) ext.insert(e->second.begin(), e->second.end());
+          }
+          std::set<std::string> all = ext;
+          for (auto& x : ext) { auto q = equiv.find(x); if (q != equiv.end()) all.insert(q->second.begin(), q->second.end()); }
+          for (auto& x : all) { auto f = jFeatIdx.find(x); if (f != jFeatIdx.end()) refAct.push_back((int32_t)f->second); }
+        }
+      }
+      refActOff.push_back((uint32_t)refAct.size());
+    }
+  }
+
+  AnnoView view() const {
+    AnnoView v{};
+    v.dictHash = dictHash.data(); v.dictVal = dictVal.data(); v.dictMask = dictMask; v.strPool = strPool.data();
+    v.refStrOff = refStrOff.data(); v.refStrLen = refStrLen.data(); v.refFlags = refFlags.data();
+    v.refVerOff = refVerOff.data(); v.refVerBucket = refVerBucket.data(); v.refActOff = refActOff.data(); v.refAct = refAct.data();
+    v.nRef = (int32_t)refStrOff.size();
+    v.bktRowOff = bktRowOff.data(); v.bktFlags = bktFlags.data(); v.nBucket = (int32_t)bktFlags.size();
+    v.rowStart = rowStart.data(); v.rowEnd = rowEnd.data(); v.rowMaxEnd = rowMaxEnd.data(); v.rowExon = rowExon.data(); v.rowFlags = rowFlags.data();
+    v.exChr = exChr.data(); v.exStart = exStart.data(); v.exEnd = exEnd.data(); v.exStrand = exStrand.data(); v.nExon = (int32_t)exChr.size();
+    for (int m = 0; m < 3; m++) { v.featOff[m] = featOff[m].data(); v.feat[m] = feat[m].data(); v.nFeat[m] = (int32_t)featIds[m].size(); }
+    return v;
+  }
+};
+
+}  // namespace eqpb

@@ -1,0 +1,238 @@
+// a15, a18-a25: alignment keys, in-fragment dedupe, multiplicity, final weight, conforming features, accumulation.
+// Reference: WeightObjectAlignment.setGenomicAlignmentString (J/bed-source/WeightObjectAlignment.java:185-219),
+// WeightObject.mergeWeightAlignments (:216-252) + combineExons (WeightObjectAlignment.java:312-374),
+// WeightObject.getNumGenomicAlignments (:819-880), CombineReadWeightFiles default mode (:173-248),
+// ComputeCounts main loop (:728-858), processWeightObject (:257-446), GenomicAlignment.getConformingCountObjects (:570-712),
+// GenomicInterval.updateExonSet (GenomicInterval.java:479-523).
+#pragma once
+#include "eqp_align.h"
+
+namespace eqpb {
+
+#define EQP_FIXED_SHIFT_D 38
+EQP_HD int eqp_popc(uint32_t m) {
+#if defined(__CUDA_ARCH__)
+  return __popc(m);
+#else
+  return __builtin_popcount(m);
+#endif
+}
+
+// ---- stage A: sort each alignment's hits, build both halves, hash the canonical key
+EQP_HD void fragment_alignments(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, uint32_t slot) {
+  uint32_t b0 = C.blkOff[slot], b1 = C.blkOff[slot + 1];
+  if (b0 == b1) return;
+  uint32_t h0 = C.hitCnt[b0], h1 = C.hitCnt[b1]; uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1]; uint32_t frag = C.base + slot;
+  for (uint32_t a = a0; a < a1; a++) { Aln& al = V.alns[a]; al.hit0 = al.hit1 = al.split = 0; al.flags = 0; al.repr = a; al.key = 0; }
+  uint32_t k = h0;
+  while (k < h1) {                                                       // hits are grouped by block, blocks by alignment
+    uint32_t aln = C.blocks[C.hits[k].block].aln; uint32_t e = k + 1;
+    while (e < h1 && C.blocks[C.hits[e].block].aln == aln) e++;
+    Aln& al = V.alns[a0 + aln];
+    for (uint32_t i = k + 1; i < e; i++) {                               // insertion sort by (readIdx, readStart, eRefStart, eRefEnd, strand, row)
+      Hit cur = C.hits[i]; RecKey ck = rec_key(A, C, cur); uint32_t j = i;
+      while (j > k) { RecKey pk = rec_key(A, C, C.hits[j - 1]); int c = rec_cmp(pk, ck); if (c < 0 || (c == 0 && pk.row <= ck.row)) break; C.hits[j] = C.hits[j - 1]; j--; }
+      C.hits[j] = cur;
+    }
+    uint32_t split = k; while (split < e && C.blocks[C.hits[split].block].readIdx == 1) split++;
+    al.hit0 = k; al.split = split; al.hit1 = e;
+    const Block& fb = C.blocks[C.hits[k].block];
+    uint8_t fl = fb.paired ? 1 : 0;
+    for (uint32_t i = k; i < e; i++) if ((C.blocks[C.hits[i].block].paired ? 1 : 0) != (fl & 1)) raise(C.err, DERR_INCONSISTENT, frag);
+    al.start1 = al.start2 = 0x7fffffff; al.nIv1 = al.nIv2 = 0; al.maxField1 = al.maxField2 = -1;
+    if (split > k) { build_half(A, C, V, P, k, split, 1, al.start1, al.nIv1, al.maxField1, frag); fl |= 2; }
+    if (e > split) { build_half(A, C, V, P, split, e, 2, al.start2, al.nIv2, al.maxField2, frag); fl |= 4; }
+    if (!(fl & 1)) fl |= (uint8_t)(((fl & 2) ? 1 : 2) << 3);
+    if (!(fl & 1) && (fl & 2) && (fl & 4)) raise(C.err, DERR_INCONSISTENT, frag);   // single-read alignment with both read indices
+    al.flags = fl;
+    // canonical key (strand slot is empty in the reference's strings: GenomicInterval never sets originalStrand)
+    bool both = (fl & 2) && (fl & 4); bool secondFirst = both && !(al.start1 <= al.start2);
+    uint64_t hsh = mix64(0x1234, (uint64_t)((fl & 1) ? 0 : (fl >> 3) & 3));
+    hsh = mix64(hsh, both ? 0 : (fl & 2) ? 1 : 2);
+    for (int part = 0; part < 2; part++) {
+      int half = both ? (secondFirst ? 2 - part : 1 + part) : ((fl & 2) ? 1 : 2);
+      if (!both && part == 1) break;
+      uint32_t s0 = half == 1 ? k : split, s1 = half == 1 ? split : e; int nIv = half == 1 ? al.nIv1 : al.nIv2;
+      hsh = mix64(hsh, 0xABCDEF00u + (uint64_t)nIv);
+      for (int r = 0; r < nIv; r++)
+        for (uint32_t i = s0; i < s1; i++) { const HitX& x = V.hx[i]; if ((x.flags & 1) && x.ivRank == r) { hsh = mix64(mix64(mix64(hsh, (uint64_t)x.chr), (uint64_t)x.gs), (uint64_t)x.ge); break; } }
+    }
+    al.key = hsh;
+    k = e;
+  }
+}
+
+// interval r of a half: first valid record with that rank
+EQP_HD bool half_interval(const CountView& V, uint32_t s0, uint32_t s1, int r, int32_t& chr, int32_t& gs, int32_t& ge, int& field) {
+  for (uint32_t i = s0; i < s1; i++) { const HitX& x = V.hx[i]; if ((x.flags & 1) && x.ivRank == r) { chr = x.chr; gs = x.gs; ge = x.ge; field = x.ivField; return true; } }
+  return false;
+}
+EQP_HD bool halves_equal(const CountView& V, const Aln& a, int ha, const Aln& b, int hb) {
+  int na = ha == 1 ? a.nIv1 : a.nIv2, nb = hb == 1 ? b.nIv1 : b.nIv2;
+  if (na != nb) return false;
+  uint32_t a0 = ha == 1 ? a.hit0 : a.split, a1 = ha == 1 ? a.split : a.hit1, b0 = hb == 1 ? b.hit0 : b.split, b1 = hb == 1 ? b.split : b.hit1;
+  for (int r = 0; r < na; r++) {
+    int32_t c1, s1, e1, c2, s2, e2; int f;
+    half_interval(V, a0, a1, r, c1, s1, e1, f); half_interval(V, b0, b1, r, c2, s2, e2, f);
+    if (c1 != c2 || s1 != s2 || e1 != e2) return false;
+  }
+  return true;
+}
+// string equality of two WeightObjectAlignment keys; on success `swapped` tells how b's halves map onto a's
+EQP_HD bool keys_equal(const CountView& V, const Aln& a, const Aln& b, bool& swapped) {
+  swapped = false;
+  if (a.key != b.key) return false;
+  if ((a.flags & 1) != (b.flags & 1)) return false;
+  if (!(a.flags & 1) && ((a.flags >> 3) & 3) != ((b.flags >> 3) & 3)) return false;
+  if ((a.flags & 6) != (b.flags & 6)) return false;
+  if ((a.flags & 6) == 6) {
+    bool sa = !(a.start1 <= a.start2), sb = !(b.start1 <= b.start2);     // which half is printed first
+    int a1 = sa ? 2 : 1, a2 = sa ? 1 : 2, b1 = sb ? 2 : 1, b2 = sb ? 1 : 2;
+    if (!halves_equal(V, a, a1, b, b1) || !halves_equal(V, a, a2, b, b2)) return false;
+    // combineExons (:312-337): straight pairing if ga1==ga1' and ga2==ga2', else the mate-swapped pairing
+    swapped = !(halves_equal(V, a, 1, b, 1) && halves_equal(V, a, 2, b, 2));
+    return true;
+  }
+  int h = (a.flags & 2) ? 1 : 2;
+  return halves_equal(V, a, h, b, h);
+}
+
+// ---- stage B: dedupe, a20, final weight
+EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, uint32_t slot) {
+  uint32_t b0 = C.blkOff[slot], b1 = C.blkOff[slot + 1];
+  V.a20[slot] = 0; V.nFinal[slot] = 0;
+  if (b0 == b1 || C.hitCnt[b0] == C.hitCnt[b1]) return;
+  uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1];
+  int left = 0, right = 0;
+  for (uint32_t a = a0; a < a1; a++) {
+    Aln& al = V.alns[a]; if (al.hit0 == al.hit1) continue;
+    al.repr = a;
+    for (uint32_t p = a0; p < a; p++) { const Aln& q = V.alns[p]; if (q.hit0 == q.hit1 || q.repr != p) continue; bool sw; if (keys_equal(V, q, al, sw)) { al.repr = p; break; } }
+    if (al.repr == a) { if ((al.flags & 6) == 4) right++; else left++; }   // ":r-" forms (WeightObject.java:859-865)
+  }
+  uint32_t a20 = (uint32_t)(left > right ? left : right);
+  V.a20[slot] = a20;
+  // final.wgt entry: BED weight (single-read, read index 1, n = a20) vs genome SAM weight, T+J entry as class arbiter
+  FragStat bed{}; bed.nSr1 = (uint16_t)(a20 > 65535 ? 65535 : a20); bed.flags = FS_EXISTS | (1 << 2);
+  const FragStat& g = C.st[FILE_G][slot];
+  uint32_t n = a20;
+  if (g.flags & FS_EXISTS) {
+    uint32_t ax = C.auxSlot[slot]; int cm = 0;
+    if (ax != 0xFFFFFFFFu) cm = fe_cmp_mult(C.stTJ[ax], g);               // aux.compareMultiplicity(entry2), CombineReadWeightFiles.java:192-195
+    if (cm == 1) n = a20; else if (cm == -1) n = (uint32_t)fe_n(g); else n = (int)a20 >= fe_n(g) ? a20 : (uint32_t)fe_n(g);
+  }
+  V.nFinal[slot] = n;
+}
+
+// ---- stage C: conforming features + accumulation for one run (mode)
+#define EQP_FS_CAP 160
+#define EQP_FT_CAP 320
+struct FeatSet { uint32_t id[EQP_FS_CAP]; uint32_t mask[EQP_FS_CAP]; int n; };
+EQP_HD bool fs_add(FeatSet& s, uint32_t id, uint32_t bit) {
+  for (int i = 0; i < s.n; i++) if (s.id[i] == id) { s.mask[i] |= bit; return true; }
+  if (s.n >= EQP_FS_CAP) return false;
+  s.id[s.n] = id; s.mask[s.n] = bit; s.n++; return true;
+}
+
+// features of half `h` of representative alignment R (index r) with all merged duplicates folded in
+EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t a0, uint32_t a1, uint32_t r, int h,
+                          FeatSet& out, uint32_t frag) {
+  const Aln& R = V.alns[r]; out.n = 0;
+  int nIv = h == 1 ? R.nIv1 : R.nIv2; int maxField = h == 1 ? R.maxField1 : R.maxField2;
+  uint32_t r0 = h == 1 ? R.hit0 : R.split, r1 = h == 1 ? R.split : R.hit1;
+  if (maxField >= 32) { raise(C.err, DERR_CAPACITY, frag); return; }
+  FeatSet fs; fs.n = 0;
+  for (int iv = 0; iv < nIv; iv++) {
+    int32_t chr, gs, ge; int field; half_interval(V, r0, r1, iv, chr, gs, ge, field);
+    int32_t exon[32]; uint8_t exGen[32]; int ne = 0;
+    for (uint32_t d = r; d < a1; d++) {                                   // R first, then later duplicates in file order
+      const Aln& D = V.alns[d]; if (D.hit0 == D.hit1 || D.repr != r) continue;
+      int hd = h; if (d != r) { bool sw; keys_equal(V, R, D, sw); if (sw) hd = 3 - h; }
+      uint32_t d0 = hd == 1 ? D.hit0 : D.split, d1 = hd == 1 ? D.split : D.hit1;
+      for (uint32_t i = d0; i < d1; i++) {
+        const HitX& x = V.hx[i];
+        if (!(x.flags & 1) || x.ivRank != iv || !(x.flags & (4 << mode))) continue;
+        int ex = A.rowExon[C.hits[i].row]; bool have = false;
+        for (int q = 0; q < ne; q++) if (exon[q] == ex) { have = true; break; }
+        if (have) continue;
+        if (ne >= 32) { raise(C.err, DERR_CAPACITY, frag); return; }
+        exon[ne] = ex; exGen[ne] = (x.flags & 2) ? 1 : 0; ne++;
+      }
+    }
+    if (ne > 1) {                                                          // updateExonSet: keep max-overlap non-genomic exons
+      int maxOv = 0;
+      for (int q = 0; q < ne; q++) if (!exGen[q]) { int e = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = e - gs + 1; if (ov < 0) ov = 0; if (ov > maxOv) maxOv = ov; }
+      if (maxOv > 0) { int w = 0; for (int q = 0; q < ne; q++) { int e = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = e - gs + 1; if (ov < 0) ov = 0; if (exGen[q] || ov >= maxOv) { exon[w] = exon[q]; exGen[w] = exGen[q]; w++; } } ne = w; }
+    }
+    if (mode == MODE_EXON && P.unambiguous[mode] && ne >= 2) ne = 0;      // -U with genomicIntervalMode (:603-608)
+    for (int q = 0; q < ne; q++) {
+      int ex = exon[q]; uint32_t f0 = A.featOff[mode][ex], f1 = A.featOff[mode][ex + 1]; bool any = false;
+      for (uint32_t f = f0; f < f1; f++) {
+        uint32_t v = A.feat[mode][f]; uint32_t id = v & 0x7fffffffu;
+        if (mode == MODE_JUNCTION && !(v & 0x80000000u) && !V.junctionActive[id]) continue;   // row removed by the per-chunk map filter (a27)
+        any = true;
+        if (!fs_add(fs, id, 1u << field)) { raise(C.err, DERR_CAPACITY, frag); return; }
+      }
+      if (!any && !fs_add(fs, (uint32_t)A.nFeat[mode] + (uint32_t)ex, 1u << field)) { raise(C.err, DERR_CAPACITY, frag); return; }   // unknown exon: own pseudo id
+    }
+  }
+  for (int i = 0; i < fs.n; i++) {
+    uint32_t m = fs.mask[i]; bool okf;
+    if (mode == MODE_GENE) okf = eqp_popc(m) >= maxField + 1;
+    else if (mode == MODE_EXON) okf = m != 0;
+    else okf = (m & (m >> 1)) != 0;                                       // two consecutive field indices (:679-701)
+    if (okf) { out.id[out.n] = fs.id[i]; out.mask[out.n] = 0; out.n++; }
+  }
+}
+
+EQP_HD void atomic_add_u64(unsigned long long* p, unsigned long long v) {
+#if defined(__CUDA_ARCH__)
+  atomicAdd(p, v);
+#else
+  *p += v;
+#endif
+}
+
+EQP_HD void fragment_count(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t slot) {
+  uint32_t a20 = V.a20[slot];
+  if (a20 == 0) return;
+  uint32_t frag = C.base + slot; uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1];
+  atomic_add_u64(&V.stats[mode * 3 + 0], 1);
+  double w = 1.0 / (double)V.nFinal[slot];
+  if (w > 1.0 / (double)a20) w = 1.0 / (double)a20;                      // ComputeCounts.java:762-764
+  if (!(w >= P.weightThreshold)) { atomic_add_u64(&V.stats[mode * 3 + 2], 1); return; }
+  double addW = P.unweighted ? 1.0 : w;
+  uint32_t fid[EQP_FT_CAP]; uint16_t k1[EQP_FT_CAP], k2[EQP_FT_CAP]; int nf = 0;
+  FeatSet s1, s2;
+  for (uint32_t r = a0; r < a1; r++) {
+    const Aln& R = V.alns[r]; if (R.hit0 == R.hit1 || R.repr != r) continue;
+    s1.n = s2.n = 0;
+    if (R.flags & 2) half_features(A, C, V, P, mode, a0, a1, r, 1, s1, frag);
+    if (R.flags & 4) half_features(A, C, V, P, mode, a0, a1, r, 2, s2, frag);
+    if (R.flags & 1) {                                                     // paired: gene run intersects, others unite (:325-335)
+      if (mode == MODE_GENE) { int wn = 0; for (int i = 0; i < s1.n; i++) { bool in2 = false; for (int j = 0; j < s2.n; j++) if (s2.id[j] == s1.id[i]) { in2 = true; break; } if (in2) s1.id[wn++] = s1.id[i]; } s1.n = wn; }
+      else for (int j = 0; j < s2.n; j++) { bool in1 = false; for (int i = 0; i < s1.n; i++) if (s1.id[i] == s2.id[j]) { in1 = true; break; } if (!in1) { if (s1.n >= EQP_FS_CAP) { raise(C.err, DERR_CAPACITY, frag); return; } s1.id[s1.n++] = s2.id[j]; } }
+      s2.n = 0;
+    }
+    for (int side = 0; side < 2; side++) {
+      FeatSet& s = side ? s2 : s1;
+      for (int i = 0; i < s.n; i++) {
+        int q = 0; for (; q < nf; q++) if (fid[q] == s.id[i]) break;
+        if (q == nf) { if (nf >= EQP_FT_CAP) { raise(C.err, DERR_CAPACITY, frag); return; } fid[nf] = s.id[i]; k1[nf] = k2[nf] = 0; nf++; }
+        if (side) k2[q]++; else k1[q]++;
+      }
+    }
+  }
+  if (P.unambiguous[mode] && mode != MODE_EXON && nf >= 2) { atomic_add_u64(&V.stats[mode * 3 + 2], 1); return; }   // :371-382 returns 0
+  bool added = false;
+  for (int q = 0; q < nf; q++) {
+    int k = k1[q] > k2[q] ? k1[q] : k2[q];
+    double t = 0; for (int i = 0; i < k && t < 1.0; i++) t = t + addW;     // repeated addition (:100-111, :343); min(1, max(w1, w2)) (:427-428)
+    double c = t < 1.0 ? t : 1.0;
+    if (c > 0) added = true;
+    if (fid[q] < (uint32_t)A.nFeat[mode]) atomic_add_u64(&V.acc[mode][fid[q]], (unsigned long long)(c * (double)(1ULL << EQP_FIXED_SHIFT_D) + 0.5));
+  }
+  atomic_add_u64(&V.stats[mode * 3 + (added ? 1 : 2)], 1);
+}
+
+}  // namespace eqpb

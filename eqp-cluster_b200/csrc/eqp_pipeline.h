@@ -1,0 +1,206 @@
+// Chunk pipeline: the order of stages that replaces compute-counts.sh:733-1037 for one chunk.
+// Templated on a backend that provides alloc/memset/launch/scan, so that the identical per-item device functions
+// run (a) as CUDA kernels in libeqpcount.so and (b) in the host emulation harness under tests/emu (test-only).
+#pragma once
+#include <string>
+#include <vector>
+#include "eqp_count.h"
+
+#if defined(__CUDACC__)
+#define EQP_LAMBDA __host__ __device__
+#else
+#define EQP_LAMBDA
+#endif
+
+namespace eqpb {
+
+EQP_HD void atomic_min_u32(uint32_t* p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+  atomicMin(p, v);
+#else
+  if (v < *p) *p = v;
+#endif
+}
+EQP_HD void atomic_max_u32(uint32_t* p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+  atomicMax(p, v);
+#else
+  if (v > *p) *p = v;
+#endif
+}
+
+struct ChunkResult {
+  std::vector<double> counts[3]; std::vector<unsigned long long> fixed[3]; std::vector<uint8_t> junctionActive;
+  unsigned long long stats[16]; uint32_t nRecords[3]; uint32_t err[2];
+};
+
+static const uint32_t LINE_TILE = 1024;               // bytes per newline-count item
+
+template <class BE>
+struct Pipeline {
+  BE& be; AnnoView A; RunParams P;
+  ChunkView C{}; CountView V{};
+  uint32_t nBlocks = 0, nAln = 0, nHits = 0;
+  uint32_t* scal = nullptr;                           // device scalars: [0..1] err, [2..7] min/max frag per file, [8..] presence bounds
+  uint32_t* tileCnt[3] = {nullptr, nullptr, nullptr};
+
+  Pipeline(BE& b, const AnnoView& a, const RunParams& p) : be(b), A(a), P(p) {}
+
+  void index_lines(int f, const char* text, uint64_t len) {
+    SamView& S = C.sam[f]; S.text = text; S.len = len;
+    uint64_t nTiles = (len + LINE_TILE - 1) / LINE_TILE;
+    uint32_t* cnt = be.template alloc<uint32_t>(nTiles + 1); tileCnt[f] = cnt;
+    be.launch(nTiles, [=] EQP_LAMBDA(uint64_t t) {
+      uint64_t b = t * LINE_TILE, e = b + LINE_TILE < len ? b + LINE_TILE : len; uint32_t c = 0;
+      for (uint64_t i = b; i < e; i++) c += text[i] == '\n';
+      cnt[t] = c;
+    });
+    be.scan(cnt, nTiles);
+    uint32_t nl = 0; be.to_host(&nl, cnt + nTiles, sizeof nl);
+    char last = 0; if (len) be.to_host(&last, text + len - 1, 1);
+    S.nLines = len == 0 ? 0 : (last == '\n' ? nl : nl + 1);
+    S.lineOff = be.template alloc<uint64_t>((uint64_t)S.nLines + 1);
+    uint64_t* lo = S.lineOff; uint32_t nLines = S.nLines;
+    be.launch(nTiles, [=] EQP_LAMBDA(uint64_t t) {
+      uint64_t b = t * LINE_TILE, e = b + LINE_TILE < len ? b + LINE_TILE : len; uint32_t k = cnt[t];
+      if (t == 0) lo[0] = 0;
+      for (uint64_t i = b; i < e; i++) if (text[i] == '\n') { lo[++k] = i + 1; }
+      if (e == len && last != '\n') lo[nLines] = len + 1;
+    });
+    uint64_t n = S.nLines;
+    S.frag = be.template alloc<uint32_t>(n); S.ref = be.template alloc<int32_t>(n); S.pos = be.template alloc<int32_t>(n);
+    S.rnext = be.template alloc<int32_t>(n); S.pnext = be.template alloc<int32_t>(n); S.flag = be.template alloc<uint16_t>(n);
+    S.nm = be.template alloc<int16_t>(n); S.cigOff = be.template alloc<uint16_t>(n); S.cigLen = be.template alloc<uint16_t>(n);
+    S.seqLen = be.template alloc<uint16_t>(n); S.rf = be.template alloc<uint8_t>(n); C.proc[f] = be.template alloc<uint8_t>(n);
+  }
+
+  int run(const char* const text[3], const uint64_t len[3], ChunkResult& R) {
+    scal = be.template alloc<uint32_t>(32); be.memset(scal, 0, 32 * sizeof(uint32_t));
+    C.err = scal;
+    const AnnoView A = this->A; const RunParams P = this->P;
+    // ---- a1/a2: line index + decode
+    for (int f = 0; f < 3; f++) {
+      index_lines(f, text[f], len[f]);
+      const SamView S = C.sam[f]; uint32_t* err = scal;
+      be.decode(A, S, err);                           // per-line decode_line(); CUDA backend uses the tiled shared-memory kernel
+      R.nRecords[f] = S.nLines;
+    }
+    // fragment id range
+    { uint32_t init[6] = {0xFFFFFFFFu, 0, 0xFFFFFFFFu, 0, 0xFFFFFFFFu, 0}; be.to_device(scal + 2, init, sizeof init);
+      for (int f = 0; f < 3; f++) { const SamView S = C.sam[f]; uint32_t* mm = scal + 2 + 2 * f;
+        be.launch(S.nLines, [=] EQP_LAMBDA(uint64_t i) { if (S.rf[i] & RF_REC) { atomic_min_u32(mm, S.frag[i]); atomic_max_u32(mm + 1, S.frag[i]); } }); } }
+    uint32_t h[8]; be.to_host(h, scal, sizeof h);
+    if (h[0]) { R.err[0] = h[0]; R.err[1] = h[1]; return -1; }
+    uint32_t lo = 0xFFFFFFFFu, hi = 0; bool anyRec = false;
+    for (int f = 0; f < 3; f++) if (h[2 + 2 * f] != 0xFFFFFFFFu) { anyRec = true; lo = std::min(lo, h[2 + 2 * f]); hi = std::max(hi, h[3 + 2 * f]); }
+    C.base = anyRec ? lo : 0; C.nSlots = anyRec ? hi - lo + 1 : 0;
+    uint64_t totalLines = (uint64_t)C.sam[0].nLines + C.sam[1].nLines + C.sam[2].nLines;
+    if ((uint64_t)C.nSlots > 8 * totalLines + 1024) { R.err[0] = DERR_CAPACITY; R.err[1] = 0; return -1; }
+    const uint32_t N = C.nSlots;
+    for (int f = 0; f < 3; f++) { C.ff[f] = be.template alloc<FragFile>(N); be.memset(C.ff[f], 0, (uint64_t)N * sizeof(FragFile)); C.st[f] = be.template alloc<FragStat>(N); }
+    C.stTJ = be.template alloc<FragStat>(N); C.setTJ = be.template alloc<SetDesc>(N); C.setC = be.template alloc<SetDesc>(N);
+    C.auxSlot = be.template alloc<uint32_t>((uint64_t)N + 1); C.blkOff = be.template alloc<uint32_t>((uint64_t)N + 1); C.alnOff = be.template alloc<uint32_t>((uint64_t)N + 1);
+    C.seenRef = be.template alloc<uint8_t>((uint64_t)A.nRef + 1); be.memset(C.seenRef, 0, (uint64_t)A.nRef + 1);
+    // ---- fragment table: [first,end) line range per (file, slot); order check (CombineSamFiles.java:191-193)
+    for (int f = 0; f < 3; f++) { const SamView S = C.sam[f]; FragFile* ff = C.ff[f]; uint32_t base = C.base; uint32_t* err = scal;
+      be.launch(S.nLines, [=] EQP_LAMBDA(uint64_t i) {
+        if (!(S.rf[i] & RF_REC)) return;
+        uint32_t fr = S.frag[i];
+        bool prevRec = i > 0 && (S.rf[i - 1] & RF_REC), nextRec = i + 1 < S.nLines && (S.rf[i + 1] & RF_REC);
+        if (prevRec && S.frag[i - 1] > fr) raise(err, DERR_ORDER, fr);
+        if (!prevRec || S.frag[i - 1] != fr) ff[fr - base].first = (uint32_t)i;
+        if (!nextRec || S.frag[i + 1] != fr) ff[fr - base].end = (uint32_t)i + 1;
+      }); }
+    // ---- a3/a4: per-fragment statistics in each input
+    for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
+    { const ChunkView C = this->C;
+      be.launch((uint64_t)N * 3, [=] EQP_LAMBDA(uint64_t k) {
+        int f = (int)(k / N); uint32_t s = (uint32_t)(k % N); FragFile ff = C.ff[f][s]; FragStat st{};
+        fragment_stats(A, C.sam[f], ff.first, ff.end, f == FILE_G, C.proc[f], st, ff, C.err, C.base + s);
+        C.st[f][s] = st; C.ff[f][s].bits = ff.bits;
+      }); }
+    // ---- a5-a7: T+J weights, stage-1 selection, presence bounds, stage-2 selection, aux lookup table
+    uint32_t* bnd = scal + 8;                          // [0] firstT [1] firstJ [2] lastT [3] anyT [4] anyJ | [5] firstTJ [6] firstG [7] lastTJ [8] anyTJ [9] anyG
+    { uint32_t init[10] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0, 0, 0, 0xFFFFFFFFu, 0xFFFFFFFFu, 0, 0, 0}; be.to_device(bnd, init, sizeof init); }
+    { const ChunkView C = this->C;
+      be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
+        if (C.ff[FILE_T][s].bits & 1) { atomic_min_u32(bnd + 0, (uint32_t)s); atomic_max_u32(bnd + 2, (uint32_t)s); bnd[3] = 1; }
+        if (C.ff[FILE_J][s].bits & 1) { atomic_min_u32(bnd + 1, (uint32_t)s); bnd[4] = 1; }
+        if (C.ff[FILE_G][s].bits & 1) { atomic_min_u32(bnd + 6, (uint32_t)s); bnd[9] = 1; }
+        C.stTJ[s] = combine_weights_ed(C.st[FILE_T][s], C.st[FILE_J][s], P.slack);
+      });
+      be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
+        Side a = side_of_file(FILE_T, C.ff[FILE_T][s], C.st[FILE_T][s]), b = side_of_file(FILE_J, C.ff[FILE_J][s], C.st[FILE_J][s]);
+        SetDesc r = combine_stage(a, b, (uint32_t)s, bnd[0], bnd[1], bnd[2], bnd[3] != 0, bnd[4] != 0, P.slack, C.err, C.base + (uint32_t)s);
+        C.setTJ[s] = r;
+        if (sd_n(r)) { atomic_min_u32(bnd + 5, (uint32_t)s); atomic_max_u32(bnd + 7, (uint32_t)s); bnd[8] = 1; }
+      });
+      be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
+        FragFile ffs[3] = {C.ff[0][s], C.ff[1][s], C.ff[2][s]};
+        Side a = side_of_set(C.setTJ[s], ffs, C.stTJ[s]), b = side_of_file(FILE_G, C.ff[FILE_G][s], C.st[FILE_G][s]);
+        C.setC[s] = combine_stage(a, b, (uint32_t)s, bnd[5], bnd[6], bnd[7], bnd[8] != 0, bnd[9] != 0, P.slack, C.err, C.base + (uint32_t)s);
+      });
+      // aux: first slot >= s with a T+J weight entry (FragmentEntryFactory.getNextFragmentEntry(query), :75-106)
+      const uint32_t CH = 512; uint64_t nCh = ((uint64_t)N + CH - 1) / CH;
+      uint32_t* chNext = be.template alloc<uint32_t>(nCh + 1);
+      be.launch(nCh, [=] EQP_LAMBDA(uint64_t c) {
+        uint64_t b = c * CH, e = b + CH < N ? b + CH : N; uint32_t nx = 0xFFFFFFFFu;
+        for (uint64_t s = e; s-- > b;) { if (C.stTJ[s].flags & FS_EXISTS) nx = (uint32_t)s; C.auxSlot[s] = nx; }
+        chNext[c] = nx;
+      });
+      be.launch(1, [=] EQP_LAMBDA(uint64_t) { uint32_t nx = 0xFFFFFFFFu; for (uint64_t c = nCh; c-- > 0;) { uint32_t own = chNext[c]; chNext[c] = nx; if (own != 0xFFFFFFFFu) nx = own; } });
+      be.launch(N, [=] EQP_LAMBDA(uint64_t s) { if (C.auxSlot[s] == 0xFFFFFFFFu) C.auxSlot[s] = chNext[s / CH]; });
+    }
+    // ---- a27: reference ids seen (combined SAM + junction SAM) -> active junction features
+    V.junctionActive = be.template alloc<uint8_t>((uint64_t)A.nFeat[2] + 1); be.memset((void*)V.junctionActive, 0, (uint64_t)A.nFeat[2] + 1);
+    { const ChunkView C = this->C; uint8_t* act = (uint8_t*)V.junctionActive; const SamView J = C.sam[FILE_J];
+      be.launch(J.nLines, [=] EQP_LAMBDA(uint64_t i) { if ((J.rf[i] & RF_REC) && J.ref[i] >= 0) C.seenRef[J.ref[i]] = 1; });
+      be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
+        SetDesc sd = C.setC[s];
+        for (int k = 0; k < sd_n(sd); k++) { int f = sd_file(sd, k), flt = sd_filter(sd, k); FragFile ff = C.ff[f][s];
+          for (uint32_t i = ff.first; i < ff.end; i++) { uint8_t rf = C.sam[f].rf[i]; if ((rf & RF_REC) && (!flt || rf_read_index(rf) == flt) && C.sam[f].ref[i] >= 0) C.seenRef[C.sam[f].ref[i]] = 1; } }
+      });
+      be.launch((uint64_t)A.nRef, [=] EQP_LAMBDA(uint64_t r) {
+        if (!C.seenRef[r]) return;
+        if (A.refFlags[r] & 2) raise(C.err, DERR_BAD_JUNCTION_ID, (uint32_t)r);
+        for (uint32_t k = A.refActOff[r]; k < A.refActOff[r + 1]; k++) act[A.refAct[k]] = 1;
+      }); }
+    // ---- a8-a10: blocks (count, scan, fill)
+    V.stats = be.template alloc<unsigned long long>(16); be.memset(V.stats, 0, 16 * sizeof(unsigned long long));
+    for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
+    { const ChunkView C = this->C; unsigned long long* stats = V.stats;
+      be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, false, nb, na); C.blkOff[s] = nb; C.alnOff[s] = na;
+        SetCursor c{0, 0xFFFFFFFFu}; int f; if (set_next(C, C.setC[s], (uint32_t)s, c, f)) atomic_add_u64(&stats[9], 1); }); }
+    be.scan(C.blkOff, N); be.scan(C.alnOff, N);
+    be.to_host(&nBlocks, C.blkOff + N, 4); be.to_host(&nAln, C.alnOff + N, 4);
+    C.blocks = be.template alloc<Block>((uint64_t)nBlocks + 1); C.hitCnt = be.template alloc<uint32_t>((uint64_t)nBlocks + 1);
+    for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
+    { const ChunkView C = this->C; be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, nb, na); }); }
+    // ---- a11: interval join (count, scan, fill)
+    { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { C.hitCnt[b] = join_block(A, C.blocks[b], nullptr, (uint32_t)b); }); }
+    be.scan(C.hitCnt, nBlocks); be.to_host(&nHits, C.hitCnt + nBlocks, 4);
+    C.hits = be.template alloc<Hit>((uint64_t)nHits + 1);
+    { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { join_block(A, C.blocks[b], C.hits + C.hitCnt[b], (uint32_t)b); }); }
+    // ---- a12-a25
+    V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
+    V.a20 = be.template alloc<uint32_t>((uint64_t)N + 1); V.nFinal = be.template alloc<uint32_t>((uint64_t)N + 1);
+    for (int m = 0; m < 3; m++) { V.acc[m] = be.template alloc<unsigned long long>((uint64_t)A.nFeat[m] + 1); be.memset(V.acc[m], 0, ((uint64_t)A.nFeat[m] + 1) * 8); }
+    { const ChunkView C = this->C; const CountView V = this->V;
+      be.launch(N, [=] EQP_LAMBDA(uint64_t s) { fragment_alignments(A, C, V, P, (uint32_t)s); });
+      be.launch(N, [=] EQP_LAMBDA(uint64_t s) { fragment_weight(A, C, V, P, (uint32_t)s); });
+      for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) be.launch(N, [=] EQP_LAMBDA(uint64_t s) { fragment_count(A, C, V, P, m, (uint32_t)s); }); }
+    // ---- results
+    be.to_host(R.err, scal, 8);
+    if (R.err[0]) return -1;
+    be.to_host(R.stats, V.stats, sizeof R.stats);
+    for (int m = 0; m < 3; m++) {
+      R.fixed[m].resize(A.nFeat[m]); if (A.nFeat[m]) be.to_host(R.fixed[m].data(), V.acc[m], (uint64_t)A.nFeat[m] * 8);
+      R.counts[m].resize(A.nFeat[m]);
+      for (int i = 0; i < A.nFeat[m]; i++) R.counts[m][i] = (double)R.fixed[m][i] / (double)(1ULL << EQP_FIXED_SHIFT_D);
+    }
+    R.junctionActive.resize(A.nFeat[2]); if (A.nFeat[2]) be.to_host(R.junctionActive.data(), V.junctionActive, A.nFeat[2]);
+    return 0;
+  }
+};
+
+}  // namespace eqpb

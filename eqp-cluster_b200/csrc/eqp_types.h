@@ -1,0 +1,112 @@
+// Plain-old-data views shared by the CUDA pipeline and the host-side annotation builder.
+// Layouts are described in DESIGN.md ("Data layout in HBM").
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define EQP_HD __host__ __device__ __forceinline__
+#else
+#define EQP_HD inline
+#endif
+
+namespace eqpb {
+
+enum { FILE_T = 0, FILE_J = 1, FILE_G = 2 };
+enum { MODE_GENE = 0, MODE_EXON = 1, MODE_JUNCTION = 2 };
+
+// device error word: first error wins (atomicCAS), detail = fragment id or record index
+enum {
+  DERR_NONE = 0,
+  DERR_QNAME = 1,          // QNAME is not Fnnnnnnnnn[/1|/2]  (SamReader.java:157 would renumber)
+  DERR_FIELDS = 2,         // too few / too many SAM fields (SamRecord.java:251-257)
+  DERR_SEQ_QUAL = 3,       // SEQ/QUAL length mismatch (SamRecord.java:246-249)
+  DERR_READ_INDEX = 4,     // read index in flag differs from name (SamRecord.java:182-186)
+  DERR_ORDER = 5,          // SAM records out of order (CombineSamFiles.java:191-193)
+  DERR_NULL_WEIGHT = 6,    // fragment with only non-whitelisted genome hits: reference prints "null" and aborts
+  DERR_CIGAR_OP = 7,       // unknown CIGAR operation (SamRecord.java:419-421)
+  DERR_CIGAR_LEN = 8,      // read length != M+I+S (SamRecord.java:463-466)
+  DERR_MATE_REF = 9,       // "Differing referenceName mate found" (SamRecord.java:567-571)
+  DERR_TR_EXON = 10,       // unsupported: tr- transcript exon hit
+  DERR_POS_LENDIFF = 11,   // unsupported: transcript exon longer than genome exon (a17 becomes effective)
+  DERR_CAPACITY = 12,      // per-fragment table overflow
+  DERR_GENOME_COORD = 13,  // BedRecord.java:669-673 / :683-687 self-checks
+  DERR_INCONSISTENT = 14,  // GenomicAlignment.java consistency throws (:123-148, :245-300)
+  DERR_BAD_JUNCTION_ID = 15,
+  DERR_STRANDED = 16,      // unsupported: strand-specific mode
+  DERR_INT = 17            // integer field does not parse
+};
+
+struct AnnoView {
+  // reference-name dictionary (open addressing, power-of-two capacity)
+  const uint64_t* dictHash; const int32_t* dictVal; uint32_t dictMask;
+  const char* strPool; const uint32_t* refStrOff; const uint16_t* refStrLen;
+  const uint8_t* refFlags;          // bit0 in genome.fa.fai, bit1 malformed junction-like id
+  const uint32_t* refVerOff; const int32_t* refVerBucket;   // SAM name -> B buckets (a8 version expansion)
+  const uint32_t* refActOff; const int32_t* refAct;         // SAM name -> junction features it activates (a27)
+  int32_t nRef;
+  // B index: buckets -> rows sorted by start
+  const uint32_t* bktRowOff; const uint8_t* bktFlags;       // bit0 junction, bit1 .inv-strand
+  int32_t nBucket;
+  const int32_t* rowStart; const int32_t* rowEnd; const int32_t* rowMaxEnd; const int32_t* rowExon;
+  const uint8_t* rowFlags;          // bit0 genomic row (bucket name == exon chromosome), bits1-2 row strand (0 '+', 1 '-', 2 other)
+  // distinct exons
+  const int32_t* exChr; const int32_t* exStart; const int32_t* exEnd; const uint8_t* exStrand;   // exChr -2 = tr- exon
+  int32_t nExon;
+  // exon -> feature lists per mode; junction entries carry bit31 = "row also in exon_junction_transcript.map"
+  const uint32_t* featOff[3]; const uint32_t* feat[3]; int32_t nFeat[3];
+};
+
+struct SamView {                   // one decoded SAM input (structure of arrays, one entry per text line)
+  const char* text; uint64_t len;
+  uint64_t* lineOff;               // nLines + 1 entries
+  uint32_t nLines;
+  uint32_t* frag; int32_t* ref; int32_t* pos; int32_t* rnext; int32_t* pnext;
+  uint16_t* flag; int16_t* nm; uint16_t* cigOff; uint16_t* cigLen; uint16_t* seqLen;
+  uint8_t* rf;                     // bit0 record (not header/empty), bit1 mapped, bit2 hasMate, bits3-4 readIndex
+};
+enum { RF_REC = 1, RF_MAPPED = 2, RF_HASMATE = 4 };
+EQP_HD int rf_read_index(uint8_t rf) { return (rf >> 3) & 3; }
+
+struct FragStat {                  // FragmentEntry of one fragment in one file (a4), 20 bytes
+  uint16_t nPe, nSr1, nSr2; uint16_t flags;        // flags: bit0 entry exists, bit1 hasMate(last add), bits2-3 readIndex state (1,2,3)
+  int32_t edPe, edSr1, edSr2;                      // NM sums (a missing NM tag contributes -1, SamRecord.java:1063-1065)
+};
+enum { FS_EXISTS = 1, FS_HASMATE = 2 };
+EQP_HD int fs_read_index(const FragStat& f) { return (f.flags >> 2) & 3; }
+
+struct FragFile {                  // record range + presence bits of one fragment in one file
+  uint32_t first, end;             // line range [first, end)
+  uint8_t bits;                    // bit0 present, bit1 mapped idx1, bit2 mapped idx2, bit3 has idx1 rec, bit4 has idx2 rec, bit5 mapped idx0
+};
+
+struct Block {                     // one aligned block of the combined BED (a10), 32 bytes
+  int32_t bucket; int32_t start, end;              // 0-based half-open, in the bucket's coordinates
+  uint16_t L, I, D; uint8_t seg, maxSeg;           // -L -I -D -F<seg>-<maxSeg>
+  uint32_t aln;                                    // alignment number within the fragment (A-counter - 1)
+  uint8_t readIdx, paired, strand, pad;            // strand '+'/'-'
+  uint32_t hitOff;                                 // first hit of this block (filled by the join)
+};
+
+struct Hit { uint32_t block; int32_t row; int32_t overlap; };   // a11 output (12 bytes)
+
+struct HitX {                      // per hit, after the per-alignment sort/dedupe (a12-a16), 24 bytes
+  int32_t gs, ge;                  // genomic interval, 1-based closed
+  int32_t chr;                     // chromosome index of the exon
+  int16_t ivField;                 // field index of the (kept) interval this record belongs to
+  uint16_t ivRank;                 // rank of that interval among the distinct intervals of its half
+  int32_t exonLen;
+  uint8_t flags;                   // bit0 valid, bit1 genomic row, bits2-4 conforming in gene/exon/junction run, bit5 interval strand '-'
+  uint8_t half; uint16_t pad;      // half: 1 or 2 (read index)
+};
+
+struct Aln {                       // one WeightObjectAlignment (a15-a19), 48 bytes
+  uint32_t hit0, split, hit1;      // hits [hit0,split) read 1, [split,hit1) read 2
+  uint32_t repr;                   // global index of the first alignment of the fragment with the same key
+  uint64_t key;
+  int32_t start1, start2;          // GenomicAlignment.start per half
+  uint16_t nIv1, nIv2; int16_t maxField1, maxField2;
+  uint8_t flags; uint8_t pad[7];   // bit0 paired, bit1 has half 1, bit2 has half 2, bits3-4 SR read index
+};
+
+}  // namespace eqpb

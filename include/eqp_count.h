@@ -1,0 +1,124 @@
+/* eqp_count.h — C ABI of libeqpcount.so: the B200 replacement for EQP-cluster's compute-counts hot path.
+ *
+ * The reference has no FFI for this path; its seam is "process + files" (SURVEY.md §8b):
+ *   exon-pipeline-scripts/bin/process-scripts/compute-counts.sh:733-1037 spawns
+ *     ComputeReadWeightsSam x3, CombineReadWeightFiles x2, CombineSamFiles x2, ConvertSamBed,
+ *     bedtools intersect, ComputeReadWeights and ComputeCounts x3
+ *   (exon-pipeline-scripts/java/source/{sam-source,bed-source,util-source}).
+ * One eqp_count_chunk() call replaces that whole process tree for one chunk; the Java side keeps
+ * option parsing, inflate, the .cnt writers and the log lines (INTEGRATION.md shows the JNI / Panama stub).
+ *
+ * All functions return 0 on success or a negative EQP_ERR_* code; eqp_last_error() gives the message
+ * the Java main prints as "ERROR: <msg>" before System.exit(1) (ComputeCounts.java:996-999).
+ * There is NO CPU fallback: without a CUDA device every compute entry point fails with EQP_ERR_CUDA.
+ * An eqp_ctx is bound to one GPU, is not thread-safe and runs one chunk at a time.
+ */
+#ifndef EQP_COUNT_H
+#define EQP_COUNT_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EQP_ABI_VERSION 1
+
+enum {
+  EQP_OK = 0,
+  EQP_ERR_ARG = -1,          /* bad argument / call order */
+  EQP_ERR_CUDA = -2,         /* no device, driver or allocation failure */
+  EQP_ERR_IO = -3,           /* annotation file missing or malformed */
+  EQP_ERR_FORMAT = -4,       /* input violates a check the reference aborts on */
+  EQP_ERR_UNSUPPORTED = -5,  /* valid for the reference, not yet handled on the device (DESIGN.md "out of scope") */
+  EQP_ERR_CAPACITY = -6      /* a per-fragment device table overflowed */
+};
+
+typedef struct eqp_ctx eqp_ctx;
+
+/* Annotation inputs: the files compute-counts.sh reads from <project>/exon-pipeline-files
+ * (compute-counts.sh:584-603, compute-intersection-bed-file.sh:551-572, filter-junction-map-files.sh:207-236).
+ * Plain (uncompressed) paths; the Java caller inflates *.gz maps. */
+typedef struct eqp_annotation_files {
+  const char* combined_exons_bed;              /* <base>_<R>_combined_exons.bed  (bedtools -b file) */
+  const char* transcript_exons_bed;            /* <base>_transcript_exons.bed    (ConvertSamBed -T) */
+  const char* exon_gene_map;                   /* ComputeCounts -g -m */
+  const char* exon_exon_map;                   /* ComputeCounts -e -m */
+  const char* exon_junction_map;               /* unfiltered; filtered per chunk on the device */
+  const char* exon_junction_transcript_map;
+  const char* junction_junction_coordinate_map;
+  const char* equivalent_junctions_map;
+  const char* genome_fai;                      /* ComputeReadWeightsSam -c */
+} eqp_annotation_files;
+
+/* The flags process-samples.sh passes (process-samples.sh:1480-1481) and compute-counts.sh forwards
+ * (compute-counts.sh:932-935,959-960,1034-1035); replaces the UtilLib statics (UtilLib.java:101-226). */
+typedef struct eqp_params {
+  int32_t paired_end;            /* informational: layout is read from the SAM flags */
+  int32_t stranded;              /* -s: 0 none (only 0 is supported on the device in this round) */
+  int32_t gene_overlap;          /* 1 */
+  int32_t exon_overlap;          /* -E, default 5  (compute-counts.sh:136) */
+  int32_t junction_overlap;      /* -J, default 8  (compute-counts.sh:137,391-401) */
+  double  read_weight_threshold; /* -W, default 0.01 (compute-counts.sh:139) */
+  int32_t unweighted;            /* --unweighted -> ComputeCounts -u */
+  int32_t unambiguous;           /* --unambig    -> ComputeCounts -U (gene and exon runs) */
+  int32_t containment;           /* -C (gene run) */
+  int32_t nonsplice_conforming;  /* -N (gene and exon runs) */
+  double  distance_slack;        /* CombineSamFiles -s, default 0.25 */
+  int32_t modes;                 /* bit0 gene, bit1 exon, bit2 junction */
+  int32_t reserved;
+} eqp_params;
+
+/* Results of one chunk.  Vectors are indexed by the rank of the feature id in the map's sorted id set
+ * (ComputeCounts.java:877-897 prints in TreeSet order); eqp_feature_id() gives the id strings.
+ * `*_fixed` are the exact accumulators: value = fixed / 2^EQP_FIXED_SHIFT.  They are what eqp_reduce adds. */
+#define EQP_FIXED_SHIFT 38
+typedef struct eqp_counts {
+  int64_t n_gene, n_exon, n_junction;
+  const double* gene; const double* exon; const double* junction;
+  const uint64_t* gene_fixed; const uint64_t* exon_fixed; const uint64_t* junction_fixed;
+  const uint8_t* junction_active;            /* 1 = id survives filter-junction-map-files.sh for this chunk */
+  int64_t number_mapped_reads;               /* NUMBER_MAPPED_READS=   (ConvertSamBed.java:266) */
+  int64_t number_expressed_reads;            /* NUMBER_EXPRESSED_READS= (ComputeCounts.java:991-993, gene run) */
+  int64_t num_weight_objects[3];             /* per mode: gene, exon, junction (ComputeCounts.java:986-989) */
+  int64_t num_weight_objects_included[3];
+  int64_t num_weight_objects_excluded[3];
+  int64_t n_records[3];                      /* SAM records decoded per input: transcript, junction, genome */
+  double  device_ms;                         /* first kernel launch -> counts ready, CUDA events */
+  double  dominant_kernel_ms;                /* the SAM decode kernel, summed over the three inputs */
+  int64_t kernel_launches;
+} eqp_counts;
+
+int  eqp_version(void);
+void eqp_default_params(eqp_params* p);
+int  eqp_create(int device, eqp_ctx** out);
+int  eqp_load_annotation(eqp_ctx* ctx, const eqp_annotation_files* files);
+
+/* Count one chunk.  t_sam/j_sam/g_sam are UNCOMPRESSED SAM text (what `zcat` feeds the Java mains,
+ * compute-intersection-bed-file.sh:644-662).  *_on_device != 0 means the pointer is device memory already
+ * resident in HBM; otherwise it is host memory (pinned or pageable) and the call copies it.
+ * `out` stays valid until the next eqp_count_chunk / eqp_destroy on this ctx. */
+int  eqp_count_chunk(eqp_ctx* ctx, const eqp_params* params,
+                     const uint8_t* t_sam, size_t t_len, const uint8_t* j_sam, size_t j_len,
+                     const uint8_t* g_sam, size_t g_len, int on_device, eqp_counts* out);
+
+/* Feature ids, mode = 0 gene, 1 exon, 2 junction. */
+int64_t     eqp_feature_count(eqp_ctx* ctx, int mode);
+const char* eqp_feature_id(eqp_ctx* ctx, int mode, int64_t index);
+
+/* Device pointer + length (uint64 elements) of the concatenated gene|exon|junction fixed-point vector of the
+ * last chunk — what a sample-level NCCL sum reduces (replaces `combineCounts.py -A`, combineCounts.py:199-210). */
+int  eqp_device_vector(eqp_ctx* ctx, uint64_t** dev_ptr, int64_t* n_elements);
+/* Add the last chunk's vector into a caller-owned device accumulator of the same length (multi-chunk samples). */
+int  eqp_accumulate(eqp_ctx* ctx, uint64_t* dev_accumulator);
+
+/* Debug/parity taps: copy a device intermediate of the last chunk to the host.
+ * what: "weights:<T|J|G|TJ|final>", "selection", "blocks", "hits", "a20".  Layouts are documented in DESIGN.md. */
+int  eqp_debug_fetch(eqp_ctx* ctx, const char* what, void* dst, size_t dst_bytes, size_t* n_written);
+
+const char* eqp_last_error(eqp_ctx* ctx);
+void eqp_destroy(eqp_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

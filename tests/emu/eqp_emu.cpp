@@ -1,0 +1,69 @@
+// TEST-ONLY host emulation of the device pipeline: runs the very same per-item device functions
+// (eqp-cluster_b200/csrc/*.h) in plain loops on the CPU so their logic can be diffed against the oracle
+// in a container without a GPU.  Never linked into libeqpcount.so; the product path has no CPU fallback.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../../eqp-cluster_b200/csrc/eqp_pipeline.h"
+using namespace eqpb;
+
+struct HostBackend {
+  std::vector<void*> allocs;
+  template <class T> T* alloc(uint64_t n) { void* p = calloc(n ? n : 1, sizeof(T)); allocs.push_back(p); return (T*)p; }
+  void memset(void* p, int v, uint64_t bytes) { ::memset(p, v, bytes); }
+  template <class F> void launch(uint64_t n, F f) { for (uint64_t i = 0; i < n; i++) f(i); }
+  void scan(uint32_t* p, uint64_t n) { uint32_t acc = 0; for (uint64_t i = 0; i < n; i++) { uint32_t v = p[i]; p[i] = acc; acc += v; } p[n] = acc; }
+  void to_host(void* dst, const void* src, uint64_t bytes) { memcpy(dst, src, bytes); }
+  void to_device(void* dst, const void* src, uint64_t bytes) { memcpy(dst, src, bytes); }
+  void decode(const AnnoView& A, const SamView& S, uint32_t* err) { for (uint32_t i = 0; i < S.nLines; i++) decode_line(A, S, i, err); }
+  ~HostBackend() { for (void* p : allocs) free(p); }
+};
+
+static std::string slurp(const std::string& p) { return AnnoHost::slurp(p.c_str()); }
+
+int main(int argc, char** argv) {
+  if (argc < 5) { fprintf(stderr, "usage: eqp_emu <annodir> <chunkdir> <se|pe> <outdir>\n"); return 2; }
+  std::string anno = argv[1], chunk = argv[2], sfx = !strcmp(argv[3], "pe") ? "pe" : "sr", outd = argv[4], base = anno + "/ensembl_rna_hs";
+  try {
+    AnnoHost H;
+    H.load((base + "_100_combined_exons.bed").c_str(), (base + "_transcript_exons.bed").c_str(), (base + "_exon_gene.map").c_str(),
+           (base + "_exon_exon.map").c_str(), (base + "_exon_junction.map").c_str(), (base + "_exon_junction_transcript.map").c_str(),
+           (base + "_100_junction_junction_coordinate.map").c_str(), (base + "_equivalent_junctions.map").c_str(), (anno + "/genome.fa.fai").c_str());
+    std::string T = slurp(chunk + "/transcript-" + sfx + ".sam"), J = slurp(chunk + "/junction-" + sfx + ".sam"), G = slurp(chunk + "/genome-" + sfx + ".sam");
+    RunParams P{}; P.overlap[0] = 1; P.overlap[1] = 5; P.overlap[2] = 8;
+    for (int m = 0; m < 3; m++) { P.spliceConforming[m] = 1; P.containment[m] = 0; P.unambiguous[m] = 0; }
+    P.unweighted = 0; P.modes = 7; P.weightThreshold = 0.01; P.slack = 0.25;
+    HostBackend be; Pipeline<HostBackend> pl(be, H.view(), P);
+    const char* text[3] = {T.data(), J.data(), G.data()}; uint64_t len[3] = {T.size(), J.size(), G.size()};
+    ChunkResult R{};
+    int rc = pl.run(text, len, R);
+    if (rc) { fprintf(stderr, "ERROR: device error %u detail %u\n", R.err[0], R.err[1]); return 1; }
+    const char* names[3] = {"gene", "exon", "junction"};
+    for (int m = 0; m < 3; m++) {
+      FILE* f = fopen((outd + "/" + names[m] + ".tsv").c_str(), "w");
+      for (size_t i = 0; i < H.featIds[m].size(); i++) {
+        if (m == 2 && R.fixed[m][i] == 0) continue;
+        fprintf(f, "%s\t%llu\t%.17g\n", H.featIds[m][i].c_str(), R.fixed[m][i], R.counts[m][i]);
+      }
+      fclose(f);
+    }
+    { FILE* f = fopen((outd + "/weights.tsv").c_str(), "w");
+      for (uint32_t s = 0; s < pl.C.nSlots; s++) if (pl.V.a20[s]) fprintf(f, "F%09u\t%u\t%u\n", pl.C.base + s, pl.V.a20[s], pl.V.nFinal[s]);
+      fclose(f); }
+    { FILE* f = fopen((outd + "/samweights.tsv").c_str(), "w");
+      const char* fn[4] = {"T", "J", "G", "TJ"};
+      for (int k = 0; k < 4; k++) for (uint32_t s = 0; s < pl.C.nSlots; s++) {
+        const FragStat& st = k < 3 ? pl.C.st[k][s] : pl.C.stTJ[s];
+        if (!(st.flags & FS_EXISTS)) continue;
+        const char* cls = fe_mate(st) ? "paired-end" : (fe_mult(st) == 2 ? "single-read (both)" : "single-read");
+        fprintf(f, "%s\tF%09u\t%d\t%d\t%s\n", fn[k], pl.C.base + s, fe_n(st), fe_sum(st), cls);
+      }
+      fclose(f); }
+    { FILE* f = fopen((outd + "/stats.txt").c_str(), "w");
+      fprintf(f, "NUMBER_MAPPED_READS=%llu\nNUMBER_EXPRESSED_READS=%llu\nNUM_WEIGHT_OBJECTS=%llu\nBLOCKS=%u\nHITS=%u\nALIGNMENTS=%u\n", R.stats[9], R.stats[1], R.stats[0], pl.nBlocks, pl.nHits, pl.nAln);
+      fclose(f); }
+    return 0;
+  } catch (const std::exception& e) { fprintf(stderr, "ERROR: %s\n", e.what()); return 1; }
+}
