@@ -1,0 +1,223 @@
+// CUDA backend of the chunk pipeline (sm_100a): stream-ordered allocation, the generic per-item launcher,
+// a three-phase exclusive scan, the SAM line-index kernels and the tiled shared-memory SAM decode kernel.
+// The per-item logic lives in the eqp_*.h headers; this file owns how it is mapped to the machine.
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include "eqp_pipeline.h"
+
+namespace eqpb {
+
+struct CudaError : std::runtime_error { CudaError(const std::string& m) : std::runtime_error(m) {} };
+#define EQP_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) throw CudaError(std::string(#x) + ": " + cudaGetErrorString(e_)); } while (0)
+
+static const int EQP_NUM_SMS_DEFAULT = 148;
+
+// ---------------------------------------------------------------- generic per-item kernel
+template <class F>
+__global__ void __launch_bounds__(256) k_items(uint64_t n, F f) {
+  uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
+}
+
+// ---------------------------------------------------------------- scan (exclusive, in place, total at p[n])
+static const int SCAN_THREADS = 256, SCAN_ITEMS = 8, SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* total) {   // 256 threads
+  __shared__ uint32_t warpSum[8];
+  uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5, x = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= (uint32_t)d) x += y; }
+  if (lane == 31) warpSum[w] = x;
+  __syncthreads();
+  if (w == 0) {
+    uint32_t s = lane < 8 ? warpSum[lane] : 0;
+#pragma unroll
+    for (int d = 1; d < 8; d <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, s, d); if (lane >= (uint32_t)d) s += y; }
+    if (lane < 8) warpSum[lane] = s;
+  }
+  __syncthreads();
+  uint32_t base = w ? warpSum[w - 1] : 0;
+  *total = warpSum[7];
+  __syncthreads();
+  return base + x - v;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_tile_sums(const uint32_t* __restrict__ p, uint64_t n, uint32_t* __restrict__ sums) {
+  uint64_t b = (uint64_t)blockIdx.x * SCAN_TILE; uint32_t s = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) { uint64_t i = b + (uint64_t)k * SCAN_THREADS + threadIdx.x; if (i < n) s += p[i]; }
+  uint32_t tot; block_exclusive_scan(s, &tot);
+  if (threadIdx.x == 0) sums[blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_single(uint32_t* p, uint64_t n) {       // one block walks the whole array
+  uint32_t carry = 0;
+  for (uint64_t b = 0; b < n; b += SCAN_THREADS) {
+    uint64_t i = b + threadIdx.x; uint32_t v = i < n ? p[i] : 0, tot;
+    uint32_t ex = block_exclusive_scan(v, &tot);
+    if (i < n) p[i] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) p[n] = carry;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(uint32_t* __restrict__ p, uint64_t n, const uint32_t* __restrict__ tileOff, uint64_t nTiles) {
+  uint64_t b = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_ITEMS; uint32_t v[SCAN_ITEMS]; uint32_t s = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) { v[k] = b + k < n ? p[b + k] : 0; s += v[k]; }
+  uint32_t tot; uint32_t ex = block_exclusive_scan(s, &tot) + tileOff[blockIdx.x];
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) { if (b + k < n) p[b + k] = ex; ex += v[k]; }
+  if (blockIdx.x == nTiles - 1 && threadIdx.x == 0) p[n] = tileOff[nTiles];
+}
+
+// ---------------------------------------------------------------- line index
+// One warp per LINE_TILE (1024 B) tile: 16-byte loads, per-byte compare with '\n', warp reduction.
+static const int LI_WARPS = 8;
+__device__ __forceinline__ uint32_t nl_mask16(uint4 v) {                // bit k set iff byte k == '\n'
+  uint32_t w[4] = {v.x, v.y, v.z, v.w}; uint32_t m = 0;
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    uint32_t x = w[q] ^ 0x0a0a0a0au;                                     // zero bytes mark newlines
+    uint32_t z = ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu); // 0x80 in every zero byte (exact, no carries across bytes)
+    m |= (((z >> 7) & 1u) | ((z >> 14) & 2u) | ((z >> 21) & 4u) | ((z >> 28) & 8u)) << (4 * q);
+  }
+  return m;
+}
+__global__ void __launch_bounds__(LI_WARPS * 32) k_count_newlines(const char* __restrict__ text, uint64_t len, uint64_t nTiles, uint32_t* __restrict__ cnt) {
+  uint64_t t = (uint64_t)blockIdx.x * LI_WARPS + (threadIdx.x >> 5); uint32_t lane = threadIdx.x & 31;
+  if (t >= nTiles) return;
+  uint64_t b = t * LINE_TILE; uint32_t c = 0;
+  if (b + LINE_TILE <= len && (((uintptr_t)(text + b)) & 15) == 0) {
+    const uint4* q = reinterpret_cast<const uint4*>(text + b);
+#pragma unroll
+    for (int k = 0; k < (int)(LINE_TILE / 512); k++) c += __popc(nl_mask16(__ldg(q + k * 32 + lane)));
+  } else {
+    uint64_t e = b + LINE_TILE < len ? b + LINE_TILE : len;
+    for (uint64_t i = b + lane; i < e; i += 32) c += text[i] == '\n';
+  }
+  c = __reduce_add_sync(0xffffffffu, c);
+  if (lane == 0) cnt[t] = c;
+}
+// cnt[] now holds exclusive tile offsets; write lineOff[k] = byte after the k-th newline (k >= 1), lineOff[0] = 0.
+__global__ void __launch_bounds__(LI_WARPS * 32) k_fill_line_offsets(const char* __restrict__ text, uint64_t len, uint64_t nTiles, const uint32_t* __restrict__ cnt,
+                                                                     uint64_t* __restrict__ lineOff, uint32_t nLines, int lastIsNewline) {
+  uint64_t t = (uint64_t)blockIdx.x * LI_WARPS + (threadIdx.x >> 5); uint32_t lane = threadIdx.x & 31;
+  if (t >= nTiles) return;
+  uint64_t b = t * LINE_TILE, e = b + LINE_TILE < len ? b + LINE_TILE : len; uint32_t k = cnt[t];
+  if (t == 0 && lane == 0) lineOff[0] = 0;
+  if (e == len && !lastIsNewline && lane == 0) lineOff[nLines] = len + 1;
+  if (b + LINE_TILE <= len && (((uintptr_t)(text + b)) & 15) == 0) {
+    const uint4* q = reinterpret_cast<const uint4*>(text + b);
+#pragma unroll
+    for (int r = 0; r < (int)(LINE_TILE / 512); r++) {
+      uint32_t m = nl_mask16(__ldg(q + r * 32 + lane)); uint32_t c = __popc(m);
+      uint32_t x = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= (uint32_t)d) x += y; }
+      uint32_t mine = k + x - c; uint64_t base = b + (uint64_t)r * 512 + lane * 16;
+      while (m) { int bit = __ffs(m) - 1; m &= m - 1; lineOff[++mine] = base + bit + 1; }
+      k += __shfl_sync(0xffffffffu, x, 31);
+    }
+  } else {
+    for (uint64_t i0 = b; i0 < e; i0 += 32) {
+      uint64_t i = i0 + lane; bool nl = i < e && text[i] == '\n';
+      uint32_t bal = __ballot_sync(0xffffffffu, nl);
+      if (nl) lineOff[k + __popc(bal & ((1u << lane) - 1)) + 1] = i + 1;
+      k += __popc(bal);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- SAM decode (the dominant kernel)
+// A CTA owns DEC_LINES consecutive lines.  Their bytes are one contiguous range of the text, which the CTA stages
+// in shared memory with coalesced 16-byte loads; each thread then tokenises its own line out of shared memory
+// (decode_line, eqp_decode.h).  Ranges larger than the staging buffer (pathological line lengths) are parsed from
+// global memory directly.
+static const int DEC_LINES = 128;
+static const int DEC_SMEM = 55 * 1024;
+__global__ void __launch_bounds__(DEC_LINES) k_decode_sam(AnnoView A, SamView S, uint32_t* err) {
+  extern __shared__ __align__(16) char stage[];
+  uint32_t l0 = blockIdx.x * DEC_LINES, l1 = l0 + DEC_LINES < S.nLines ? l0 + DEC_LINES : S.nLines;
+  uint64_t b = S.lineOff[l0], e = S.lineOff[l1] - 1;                    // bytes [b, e) incl. the final '\n' (or len)
+  if (e > S.len) e = S.len;
+  const char* g0 = S.text + b; uint64_t nBytes = e > b ? e - b : 0;
+  uint32_t mis = (uint32_t)((uintptr_t)g0 & 15);                        // stage from the 16-byte boundary below g0
+  uint32_t li = l0 + threadIdx.x;
+  if (nBytes + mis <= (uint64_t)DEC_SMEM) {
+    const char* ga = g0 - mis; uint64_t tot = nBytes + mis; uint64_t nVec = tot / 16;
+    const uint4* gv = reinterpret_cast<const uint4*>(ga); uint4* sv = reinterpret_cast<uint4*>(stage);
+    for (uint64_t i = threadIdx.x; i < nVec; i += DEC_LINES) sv[i] = __ldg(gv + i);
+    for (uint64_t i = nVec * 16 + threadIdx.x; i < tot; i += DEC_LINES) stage[i] = ga[i];
+    __syncthreads();
+    if (li < l1) { SamView T = S; T.text = stage + mis - b; decode_line(A, T, li, err); }
+  } else if (li < l1) {
+    decode_line(A, S, li, err);
+  }
+}
+
+// ---------------------------------------------------------------- backend
+struct CudaBackend {
+  cudaStream_t stream; int nSm;
+  std::vector<void*> allocs;
+  cudaEvent_t evDec0 = nullptr, evDec1 = nullptr; float decodeMs = 0; long launches = 0; uint64_t bytesAllocated = 0;
+
+  explicit CudaBackend(cudaStream_t s, int sms) : stream(s), nSm(sms > 0 ? sms : EQP_NUM_SMS_DEFAULT) {
+    EQP_CUDA(cudaEventCreate(&evDec0)); EQP_CUDA(cudaEventCreate(&evDec1));
+  }
+  ~CudaBackend() { release(); if (evDec0) cudaEventDestroy(evDec0); if (evDec1) cudaEventDestroy(evDec1); }
+  void release() { for (void* p : allocs) cudaFreeAsync(p, stream); allocs.clear(); bytesAllocated = 0; }
+
+  template <class T> T* alloc(uint64_t n) {
+    void* p = nullptr; uint64_t bytes = (n ? n : 1) * sizeof(T) + 16;
+    EQP_CUDA(cudaMallocAsync(&p, bytes, stream)); allocs.push_back(p); bytesAllocated += bytes; return (T*)p;
+  }
+  void memset(void* p, int v, uint64_t bytes) { if (bytes) EQP_CUDA(cudaMemsetAsync(p, v, bytes, stream)); }
+  void to_host(void* dst, const void* src, uint64_t bytes) {
+    EQP_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream)); EQP_CUDA(cudaStreamSynchronize(stream));
+  }
+  void to_device(void* dst, const void* src, uint64_t bytes) {
+    EQP_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream)); EQP_CUDA(cudaStreamSynchronize(stream));
+  }
+  int grid_for(uint64_t n, int threads) const {
+    uint64_t g = (n + threads - 1) / threads, cap = (uint64_t)nSm * 32;  // grid-stride beyond 32 CTAs per SM
+    return (int)(g < cap ? (g ? g : 1) : cap);
+  }
+  template <class F> void launch(uint64_t n, F f) {
+    if (!n) return;
+    k_items<<<grid_for(n, 256), 256, 0, stream>>>(n, f); launches++;
+    EQP_CUDA(cudaGetLastError());
+  }
+  void scan(uint32_t* p, uint64_t n) {
+    if (n <= (uint64_t)SCAN_TILE * 4) { k_scan_single<<<1, SCAN_THREADS, 0, stream>>>(p, n); launches++; EQP_CUDA(cudaGetLastError()); return; }
+    uint64_t nTiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    uint32_t* sums = alloc<uint32_t>(nTiles + 1);
+    k_scan_tile_sums<<<(unsigned)nTiles, SCAN_THREADS, 0, stream>>>(p, n, sums); launches++;
+    scan(sums, nTiles);
+    k_scan_apply<<<(unsigned)nTiles, SCAN_THREADS, 0, stream>>>(p, n, sums, nTiles); launches++;
+    EQP_CUDA(cudaGetLastError());
+  }
+  // line index: counts per LINE_TILE tile, then offsets (Pipeline::index_lines calls these instead of the generic lambdas)
+  void count_newlines(const char* text, uint64_t len, uint64_t nTiles, uint32_t* cnt) {
+    if (!nTiles) return;
+    k_count_newlines<<<(unsigned)((nTiles + LI_WARPS - 1) / LI_WARPS), LI_WARPS * 32, 0, stream>>>(text, len, nTiles, cnt); launches++;
+    EQP_CUDA(cudaGetLastError());
+  }
+  void fill_line_offsets(const char* text, uint64_t len, uint64_t nTiles, const uint32_t* cnt, uint64_t* lineOff, uint32_t nLines, char last) {
+    if (!nTiles) return;
+    k_fill_line_offsets<<<(unsigned)((nTiles + LI_WARPS - 1) / LI_WARPS), LI_WARPS * 32, 0, stream>>>(text, len, nTiles, cnt, lineOff, nLines, last == '\n'); launches++;
+    EQP_CUDA(cudaGetLastError());
+  }
+  void decode(const AnnoView& A, const SamView& S, uint32_t* err) {
+    if (!S.nLines) return;
+    static bool attr = false;
+    if (!attr) { EQP_CUDA(cudaFuncSetAttribute(k_decode_sam, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_SMEM)); attr = true; }
+    EQP_CUDA(cudaEventRecord(evDec0, stream));
+    k_decode_sam<<<(S.nLines + DEC_LINES - 1) / DEC_LINES, DEC_LINES, DEC_SMEM, stream>>>(A, S, err); launches++;
+    EQP_CUDA(cudaGetLastError());
+    EQP_CUDA(cudaEventRecord(evDec1, stream)); EQP_CUDA(cudaEventSynchronize(evDec1));
+    float ms = 0; EQP_CUDA(cudaEventElapsedTime(&ms, evDec0, evDec1)); decodeMs += ms;
+  }
+};
+
+}  // namespace eqpb

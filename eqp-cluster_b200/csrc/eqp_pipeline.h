@@ -4,7 +4,7 @@
 #pragma once
 #include <string>
 #include <vector>
-#include "eqp_count.h"
+#include "eqp_accumulate.h"
 
 #if defined(__CUDACC__)
 #define EQP_LAMBDA __host__ __device__
@@ -43,6 +43,7 @@ struct Pipeline {
   uint32_t nBlocks = 0, nAln = 0, nHits = 0;
   uint32_t* scal = nullptr;                           // device scalars: [0..1] err, [2..7] min/max frag per file, [8..] presence bounds
   uint32_t* tileCnt[3] = {nullptr, nullptr, nullptr};
+  unsigned long long* accOut[3] = {nullptr, nullptr, nullptr};   // caller-owned accumulators (nFeat[m] + 1 entries); allocated here when null
 
   Pipeline(BE& b, const AnnoView& a, const RunParams& p) : be(b), A(a), P(p) {}
 
@@ -50,23 +51,14 @@ struct Pipeline {
     SamView& S = C.sam[f]; S.text = text; S.len = len;
     uint64_t nTiles = (len + LINE_TILE - 1) / LINE_TILE;
     uint32_t* cnt = be.template alloc<uint32_t>(nTiles + 1); tileCnt[f] = cnt;
-    be.launch(nTiles, [=] EQP_LAMBDA(uint64_t t) {
-      uint64_t b = t * LINE_TILE, e = b + LINE_TILE < len ? b + LINE_TILE : len; uint32_t c = 0;
-      for (uint64_t i = b; i < e; i++) c += text[i] == '\n';
-      cnt[t] = c;
-    });
+    be.count_newlines(text, len, nTiles, cnt);
     be.scan(cnt, nTiles);
     uint32_t nl = 0; be.to_host(&nl, cnt + nTiles, sizeof nl);
     char last = 0; if (len) be.to_host(&last, text + len - 1, 1);
     S.nLines = len == 0 ? 0 : (last == '\n' ? nl : nl + 1);
     S.lineOff = be.template alloc<uint64_t>((uint64_t)S.nLines + 1);
     uint64_t* lo = S.lineOff; uint32_t nLines = S.nLines;
-    be.launch(nTiles, [=] EQP_LAMBDA(uint64_t t) {
-      uint64_t b = t * LINE_TILE, e = b + LINE_TILE < len ? b + LINE_TILE : len; uint32_t k = cnt[t];
-      if (t == 0) lo[0] = 0;
-      for (uint64_t i = b; i < e; i++) if (text[i] == '\n') { lo[++k] = i + 1; }
-      if (e == len && last != '\n') lo[nLines] = len + 1;
-    });
+    be.fill_line_offsets(text, len, nTiles, cnt, lo, nLines, last);
     uint64_t n = S.nLines;
     S.frag = be.template alloc<uint32_t>(n); S.ref = be.template alloc<int32_t>(n); S.pos = be.template alloc<int32_t>(n);
     S.rnext = be.template alloc<int32_t>(n); S.pnext = be.template alloc<int32_t>(n); S.flag = be.template alloc<uint16_t>(n);
@@ -184,7 +176,7 @@ struct Pipeline {
     // ---- a12-a25
     V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
     V.a20 = be.template alloc<uint32_t>((uint64_t)N + 1); V.nFinal = be.template alloc<uint32_t>((uint64_t)N + 1);
-    for (int m = 0; m < 3; m++) { V.acc[m] = be.template alloc<unsigned long long>((uint64_t)A.nFeat[m] + 1); be.memset(V.acc[m], 0, ((uint64_t)A.nFeat[m] + 1) * 8); }
+    for (int m = 0; m < 3; m++) { V.acc[m] = accOut[m] ? accOut[m] : be.template alloc<unsigned long long>((uint64_t)A.nFeat[m] + 1); be.memset(V.acc[m], 0, ((uint64_t)A.nFeat[m] + 1) * 8); }
     { const ChunkView C = this->C; const CountView V = this->V;
       be.launch(N, [=] EQP_LAMBDA(uint64_t s) { fragment_alignments(A, C, V, P, (uint32_t)s); });
       be.launch(N, [=] EQP_LAMBDA(uint64_t s) { fragment_weight(A, C, V, P, (uint32_t)s); });

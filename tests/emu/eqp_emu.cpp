@@ -17,6 +17,17 @@ struct HostBackend {
   void scan(uint32_t* p, uint64_t n) { uint32_t acc = 0; for (uint64_t i = 0; i < n; i++) { uint32_t v = p[i]; p[i] = acc; acc += v; } p[n] = acc; }
   void to_host(void* dst, const void* src, uint64_t bytes) { memcpy(dst, src, bytes); }
   void to_device(void* dst, const void* src, uint64_t bytes) { memcpy(dst, src, bytes); }
+  void count_newlines(const char* text, uint64_t len, uint64_t nTiles, uint32_t* cnt) {
+    for (uint64_t t = 0; t < nTiles; t++) { uint64_t b = t * LINE_TILE, e = b + LINE_TILE < len ? b + LINE_TILE : len; uint32_t c = 0; for (uint64_t i = b; i < e; i++) c += text[i] == '\n'; cnt[t] = c; }
+  }
+  void fill_line_offsets(const char* text, uint64_t len, uint64_t nTiles, const uint32_t* cnt, uint64_t* lo, uint32_t nLines, char last) {
+    for (uint64_t t = 0; t < nTiles; t++) {
+      uint64_t b = t * LINE_TILE, e = b + LINE_TILE < len ? b + LINE_TILE : len; uint32_t k = cnt[t];
+      if (t == 0) lo[0] = 0;
+      for (uint64_t i = b; i < e; i++) if (text[i] == '\n') lo[++k] = i + 1;
+      if (e == len && last != '\n') lo[nLines] = len + 1;
+    }
+  }
   void decode(const AnnoView& A, const SamView& S, uint32_t* err) { for (uint32_t i = 0; i < S.nLines; i++) decode_line(A, S, i, err); }
   ~HostBackend() { for (void* p : allocs) free(p); }
 };
