@@ -92,6 +92,8 @@ int  eqp_version(void);
 void eqp_default_params(eqp_params* p);
 int  eqp_create(int device, eqp_ctx** out);
 int  eqp_load_annotation(eqp_ctx* ctx, const eqp_annotation_files* files);
+/* Device-resident bytes of the annotation index (the |annotation index| term of the algorithmic bytes). */
+int64_t eqp_annotation_bytes(eqp_ctx* ctx);
 
 /* Count one chunk.  t_sam/j_sam/g_sam are UNCOMPRESSED SAM text (what `zcat` feeds the Java mains,
  * compute-intersection-bed-file.sh:644-662).  *_on_device != 0 means the pointer is device memory already

@@ -45,7 +45,14 @@ int main(int argc, char** argv) {
     std::string T = slurp(chunk + "/transcript-" + sfx + ".sam"), J = slurp(chunk + "/junction-" + sfx + ".sam"), G = slurp(chunk + "/genome-" + sfx + ".sam");
     RunParams P{}; P.overlap[0] = 1; P.overlap[1] = 5; P.overlap[2] = 8;
     for (int m = 0; m < 3; m++) { P.spliceConforming[m] = 1; P.containment[m] = 0; P.unambiguous[m] = 0; }
-    P.unweighted = 0; P.modes = 7; P.weightThreshold = 0.01; P.slack = 0.25;
+    P.unweighted = 0;
+    for (int i = 5; i < argc; i++) {                                     // same switches as the oracle driver
+      if (!strcmp(argv[i], "--unweighted")) P.unweighted = 1;
+      else if (!strcmp(argv[i], "--unambig")) P.unambiguous[0] = P.unambiguous[1] = 1;
+      else if (!strcmp(argv[i], "--containment")) P.containment[0] = 1;
+      else if (!strcmp(argv[i], "--nonsplice")) P.spliceConforming[0] = P.spliceConforming[1] = 0;
+    }
+    P.modes = 7; P.weightThreshold = 0.01; P.slack = 0.25;
     HostBackend be; Pipeline<HostBackend> pl(be, H.view(), P);
     const char* text[3] = {T.data(), J.data(), G.data()}; uint64_t len[3] = {T.size(), J.size(), G.size()};
     ChunkResult R{};
