@@ -98,10 +98,13 @@ struct Pipeline {
       be.launch(S.nLines, [=] EQP_LAMBDA(uint64_t i) {
         if (!(S.rf[i] & RF_REC)) return;
         uint32_t fr = S.frag[i];
-        bool prevRec = i > 0 && (S.rf[i - 1] & RF_REC), nextRec = i + 1 < S.nLines && (S.rf[i + 1] & RF_REC);
-        if (prevRec && S.frag[i - 1] > fr) raise(err, DERR_ORDER, fr);
-        if (!prevRec || S.frag[i - 1] != fr) ff[fr - base].first = (uint32_t)i;
-        if (!nextRec || S.frag[i + 1] != fr) ff[fr - base].end = (uint32_t)i + 1;
+        uint64_t pi = i, ni = i + 1;                                     // nearest record lines around i (header / empty lines skipped)
+        while (pi > 0 && !(S.rf[pi - 1] & RF_REC)) pi--;
+        while (ni < S.nLines && !(S.rf[ni] & RF_REC)) ni++;
+        bool prevRec = pi > 0, nextRec = ni < S.nLines;
+        if (prevRec && S.frag[pi - 1] > fr) raise(err, DERR_ORDER, fr);
+        if (!prevRec || S.frag[pi - 1] != fr) ff[fr - base].first = (uint32_t)i;
+        if (!nextRec || S.frag[ni] != fr) ff[fr - base].end = (uint32_t)i + 1;
       }); }
     // ---- a3/a4: per-fragment statistics in each input
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
