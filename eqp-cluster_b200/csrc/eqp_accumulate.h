@@ -18,48 +18,42 @@ EQP_HD int eqp_popc(uint32_t m) {
 #endif
 }
 
-// ---- stage A: sort each alignment's hits, build both halves, hash the canonical key
-EQP_HD void fragment_alignments(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, uint32_t slot) {
-  uint32_t b0 = C.blkOff[slot], b1 = C.blkOff[slot + 1];
-  if (b0 == b1) return;
-  uint32_t h0 = C.hitCnt[b0], h1 = C.hitCnt[b1]; uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1]; uint32_t frag = C.base + slot;
-  for (uint32_t a = a0; a < a1; a++) { Aln& al = V.alns[a]; al.hit0 = al.hit1 = al.split = 0; al.flags = 0; al.repr = a; al.key = 0; }
-  uint32_t k = h0;
-  while (k < h1) {                                                       // hits are grouped by block, blocks by alignment
-    uint32_t aln = C.blocks[C.hits[k].block].aln; uint32_t e = k + 1;
-    while (e < h1 && C.blocks[C.hits[e].block].aln == aln) e++;
-    Aln& al = V.alns[a0 + aln];
-    for (uint32_t i = k + 1; i < e; i++) {                               // insertion sort by (readIdx, readStart, eRefStart, eRefEnd, strand, row)
-      Hit cur = C.hits[i]; RecKey ck = rec_key(A, C, cur); uint32_t j = i;
-      while (j > k) { RecKey pk = rec_key(A, C, C.hits[j - 1]); int c = rec_cmp(pk, ck); if (c < 0 || (c == 0 && pk.row <= ck.row)) break; C.hits[j] = C.hits[j - 1]; j--; }
-      C.hits[j] = cur;
-    }
-    uint32_t split = k; while (split < e && C.blocks[C.hits[split].block].readIdx == 1) split++;
-    al.hit0 = k; al.split = split; al.hit1 = e;
-    const Block& fb = C.blocks[C.hits[k].block];
-    uint8_t fl = fb.paired ? 1 : 0;
-    for (uint32_t i = k; i < e; i++) if ((C.blocks[C.hits[i].block].paired ? 1 : 0) != (fl & 1)) raise(C.err, DERR_INCONSISTENT, frag);
-    al.start1 = al.start2 = 0x7fffffff; al.nIv1 = al.nIv2 = 0; al.maxField1 = al.maxField2 = -1;
-    if (split > k) { build_half(A, C, V, P, k, split, 1, al.start1, al.nIv1, al.maxField1, frag); fl |= 2; }
-    if (e > split) { build_half(A, C, V, P, split, e, 2, al.start2, al.nIv2, al.maxField2, frag); fl |= 4; }
-    if (!(fl & 1)) fl |= (uint8_t)(((fl & 2) ? 1 : 2) << 3);
-    if (!(fl & 1) && (fl & 2) && (fl & 4)) raise(C.err, DERR_INCONSISTENT, frag);   // single-read alignment with both read indices
-    al.flags = fl;
-    // canonical key (strand slot is empty in the reference's strings: GenomicInterval never sets originalStrand)
-    bool both = (fl & 2) && (fl & 4); bool secondFirst = both && !(al.start1 <= al.start2);
-    uint64_t hsh = mix64(0x1234, (uint64_t)((fl & 1) ? 0 : (fl >> 3) & 3));
-    hsh = mix64(hsh, both ? 0 : (fl & 2) ? 1 : 2);
-    for (int part = 0; part < 2; part++) {
-      int half = both ? (secondFirst ? 2 - part : 1 + part) : ((fl & 2) ? 1 : 2);
-      if (!both && part == 1) break;
-      uint32_t s0 = half == 1 ? k : split, s1 = half == 1 ? split : e; int nIv = half == 1 ? al.nIv1 : al.nIv2;
-      hsh = mix64(hsh, 0xABCDEF00u + (uint64_t)nIv);
-      for (int r = 0; r < nIv; r++)
-        for (uint32_t i = s0; i < s1; i++) { const HitX& x = V.hx[i]; if ((x.flags & 1) && x.ivRank == r) { hsh = mix64(mix64(mix64(hsh, (uint64_t)x.chr), (uint64_t)x.gs), (uint64_t)x.ge); break; } }
-    }
-    al.key = hsh;
-    k = e;
+// ---- stage A (one alignment per item): sort the alignment's hits, build both halves, hash the canonical key
+EQP_HD void alignment_build(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, uint32_t a) {
+  uint32_t b0 = C.alnBlk[a], b1 = C.alnBlk[a + 1];
+  uint32_t k = C.hitCnt[b0], e = C.hitCnt[b1];                           // hits are grouped by block, blocks by alignment
+  Aln& al = V.alns[a]; al.hit0 = al.hit1 = al.split = 0; al.flags = 0; al.repr = a; al.key = 0; al.next = 0xFFFFFFFFu;
+  if (k == e) return;
+  uint32_t frag = C.base + C.blocks[b0].slot;
+  for (uint32_t i = k + 1; i < e; i++) {                                 // insertion sort by (readIdx, readStart, eRefStart, eRefEnd, strand, row)
+    Hit cur = C.hits[i]; RecKey ck = rec_key(A, C, cur); uint32_t j = i;
+    while (j > k) { RecKey pk = rec_key(A, C, C.hits[j - 1]); int c = rec_cmp(pk, ck); if (c < 0 || (c == 0 && pk.row <= ck.row)) break; C.hits[j] = C.hits[j - 1]; j--; }
+    C.hits[j] = cur;
   }
+  uint32_t split = k; while (split < e && C.blocks[C.hits[split].block].readIdx == 1) split++;
+  al.hit0 = k; al.split = split; al.hit1 = e;
+  const Block& fb = C.blocks[C.hits[k].block];
+  uint8_t fl = fb.paired ? 1 : 0;
+  for (uint32_t i = k; i < e; i++) if ((C.blocks[C.hits[i].block].paired ? 1 : 0) != (fl & 1)) raise(C.err, DERR_INCONSISTENT, frag);
+  al.start1 = al.start2 = 0x7fffffff; al.nIv1 = al.nIv2 = 0; al.maxField1 = al.maxField2 = -1;
+  if (split > k) { build_half(A, C, V, P, k, split, 1, al.start1, al.nIv1, al.maxField1, frag); fl |= 2; }
+  if (e > split) { build_half(A, C, V, P, split, e, 2, al.start2, al.nIv2, al.maxField2, frag); fl |= 4; }
+  if (!(fl & 1)) fl |= (uint8_t)(((fl & 2) ? 1 : 2) << 3);
+  if (!(fl & 1) && (fl & 2) && (fl & 4)) raise(C.err, DERR_INCONSISTENT, frag);     // single-read alignment with both read indices
+  al.flags = fl;
+  // canonical key (strand slot is empty in the reference's strings: GenomicInterval never sets originalStrand)
+  bool both = (fl & 2) && (fl & 4); bool secondFirst = both && !(al.start1 <= al.start2);
+  uint64_t hsh = mix64(0x1234, (uint64_t)((fl & 1) ? 0 : (fl >> 3) & 3));
+  hsh = mix64(hsh, both ? 0 : (fl & 2) ? 1 : 2);
+  for (int part = 0; part < 2; part++) {
+    int half = both ? (secondFirst ? 2 - part : 1 + part) : ((fl & 2) ? 1 : 2);
+    if (!both && part == 1) break;
+    uint32_t s0 = half == 1 ? k : split, s1 = half == 1 ? split : e; int nIv = half == 1 ? al.nIv1 : al.nIv2;
+    hsh = mix64(hsh, 0xABCDEF00u + (uint64_t)nIv);
+    for (int r = 0; r < nIv; r++)
+      for (uint32_t i = s0; i < s1; i++) { const HitX& x = V.hx[i]; if ((x.flags & 1) && x.ivRank == r) { hsh = mix64(mix64(mix64(hsh, (uint64_t)x.chr), (uint64_t)x.gs), (uint64_t)x.ge); break; } }
+  }
+  al.key = hsh;
 }
 
 // interval r of a half: first valid record with that rank
@@ -107,7 +101,15 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
   for (uint32_t a = a0; a < a1; a++) {
     Aln& al = V.alns[a]; if (al.hit0 == al.hit1) continue;
     al.repr = a;
-    for (uint32_t p = a0; p < a; p++) { const Aln& q = V.alns[p]; if (q.hit0 == q.hit1 || q.repr != p) continue; bool sw; if (keys_equal(V, q, al, sw)) { al.repr = p; break; } }
+    for (uint32_t p = a0; p < a; p++) {
+      const Aln& q = V.alns[p]; if (q.hit0 == q.hit1 || q.repr != p) continue;
+      bool sw;
+      if (keys_equal(V, q, al, sw)) {                                      // duplicate: append to the representative's chain (file order)
+        al.repr = p; if (sw) al.flags |= 32;
+        uint32_t t = p; while (V.alns[t].next != 0xFFFFFFFFu) t = V.alns[t].next;
+        V.alns[t].next = a; break;
+      }
+    }
     if (al.repr == a) { if ((al.flags & 6) == 4) right++; else left++; }   // ":r-" forms (WeightObject.java:859-865)
   }
   uint32_t a20 = (uint32_t)(left > right ? left : right);
@@ -145,9 +147,9 @@ EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView
   for (int iv = 0; iv < nIv; iv++) {
     int32_t chr, gs, ge; int field; half_interval(V, r0, r1, iv, chr, gs, ge, field);
     int32_t exon[32]; uint8_t exGen[32]; int ne = 0;
-    for (uint32_t d = r; d < a1; d++) {                                   // R first, then later duplicates in file order
-      const Aln& D = V.alns[d]; if (D.hit0 == D.hit1 || D.repr != r) continue;
-      int hd = h; if (d != r) { bool sw; keys_equal(V, R, D, sw); if (sw) hd = 3 - h; }
+    for (uint32_t d = r; d != 0xFFFFFFFFu; d = V.alns[d].next) {          // R first, then later duplicates in file order
+      const Aln& D = V.alns[d];
+      int hd = (d != r && (D.flags & 32)) ? 3 - h : h;
       uint32_t d0 = hd == 1 ? D.hit0 : D.split, d1 = hd == 1 ? D.split : D.hit1;
       for (uint32_t i = d0; i < d1; i++) {
         const HitX& x = V.hx[i];

@@ -24,10 +24,12 @@ EQP_HD uint64_t fnv1a(const char* p, int n) {
   return h ? h : 1;                                   // 0 marks an empty slot
 }
 
+EQP_HD uint64_t dict_key(uint64_t h, int len) { uint64_t k = (h & ~0xFFFFULL) | (uint64_t)(len & 0xFFFF); return k ? k : 0x10000ULL; }
+
 struct AnnoError : std::runtime_error { int code; AnnoError(int c, const std::string& m) : std::runtime_error(m), code(c) {} };
 
 struct AnnoHost {
-  std::vector<uint64_t> dictHash; std::vector<int32_t> dictVal; uint32_t dictMask = 0;
+  std::vector<DictEntry> dict; uint32_t dictMask = 0;
   std::string strPool; std::vector<uint32_t> refStrOff; std::vector<uint16_t> refStrLen; std::vector<uint8_t> refFlags;
   std::vector<uint32_t> refVerOff; std::vector<int32_t> refVerBucket;
   std::vector<uint32_t> refActOff; std::vector<int32_t> refAct;
@@ -147,11 +149,11 @@ struct AnnoHost {
       refVerOff.push_back((uint32_t)refVerBucket.size());
     }
     uint32_t cap = 16; while (cap < (uint32_t)nRef * 2u) cap <<= 1;
-    dictHash.assign(cap, 0); dictVal.assign(cap, -1); dictMask = cap - 1;
+    dict.assign(cap, DictEntry{0, -1, 0}); dictMask = cap - 1;
     for (int32_t r = 0; r < nRef; r++) {
       uint64_t h = fnv1a(refNames[r].data(), (int)refNames[r].size()); uint32_t s = (uint32_t)h & dictMask;
-      while (dictHash[s]) s = (s + 1) & dictMask;
-      dictHash[s] = h; dictVal[s] = r;
+      while (dict[s].key) s = (s + 1) & dictMask;
+      dict[s] = DictEntry{dict_key(h, (int)refNames[r].size()), r, refStrOff[r]};
     }
     // ---- exon -> feature lists (2- or 3-column maps; 3-column maps are rejected for now)
     const char* maps[3] = {geneMap, exonMap, junctionMap};
@@ -219,7 +221,7 @@ struct AnnoHost {
 
   AnnoView view() const {
     AnnoView v{};
-    v.dictHash = dictHash.data(); v.dictVal = dictVal.data(); v.dictMask = dictMask; v.strPool = strPool.data();
+    v.dict = dict.data(); v.dictMask = dictMask; v.strPool = strPool.data();
     v.refStrOff = refStrOff.data(); v.refStrLen = refStrLen.data(); v.refFlags = refFlags.data();
     v.refVerOff = refVerOff.data(); v.refVerBucket = refVerBucket.data(); v.refActOff = refActOff.data(); v.refAct = refAct.data();
     v.nRef = (int32_t)refStrOff.size();

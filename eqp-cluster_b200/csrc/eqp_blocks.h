@@ -15,6 +15,7 @@ struct ChunkView {                 // everything the per-fragment stages read/wr
   uint32_t* auxSlot;               // first slot >= s that has a T+J weight entry (UINT32_MAX if none)
   uint32_t* blkOff; uint32_t* alnOff;        // per slot: exclusive offsets (nSlots + 1)
   Block* blocks; uint32_t* hitCnt;           // hitCnt: per block count, then exclusive offsets (nBlocks + 1)
+  uint32_t* alnBlk;                          // per alignment: its first block (nAln + 1 entries; blocks of an alignment are contiguous)
   Hit* hits;
   uint8_t* seenRef;                // a27: reference ids seen in combined SAM or junction SAM
   uint32_t* err;
@@ -93,6 +94,7 @@ EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot
     uint32_t v0 = ref >= 0 ? A.refVerOff[ref] : 0, v1 = ref >= 0 ? A.refVerOff[ref + 1] : 0;
     for (uint32_t v = v0; v < v1; v++) {
       int32_t bucket = A.refVerBucket[v];
+      if (fill) C.alnBlk[C.alnOff[slot] + na] = bo + nb;                 // first block of this alignment
       for (int side = 0; side < 2; side++) {
         if (side == 1 && mateFile < 0) break;
         const SamView& R = side ? C.sam[mateFile] : S; uint32_t li = side ? mateLine : i;
@@ -105,7 +107,7 @@ EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot
           if (fill) {
             Block& b = C.blocks[bo + nb];
             b.bucket = bucket; b.start = bedStart + off; b.end = bedStart + off + refLen; b.L = (uint16_t)readLen; b.I = (uint16_t)insSoft; b.D = (uint16_t)del;
-            b.seg = (uint8_t)seg; b.maxSeg = 0; b.aln = na; b.readIdx = ridx; b.paired = paired; b.strand = strand; b.pad = 0; b.hitOff = 0;
+            b.seg = (uint8_t)seg; b.maxSeg = 0; b.aln = na; b.readIdx = ridx; b.paired = paired; b.strand = strand; b.pad = 0; b.slot = slot;
           }
           nb++;
         }, sumRead, bad);

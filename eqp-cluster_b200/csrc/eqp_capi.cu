@@ -23,24 +23,24 @@ template <class T> struct DevArray {
 };
 
 struct AnnoDevice {
-  DevArray<uint64_t> dictHash; DevArray<int32_t> dictVal; DevArray<char> strPool; DevArray<uint32_t> refStrOff; DevArray<uint16_t> refStrLen;
+  DevArray<DictEntry> dict; DevArray<char> strPool; DevArray<uint32_t> refStrOff; DevArray<uint16_t> refStrLen;
   DevArray<uint8_t> refFlags; DevArray<uint32_t> refVerOff; DevArray<int32_t> refVerBucket; DevArray<uint32_t> refActOff; DevArray<int32_t> refAct;
   DevArray<uint32_t> bktRowOff; DevArray<uint8_t> bktFlags; DevArray<int32_t> rowStart, rowEnd, rowMaxEnd, rowExon; DevArray<uint8_t> rowFlags;
   DevArray<int32_t> exChr, exStart, exEnd; DevArray<uint8_t> exStrand; DevArray<uint32_t> featOff[3], feat[3];
   size_t bytes = 0;
   AnnoView upload(const AnnoHost& H) {
     AnnoView v = H.view();
-    dictHash.upload(H.dictHash); dictVal.upload(H.dictVal); strPool.upload(H.strPool.data(), H.strPool.size()); refStrOff.upload(H.refStrOff);
+    dict.upload(H.dict); strPool.upload(H.strPool.data(), H.strPool.size()); refStrOff.upload(H.refStrOff);
     refStrLen.upload(H.refStrLen); refFlags.upload(H.refFlags); refVerOff.upload(H.refVerOff); refVerBucket.upload(H.refVerBucket);
     refActOff.upload(H.refActOff); refAct.upload(H.refAct); bktRowOff.upload(H.bktRowOff); bktFlags.upload(H.bktFlags);
     rowStart.upload(H.rowStart); rowEnd.upload(H.rowEnd); rowMaxEnd.upload(H.rowMaxEnd); rowExon.upload(H.rowExon); rowFlags.upload(H.rowFlags);
     exChr.upload(H.exChr); exStart.upload(H.exStart); exEnd.upload(H.exEnd); exStrand.upload(H.exStrand);
-    v.dictHash = dictHash.p; v.dictVal = dictVal.p; v.strPool = strPool.p; v.refStrOff = refStrOff.p; v.refStrLen = refStrLen.p; v.refFlags = refFlags.p;
+    v.dict = dict.p; v.strPool = strPool.p; v.refStrOff = refStrOff.p; v.refStrLen = refStrLen.p; v.refFlags = refFlags.p;
     v.refVerOff = refVerOff.p; v.refVerBucket = refVerBucket.p; v.refActOff = refActOff.p; v.refAct = refAct.p;
     v.bktRowOff = bktRowOff.p; v.bktFlags = bktFlags.p; v.rowStart = rowStart.p; v.rowEnd = rowEnd.p; v.rowMaxEnd = rowMaxEnd.p; v.rowExon = rowExon.p; v.rowFlags = rowFlags.p;
     v.exChr = exChr.p; v.exStart = exStart.p; v.exEnd = exEnd.p; v.exStrand = exStrand.p;
     for (int m = 0; m < 3; m++) { featOff[m].upload(H.featOff[m]); feat[m].upload(H.feat[m]); v.featOff[m] = featOff[m].p; v.feat[m] = feat[m].p; }
-    bytes = H.dictHash.size() * 12 + H.strPool.size() + H.refStrOff.size() * 7 + H.refVerOff.size() * 4 + H.refVerBucket.size() * 4 + H.refActOff.size() * 4 + H.refAct.size() * 4 +
+    bytes = H.dict.size() * 16 + H.strPool.size() + H.refStrOff.size() * 7 + H.refVerOff.size() * 4 + H.refVerBucket.size() * 4 + H.refActOff.size() * 4 + H.refAct.size() * 4 +
             H.bktRowOff.size() * 5 + H.rowStart.size() * 17 + H.exChr.size() * 13;
     for (int m = 0; m < 3; m++) bytes += (H.featOff[m].size() + H.feat[m].size()) * 4;
     return v;

@@ -3,6 +3,7 @@
 // The per-item logic lives in the eqp_*.h headers; this file owns how it is mapped to the machine.
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_pipeline.h>
 #include <string>
 #include <vector>
 #include "eqp_pipeline.h"
@@ -69,6 +70,40 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(uint32_t* __restric
 #pragma unroll
   for (int k = 0; k < SCAN_ITEMS; k++) { if (b + k < n) p[b + k] = ex; ex += v[k]; }
   if (blockIdx.x == nTiles - 1 && threadIdx.x == 0) p[n] = tileOff[nTiles];
+}
+
+// ---------------------------------------------------------------- work ordering
+// Counting sort of the fragment slots by a small work key (descending, key 0 dropped), so that the lanes of a warp in the
+// thread-per-fragment kernels get fragments of equal cost and the expensive fragments start first.
+static const int ORD_BINS = 256, ORD_THREADS = 256, ORD_TILE = 4096;
+__global__ void __launch_bounds__(ORD_THREADS) k_order_hist(const uint32_t* __restrict__ key, uint64_t n, uint32_t* __restrict__ blockHist, uint32_t nBlocks) {
+  __shared__ uint32_t h[ORD_BINS];
+  h[threadIdx.x] = 0; __syncthreads();
+  uint64_t b = (uint64_t)blockIdx.x * ORD_TILE;
+  for (int k = 0; k < ORD_TILE / ORD_THREADS; k++) {
+    uint64_t i = b + (uint64_t)k * ORD_THREADS + threadIdx.x; bool ok = i < n; uint32_t v = ok ? key[i] : 0; if (v >= ORD_BINS) v = ORD_BINS - 1;
+    uint32_t act = __ballot_sync(0xffffffffu, ok);
+    if (ok) { uint32_t peers = __match_any_sync(act, v); if ((threadIdx.x & 31) == (uint32_t)(__ffs(peers) - 1)) atomicAdd(&h[v], __popc(peers)); }
+  }
+  __syncthreads();
+  blockHist[(uint64_t)(ORD_BINS - 1 - threadIdx.x) * nBlocks + blockIdx.x] = h[threadIdx.x];      // bin-major, large keys first
+}
+__global__ void __launch_bounds__(ORD_THREADS) k_order_scatter(const uint32_t* __restrict__ key, uint64_t n, const uint32_t* __restrict__ blockBase, uint32_t nBlocks,
+                                                               uint32_t* __restrict__ perm, uint32_t nKeep) {
+  __shared__ uint32_t cur[ORD_BINS];
+  cur[threadIdx.x] = blockBase[(uint64_t)(ORD_BINS - 1 - threadIdx.x) * nBlocks + blockIdx.x]; __syncthreads();
+  uint64_t b = (uint64_t)blockIdx.x * ORD_TILE;
+  for (int k = 0; k < ORD_TILE / ORD_THREADS; k++) {
+    uint64_t i = b + (uint64_t)k * ORD_THREADS + threadIdx.x; bool ok = i < n; uint32_t v = ok ? key[i] : 0; if (v >= ORD_BINS) v = ORD_BINS - 1;
+    uint32_t act = __ballot_sync(0xffffffffu, ok);
+    if (ok) {
+      uint32_t peers = __match_any_sync(act, v); uint32_t lane = threadIdx.x & 31, leader = __ffs(peers) - 1, base = 0;
+      if (lane == leader) base = atomicAdd(&cur[v], __popc(peers));
+      base = __shfl_sync(peers, base, leader);
+      uint32_t pos = base + __popc(peers & ((1u << lane) - 1));
+      if (pos < nKeep) perm[pos] = (uint32_t)i;                          // key-0 slots sort last and fall off the end
+    }
+  }
 }
 
 // ---------------------------------------------------------------- line index
@@ -147,10 +182,12 @@ __global__ void __launch_bounds__(DEC_LINES) k_decode_sam(AnnoView A, SamView S,
   if (nBytes + mis <= (uint64_t)DEC_SMEM) {
     const char* ga = g0 - mis; uint64_t tot = nBytes + mis; uint64_t nVec = tot / 16;
     const uint4* gv = reinterpret_cast<const uint4*>(ga); uint4* sv = reinterpret_cast<uint4*>(stage);
-    for (uint64_t i = threadIdx.x; i < nVec; i += DEC_LINES) sv[i] = __ldg(gv + i);
+    for (uint64_t i = threadIdx.x; i < nVec; i += DEC_LINES) __pipeline_memcpy_async(sv + i, gv + i, 16);   // LDGSTS: the whole tile in flight at once
+    __pipeline_commit();
     for (uint64_t i = nVec * 16 + threadIdx.x; i < tot; i += DEC_LINES) stage[i] = ga[i];
+    __pipeline_wait_prior(0);
     __syncthreads();
-    if (li < l1) { SamView T = S; T.text = stage + mis - b; decode_line(A, T, li, err); }
+    if (li < l1) { uint64_t lb = S.lineOff[li], le = S.lineOff[li + 1] - 1; decode_record(A, S, li, stage + mis + (lb - b), (int)(le - lb), err); }
   } else if (li < l1) {
     decode_line(A, S, li, err);
   }
@@ -196,6 +233,18 @@ struct CudaBackend {
     scan(sums, nTiles);
     k_scan_apply<<<(unsigned)nTiles, SCAN_THREADS, 0, stream>>>(p, n, sums, nTiles); launches++;
     EQP_CUDA(cudaGetLastError());
+  }
+  // perm[0..returned) = slots with key > 0, ordered by descending key bin
+  uint32_t order_by_work(const uint32_t* key, uint64_t n, uint32_t* perm) {
+    if (!n) return 0;
+    uint32_t nBlocks = (uint32_t)((n + ORD_TILE - 1) / ORD_TILE); uint64_t m = (uint64_t)ORD_BINS * nBlocks;
+    uint32_t* hist = alloc<uint32_t>(m + 1);
+    k_order_hist<<<nBlocks, ORD_THREADS, 0, stream>>>(key, n, hist, nBlocks); launches++;
+    scan(hist, m);
+    uint32_t nKeep = 0; to_host(&nKeep, hist + (uint64_t)(ORD_BINS - 1) * nBlocks, 4);       // start of the key-0 bin = number of slots kept
+    k_order_scatter<<<nBlocks, ORD_THREADS, 0, stream>>>(key, n, hist, nBlocks, perm, nKeep); launches++;
+    EQP_CUDA(cudaGetLastError());
+    return nKeep;
   }
   // line index: counts per LINE_TILE tile, then offsets (Pipeline::index_lines calls these instead of the generic lambdas)
   void count_newlines(const char* text, uint64_t len, uint64_t nTiles, uint32_t* cnt) {

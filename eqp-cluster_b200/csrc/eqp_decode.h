@@ -16,17 +16,14 @@ EQP_HD void raise(uint32_t* err, uint32_t code, uint32_t detail) {
 
 EQP_HD int32_t lookup_ref(const AnnoView& A, const char* p, int n) {
   if (n == 1 && p[0] == '*') return -1;
-  uint64_t h = fnv1a(p, n); uint32_t s = (uint32_t)h & A.dictMask;
-  while (true) {
-    uint64_t k = A.dictHash[s];
-    if (!k) break;
-    if (k == h) {
-      int32_t r = A.dictVal[s];
-      if (A.refStrLen[r] == n) {
-        const char* q = A.strPool + A.refStrOff[r]; bool eq = true;
-        for (int i = 0; i < n; i++) if (q[i] != p[i]) { eq = false; break; }
-        if (eq) return r;
-      }
+  uint64_t h = fnv1a(p, n), key = dict_key(h, n); uint32_t s = (uint32_t)h & A.dictMask;
+  if (n < 0x10000) while (true) {
+    DictEntry e = A.dict[s];                                            // one 16-byte load: key (hash | length), id, string offset
+    if (!e.key) break;
+    if (e.key == key) {
+      const char* q = A.strPool + e.off; int diff = 0;
+      for (int i = 0; i < n; i++) diff |= q[i] ^ p[i];                   // no early exit: the loads are independent and overlap
+      if (!diff) return e.val;
     }
     s = (s + 1) & A.dictMask;
   }
@@ -51,31 +48,71 @@ EQP_HD int flag_read_index(int flag, int suffix, int readIndex) {     // SamReco
   return 1;
 }
 
-EQP_HD void decode_line(const AnnoView& A, const SamView& S, uint32_t li, uint32_t* err) {
-  uint64_t b = S.lineOff[li], e = S.lineOff[li + 1] - 1;              // [b,e): line without '\n'
-  const char* t = S.text;
-  if (e > b && t[e - 1] == '\r') e--;
+// first '\t' in p[from, n), or n.  Word-wise: aligned 4-byte loads, exact zero-byte test on (word ^ 0x09090909).
+// Reads only aligned words that contain at least one byte of [from, n), so it never touches another page.
+EQP_HD int find_tab(const char* p, int from, int n) {
+  if (from >= n) return n;
+  const char* q = p + from; int mis = (int)((uintptr_t)q & 3);
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(q - mis);
+  int idx = from - mis;                                                 // index (relative to p) of byte 0 of *w
+  uint32_t x = *w ^ 0x09090909u;
+  x |= (mis ? (0xFFFFFFFFu >> (32 - 8 * mis)) : 0u);                     // bytes before `from` cannot match
+  while (true) {
+    uint32_t z = (x - 0x01010101u) & ~x & 0x80808080u;                   // lowest set marker is exact
+    if (z) {
+#if defined(__CUDA_ARCH__)
+      int k = idx + ((__ffs((int)z) - 1) >> 3);
+#else
+      int k = idx + (__builtin_ctz(z) >> 3);
+#endif
+      return k < n ? k : n;
+    }
+    idx += 4; if (idx >= n) return n;
+    x = *++w ^ 0x09090909u;
+  }
+}
+
+// One SAM line [p, p+n) (no '\n').  The text may live in shared or global memory.
+EQP_HD void decode_record(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, uint32_t* err) {
+  if (n > 0 && p[n - 1] == '\r') n--;
   S.frag[li] = 0xFFFFFFFFu; S.rf[li] = 0;
-  if (e <= b || t[b] == '@') return;                                  // SamReader.java:173
-  const char* p = t + b; int n = (int)(e - b);
-  int tab[11]; int nt = 0; int fields = 0;
-  // field count with the reference's rule: from field 11 on, tokens containing ':' do not advance (SamRecord.java:223-232)
-  { int pos = 0;
-    while (pos < n) {
-      int q = pos; bool colon = false;
-      while (q < n && p[q] != '\t') { colon |= p[q] == ':'; q++; }
-      if (nt < 11 && q < n) tab[nt++] = q;
-      if (fields < 11 || !colon) fields++;
-      pos = q + 1;
-    } }
-  if (fields < 11) { raise(err, DERR_FIELDS, li); return; }
-  if (fields > 12) { raise(err, DERR_FIELDS, li); return; }
-  int f0 = 0, e0 = tab[0];
+  if (n <= 0 || p[0] == '@') return;                                    // SamReader.java:173
+  int tab[11]; int nt = 0;
+  { int pos = 0; while (nt < 11) { int q = find_tab(p, pos, n); if (q >= n) break; tab[nt++] = q; pos = q + 1; } }
+  // field count with the reference's rule: the 11 mandatory tokens count, later tokens only when they hold no ':' (SamRecord.java:223-232).
+  // The same pass over the tag block finds the first [nN]M:i:<digits> and rejects an HI:i: tag.
+  int nm = -1; int fields;
+  if (nt < 10) fields = nt + (((nt ? tab[nt - 1] + 1 : 0) < n) ? 1 : 0);
+  else if (nt == 10) fields = (tab[9] + 1 < n) ? 11 : 10;
+  else {
+    fields = 11; int k = tab[10] + 1; bool colon = false, any = k < n;
+    for (; k < n; k++) {
+      char c = p[k];
+      if (c == '\t') { if (!colon) fields++; colon = false; any = k + 1 < n; continue; }
+      if (c == ':') {
+        colon = true;
+        if (k + 2 < n && p[k + 1] == 'i' && p[k + 2] == ':' && p[k - 1] == 'M' && k - 2 > tab[10]) {
+          char c0 = p[k - 2];
+          if (nm < 0 && (c0 == 'N' || c0 == 'n')) {
+            int d = k + 3, v = 0; bool dig = false;
+            while (d < n && p[d] >= '0' && p[d] <= '9') { v = v * 10 + (p[d] - '0'); d++; dig = true; if (v > 30000) break; }
+            if (dig) nm = v;
+          }
+        }
+        if (k + 2 < n && p[k + 1] == 'i' && p[k + 2] == ':' && p[k - 1] == 'I' && k - 2 > tab[10] && p[k - 2] == 'H' && (k - 3 == tab[10] || p[k - 3] == '\t')) {
+          raise(err, DERR_FIELDS, li); return;                           // HI:i: changes isMate (SamRecord.java:658-660): not produced by bowtie2
+        }
+      }
+    }
+    if (any && !colon) fields++;                                         // last token (a trailing empty token is not one)
+  }
+  if (fields < 11 || fields > 12) { raise(err, DERR_FIELDS, li); return; }
+  int e0 = tab[0];
   // QNAME (SamRecord.java:155-176)
   int qe = e0; { for (int i = 1; i < e0; i++) if (p[i] == ' ') { qe = i; break; } }
   int suffix = 0;
   if (e0 >= 2 && p[e0 - 2] == '/' && (p[e0 - 1] == '1' || p[e0 - 1] == '2')) { suffix = p[e0 - 1] - '0'; if (qe == e0) qe = e0 - 2; }
-  if (qe - f0 != 10 || p[0] != 'F') { raise(err, DERR_QNAME, li); return; }
+  if (qe != 10 || p[0] != 'F') { raise(err, DERR_QNAME, li); return; }
   uint32_t frag = 0;
   for (int i = 1; i < 10; i++) { char c = p[i]; if (c < '0' || c > '9') { raise(err, DERR_QNAME, li); return; } frag = frag * 10 + (uint32_t)(c - '0'); }
   int32_t flag, pos, mapq, pnext;
@@ -97,23 +134,16 @@ EQP_HD void decode_line(const AnnoView& A, const SamView& S, uint32_t li, uint32
   int seqLen = tab[9] - tab[8] - 1;
   int qualEnd = nt >= 11 ? tab[10] : n, qualLen = qualEnd - tab[9] - 1;
   if (!(qualLen == 1 && p[tab[9] + 1] == '*') && qualLen != seqLen) { raise(err, DERR_SEQ_QUAL, li); return; }
-  int nm = -1;
-  if (nt >= 11) {                                                      // first match of [nN]M:i:[0-9]+ in the tag block
-    for (int k = tab[10] + 1; k + 5 < n + 1 && k + 5 <= n; k++) {
-      if ((p[k] == 'N' || p[k] == 'n') && p[k + 1] == 'M' && p[k + 2] == ':' && p[k + 3] == 'i' && p[k + 4] == ':') {
-        int d = k + 5, v = 0; bool any = false;
-        while (d < n && p[d] >= '0' && p[d] <= '9') { v = v * 10 + (p[d] - '0'); d++; any = true; if (v > 30000) break; }
-        if (any) { nm = v; break; }
-      }
-    }
-    for (int k = tab[10] + 1; k + 5 <= n; k++)                          // HI:i: changes isMate (SamRecord.java:658-660): not produced by bowtie2
-      if ((k == tab[10] + 1 || p[k - 1] == '\t') && p[k] == 'H' && p[k + 1] == 'I' && p[k + 2] == ':' && p[k + 3] == 'i' && p[k + 4] == ':') { raise(err, DERR_FIELDS, li); return; }
-  }
   bool mapped = pos >= 0 && (flag & 4) == 0;                            // :980-982
   bool hasMate = (flag & 1) && (flag & 2);                              // :964-966
   S.frag[li] = frag; S.flag[li] = (uint16_t)flag; S.ref[li] = ref; S.pos[li] = pos; S.rnext[li] = rnext; S.pnext[li] = pnext;
   S.nm[li] = (int16_t)nm; S.cigOff[li] = (uint16_t)cigOff; S.cigLen[li] = (uint16_t)cigLen; S.seqLen[li] = (uint16_t)seqLen;
   S.rf[li] = (uint8_t)(RF_REC | (mapped ? RF_MAPPED : 0) | (hasMate ? RF_HASMATE : 0) | (readIndex << 3) | (suffix << 5));
+}
+
+EQP_HD void decode_line(const AnnoView& A, const SamView& S, uint32_t li, uint32_t* err) {
+  uint64_t b = S.lineOff[li], e = S.lineOff[li + 1] - 1;              // [b,e): line without '\n'
+  decode_record(A, S, li, S.text + b, (int)(e - b), err);
 }
 
 }  // namespace eqpb

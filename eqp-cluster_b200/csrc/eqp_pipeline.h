@@ -169,6 +169,7 @@ struct Pipeline {
     be.scan(C.blkOff, N); be.scan(C.alnOff, N);
     be.to_host(&nBlocks, C.blkOff + N, 4); be.to_host(&nAln, C.alnOff + N, 4);
     C.blocks = be.template alloc<Block>((uint64_t)nBlocks + 1); C.hitCnt = be.template alloc<uint32_t>((uint64_t)nBlocks + 1);
+    C.alnBlk = be.template alloc<uint32_t>((uint64_t)nAln + 1); be.to_device(C.alnBlk + nAln, &nBlocks, 4);
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
     { const ChunkView C = this->C; be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, nb, na); }); }
     // ---- a11: interval join (count, scan, fill)
@@ -180,10 +181,16 @@ struct Pipeline {
     V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
     V.a20 = be.template alloc<uint32_t>((uint64_t)N + 1); V.nFinal = be.template alloc<uint32_t>((uint64_t)N + 1);
     for (int m = 0; m < 3; m++) { V.acc[m] = accOut[m] ? accOut[m] : be.template alloc<unsigned long long>((uint64_t)A.nFeat[m] + 1); be.memset(V.acc[m], 0, ((uint64_t)A.nFeat[m] + 1) * 8); }
+    be.memset(V.a20, 0, ((uint64_t)N + 1) * 4); be.memset(V.nFinal, 0, ((uint64_t)N + 1) * 4);
+    // fragments with hits, ordered by descending hit-count class (stable within a class): warps of the thread-per-fragment stages get
+    // fragments of similar cost while neighbouring lanes still touch neighbouring memory
+    uint32_t* work = be.template alloc<uint32_t>((uint64_t)N + 1); uint32_t* perm = be.template alloc<uint32_t>((uint64_t)N + 1);
+    { const ChunkView C = this->C; be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t h = C.hitCnt[C.blkOff[s + 1]] - C.hitCnt[C.blkOff[s]]; uint32_t c = 0; while (h) { c++; h >>= 1; } work[s] = c; }); }   // class = 1 + floor(log2(hits)): coarse, so neighbouring slots stay neighbours
+    uint32_t nWork = be.order_by_work(work, N, perm);
     { const ChunkView C = this->C; const CountView V = this->V;
-      be.launch(N, [=] EQP_LAMBDA(uint64_t s) { fragment_alignments(A, C, V, P, (uint32_t)s); });
-      be.launch(N, [=] EQP_LAMBDA(uint64_t s) { fragment_weight(A, C, V, P, (uint32_t)s); });
-      for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) be.launch(N, [=] EQP_LAMBDA(uint64_t s) { fragment_count(A, C, V, P, m, (uint32_t)s); }); }
+      be.launch(nAln, [=] EQP_LAMBDA(uint64_t a) { alignment_build(A, C, V, P, (uint32_t)a); });
+      be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
+      for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_count(A, C, V, P, m, perm[i]); }); }
     // ---- results
     be.to_host(R.err, scal, 8);
     if (R.err[0]) return -1;

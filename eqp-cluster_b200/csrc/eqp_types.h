@@ -37,9 +37,12 @@ enum {
   DERR_INT = 17            // integer field does not parse
 };
 
+// reference-name dictionary slot: key = (fnv1a(name) & ~0xFFFF) | length, 0 = empty.  One 16-byte load yields everything lookup_ref needs.
+struct alignas(16) DictEntry { uint64_t key; int32_t val; uint32_t off; };
+
 struct AnnoView {
   // reference-name dictionary (open addressing, power-of-two capacity)
-  const uint64_t* dictHash; const int32_t* dictVal; uint32_t dictMask;
+  const DictEntry* dict; uint32_t dictMask;
   const char* strPool; const uint32_t* refStrOff; const uint16_t* refStrLen;
   const uint8_t* refFlags;          // bit0 in genome.fa.fai, bit1 malformed junction-like id
   const uint32_t* refVerOff; const int32_t* refVerBucket;   // SAM name -> B buckets (a8 version expansion)
@@ -85,7 +88,7 @@ struct Block {                     // one aligned block of the combined BED (a10
   uint16_t L, I, D; uint8_t seg, maxSeg;           // -L -I -D -F<seg>-<maxSeg>
   uint32_t aln;                                    // alignment number within the fragment (A-counter - 1)
   uint8_t readIdx, paired, strand, pad;            // strand '+'/'-'
-  uint32_t hitOff;                                 // first hit of this block (filled by the join)
+  uint32_t slot;                                   // fragment slot the block belongs to
 };
 
 struct Hit { uint32_t block; int32_t row; int32_t overlap; };   // a11 output (12 bytes)
@@ -106,7 +109,8 @@ struct Aln {                       // one WeightObjectAlignment (a15-a19), 48 by
   uint64_t key;
   int32_t start1, start2;          // GenomicAlignment.start per half
   uint16_t nIv1, nIv2; int16_t maxField1, maxField2;
-  uint8_t flags; uint8_t pad[7];   // bit0 paired, bit1 has half 1, bit2 has half 2, bits3-4 SR read index
+  uint8_t flags; uint8_t pad[3];   // bit0 paired, bit1 has half 1, bit2 has half 2, bits3-4 SR read index, bit5 halves swapped relative to repr
+  uint32_t next;                   // next alignment of the fragment with the same key (duplicate chain, file order), UINT32_MAX = end
 };
 
 }  // namespace eqpb

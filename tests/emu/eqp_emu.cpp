@@ -28,6 +28,11 @@ struct HostBackend {
       if (e == len && last != '\n') lo[nLines] = len + 1;
     }
   }
+  uint32_t order_by_work(const uint32_t* key, uint64_t n, uint32_t* perm) {
+    uint32_t k = 0;
+    for (int b = 255; b >= 1; b--) for (uint64_t i = 0; i < n; i++) { uint32_t v = key[i] > 255 ? 255 : key[i]; if ((int)v == b) perm[k++] = (uint32_t)i; }
+    return k;
+  }
   void decode(const AnnoView& A, const SamView& S, uint32_t* err) { for (uint32_t i = 0; i < S.nLines; i++) decode_line(A, S, i, err); }
   ~HostBackend() { for (void* p : allocs) free(p); }
 };
