@@ -97,19 +97,29 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
   V.a20[slot] = 0; V.nFinal[slot] = 0;
   if (b0 == b1 || C.hitCnt[b0] == C.hitCnt[b1]) return;
   uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1];
-  int left = 0, right = 0;
+  int left = 0, right = 0; uint32_t nA = a1 - a0, cap = 2 * nA; uint32_t* tab = V.dedupTab + 2 * (uint64_t)a0;
   for (uint32_t a = a0; a < a1; a++) {
     Aln& al = V.alns[a]; if (al.hit0 == al.hit1) continue;
     al.repr = a;
-    for (uint32_t p = a0; p < a; p++) {
-      const Aln& q = V.alns[p]; if (q.hit0 == q.hit1 || q.repr != p) continue;
-      bool sw;
-      if (keys_equal(V, q, al, sw)) {                                      // duplicate: append to the representative's chain (file order)
-        al.repr = p; if (sw) al.flags |= 32;
-        uint32_t t = p; while (V.alns[t].next != 0xFFFFFFFFu) t = V.alns[t].next;
-        V.alns[t].next = a; break;
+    uint32_t found = 0xFFFFFFFFu; bool sw = false;
+    if (nA <= 4) {                                                         // tiny fragment: compare with the earlier representatives directly
+      for (uint32_t p = a0; p < a; p++) {
+        const Aln& q = V.alns[p]; if (q.hit0 == q.hit1 || q.repr != p) continue;
+        if (keys_equal(V, q, al, sw)) { found = p; break; }
+      }
+    } else {                                                               // per-fragment open-addressing table of representatives (2 slots per alignment, zeroed)
+      uint32_t s = (uint32_t)(((al.key * 0x9E3779B97F4A7C15ULL) >> 32) % cap);
+      while (true) {
+        uint32_t e = tab[s];
+        if (!e) { tab[s] = a - a0 + 1; break; }
+        if (keys_equal(V, V.alns[a0 + e - 1], al, sw)) { found = a0 + e - 1; break; }   // insertion order along the probe path = file order: first equal key wins
+        s = s + 1 == cap ? 0 : s + 1;
       }
     }
+    if (found != 0xFFFFFFFFu) {                                            // duplicate: append to the representative's chain (file order)
+      al.repr = found; if (sw) al.flags |= 32;
+      V.alns[V.alnTail[found]].next = a; V.alnTail[found] = a;
+    } else V.alnTail[a] = a;
     if (al.repr == a) { if ((al.flags & 6) == 4) right++; else left++; }   // ":r-" forms (WeightObject.java:859-865)
   }
   uint32_t a20 = (uint32_t)(left > right ? left : right);

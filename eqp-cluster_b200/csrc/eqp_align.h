@@ -16,6 +16,7 @@ struct RunParams {                 // eqp_params, device form
 
 struct CountView {
   HitX* hx; Aln* alns;             // hx parallel to hits; alns indexed by alnOff[slot] + alignment number
+  uint32_t* dedupTab; uint32_t* alnTail;   // a19 scratch: per-fragment representative table (2 per alignment, zeroed), chain tails
   uint32_t* a20;                   // per slot: number of genomic alignments (0 = fragment not in the intersection)
   uint32_t* nFinal;                // per slot: numAlignments of the final.wgt entry
   unsigned long long* acc[3];      // fixed-point accumulators per mode (nFeat entries)

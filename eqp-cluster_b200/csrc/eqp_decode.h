@@ -48,8 +48,17 @@ EQP_HD int flag_read_index(int flag, int suffix, int readIndex) {     // SamReco
   return 1;
 }
 
-// first '\t' in p[from, n), or n.  Word-wise: aligned 4-byte loads, exact zero-byte test on (word ^ 0x09090909).
-// Reads only aligned words that contain at least one byte of [from, n), so it never touches another page.
+struct alignas(16) Word4 { uint32_t x, y, z, w; };
+EQP_HD uint32_t tab_marker(uint32_t w) { uint32_t x = w ^ 0x09090909u; return (x - 0x01010101u) & ~x & 0x80808080u; }   // lowest set marker is exact
+EQP_HD int first_marker(uint32_t z) {
+#if defined(__CUDA_ARCH__)
+  return (__ffs((int)z) - 1) >> 3;
+#else
+  return __builtin_ctz(z) >> 3;
+#endif
+}
+// first '\t' in p[from, n), or n.  Aligned 4-byte loads up to the next 16-byte boundary, then aligned 16-byte loads.
+// Only aligned words / quads holding at least one byte of [from, n) are read, so no other page is ever touched.
 EQP_HD int find_tab(const char* p, int from, int n) {
   if (from >= n) return n;
   const char* q = p + from; int mis = (int)((uintptr_t)q & 3);
@@ -57,19 +66,46 @@ EQP_HD int find_tab(const char* p, int from, int n) {
   int idx = from - mis;                                                 // index (relative to p) of byte 0 of *w
   uint32_t x = *w ^ 0x09090909u;
   x |= (mis ? (0xFFFFFFFFu >> (32 - 8 * mis)) : 0u);                     // bytes before `from` cannot match
+  uint32_t z = (x - 0x01010101u) & ~x & 0x80808080u;
   while (true) {
-    uint32_t z = (x - 0x01010101u) & ~x & 0x80808080u;                   // lowest set marker is exact
-    if (z) {
-#if defined(__CUDA_ARCH__)
-      int k = idx + ((__ffs((int)z) - 1) >> 3);
-#else
-      int k = idx + (__builtin_ctz(z) >> 3);
-#endif
+    if (z) { int k = idx + first_marker(z); return k < n ? k : n; }
+    idx += 4; ++w; if (idx >= n) return n;
+    if (!((uintptr_t)w & 15)) break;
+    z = tab_marker(*w);
+  }
+  const Word4* v = reinterpret_cast<const Word4*>(w);
+  while (true) {
+    Word4 c = *v; uint32_t z0 = tab_marker(c.x), z1 = tab_marker(c.y), z2 = tab_marker(c.z), z3 = tab_marker(c.w);
+    if (z0 | z1 | z2 | z3) {
+      int k = idx + (z0 ? first_marker(z0) : z1 ? 4 + first_marker(z1) : z2 ? 8 + first_marker(z2) : 12 + first_marker(z3));
       return k < n ? k : n;
     }
-    idx += 4; if (idx >= n) return n;
-    x = *++w ^ 0x09090909u;
+    idx += 16; ++v; if (idx >= n) return n;
   }
+}
+
+// General tag-block scan (any token shape): field count with the reference's rule, first [nN]M:i:<digits>, HI:i: at a token start.
+// Returns false when an HI tag is present.  Only reached for lines whose tags are not all of the form XX:T:value.
+EQP_HD bool tags_general(const char* p, int t0, int n, int& fields, int& nm) {
+  fields = 11; nm = -1; int k = t0; bool colon = false, any = k < n;
+  for (; k < n; k++) {
+    char c = p[k];
+    if (c == '\t') { if (!colon) fields++; colon = false; any = k + 1 < n; continue; }
+    if (c == ':') {
+      colon = true;
+      if (k + 2 < n && p[k + 1] == 'i' && p[k + 2] == ':' && k - 2 >= t0) {
+        char c1 = p[k - 1], c0 = p[k - 2];
+        if (nm < 0 && c1 == 'M' && (c0 == 'N' || c0 == 'n')) {
+          int d = k + 3, v = 0; bool dig = false;
+          while (d < n && p[d] >= '0' && p[d] <= '9') { v = v * 10 + (p[d] - '0'); d++; dig = true; if (v > 30000) break; }
+          if (dig) nm = v;
+        }
+        if (c1 == 'I' && c0 == 'H' && (k - 2 == t0 || p[k - 3] == '\t')) return false;
+      }
+    }
+  }
+  if (any && !colon) fields++;                                           // last token (a trailing empty token is not one)
+  return true;
 }
 
 // One SAM line [p, p+n) (no '\n').  The text may live in shared or global memory.
@@ -85,26 +121,25 @@ EQP_HD void decode_record(const AnnoView& A, const SamView& S, uint32_t li, cons
   if (nt < 10) fields = nt + (((nt ? tab[nt - 1] + 1 : 0) < n) ? 1 : 0);
   else if (nt == 10) fields = (tab[9] + 1 < n) ? 11 : 10;
   else {
-    fields = 11; int k = tab[10] + 1; bool colon = false, any = k < n;
-    for (; k < n; k++) {
-      char c = p[k];
-      if (c == '\t') { if (!colon) fields++; colon = false; any = k + 1 < n; continue; }
-      if (c == ':') {
-        colon = true;
-        if (k + 2 < n && p[k + 1] == 'i' && p[k + 2] == ':' && p[k - 1] == 'M' && k - 2 > tab[10]) {
-          char c0 = p[k - 2];
-          if (nm < 0 && (c0 == 'N' || c0 == 'n')) {
-            int d = k + 3, v = 0; bool dig = false;
-            while (d < n && p[d] >= '0' && p[d] <= '9') { v = v * 10 + (p[d] - '0'); d++; dig = true; if (v > 30000) break; }
-            if (dig) nm = v;
-          }
-        }
-        if (k + 2 < n && p[k + 1] == 'i' && p[k + 2] == ':' && p[k - 1] == 'I' && k - 2 > tab[10] && p[k - 2] == 'H' && (k - 3 == tab[10] || p[k - 3] == '\t')) {
-          raise(err, DERR_FIELDS, li); return;                           // HI:i: changes isMate (SamRecord.java:658-660): not produced by bowtie2
-        }
+    // tag block, one token per iteration.  bowtie2 tags are XX:T:value with no ':' in the value: then the token counts as a tag
+    // (no field increment), the NM regex can only match at the token start and HI:i: is a plain prefix test.
+    fields = 11; bool odd = false, hi = false; int t = tab[10] + 1;
+    while (t < n) {
+      int te = find_tab(p, t, n), len = te - t;
+      bool shape = len >= 5 && p[t + 2] == ':' && p[t + 4] == ':' && p[t] != ':' && p[t + 1] != ':' && p[t + 3] != ':';
+      int extra = 0; for (int k = t + 5; k < te; k++) extra |= (p[k] == ':');
+      if (!shape || extra) { odd = true; break; }
+      bool isI = p[t + 3] == 'i';
+      if (isI && p[t + 1] == 'M' && (p[t] == 'N' || p[t] == 'n') && nm < 0) {
+        int d = t + 5, v = 0; bool dig = false;
+        while (d < te && p[d] >= '0' && p[d] <= '9') { v = v * 10 + (p[d] - '0'); d++; dig = true; if (v > 30000) break; }
+        if (dig) nm = v;
       }
+      hi |= isI && p[t] == 'H' && p[t + 1] == 'I';
+      t = te + 1;
     }
-    if (any && !colon) fields++;                                         // last token (a trailing empty token is not one)
+    if (odd) hi = !tags_general(p, tab[10] + 1, n, fields, nm);
+    if (hi) { raise(err, DERR_FIELDS, li); return; }                      // HI:i: changes isMate (SamRecord.java:658-660): not produced by bowtie2
   }
   if (fields < 11 || fields > 12) { raise(err, DERR_FIELDS, li); return; }
   int e0 = tab[0];

@@ -179,6 +179,7 @@ struct Pipeline {
     { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { join_block(A, C.blocks[b], C.hits + C.hitCnt[b], (uint32_t)b); }); }
     // ---- a12-a25
     V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
+    V.dedupTab = be.template alloc<uint32_t>(2 * (uint64_t)nAln + 2); be.memset(V.dedupTab, 0, (2 * (uint64_t)nAln + 2) * 4); V.alnTail = be.template alloc<uint32_t>((uint64_t)nAln + 1);
     V.a20 = be.template alloc<uint32_t>((uint64_t)N + 1); V.nFinal = be.template alloc<uint32_t>((uint64_t)N + 1);
     for (int m = 0; m < 3; m++) { V.acc[m] = accOut[m] ? accOut[m] : be.template alloc<unsigned long long>((uint64_t)A.nFeat[m] + 1); be.memset(V.acc[m], 0, ((uint64_t)A.nFeat[m] + 1) * 8); }
     be.memset(V.a20, 0, ((uint64_t)N + 1) * 4); be.memset(V.nFinal, 0, ((uint64_t)N + 1) * 4);
@@ -190,7 +191,9 @@ struct Pipeline {
     { const ChunkView C = this->C; const CountView V = this->V;
       be.launch(nAln, [=] EQP_LAMBDA(uint64_t a) { alignment_build(A, C, V, P, (uint32_t)a); });
       be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
-      for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_count(A, C, V, P, m, perm[i]); }); }
+      be.fork();
+      for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) { be.branch(m); be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_count(A, C, V, P, m, perm[i]); }); }
+      be.join(); }
     // ---- results
     be.to_host(R.err, scal, 8);
     if (R.err[0]) return -1;

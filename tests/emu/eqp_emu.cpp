@@ -28,6 +28,9 @@ struct HostBackend {
       if (e == len && last != '\n') lo[nLines] = len + 1;
     }
   }
+  void fork() {}
+  void branch(int) {}
+  void join() {}
   uint32_t order_by_work(const uint32_t* key, uint64_t n, uint32_t* perm) {
     uint32_t k = 0;
     for (int b = 255; b >= 1; b--) for (uint64_t i = 0; i < n; i++) { uint32_t v = key[i] > 255 ? 255 : key[i]; if ((int)v == b) perm[k++] = (uint32_t)i; }
@@ -39,7 +42,31 @@ struct HostBackend {
 
 static std::string slurp(const std::string& p) { return AnnoHost::slurp(p.c_str()); }
 
+// `eqp_emu decode <annodir> <sam>`: decode every line on its own and print the SoA fields (or the error code) — decoder unit tests
+static int decode_only(const char* annoDir, const char* samPath) {
+  std::string anno = annoDir, base = anno + "/ensembl_rna_hs";
+  AnnoHost H;
+  H.load((base + "_100_combined_exons.bed").c_str(), (base + "_transcript_exons.bed").c_str(), (base + "_exon_gene.map").c_str(),
+         (base + "_exon_exon.map").c_str(), (base + "_exon_junction.map").c_str(), (base + "_exon_junction_transcript.map").c_str(),
+         (base + "_100_junction_junction_coordinate.map").c_str(), (base + "_equivalent_junctions.map").c_str(), (anno + "/genome.fa.fai").c_str());
+  std::string T = slurp(samPath);
+  HostBackend be; RunParams P{}; Pipeline<HostBackend> pl(be, H.view(), P);
+  pl.index_lines(0, T.data(), T.size());
+  const SamView& S = pl.C.sam[0]; AnnoView A = H.view();
+  for (uint32_t i = 0; i < S.nLines; i++) {
+    uint32_t err[2] = {0, 0};
+    decode_line(A, S, i, err);
+    if (err[0]) { printf("%u\tERR\t%u\n", i, err[0]); continue; }
+    if (!(S.rf[i] & RF_REC)) { printf("%u\tSKIP\n", i); continue; }
+    std::string ref = S.ref[i] >= 0 ? std::string(A.strPool + A.refStrOff[S.ref[i]], A.refStrLen[S.ref[i]]) : (S.ref[i] == -1 ? "*" : "?");
+    printf("%u\tREC\t%u\t%u\t%s\t%d\t%d\t%d\t%.*s\t%u\t%u\n", i, S.frag[i], S.flag[i], ref.c_str(), S.pos[i], S.pnext[i], S.nm[i],
+           (int)S.cigLen[i], S.text + S.lineOff[i] + S.cigOff[i], S.seqLen[i], S.rf[i]);
+  }
+  return 0;
+}
+
 int main(int argc, char** argv) {
+  if (argc == 4 && !strcmp(argv[1], "decode")) { try { return decode_only(argv[2], argv[3]); } catch (const std::exception& e) { fprintf(stderr, "ERROR: %s\n", e.what()); return 1; } }
   if (argc < 5) { fprintf(stderr, "usage: eqp_emu <annodir> <chunkdir> <se|pe> <outdir>\n"); return 2; }
   std::string anno = argv[1], chunk = argv[2], sfx = !strcmp(argv[3], "pe") ? "pe" : "sr", outd = argv[4], base = anno + "/ensembl_rna_hs";
   try {
