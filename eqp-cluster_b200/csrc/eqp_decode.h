@@ -60,28 +60,38 @@ EQP_HD int first_marker(uint32_t z) {
 // first '\t' in p[from, n), or n.  Aligned 4-byte loads up to the next 16-byte boundary, then aligned 16-byte loads.
 // Only aligned words / quads holding at least one byte of [from, n) are read, so no other page is ever touched.
 EQP_HD int find_tab(const char* p, int from, int n) {
-  if (from >= n) return n;
-  const char* q = p + from; int mis = (int)((uintptr_t)q & 3);
-  const uint32_t* w = reinterpret_cast<const uint32_t*>(q - mis);
-  int idx = from - mis;                                                 // index (relative to p) of byte 0 of *w
-  uint32_t x = *w ^ 0x09090909u;
-  x |= (mis ? (0xFFFFFFFFu >> (32 - 8 * mis)) : 0u);                     // bytes before `from` cannot match
-  uint32_t z = (x - 0x01010101u) & ~x & 0x80808080u;
-  while (true) {
-    if (z) { int k = idx + first_marker(z); return k < n ? k : n; }
-    idx += 4; ++w; if (idx >= n) return n;
-    if (!((uintptr_t)w & 15)) break;
-    z = tab_marker(*w);
-  }
-  const Word4* v = reinterpret_cast<const Word4*>(w);
-  while (true) {
-    Word4 c = *v; uint32_t z0 = tab_marker(c.x), z1 = tab_marker(c.y), z2 = tab_marker(c.z), z3 = tab_marker(c.w);
-    if (z0 | z1 | z2 | z3) {
-      int k = idx + (z0 ? first_marker(z0) : z1 ? 4 + first_marker(z1) : z2 ? 8 + first_marker(z2) : 12 + first_marker(z3));
-      return k < n ? k : n;
+  // Single exit on purpose: with several `return`s inside the loops the compiler duplicated the caller's continuation per exit
+  // and the lanes of a warp never reconverged (ncu: 1.3 active threads per instruction).
+  int res = n;
+  if (from < n) {
+    const char* q = p + from; int mis = (int)((uintptr_t)q & 3);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(q - mis);
+    int idx = from - mis;                                               // index (relative to p) of byte 0 of *w
+    uint32_t x = *w ^ 0x09090909u;
+    x |= (mis ? (0xFFFFFFFFu >> (32 - 8 * mis)) : 0u);                   // bytes before `from` cannot match
+    uint32_t z = (x - 0x01010101u) & ~x & 0x80808080u;
+    while (!z) {                                                        // single words up to the next 16-byte boundary
+      idx += 4; ++w;
+      if (idx >= n || !((uintptr_t)w & 15)) break;
+      z = tab_marker(*w);
     }
-    idx += 16; ++v; if (idx >= n) return n;
+    if (!z && idx < n) {                                                // 16 bytes per step
+      const Word4* v = reinterpret_cast<const Word4*>(w);
+      uint32_t z0, z1, z2, z3;
+      while (true) {
+        Word4 c = *v; z0 = tab_marker(c.x); z1 = tab_marker(c.y); z2 = tab_marker(c.z); z3 = tab_marker(c.w);
+        if ((z0 | z1 | z2 | z3) || idx + 16 >= n) break;
+        idx += 16; ++v;
+      }
+      int add = 0; z = z0;
+      if (!z) { z = z1; add = 4; }
+      if (!z) { z = z2; add = 8; }
+      if (!z) { z = z3; add = 12; }
+      idx += add;
+    }
+    if (z) { int k = idx + first_marker(z); res = k < n ? k : n; }
   }
+  return res;
 }
 
 // General tag-block scan (any token shape): field count with the reference's rule, first [nN]M:i:<digits>, HI:i: at a token start.
@@ -124,6 +134,9 @@ EQP_HD void decode_record(const AnnoView& A, const SamView& S, uint32_t li, cons
     // tag block, one token per iteration.  bowtie2 tags are XX:T:value with no ':' in the value: then the token counts as a tag
     // (no field increment), the NM regex can only match at the token start and HI:i: is a plain prefix test.
     fields = 11; bool odd = false, hi = false; int t = tab[10] + 1;
+#if defined(EQP_TAGS_BYTEWISE)
+    odd = true; t = n;
+#endif
     while (t < n) {
       int te = find_tab(p, t, n), len = te - t;
       bool shape = len >= 5 && p[t + 2] == ':' && p[t + 4] == ':' && p[t] != ':' && p[t + 1] != ':' && p[t + 3] != ':';
