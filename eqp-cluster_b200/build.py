@@ -50,7 +50,7 @@ def build_library(force=False):
     srcs = _glob(CSRC, (".cu", ".cuh", ".h", ".hpp")) + [os.path.join(ROOT, "include", "eqp_count.h")]
     if force or _newer(srcs, LIB_PATH):
         os.makedirs(LIB_DIR, exist_ok=True)
-        _run([nvcc_path()] + NVCC_FLAGS + ["-o", LIB_PATH, os.path.join(CSRC, "eqp_capi.cu")])
+        _run([nvcc_path()] + NVCC_FLAGS + ["-o", LIB_PATH, os.path.join(CSRC, "eqp_capi.cu"), "-lz"])
     return LIB_PATH
 
 
@@ -61,7 +61,7 @@ def build_cli(force=False):
     srcs = _glob(os.path.join(PKG_DIR, "host"), (".cpp", ".hpp")) + [os.path.join(ROOT, "include", "eqp_count.h")]
     if force or _newer(srcs, CLI_PATH):
         os.makedirs(LIB_DIR, exist_ok=True)
-        _run(["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "include"), "-o", CLI_PATH, src, "-ldl", "-lpthread"])
+        _run(["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "include"), "-o", CLI_PATH, src, "-ldl", "-lz"])
     return CLI_PATH
 
 
@@ -80,7 +80,7 @@ def build_tools(force=False):
         _run(["g++", "-std=c++17", "-O2", "-o", WORLDGEN_BIN, os.path.join(d, "worldgen.cpp")])
     emu_src = os.path.join(ROOT, "tests", "emu", "eqp_emu.cpp")
     if force or _newer(_glob(CSRC, (".h", ".hpp")) + [emu_src], EMU_BIN):
-        _run(["g++", "-std=c++17", "-O2", "-o", EMU_BIN, emu_src])
+        _run(["g++", "-std=c++17", "-O2", "-o", EMU_BIN, emu_src, "-lz"])
     return WORLDGEN_BIN, EMU_BIN
 
 

@@ -4,6 +4,7 @@
 // (J/bed-source/Exon.java:70-152), Exon(String,String) (:230-301), ComputeReadWeightsSam.readChromosomeNames (:44-58),
 // filter-junction-map-files.sh:254-304 + createExtendedJunctionIds.py:93-114 + filterFile.py:131-194.
 #pragma once
+#include <zlib.h>
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
@@ -41,11 +42,14 @@ struct AnnoHost {
 
   static std::string slurp(const char* path) {
     if (!path) throw AnnoError(-1, "annotation path is null");
-    FILE* f = fopen(path, "rb");
+    gzFile f = gzopen(path, "rb");                    // plain or gzip (UtilLib.getBufferedReader: ".gz" => GZIPInputStream, UtilLib.java:322-383)
     if (!f) throw AnnoError(-3, std::string("Warning: file ") + path + " not found.");
-    std::string s; char buf[1 << 16]; size_t n;
-    while ((n = fread(buf, 1, sizeof buf, f)) > 0) s.append(buf, n);
-    fclose(f); return s;
+    gzbuffer(f, 1 << 20);
+    std::string s; std::vector<char> buf(1 << 22); int n;
+    while ((n = gzread(f, buf.data(), (unsigned)buf.size())) > 0) s.append(buf.data(), (size_t)n);
+    bool bad = n < 0; gzclose(f);
+    if (bad) throw AnnoError(-3, std::string("Problem reading ") + path);
+    return s;
   }
   template <class F> static void lines(const std::string& s, F&& fn) {
     size_t p = 0;
