@@ -91,7 +91,7 @@ struct eqp_ctx {
   ChunkResult R{}; bool haveChunk = false;
   unsigned long long* vec = nullptr; int64_t vecLen = 0;           // gene|exon|junction fixed-point vector of the last chunk
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  std::string err;
+  std::string err, debugText;
 };
 
 static thread_local std::string g_err;                              // errors raised before a ctx exists
@@ -180,6 +180,7 @@ int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, siz
     }
     EQP_CUDA(cudaEventRecord(ctx->ev1, ctx->stream)); EQP_CUDA(cudaEventSynchronize(ctx->ev1));
     float ms = 0; EQP_CUDA(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    ctx->be->finish_timing(); ctx->be->report_stages();
     if (rc) {
       char buf[512]; snprintf(buf, sizeof buf, "%s [code %u, detail %u]", derr_text(ctx->R.err[0]), ctx->R.err[0], ctx->R.err[1]);
       return fail(ctx, derr_class(ctx->R.err[0]), buf);
@@ -240,6 +241,39 @@ int eqp_debug_fetch(eqp_ctx* ctx, const char* what, void* dst, size_t dstBytes, 
   if (dstBytes < bytes) return fail(ctx, EQP_ERR_ARG, "eqp_debug_fetch: buffer too small");
   try { EQP_CUDA(cudaSetDevice(ctx->device)); if (bytes) ctx->be->to_host(dst, src, bytes); return EQP_OK; }
   catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+
+int eqp_debug_decode(eqp_ctx* ctx, const uint8_t* sam, size_t len, int misalign, const char** text, size_t* textLen, uint32_t* errCode, uint32_t* errDetail) {
+  if (!ctx || !text || !textLen || !errCode || !errDetail || (len && !sam) || misalign < 0 || misalign > 15) return fail(ctx, EQP_ERR_ARG, "eqp_debug_decode: bad argument");
+  if (!ctx->annoLoaded) return fail(ctx, EQP_ERR_ARG, "eqp_debug_decode: call eqp_load_annotation first");
+  try {
+    EQP_CUDA(cudaSetDevice(ctx->device));
+    CudaBackend be(ctx->stream, ctx->nSm);
+    char* d = be.alloc<char>(len + 64); d += (16 - ((uintptr_t)d & 15)) % 16 + misalign;
+    if (len) EQP_CUDA(cudaMemcpyAsync(d, sam, len, cudaMemcpyHostToDevice, ctx->stream));
+    uint32_t* err = be.alloc<uint32_t>(2); be.memset(err, 0, 8);
+    SamView S{}; uint8_t* proc = nullptr;
+    be.decode_fused(ctx->A, S, proc, d, len, err);
+    uint32_t h[2]; be.to_host(h, err, 8); *errCode = h[0]; *errDetail = h[1];
+    size_t n = S.nLines;
+    std::vector<uint64_t> lo(n + 1); std::vector<uint32_t> frag(n); std::vector<int32_t> ref(n), pos(n), pnext(n); std::vector<uint16_t> flag(n), co(n), cl(n), sl(n); std::vector<int16_t> nm(n); std::vector<uint8_t> rf(n);
+    be.to_host(lo.data(), S.lineOff, (n + 1) * 8);
+    if (n) { be.to_host(frag.data(), S.frag, n * 4); be.to_host(ref.data(), S.ref, n * 4); be.to_host(pos.data(), S.pos, n * 4); be.to_host(pnext.data(), S.pnext, n * 4);
+      be.to_host(flag.data(), S.flag, n * 2); be.to_host(co.data(), S.cigOff, n * 2); be.to_host(cl.data(), S.cigLen, n * 2); be.to_host(sl.data(), S.seqLen, n * 2);
+      be.to_host(nm.data(), S.nm, n * 2); be.to_host(rf.data(), S.rf, n); }
+    std::string& out = ctx->debugText; out.clear(); char buf[256];
+    for (size_t i = 0; i < n; i++) {
+      uint64_t b = lo[i], e = lo[i + 1] - 1;
+      if (b > len || e > len || e < b) { snprintf(buf, sizeof buf, "%zu\tBADOFF\t%llu\t%llu\n", i, (unsigned long long)b, (unsigned long long)e); out += buf; continue; }
+      if (h[0]) { snprintf(buf, sizeof buf, "%zu\tLINE\t%llu\n", i, (unsigned long long)b); out += buf; continue; }    // records are undefined after an error: offsets only
+      if (!(rf[i] & RF_REC)) { snprintf(buf, sizeof buf, "%zu\tSKIP\n", i); out += buf; continue; }
+      std::string r = ref[i] >= 0 ? ctx->H.strPool.substr(ctx->H.refStrOff[(size_t)ref[i]], ctx->H.refStrLen[(size_t)ref[i]]) : (ref[i] == -1 ? "*" : "?");
+      snprintf(buf, sizeof buf, "%zu\tREC\t%u\t%u\t%s\t%d\t%d\t%d\t", i, frag[i], flag[i], r.c_str(), pos[i], pnext[i], nm[i]); out += buf;
+      out.append((const char*)sam + b + co[i], cl[i]);
+      snprintf(buf, sizeof buf, "\t%u\t%u\n", sl[i], rf[i]); out += buf;
+    }
+    *text = out.c_str(); *textLen = out.size(); return EQP_OK;
+  } catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
 }
 
 const char* eqp_last_error(eqp_ctx* ctx) { return ctx ? ctx->err.c_str() : g_err.c_str(); }

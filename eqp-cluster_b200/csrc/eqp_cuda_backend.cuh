@@ -4,9 +4,12 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_pipeline.h>
+#include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <vector>
 #include "eqp_pipeline.h"
+#include "eqp_tokenize.cuh"
 
 namespace eqpb {
 
@@ -164,35 +167,6 @@ __global__ void __launch_bounds__(LI_WARPS * 32) k_fill_line_offsets(const char*
   }
 }
 
-// ---------------------------------------------------------------- SAM decode (the dominant kernel)
-// A CTA owns DEC_LINES consecutive lines.  Their bytes are one contiguous range of the text, which the CTA stages
-// in shared memory with coalesced 16-byte loads; each thread then tokenises its own line out of shared memory
-// (decode_line, eqp_decode.h).  Ranges larger than the staging buffer (pathological line lengths) are parsed from
-// global memory directly.
-static const int DEC_LINES = 128;
-static const int DEC_SMEM = 55 * 1024;
-__global__ void __launch_bounds__(DEC_LINES) k_decode_sam(AnnoView A, SamView S, uint32_t* err) {
-  extern __shared__ __align__(16) char stage[];
-  uint32_t l0 = blockIdx.x * DEC_LINES, l1 = l0 + DEC_LINES < S.nLines ? l0 + DEC_LINES : S.nLines;
-  uint64_t b = S.lineOff[l0], e = S.lineOff[l1] - 1;                    // bytes [b, e) incl. the final '\n' (or len)
-  if (e > S.len) e = S.len;
-  const char* g0 = S.text + b; uint64_t nBytes = e > b ? e - b : 0;
-  uint32_t mis = (uint32_t)((uintptr_t)g0 & 15);                        // stage from the 16-byte boundary below g0
-  uint32_t li = l0 + threadIdx.x;
-  if (nBytes + mis <= (uint64_t)DEC_SMEM) {
-    const char* ga = g0 - mis; uint64_t tot = nBytes + mis; uint64_t nVec = tot / 16;
-    const uint4* gv = reinterpret_cast<const uint4*>(ga); uint4* sv = reinterpret_cast<uint4*>(stage);
-    for (uint64_t i = threadIdx.x; i < nVec; i += DEC_LINES) __pipeline_memcpy_async(sv + i, gv + i, 16);   // LDGSTS: the whole tile in flight at once
-    __pipeline_commit();
-    for (uint64_t i = nVec * 16 + threadIdx.x; i < tot; i += DEC_LINES) stage[i] = ga[i];
-    __pipeline_wait_prior(0);
-    __syncthreads();
-    if (li < l1) { uint64_t lb = S.lineOff[li], le = S.lineOff[li + 1] - 1; decode_record(A, S, li, stage + mis + (lb - b), (int)(le - lb), err); }
-  } else if (li < l1) {
-    decode_line(A, S, li, err);
-  }
-}
-
 // ---------------------------------------------------------------- backend
 struct CudaBackend {
   cudaStream_t stream; int nSm;
@@ -206,7 +180,7 @@ struct CudaBackend {
     EQP_CUDA(cudaEventCreate(&evDec0)); EQP_CUDA(cudaEventCreate(&evDec1));
   }
   ~CudaBackend() {
-    release(); if (evDec0) cudaEventDestroy(evDec0); if (evDec1) cudaEventDestroy(evDec1); if (evFork) cudaEventDestroy(evFork);
+    finish_timing(); release(); if (evDec0) cudaEventDestroy(evDec0); if (evDec1) cudaEventDestroy(evDec1); if (evFork) cudaEventDestroy(evFork);
     for (int i = 0; i < 3; i++) { if (evJoin[i]) cudaEventDestroy(evJoin[i]); if (side[i]) cudaStreamDestroy(side[i]); }
   }
   // Independent stages (the three counting runs) go to side streams so that their low-occupancy tails overlap.
@@ -215,6 +189,20 @@ struct CudaBackend {
   void join() {
     for (int i = 0; i < 3; i++) { EQP_CUDA(cudaEventRecord(evJoin[i], side[i])); EQP_CUDA(cudaStreamWaitEvent(mainStream, evJoin[i], 0)); }
     stream = mainStream;
+  }
+  // EQP_STAGE_TIMING=1: CUDA-event time between consecutive stage() marks on the main stream, printed to stderr per chunk
+  bool timing = getenv("EQP_STAGE_TIMING") != nullptr; std::vector<std::pair<const char*, cudaEvent_t>> marks;
+  void stage(const char* name) {
+    if (!timing) return;
+    cudaEvent_t e; EQP_CUDA(cudaEventCreate(&e)); EQP_CUDA(cudaEventRecord(e, mainStream)); marks.push_back({name, e});
+  }
+  void report_stages() {
+    if (!timing || marks.empty()) return;
+    EQP_CUDA(cudaEventSynchronize(marks.back().second)); float tot = 0;
+    for (size_t i = 1; i < marks.size(); i++) { float ms = 0; cudaEventElapsedTime(&ms, marks[i - 1].second, marks[i].second); tot += ms; fprintf(stderr, "[eqp stage] %-20s %9.3f ms\n", marks[i].first, ms); }
+    fprintf(stderr, "[eqp stage] %-20s %9.3f ms (decode kernels %.3f ms)\n", "total", tot, decodeMs);
+    for (auto& m : marks) cudaEventDestroy(m.second);
+    marks.clear();
   }
   void release() { for (void* p : allocs) cudaFreeAsync(p, stream); allocs.clear(); bytesAllocated = 0; }
 
@@ -270,16 +258,48 @@ struct CudaBackend {
     k_fill_line_offsets<<<(unsigned)((nTiles + LI_WARPS - 1) / LI_WARPS), LI_WARPS * 32, 0, stream>>>(text, len, nTiles, cnt, lineOff, nLines, last == '\n'); launches++;
     EQP_CUDA(cudaGetLastError());
   }
-  void decode(const AnnoView& A, const SamView& S, uint32_t* err) {
-    if (!S.nLines) return;
-    static bool attr = false;
-    if (!attr) { EQP_CUDA(cudaFuncSetAttribute(k_decode_sam, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_SMEM)); attr = true; }
-    EQP_CUDA(cudaEventRecord(evDec0, stream));
-    k_decode_sam<<<(S.nLines + DEC_LINES - 1) / DEC_LINES, DEC_LINES, DEC_SMEM, stream>>>(A, S, err); launches++;
-    EQP_CUDA(cudaGetLastError());
-    EQP_CUDA(cudaEventRecord(evDec1, stream)); EQP_CUDA(cudaEventSynchronize(evDec1));
-    float ms = 0; EQP_CUDA(cudaEventElapsedTime(&ms, evDec0, evDec1)); decodeMs += ms;
+  // a1/a2 in one pass (eqp_tokenize.cuh): allocates the line index + record SoA of `S`, launches the tokenizer, returns with S.nLines set.
+  // The number of lines is only known afterwards, so the tables are sized for len/160 lines and the pass is repeated when that was too small.
+  static const bool kFusedDecode = true;
+  void alloc_records(SamView& S, uint8_t*& proc, uint64_t cap) {
+    S.lineOff = alloc<uint64_t>(cap + 1);
+    S.frag = alloc<uint32_t>(cap); S.ref = alloc<int32_t>(cap); S.pos = alloc<int32_t>(cap); S.rnext = alloc<int32_t>(cap); S.pnext = alloc<int32_t>(cap);
+    S.flag = alloc<uint16_t>(cap); S.nm = alloc<int16_t>(cap); S.cigOff = alloc<uint16_t>(cap); S.cigLen = alloc<uint16_t>(cap); S.seqLen = alloc<uint16_t>(cap);
+    S.rf = alloc<uint8_t>(cap); proc = alloc<uint8_t>(cap);
   }
+  void decode_fused(const AnnoView& A, SamView& S, uint8_t*& proc, const char* text, uint64_t len, uint32_t* err) {
+    S.text = text; S.len = len; S.nLines = 0;
+    if (!len) { alloc_records(S, proc, 1); return; }
+    static bool attr = false;
+    if (!attr) { EQP_CUDA(cudaFuncSetAttribute(k_tokenize_sam, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TokShared))); attr = true; }
+    uint64_t vEnd = len + ((uintptr_t)text & 15); uint64_t nTiles = vEnd / TK_OWNED + 1;
+    if (nTiles > 0xFFFFFFF0ull) throw CudaError("SAM input too large for the tile counter");
+    unsigned long long* status = alloc<unsigned long long>(nTiles + 2);      // [nTiles] = newline total, [nTiles + 1] = tile ticket
+    uint64_t cap = len / 160 + 1024;
+    for (int attempt = 0; attempt < 2; attempt++) {
+      if (cap > 0xFFFFFFF0ull) throw CudaError("more than 2^32 SAM lines in one input");
+      alloc_records(S, proc, cap);
+      memset(status, 0, (nTiles + 2) * 8);
+      cudaEvent_t e0, e1; EQP_CUDA(cudaEventCreate(&e0)); EQP_CUDA(cudaEventCreate(&e1)); decEv.push_back({e0, e1});
+      EQP_CUDA(cudaEventRecord(e0, stream));
+      k_tokenize_sam<<<(unsigned)nTiles, TK_THREADS, sizeof(TokShared), stream>>>(A, S, (uint32_t)cap, (uint32_t)nTiles, status, (uint32_t*)(status + nTiles + 1), status + nTiles, err); launches++;
+      EQP_CUDA(cudaGetLastError());
+      EQP_CUDA(cudaEventRecord(e1, stream));
+      unsigned long long tot = 0; to_host(&tot, status + nTiles, 8);
+      char last = 0; to_host(&last, text + len - 1, 1);
+      uint64_t nl = tot - 1, lines = last == '\n' ? nl : nl + 1;             // tot counts the virtual newline in front of text[0]
+      S.nLines = (uint32_t)lines;
+      if (lines <= cap) return;
+      cap = lines;                                                          // tables were too small (average line under 160 bytes): once more, exact
+    }
+    throw CudaError("line count changed between two passes over the same text");
+  }
+  void decode(const AnnoView&, const SamView&, uint32_t*) {}
+  void finish_timing() {
+    for (auto& p : decEv) { float ms = 0; if (cudaEventElapsedTime(&ms, p.first, p.second) == cudaSuccess) decodeMs += ms; cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+    decEv.clear();
+  }
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> decEv;
 };
 
 }  // namespace eqpb

@@ -118,13 +118,40 @@ EQP_HD bool tags_general(const char* p, int t0, int n, int& fields, int& nm) {
   return true;
 }
 
+// number of ':' in p[a, b): aligned 4-byte words, exact SWAR byte compare.  Only words holding at least one byte of [a, b) are read.
+EQP_HD int colon_count(const char* p, int a, int b) {
+  if (a >= b) return 0;
+  uintptr_t s = (uintptr_t)(p + a), e = (uintptr_t)(p + b), wa = s & ~(uintptr_t)3; int cnt = 0;
+  for (; wa < e; wa += 4) {
+    uint32_t x = *reinterpret_cast<const uint32_t*>(wa) ^ 0x3a3a3a3au;
+    uint32_t z = ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu);   // 0x80 in every byte equal to ':'
+    if (wa < s) z &= 0xFFFFFFFFu << (8 * (int)(s - wa));
+    if (wa + 4 > e) z &= 0xFFFFFFFFu >> (8 * (int)(wa + 4 - e));
+#if defined(__CUDA_ARCH__)
+    cnt += __popc(z);
+#else
+    cnt += __builtin_popcount(z);
+#endif
+  }
+  return cnt;
+}
+
+// Tab sources for decode_record_t: next(p, from, n) = first '\t' in p[from, n), or n.  Calls come with increasing `from`.
+struct ScanTabs { EQP_HD int next(const char* p, int from, int n) { return find_tab(p, from, n); } };
+// Tabs already located by the tokenizer kernel: ev[cur, end) are this line's tab events, (position in the staged tile << 1); s = line start.
+struct EventTabs {
+  const uint16_t* ev; int cur, end, s;
+  EQP_HD int next(const char*, int, int n) { if (cur < end) { int q = (int)(ev[cur] >> 1) - s; cur++; return q < n ? q : n; } return n; }
+};
+
 // One SAM line [p, p+n) (no '\n').  The text may live in shared or global memory.
-EQP_HD void decode_record(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, uint32_t* err) {
+template <class Tabs>
+EQP_HD void decode_record_t(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, Tabs& tabs, uint32_t* err) {
   if (n > 0 && p[n - 1] == '\r') n--;
   S.frag[li] = 0xFFFFFFFFu; S.rf[li] = 0;
   if (n <= 0 || p[0] == '@') return;                                    // SamReader.java:173
   int tab[11]; int nt = 0;
-  { int pos = 0; while (nt < 11) { int q = find_tab(p, pos, n); if (q >= n) break; tab[nt++] = q; pos = q + 1; } }
+  { int pos = 0; while (nt < 11) { int q = tabs.next(p, pos, n); if (q >= n) break; tab[nt++] = q; pos = q + 1; } }
   // field count with the reference's rule: the 11 mandatory tokens count, later tokens only when they hold no ':' (SamRecord.java:223-232).
   // The same pass over the tag block finds the first [nN]M:i:<digits> and rejects an HI:i: tag.
   int nm = -1; int fields;
@@ -132,16 +159,13 @@ EQP_HD void decode_record(const AnnoView& A, const SamView& S, uint32_t li, cons
   else if (nt == 10) fields = (tab[9] + 1 < n) ? 11 : 10;
   else {
     // tag block, one token per iteration.  bowtie2 tags are XX:T:value with no ':' in the value: then the token counts as a tag
-    // (no field increment), the NM regex can only match at the token start and HI:i: is a plain prefix test.
-    fields = 11; bool odd = false, hi = false; int t = tab[10] + 1;
-#if defined(EQP_TAGS_BYTEWISE)
-    odd = true; t = n;
-#endif
+    // (no field increment), the NM regex can only match at the token start and HI:i: is a plain prefix test.  "Every token has
+    // ':' at offsets 2 and 4 and the block holds exactly two ':' per token" is that shape for all tokens at once.
+    fields = 11; bool odd = false, hi = false; int t = tab[10] + 1, nTok = 0;
     while (t < n) {
-      int te = find_tab(p, t, n), len = te - t;
-      bool shape = len >= 5 && p[t + 2] == ':' && p[t + 4] == ':' && p[t] != ':' && p[t + 1] != ':' && p[t + 3] != ':';
-      int extra = 0; for (int k = t + 5; k < te; k++) extra |= (p[k] == ':');
-      if (!shape || extra) { odd = true; break; }
+      int te = tabs.next(p, t, n), len = te - t;
+      if (!(len >= 5 && p[t + 2] == ':' && p[t + 4] == ':')) { odd = true; break; }
+      nTok++;
       bool isI = p[t + 3] == 'i';
       if (isI && p[t + 1] == 'M' && (p[t] == 'N' || p[t] == 'n') && nm < 0) {
         int d = t + 5, v = 0; bool dig = false;
@@ -151,6 +175,7 @@ EQP_HD void decode_record(const AnnoView& A, const SamView& S, uint32_t li, cons
       hi |= isI && p[t] == 'H' && p[t + 1] == 'I';
       t = te + 1;
     }
+    if (!odd && colon_count(p, tab[10] + 1, n) != 2 * nTok) odd = true;
     if (odd) hi = !tags_general(p, tab[10] + 1, n, fields, nm);
     if (hi) { raise(err, DERR_FIELDS, li); return; }                      // HI:i: changes isMate (SamRecord.java:658-660): not produced by bowtie2
   }
@@ -187,6 +212,10 @@ EQP_HD void decode_record(const AnnoView& A, const SamView& S, uint32_t li, cons
   S.frag[li] = frag; S.flag[li] = (uint16_t)flag; S.ref[li] = ref; S.pos[li] = pos; S.rnext[li] = rnext; S.pnext[li] = pnext;
   S.nm[li] = (int16_t)nm; S.cigOff[li] = (uint16_t)cigOff; S.cigLen[li] = (uint16_t)cigLen; S.seqLen[li] = (uint16_t)seqLen;
   S.rf[li] = (uint8_t)(RF_REC | (mapped ? RF_MAPPED : 0) | (hasMate ? RF_HASMATE : 0) | (readIndex << 3) | (suffix << 5));
+}
+
+EQP_HD void decode_record(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, uint32_t* err) {
+  ScanTabs tabs; decode_record_t(A, S, li, p, n, tabs, err);
 }
 
 EQP_HD void decode_line(const AnnoView& A, const SamView& S, uint32_t li, uint32_t* err) {

@@ -67,14 +67,16 @@ struct Pipeline {
   }
 
   int run(const char* const text[3], const uint64_t len[3], ChunkResult& R) {
+    be.stage(nullptr);
     scal = be.template alloc<uint32_t>(32); be.memset(scal, 0, 32 * sizeof(uint32_t));
     C.err = scal;
     const AnnoView A = this->A; const RunParams P = this->P;
     // ---- a1/a2: line index + decode
     for (int f = 0; f < 3; f++) {
-      index_lines(f, text[f], len[f]);
-      const SamView S = C.sam[f]; uint32_t* err = scal;
-      be.decode(A, S, err);                           // per-line decode_line(); CUDA backend uses the tiled shared-memory kernel
+      if (BE::kFusedDecode) be.decode_fused(A, C.sam[f], C.proc[f], text[f], len[f], scal);   // one pass: line index + records
+      else { index_lines(f, text[f], len[f]); be.stage("line-index"); be.decode(A, C.sam[f], scal); }
+      be.stage("decode");
+      const SamView S = C.sam[f];                          // per-line decode_line(); CUDA backend uses the tiled shared-memory kernel
       R.nRecords[f] = S.nLines;
     }
     // fragment id range
@@ -93,6 +95,7 @@ struct Pipeline {
     C.stTJ = be.template alloc<FragStat>(N); C.setTJ = be.template alloc<SetDesc>(N); C.setC = be.template alloc<SetDesc>(N);
     C.auxSlot = be.template alloc<uint32_t>((uint64_t)N + 1); C.blkOff = be.template alloc<uint32_t>((uint64_t)N + 1); C.alnOff = be.template alloc<uint32_t>((uint64_t)N + 1);
     C.seenRef = be.template alloc<uint8_t>((uint64_t)A.nRef + 1); be.memset(C.seenRef, 0, (uint64_t)A.nRef + 1);
+    be.stage("frag-range");
     // ---- fragment table: [first,end) line range per (file, slot); order check (CombineSamFiles.java:191-193)
     for (int f = 0; f < 3; f++) { const SamView S = C.sam[f]; FragFile* ff = C.ff[f]; uint32_t base = C.base; uint32_t* err = scal;
       be.launch(S.nLines, [=] EQP_LAMBDA(uint64_t i) {
@@ -106,6 +109,7 @@ struct Pipeline {
         if (!prevRec || S.frag[pi - 1] != fr) ff[fr - base].first = (uint32_t)i;
         if (!nextRec || S.frag[ni] != fr) ff[fr - base].end = (uint32_t)i + 1;
       }); }
+    be.stage("frag-table");
     // ---- a3/a4: per-fragment statistics in each input
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
     { const ChunkView C = this->C;
@@ -114,6 +118,7 @@ struct Pipeline {
         fragment_stats(A, C.sam[f], ff.first, ff.end, f == FILE_G, C.proc[f], st, ff, C.err, C.base + s);
         C.st[f][s] = st; C.ff[f][s].bits = ff.bits;
       }); }
+    be.stage("frag-stats");
     // ---- a5-a7: T+J weights, stage-1 selection, presence bounds, stage-2 selection, aux lookup table
     uint32_t* bnd = scal + 8;                          // [0] firstT [1] firstJ [2] lastT [3] anyT [4] anyJ | [5] firstTJ [6] firstG [7] lastTJ [8] anyTJ [9] anyG
     { uint32_t init[10] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0, 0, 0, 0xFFFFFFFFu, 0xFFFFFFFFu, 0, 0, 0}; be.to_device(bnd, init, sizeof init); }
@@ -146,6 +151,7 @@ struct Pipeline {
       be.launch(1, [=] EQP_LAMBDA(uint64_t) { uint32_t nx = 0xFFFFFFFFu; for (uint64_t c = nCh; c-- > 0;) { uint32_t own = chNext[c]; chNext[c] = nx; if (own != 0xFFFFFFFFu) nx = own; } });
       be.launch(N, [=] EQP_LAMBDA(uint64_t s) { if (C.auxSlot[s] == 0xFFFFFFFFu) C.auxSlot[s] = chNext[s / CH]; });
     }
+    be.stage("select");
     // ---- a27: reference ids seen (combined SAM + junction SAM) -> active junction features
     V.junctionActive = be.template alloc<uint8_t>((uint64_t)A.nFeat[2] + 1); be.memset((void*)V.junctionActive, 0, (uint64_t)A.nFeat[2] + 1);
     { const ChunkView C = this->C; uint8_t* act = (uint8_t*)V.junctionActive; const SamView J = C.sam[FILE_J];
@@ -160,6 +166,7 @@ struct Pipeline {
         if (A.refFlags[r] & 2) raise(C.err, DERR_BAD_JUNCTION_ID, (uint32_t)r);
         for (uint32_t k = A.refActOff[r]; k < A.refActOff[r + 1]; k++) act[A.refAct[k]] = 1;
       }); }
+    be.stage("junction-active");
     // ---- a8-a10: blocks (count, scan, fill)
     V.stats = be.template alloc<unsigned long long>(16); be.memset(V.stats, 0, 16 * sizeof(unsigned long long));
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
@@ -172,28 +179,35 @@ struct Pipeline {
     C.alnBlk = be.template alloc<uint32_t>((uint64_t)nAln + 1); be.to_device(C.alnBlk + nAln, &nBlocks, 4);
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
     { const ChunkView C = this->C; be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, nb, na); }); }
+    be.stage("blocks");
     // ---- a11: interval join (count, scan, fill)
     { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { C.hitCnt[b] = join_block(A, C.blocks[b], nullptr, (uint32_t)b); }); }
     be.scan(C.hitCnt, nBlocks); be.to_host(&nHits, C.hitCnt + nBlocks, 4);
     C.hits = be.template alloc<Hit>((uint64_t)nHits + 1);
     { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { join_block(A, C.blocks[b], C.hits + C.hitCnt[b], (uint32_t)b); }); }
+    be.stage("join");
     // ---- a12-a25
     V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
     V.dedupTab = be.template alloc<uint32_t>(2 * (uint64_t)nAln + 2); be.memset(V.dedupTab, 0, (2 * (uint64_t)nAln + 2) * 4); V.alnTail = be.template alloc<uint32_t>((uint64_t)nAln + 1);
     V.a20 = be.template alloc<uint32_t>((uint64_t)N + 1); V.nFinal = be.template alloc<uint32_t>((uint64_t)N + 1);
     for (int m = 0; m < 3; m++) { V.acc[m] = accOut[m] ? accOut[m] : be.template alloc<unsigned long long>((uint64_t)A.nFeat[m] + 1); be.memset(V.acc[m], 0, ((uint64_t)A.nFeat[m] + 1) * 8); }
     be.memset(V.a20, 0, ((uint64_t)N + 1) * 4); be.memset(V.nFinal, 0, ((uint64_t)N + 1) * 4);
+    be.stage("alloc-a12");
     // fragments with hits, ordered by descending hit-count class (stable within a class): warps of the thread-per-fragment stages get
     // fragments of similar cost while neighbouring lanes still touch neighbouring memory
     uint32_t* work = be.template alloc<uint32_t>((uint64_t)N + 1); uint32_t* perm = be.template alloc<uint32_t>((uint64_t)N + 1);
     { const ChunkView C = this->C; be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t h = C.hitCnt[C.blkOff[s + 1]] - C.hitCnt[C.blkOff[s]]; uint32_t c = 0; while (h) { c++; h >>= 1; } work[s] = c; }); }   // class = 1 + floor(log2(hits)): coarse, so neighbouring slots stay neighbours
     uint32_t nWork = be.order_by_work(work, N, perm);
     { const ChunkView C = this->C; const CountView V = this->V;
+      be.stage("order");
       be.launch(nAln, [=] EQP_LAMBDA(uint64_t a) { alignment_build(A, C, V, P, (uint32_t)a); });
+      be.stage("alignment-build");
       be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
+      be.stage("fragment-weight");
       be.fork();
       for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) { be.branch(m); be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_count(A, C, V, P, m, perm[i]); }); }
       be.join(); }
+    be.stage("fragment-count x3");
     // ---- results
     be.to_host(R.err, scal, 8);
     if (R.err[0]) return -1;

@@ -51,7 +51,7 @@ class Counts(C.Structure):
 
 
 EXPORTS = ("eqp_version", "eqp_default_params", "eqp_create", "eqp_load_annotation", "eqp_count_chunk", "eqp_feature_count",
-           "eqp_feature_id", "eqp_device_vector", "eqp_accumulate", "eqp_debug_fetch", "eqp_last_error", "eqp_destroy")
+           "eqp_feature_id", "eqp_device_vector", "eqp_accumulate", "eqp_debug_fetch", "eqp_debug_decode", "eqp_last_error", "eqp_destroy")
 
 _lib = None
 
@@ -76,6 +76,7 @@ def load_library(path=None):
     lib.eqp_device_vector.argtypes = [vp, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
     lib.eqp_accumulate.argtypes = [vp, vp]
     lib.eqp_debug_fetch.argtypes = [vp, C.c_char_p, vp, C.c_size_t, C.POINTER(C.c_size_t)]
+    lib.eqp_debug_decode.argtypes = [vp, vp, C.c_size_t, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     lib.eqp_last_error.argtypes = [vp]; lib.eqp_last_error.restype = C.c_char_p
     lib.eqp_destroy.argtypes = [vp]; lib.eqp_destroy.restype = None
     lib.eqp_annotation_bytes.argtypes = [vp]; lib.eqp_annotation_bytes.restype = C.c_int64
@@ -185,6 +186,14 @@ class CountContext:
         if n.value:
             self._check(self.lib.eqp_debug_fetch(self.h, what.encode(), out.ctypes.data, out.nbytes, C.byref(n)))
         return out
+
+    def debug_decode(self, sam, misalign=0):
+        """Run only the tokenizer kernel on one SAM text: (rows, err_code, err_detail); rows as `eqp_emu decode` prints them."""
+        addr, n, keep = _buf(sam)
+        text, tlen, ec, ed = C.c_char_p(), C.c_size_t(), C.c_uint32(), C.c_uint32()
+        self._check(self.lib.eqp_debug_decode(self.h, addr, n, misalign, C.byref(text), C.byref(tlen), C.byref(ec), C.byref(ed)))
+        rows = C.string_at(text, tlen.value).decode().splitlines() if tlen.value else []
+        return rows, ec.value, ed.value
 
     def close(self):
         if self.h:

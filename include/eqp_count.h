@@ -117,6 +117,13 @@ int  eqp_accumulate(eqp_ctx* ctx, uint64_t* dev_accumulator);
  * what: "weights:<T|J|G|TJ|final>", "selection", "blocks", "hits", "a20".  Layouts are documented in DESIGN.md. */
 int  eqp_debug_fetch(eqp_ctx* ctx, const char* what, void* dst, size_t dst_bytes, size_t* n_written);
 
+/* Test tap for the a1/a2 tokenizer kernel alone: decodes one SAM text, placed `misalign` (0-15) bytes after a 16-byte boundary in
+ * device memory, and formats one row per text line: "<line>\tREC\t<frag>\t<flag>\t<rname>\t<pos>\t<pnext>\t<nm>\t<cigar>\t<seqlen>\t<rf>",
+ * "<line>\tSKIP" (header / empty line), or "<line>\tLINE\t<offset>" for every line when the device raised an error (err_code != 0,
+ * the codes of SamRecord.java:182-186,246-257).  *text stays valid until the next call on this ctx. */
+int  eqp_debug_decode(eqp_ctx* ctx, const uint8_t* sam, size_t len, int misalign, const char** text, size_t* text_len,
+                      uint32_t* err_code, uint32_t* err_detail);
+
 const char* eqp_last_error(eqp_ctx* ctx);
 void eqp_destroy(eqp_ctx* ctx);
 

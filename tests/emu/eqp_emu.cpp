@@ -28,6 +28,9 @@ struct HostBackend {
       if (e == len && last != '\n') lo[nLines] = len + 1;
     }
   }
+  void stage(const char*) {}
+  static const bool kFusedDecode = false;
+  void decode_fused(const AnnoView&, SamView&, uint8_t*&, const char*, uint64_t, uint32_t*) {}
   void fork() {}
   void branch(int) {}
   void join() {}
