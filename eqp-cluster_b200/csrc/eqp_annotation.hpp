@@ -19,10 +19,30 @@
 
 namespace eqpb {
 
-EQP_HD uint64_t fnv1a(const char* p, int n) {
-  uint64_t h = 1469598103934665603ULL;
-  for (int i = 0; i < n; i++) { h ^= (uint8_t)p[i]; h *= 1099511628211ULL; }
-  return h ? h : 1;                                   // 0 marks an empty slot
+// Reference-name hash, defined over little-endian 4-byte groups of the name (the last group zero-padded) so that the device
+// can feed it one aligned shared-memory word pair per step instead of one byte.  Two 32-bit lanes give the 64-bit key.
+struct NameHash {
+  uint32_t a = 0x811C9DC5u, b = 0x9E3779B9u;
+  EQP_HD void add(uint32_t w) {
+    uint32_t k = w * 0xCC9E2D51u; k = (k << 15) | (k >> 17); k *= 0x1B873593u;
+    a ^= k; a = (a << 13) | (a >> 19); a = a * 5u + 0xE6546B64u;
+    b = (b ^ w) * 0x85EBCA6Bu; b ^= b >> 15;
+  }
+  EQP_HD uint64_t finish(int n) {
+    uint32_t x = a ^ (uint32_t)n; x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
+    uint32_t y = b + x; y ^= y >> 16; y *= 0x7FEB352Du; y ^= y >> 15; y *= 0x846CA68Bu; y ^= y >> 16;
+    uint64_t h = ((uint64_t)x << 32) | y;
+    return h ? h : 1;                                 // 0 marks an empty slot
+  }
+};
+EQP_HD uint32_t name_group_bytes(const char* p, int nvalid) {     // bytes p[0..min(nvalid,4)) as a little-endian word, zero-padded
+  uint32_t w = 0;
+  for (int i = 0; i < 4; i++) if (i < nvalid) w |= (uint32_t)(uint8_t)p[i] << (8 * i);
+  return w;
+}
+EQP_HD uint64_t name_hash(const char* p, int n) {
+  NameHash H; for (int i = 0; i < n; i += 4) H.add(name_group_bytes(p + i, n - i));
+  return H.finish(n);
 }
 
 EQP_HD uint64_t dict_key(uint64_t h, int len) { uint64_t k = (h & ~0xFFFFULL) | (uint64_t)(len & 0xFFFF); return k ? k : 0x10000ULL; }
@@ -88,7 +108,7 @@ struct AnnoHost {
   int32_t addRef(std::unordered_map<std::string, int32_t>& idx, const std::string& name) {
     auto it = idx.find(name); if (it != idx.end()) return it->second;
     int32_t r = (int32_t)refStrOff.size(); idx[name] = r;
-    refStrOff.push_back((uint32_t)strPool.size()); refStrLen.push_back((uint16_t)name.size()); strPool += name; refFlags.push_back(0);
+    refStrOff.push_back((uint32_t)strPool.size()); refStrLen.push_back((uint16_t)name.size()); strPool += name; while (strPool.size() & 3) strPool.push_back('\0'); refFlags.push_back(0);   // 4-byte aligned, zero-padded: lookup_ref compares words
     return r;
   }
 
@@ -155,7 +175,7 @@ struct AnnoHost {
     uint32_t cap = 16; while (cap < (uint32_t)nRef * 2u) cap <<= 1;
     dict.assign(cap, DictEntry{0, -1, 0}); dictMask = cap - 1;
     for (int32_t r = 0; r < nRef; r++) {
-      uint64_t h = fnv1a(refNames[r].data(), (int)refNames[r].size()); uint32_t s = (uint32_t)h & dictMask;
+      uint64_t h = name_hash(refNames[r].data(), (int)refNames[r].size()); uint32_t s = (uint32_t)h & dictMask;
       while (dict[s].key) s = (s + 1) & dictMask;
       dict[s] = DictEntry{dict_key(h, (int)refNames[r].size()), r, refStrOff[r]};
     }

@@ -1,6 +1,10 @@
 // a1/a2: SAM line decode into structure-of-arrays records (per-line device function).
 // Reference: J/sam-source/SamRecord.java:121-271 (field split, QNAME handling, flags),
 // :617-640 (flag read index), :960-1018 (flag helpers), :48,1052-1068 (NM:i: search).
+//
+// decode_record_t is templated on a "source" that (a) yields the line's tab positions in increasing order and (b) loads
+// unaligned 4-byte groups of the line.  ScanSrc searches the text (any memory, used by the host emulation and the kernel's
+// slow paths); the tokenizer kernel passes a source backed by the tab masks it has already built in shared memory.
 #pragma once
 #include "eqp_annotation.hpp"
 
@@ -14,30 +18,57 @@ EQP_HD void raise(uint32_t* err, uint32_t code, uint32_t detail) {
 #endif
 }
 
-EQP_HD int32_t lookup_ref(const AnnoView& A, const char* p, int n) {
-  if (n == 1 && p[0] == '*') return -1;
-  uint64_t h = fnv1a(p, n), key = dict_key(h, n); uint32_t s = (uint32_t)h & A.dictMask;
-  if (n < 0x10000) while (true) {
-    DictEntry e = A.dict[s];                                            // one 16-byte load: key (hash | length), id, string offset
-    if (!e.key) break;
-    if (e.key == key) {
-      const char* q = A.strPool + e.off; int diff = 0;
-      for (int i = 0; i < n; i++) diff |= q[i] ^ p[i];                   // no early exit: the loads are independent and overlap
-      if (!diff) return e.val;
-    }
-    s = (s + 1) & A.dictMask;
-  }
-  return -2 - (int32_t)(h & 0x3fffffffULL);           // unknown name: identity by hash only (never joins, never whitelisted)
+EQP_HD int eqp_popc32(uint32_t m) {
+#if defined(__CUDA_ARCH__)
+  return __popc(m);
+#else
+  return __builtin_popcount(m);
+#endif
 }
 
-// Integer.parseInt on [p, p+n): optional sign, digits only
+// RNAME / RNEXT -> dictionary id.  Hash and comparison run over 4-byte groups (NameHash); the string pool keeps every name
+// 4-byte aligned and zero-padded, so equal groups + equal length is string equality.
+template <class Src>
+EQP_HD int32_t lookup_ref(const AnnoView& A, const char* p, int n) {
+  int32_t res = -1;
+  if (!(n == 1 && p[0] == '*')) {
+    NameHash H; int ng = (n + 3) >> 2;
+    for (int k = 0; k < ng; k++) H.add(Src::load4(p + 4 * k, n - 4 * k));
+    uint64_t h = H.finish(n), key = dict_key(h, n); uint32_t s = (uint32_t)h & A.dictMask;
+    res = -2 - (int32_t)(h & 0x3fffffffULL);            // unknown name: identity by hash only (never joins, never whitelisted)
+    bool go = n < 0x10000;
+    while (go) {
+      DictEntry e = A.dict[s];                                           // one 16-byte load: key (hash | length), id, string offset
+      if (!e.key) go = false;
+      else {
+        if (e.key == key) {
+          const uint32_t* q = reinterpret_cast<const uint32_t*>(A.strPool + e.off); uint32_t diff = 0;
+          for (int k = 0; k < ng; k++) diff |= q[k] ^ Src::load4(p + 4 * k, n - 4 * k);   // no early exit: the loads are independent and overlap
+          if (!diff) { res = e.val; go = false; }
+        }
+        s = (s + 1) & A.dictMask;
+      }
+    }
+  }
+  return res;
+}
+
+// Integer.parseInt on [p, p+n): optional sign, digits only.  Single exit so that the lanes of a warp reconverge after the call.
 EQP_HD bool parse_int(const char* p, int n, int32_t& out) {
-  if (n <= 0) return false;
-  int i = 0; bool neg = false;
-  if (p[0] == '-' || p[0] == '+') { neg = p[0] == '-'; i = 1; if (n == 1) return false; }
+  bool ok = n > 0, neg = false; int i = 0;
+  if (ok) { char c0 = p[0]; if (c0 == '-' || c0 == '+') { neg = c0 == '-'; i = 1; ok = n > 1; } }
   int64_t v = 0;
-  for (; i < n; i++) { char c = p[i]; if (c < '0' || c > '9') return false; v = v * 10 + (c - '0'); if (v > 2147483648LL) return false; }
-  out = (int32_t)(neg ? -v : v); return true;
+  for (; ok && i < n; i++) { uint32_t c = (uint32_t)(uint8_t)p[i] - (uint32_t)'0'; v = v * 10 + (int64_t)c; ok = c <= 9u && v <= 2147483648LL; }
+  out = (int32_t)(neg ? -v : v);
+  return ok;
+}
+
+// four ASCII digits in a little-endian group (first digit in the low byte) -> value, or -1
+EQP_HD int32_t digits4(uint32_t x) {
+  uint32_t t = x - 0x30303030u;
+  bool ok = (((t + 0x76767676u) | t) & 0x80808080u) == 0;                // every byte 0..9 (a byte below '0' borrows, but is flagged itself)
+  uint32_t u = t * 10u + (t >> 8);                                       // byte 0: d0*10+d1, byte 2: d2*10+d3
+  return ok ? (int32_t)((u & 0xFFu) * 100u + ((u >> 16) & 0xFFu)) : -1;
 }
 
 // rf layout: bit0 record, bit1 mapped, bit2 hasMate, bits3-4 readIndex, bits5-6 /1 /2 name suffix
@@ -94,128 +125,143 @@ EQP_HD int find_tab(const char* p, int from, int n) {
   return res;
 }
 
+// number of ':' in p[a, b): aligned 4-byte words, exact SWAR byte compare.  Only words holding at least one byte of [a, b) are read.
+EQP_HD uint32_t colon_marker(uint32_t w) { uint32_t x = w ^ 0x3a3a3a3au; return ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu); }
+EQP_HD int colon_count(const char* p, int a, int b) {
+  int cnt = 0;
+  if (a < b) {
+    uintptr_t s = (uintptr_t)(p + a), e = (uintptr_t)(p + b), wa = s & ~(uintptr_t)3, we = (e - 1) & ~(uintptr_t)3;
+    uint32_t m0 = 0xFFFFFFFFu << (8 * (int)(s - wa)), m1 = 0xFFFFFFFFu >> (8 * (int)(we + 4 - e));
+    uint32_t z = colon_marker(*reinterpret_cast<const uint32_t*>(wa)) & m0;
+    for (; wa < we; wa += 4) { cnt += eqp_popc32(z); z = colon_marker(*reinterpret_cast<const uint32_t*>(wa + 4)); }
+    cnt += eqp_popc32(z & m1);
+  }
+  return cnt;
+}
+
 // General tag-block scan (any token shape): field count with the reference's rule, first [nN]M:i:<digits>, HI:i: at a token start.
 // Returns false when an HI tag is present.  Only reached for lines whose tags are not all of the form XX:T:value.
 EQP_HD bool tags_general(const char* p, int t0, int n, int& fields, int& nm) {
-  fields = 11; nm = -1; int k = t0; bool colon = false, any = k < n;
-  for (; k < n; k++) {
+  fields = 11; nm = -1; int k = t0; bool colon = false, any = k < n, noHi = true;
+  for (; k < n && noHi; k++) {
     char c = p[k];
-    if (c == '\t') { if (!colon) fields++; colon = false; any = k + 1 < n; continue; }
-    if (c == ':') {
+    if (c == '\t') { if (!colon) fields++; colon = false; any = k + 1 < n; }
+    else if (c == ':') {
       colon = true;
       if (k + 2 < n && p[k + 1] == 'i' && p[k + 2] == ':' && k - 2 >= t0) {
         char c1 = p[k - 1], c0 = p[k - 2];
         if (nm < 0 && c1 == 'M' && (c0 == 'N' || c0 == 'n')) {
           int d = k + 3, v = 0; bool dig = false;
-          while (d < n && p[d] >= '0' && p[d] <= '9') { v = v * 10 + (p[d] - '0'); d++; dig = true; if (v > 30000) break; }
+          while (d < n && p[d] >= '0' && p[d] <= '9' && v <= 30000) { v = v * 10 + (p[d] - '0'); d++; dig = true; }
           if (dig) nm = v;
         }
-        if (c1 == 'I' && c0 == 'H' && (k - 2 == t0 || p[k - 3] == '\t')) return false;
+        if (c1 == 'I' && c0 == 'H' && (k - 2 == t0 || p[k - 3] == '\t')) noHi = false;
       }
     }
   }
-  if (any && !colon) fields++;                                           // last token (a trailing empty token is not one)
-  return true;
+  if (noHi && any && !colon) fields++;                                   // last token (a trailing empty token is not one)
+  return noHi;
 }
 
-// number of ':' in p[a, b): aligned 4-byte words, exact SWAR byte compare.  Only words holding at least one byte of [a, b) are read.
-EQP_HD int colon_count(const char* p, int a, int b) {
-  if (a >= b) return 0;
-  uintptr_t s = (uintptr_t)(p + a), e = (uintptr_t)(p + b), wa = s & ~(uintptr_t)3; int cnt = 0;
-  for (; wa < e; wa += 4) {
-    uint32_t x = *reinterpret_cast<const uint32_t*>(wa) ^ 0x3a3a3a3au;
-    uint32_t z = ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu);   // 0x80 in every byte equal to ':'
-    if (wa < s) z &= 0xFFFFFFFFu << (8 * (int)(s - wa));
-    if (wa + 4 > e) z &= 0xFFFFFFFFu >> (8 * (int)(wa + 4 - e));
-#if defined(__CUDA_ARCH__)
-    cnt += __popc(z);
-#else
-    cnt += __builtin_popcount(z);
-#endif
-  }
-  return cnt;
-}
-
-// Tab sources for decode_record_t: next(p, from, n) = first '\t' in p[from, n), or n.  Calls come with increasing `from`.
-struct ScanTabs { EQP_HD int next(const char* p, int from, int n) { return find_tab(p, from, n); } };
-// Tabs already located by the tokenizer kernel: ev[cur, end) are this line's tab events, (position in the staged tile << 1); s = line start.
-struct EventTabs {
-  const uint16_t* ev; int cur, end, s;
-  EQP_HD int next(const char*, int, int n) { if (cur < end) { int q = (int)(ev[cur] >> 1) - s; cur++; return q < n ? q : n; } return n; }
+// Source for text in any memory: tabs by search, groups byte by byte (never reads outside [p, p+n)).
+struct ScanSrc {
+  EQP_HD int next(const char* p, int from, int n) { return find_tab(p, from, n); }
+  static EQP_HD uint32_t load4(const char* q, int nvalid) { return name_group_bytes(q, nvalid); }
 };
 
 // One SAM line [p, p+n) (no '\n').  The text may live in shared or global memory.
-template <class Tabs>
-EQP_HD void decode_record_t(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, Tabs& tabs, uint32_t* err) {
+template <class Src>
+EQP_HD void decode_record_t(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, Src& src, uint32_t* err) {
   if (n > 0 && p[n - 1] == '\r') n--;
-  S.frag[li] = 0xFFFFFFFFu; S.rf[li] = 0;
-  if (n <= 0 || p[0] == '@') return;                                    // SamReader.java:173
-  int tab[11]; int nt = 0;
-  { int pos = 0; while (nt < 11) { int q = tabs.next(p, pos, n); if (q >= n) break; tab[nt++] = q; pos = q + 1; } }
-  // field count with the reference's rule: the 11 mandatory tokens count, later tokens only when they hold no ':' (SamRecord.java:223-232).
-  // The same pass over the tag block finds the first [nN]M:i:<digits> and rejects an HI:i: tag.
-  int nm = -1; int fields;
-  if (nt < 10) fields = nt + (((nt ? tab[nt - 1] + 1 : 0) < n) ? 1 : 0);
-  else if (nt == 10) fields = (tab[9] + 1 < n) ? 11 : 10;
-  else {
-    // tag block, one token per iteration.  bowtie2 tags are XX:T:value with no ':' in the value: then the token counts as a tag
-    // (no field increment), the NM regex can only match at the token start and HI:i: is a plain prefix test.  "Every token has
-    // ':' at offsets 2 and 4 and the block holds exactly two ':' per token" is that shape for all tokens at once.
-    fields = 11; bool odd = false, hi = false; int t = tab[10] + 1, nTok = 0;
-    while (t < n) {
-      int te = tabs.next(p, t, n), len = te - t;
-      if (!(len >= 5 && p[t + 2] == ':' && p[t + 4] == ':')) { odd = true; break; }
-      nTok++;
-      bool isI = p[t + 3] == 'i';
-      if (isI && p[t + 1] == 'M' && (p[t] == 'N' || p[t] == 'n') && nm < 0) {
-        int d = t + 5, v = 0; bool dig = false;
-        while (d < te && p[d] >= '0' && p[d] <= '9') { v = v * 10 + (p[d] - '0'); d++; dig = true; if (v > 30000) break; }
-        if (dig) nm = v;
+  uint32_t code = DERR_NONE;                                            // first failed check, raised once at the end (single exit)
+  uint32_t frag = 0xFFFFFFFFu; uint8_t rf = 0;
+  int32_t flag = 0, pos = 0, pnext = 0, ref = -1, rnext = -1; int nm = -1, cigOff = 0, cigLen = 0, seqLen = 0;
+  if (n > 0 && p[0] != '@') {                                           // SamReader.java:173
+    int nt = 0, from = 0;                                                // the first 11 tabs, as scalars (an indexed array would live in local memory)
+#define EQP_TAB_STEP(i) int tab##i = n; if (nt == i) { int q = src.next(p, from, n); if (q < n) { tab##i = q; nt = i + 1; from = q + 1; } }
+    EQP_TAB_STEP(0) EQP_TAB_STEP(1) EQP_TAB_STEP(2) EQP_TAB_STEP(3) EQP_TAB_STEP(4) EQP_TAB_STEP(5)
+    EQP_TAB_STEP(6) EQP_TAB_STEP(7) EQP_TAB_STEP(8) EQP_TAB_STEP(9) EQP_TAB_STEP(10)
+#undef EQP_TAB_STEP
+    // field count with the reference's rule: the 11 mandatory tokens count, later tokens only when they hold no ':' (SamRecord.java:223-232).
+    // The same pass over the tag block finds the first [nN]M:i:<digits> and rejects an HI:i: tag.
+    int fields;
+    if (nt < 10) fields = nt + (from < n ? 1 : 0);
+    else if (nt == 10) fields = (from < n) ? 11 : 10;
+    else {
+      // tag block, one token per iteration.  bowtie2 tags are XX:T:value with no ':' in the value: then the token counts as a tag
+      // (no field increment), the NM regex can only match at the token start and HI:i: is a plain prefix test.  "Every token has
+      // ':' at offsets 2 and 4 and the block holds exactly two ':' per token" is that shape for all tokens at once.
+      const uint32_t NMI = 'n' | ('M' << 8) | (':' << 16) | ((uint32_t)'i' << 24), HII = 'H' | ('I' << 8) | (':' << 16) | ((uint32_t)'i' << 24);
+      fields = 11; bool odd = false, hi = false; int t = from, nTok = 0;
+      while (t < n && !odd) {
+        int te = src.next(p, t, n), len = te - t;
+        uint32_t w = Src::load4(p + t, len);
+        if (len >= 5 && ((w >> 16) & 0xFFu) == ':' && p[t + 4] == ':') {
+          nTok++;
+          if (nm < 0 && (w | 0x20u) == NMI) {
+            int d = t + 5, v = 0; bool dig = false;
+            while (d < te && p[d] >= '0' && p[d] <= '9' && v <= 30000) { v = v * 10 + (p[d] - '0'); d++; dig = true; }
+            if (dig) nm = v;
+          }
+          hi |= w == HII;
+          t = te + 1;
+        } else odd = true;
       }
-      hi |= isI && p[t] == 'H' && p[t + 1] == 'I';
-      t = te + 1;
+      if (!odd && colon_count(p, from, n) != 2 * nTok) odd = true;
+      if (odd) hi = !tags_general(p, from, n, fields, nm);
+      if (hi) code = DERR_FIELDS;                                        // HI:i: changes isMate (SamRecord.java:658-660): not produced by bowtie2
     }
-    if (!odd && colon_count(p, tab[10] + 1, n) != 2 * nTok) odd = true;
-    if (odd) hi = !tags_general(p, tab[10] + 1, n, fields, nm);
-    if (hi) { raise(err, DERR_FIELDS, li); return; }                      // HI:i: changes isMate (SamRecord.java:658-660): not produced by bowtie2
+    if (!code && (fields < 11 || fields > 12)) code = DERR_FIELDS;
+    if (!code) {
+      int e0 = tab0; int suffix = 0;
+      // QNAME (SamRecord.java:155-176): F + nine digits, optionally "/1" "/2" or " comment"
+      if (e0 == 10) {
+        int32_t hi4 = digits4(Src::load4(p + 1, 4)), lo4 = digits4(Src::load4(p + 5, 4)); uint32_t d9 = (uint32_t)(uint8_t)p[9] - (uint32_t)'0';
+        if (p[0] != 'F' || hi4 < 0 || lo4 < 0 || d9 > 9u) code = DERR_QNAME; else frag = (uint32_t)hi4 * 100000u + (uint32_t)lo4 * 10u + d9;
+      } else {
+        int qe = e0; bool sp = false;
+        for (int i = 1; i < e0 && !sp; i++) if (p[i] == ' ') { qe = i; sp = true; }
+        if (e0 >= 2 && p[e0 - 2] == '/' && (p[e0 - 1] == '1' || p[e0 - 1] == '2')) { suffix = p[e0 - 1] - '0'; if (qe == e0) qe = e0 - 2; }
+        if (qe != 10 || p[0] != 'F') code = DERR_QNAME;
+        else { frag = 0; for (int i = 1; i < 10; i++) { uint32_t c = (uint32_t)(uint8_t)p[i] - (uint32_t)'0'; if (c > 9u) code = DERR_QNAME; frag = frag * 10 + c; } }
+      }
+      int32_t mapq = 0; bool intsOk = true;
+      intsOk &= parse_int(p + tab0 + 1, tab1 - tab0 - 1, flag);
+      int readIndex = suffix;
+      int fri = flag_read_index(flag, suffix, readIndex);
+      bool riBad = intsOk && readIndex && readIndex != fri;
+      if (!readIndex) readIndex = fri;
+      { const char* q = p + tab2 + 1; int l = tab3 - tab2 - 1;
+        if (l == 1 && q[0] == '*') pos = -1; else intsOk &= parse_int(q, l, pos); }
+      intsOk &= parse_int(p + tab3 + 1, tab4 - tab3 - 1, mapq);
+      { const char* q = p + tab6 + 1; int l = tab7 - tab6 - 1;
+        if (l == 1 && q[0] == '*') pnext = -1; else intsOk &= parse_int(q, l, pnext); }
+      if (!code && !intsOk) code = DERR_INT;
+      if (!code && riBad) code = DERR_READ_INDEX;
+      cigOff = tab4 + 1; cigLen = tab5 - tab4 - 1;
+      seqLen = tab9 - tab8 - 1;
+      int qualEnd = nt >= 11 ? tab10 : n, qualLen = qualEnd - tab9 - 1;
+      if (!code && !(qualLen == 1 && p[tab9 + 1] == '*') && qualLen != seqLen) code = DERR_SEQ_QUAL;
+      if (!code) {
+        ref = lookup_ref<Src>(A, p + tab1 + 1, tab2 - tab1 - 1);
+        const char* q = p + tab5 + 1; int l = tab6 - tab5 - 1;
+        rnext = (l == 1 && q[0] == '=') ? ref : lookup_ref<Src>(A, q, l);   // getMateReferenceName (:888-894)
+        bool mapped = pos >= 0 && (flag & 4) == 0;                          // :980-982
+        bool hasMate = (flag & 1) && (flag & 2);                            // :964-966
+        rf = (uint8_t)(RF_REC | (mapped ? RF_MAPPED : 0) | (hasMate ? RF_HASMATE : 0) | (readIndex << 3) | (suffix << 5));
+      }
+    }
   }
-  if (fields < 11 || fields > 12) { raise(err, DERR_FIELDS, li); return; }
-  int e0 = tab[0];
-  // QNAME (SamRecord.java:155-176)
-  int qe = e0; { for (int i = 1; i < e0; i++) if (p[i] == ' ') { qe = i; break; } }
-  int suffix = 0;
-  if (e0 >= 2 && p[e0 - 2] == '/' && (p[e0 - 1] == '1' || p[e0 - 1] == '2')) { suffix = p[e0 - 1] - '0'; if (qe == e0) qe = e0 - 2; }
-  if (qe != 10 || p[0] != 'F') { raise(err, DERR_QNAME, li); return; }
-  uint32_t frag = 0;
-  for (int i = 1; i < 10; i++) { char c = p[i]; if (c < '0' || c > '9') { raise(err, DERR_QNAME, li); return; } frag = frag * 10 + (uint32_t)(c - '0'); }
-  int32_t flag, pos, mapq, pnext;
-  if (!parse_int(p + tab[0] + 1, tab[1] - tab[0] - 1, flag)) { raise(err, DERR_INT, li); return; }
-  int readIndex = suffix ? suffix : 0;
-  int fri = flag_read_index(flag, suffix, readIndex);
-  if (!readIndex) readIndex = fri; else if (readIndex != fri) { raise(err, DERR_READ_INDEX, li); return; }
-  const char* rn = p + tab[1] + 1; int rnLen = tab[2] - tab[1] - 1;
-  int32_t ref = lookup_ref(A, rn, rnLen);
-  { const char* q = p + tab[2] + 1; int l = tab[3] - tab[2] - 1;
-    if (l == 1 && q[0] == '*') pos = -1; else if (!parse_int(q, l, pos)) { raise(err, DERR_INT, li); return; } }
-  if (!parse_int(p + tab[3] + 1, tab[4] - tab[3] - 1, mapq)) { raise(err, DERR_INT, li); return; }
-  int cigOff = tab[4] + 1, cigLen = tab[5] - tab[4] - 1;
-  int32_t rnext;
-  { const char* q = p + tab[5] + 1; int l = tab[6] - tab[5] - 1;
-    rnext = (l == 1 && q[0] == '=') ? ref : lookup_ref(A, q, l); }      // getMateReferenceName (:888-894)
-  { const char* q = p + tab[6] + 1; int l = tab[7] - tab[6] - 1;
-    if (l == 1 && q[0] == '*') pnext = -1; else if (!parse_int(q, l, pnext)) { raise(err, DERR_INT, li); return; } }
-  int seqLen = tab[9] - tab[8] - 1;
-  int qualEnd = nt >= 11 ? tab[10] : n, qualLen = qualEnd - tab[9] - 1;
-  if (!(qualLen == 1 && p[tab[9] + 1] == '*') && qualLen != seqLen) { raise(err, DERR_SEQ_QUAL, li); return; }
-  bool mapped = pos >= 0 && (flag & 4) == 0;                            // :980-982
-  bool hasMate = (flag & 1) && (flag & 2);                              // :964-966
-  S.frag[li] = frag; S.flag[li] = (uint16_t)flag; S.ref[li] = ref; S.pos[li] = pos; S.rnext[li] = rnext; S.pnext[li] = pnext;
-  S.nm[li] = (int16_t)nm; S.cigOff[li] = (uint16_t)cigOff; S.cigLen[li] = (uint16_t)cigLen; S.seqLen[li] = (uint16_t)seqLen;
-  S.rf[li] = (uint8_t)(RF_REC | (mapped ? RF_MAPPED : 0) | (hasMate ? RF_HASMATE : 0) | (readIndex << 3) | (suffix << 5));
+  if (code) { raise(err, code, li); frag = 0xFFFFFFFFu; rf = 0; }
+  S.frag[li] = frag; S.rf[li] = rf;
+  if (rf) {
+    S.flag[li] = (uint16_t)flag; S.ref[li] = ref; S.pos[li] = pos; S.rnext[li] = rnext; S.pnext[li] = pnext;
+    S.nm[li] = (int16_t)nm; S.cigOff[li] = (uint16_t)cigOff; S.cigLen[li] = (uint16_t)cigLen; S.seqLen[li] = (uint16_t)seqLen;
+  }
 }
 
 EQP_HD void decode_record(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, uint32_t* err) {
-  ScanTabs tabs; decode_record_t(A, S, li, p, n, tabs, err);
+  ScanSrc src; decode_record_t(A, S, li, p, n, src, err);
 }
 
 EQP_HD void decode_line(const AnnoView& A, const SamView& S, uint32_t li, uint32_t* err) {

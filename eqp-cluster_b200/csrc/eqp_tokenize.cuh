@@ -3,14 +3,14 @@
 //
 // A CTA owns the lines that START in a 30,704-byte tile.  The tile plus a 16-byte lead-in and a 2 KB overhang (so the last
 // owned line is complete) is brought into shared memory by one TMA bulk copy (cp.async.bulk, mbarrier completion).
-//   phase 1a  byte-parallel: every 16-byte piece -> 16-bit mask of control characters (< 0x10), conflict-free LDS.128 + SWAR
-//   phase 1b  thread t owns 8 consecutive pieces: classify the few marked bytes into '\t' / '\n', block scan of (events, newlines),
-//             emit the tile's sorted event list ev[] and the event index of every newline lineEv[]
+//   phase 1a  byte-parallel: every 16-byte piece -> 16-bit masks of its '\n' and '\t' bytes (conflict-free LDS.128, exact SWAR
+//             compare, one multiply gathers both masks of a word)
+//   phase 1b  thread t owns 8 consecutive pieces: block scan of the newline counts, list of newline positions nlPos[]
 //   look-back one thread publishes the tile's newline count and chains the exclusive prefix over earlier tiles (decoupled
 //             look-back, tile ids from an atomic ticket so that every predecessor is already running) -> global line numbers
-//   phase 2   thread per owned line: the record's tabs are consecutive entries of ev[], so the field decode (decode_record_t)
-//             never searches; SoA stores are coalesced over consecutive line numbers
-// Lines longer than the overhang and tiles with more events than the tables hold take a per-line / per-tile slow path that
+//   phase 2   thread per owned line: line = (nlPos[j], nlPos[j+1]); its tabs are read off the tab masks 64 text bytes per
+//             word (StageSrc), names and tags are handled in 4-byte groups, SoA stores are coalesced over consecutive lines
+// Lines longer than the overhang and tiles with more lines than nlPos holds take a per-line / per-tile slow path that
 // parses from global memory with the generic decoder.
 #pragma once
 #include <cuda_runtime.h>
@@ -24,30 +24,63 @@ static const int TK_STAGE = TK_PIECES * 16;                          // 32 KB
 static const int TK_OV_PIECES = 128;                                 // 2 KB overhang
 static const int TK_OWNED = (TK_PIECES - 1 - TK_OV_PIECES) * 16;     // 30,704 bytes of line starts per tile
 static const int TK_PER_THREAD = TK_PIECES / TK_THREADS;             // 8 pieces = 128 bytes
-static const int TK_EV_CAP = 6144, TK_NL_CAP = 2048;
+static const int TK_NL_CAP = 2048;
 static const int TK_FIRST_OV_THREAD = (TK_PIECES - TK_OV_PIECES) / TK_PER_THREAD;   // 240
 
 struct TokShared {
   alignas(128) char stage[TK_STAGE];
-  alignas(16) uint16_t ctrl[TK_PIECES];
-  uint16_t ev[TK_EV_CAP];
-  uint16_t lineEv[TK_NL_CAP + 2];
+  alignas(16) uint16_t tabM[TK_PIECES + 8];                          // +8: StageSrc may read the 8-byte word after the last piece
+  alignas(16) uint16_t nlM[TK_PIECES];
+  uint16_t nlPos[TK_NL_CAP + 2];
   uint32_t warpTot[TK_THREADS / 32];
   alignas(8) unsigned long long bar;
   unsigned long long lineBase;
-  uint32_t tile, nEv, nNl, nOwned;
+  uint32_t tile, nNl, nOwned;
 };
 
 static const unsigned long long TK_FLAG_AGG = 1ULL << 62, TK_FLAG_PREFIX = 2ULL << 62, TK_VALUE_MASK = (1ULL << 62) - 1;
 
 __device__ __forceinline__ uint32_t tk_smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-// 4 bytes -> 4-bit mask of bytes < 0x10 (high nibble zero), exact
-__device__ __forceinline__ uint32_t tk_ctrl4(uint32_t w) {
-  uint32_t t = (w & 0x70707070u) + 0x70707070u;                      // bit 7 of a byte set iff bits 4-6 are not all zero
-  uint32_t z = ~(t | w) & 0x80808080u;                               // 0x80 iff the byte's high nibble is zero
-  return (((z >> 7) * 0x00204081u) >> 21) & 0xFu;                    // gather bits 0,8,16,24 into a nibble
+// 4 text bytes -> top byte of the result: bits 24-27 = bytes equal to '\t', bits 28-31 = bytes equal to '\n' (exact compares).
+// c holds a marker at bit 3 (tab) / bit 7 (newline) of each byte; the multiply moves marker k of byte k to bit 24+k / 28+k
+// (all 32 partial-product positions are distinct, so nothing carries).
+__device__ __forceinline__ uint32_t tk_marks4(uint32_t w) {
+  uint32_t xn = w ^ 0x0a0a0a0au, xt = w ^ 0x09090909u;
+  uint32_t zn = ~(((xn & 0x7f7f7f7fu) + 0x7f7f7f7fu) | xn | 0x7f7f7f7fu);
+  uint32_t zt = ~(((xt & 0x7f7f7f7fu) + 0x7f7f7f7fu) | xt | 0x7f7f7f7fu);
+  return (zn | (zt >> 4)) * 0x00204081u;
 }
+// four bytes (hi nibble = newline bits, lo nibble = tab bits, one byte per text word) -> 16-bit masks
+__device__ __forceinline__ uint32_t tk_nibbles16(uint32_t t) {        // t: nibbles at bits 0-3, 8-11, 16-19, 24-27
+  t = (t | (t >> 4)) & 0x00FF00FFu; return (t | (t >> 8)) & 0xFFFFu;
+}
+
+// Source for a line staged in shared memory: tabs from the tile's tab masks, 64 text bytes per 8-byte load; groups from two
+// aligned words and a funnel shift.
+struct StageSrc {
+  const unsigned long long* tabW;                                     // tab masks, one bit per staged byte
+  int s, lim, wi; unsigned long long word;                            // line start / end (staged positions), current mask word
+  __device__ __forceinline__ StageSrc(const uint16_t* tabM, int s_, int n) : tabW(reinterpret_cast<const unsigned long long*>(tabM)), s(s_), lim(s_ + n), wi(s_ >> 6) {
+    word = tabW[wi] & (~0ULL << (s & 63));
+  }
+  __device__ __forceinline__ int next(const char*, int, int n) {
+    int res = n; bool go = true;
+    while (go) {
+      if (word) { int bit = __ffsll((long long)word) - 1; word &= word - 1; int q = (wi << 6) + bit - s; res = q < n ? q : n; go = false; }
+      else if (((wi + 1) << 6) >= lim) go = false;
+      else word = tabW[++wi];
+    }
+    return res;
+  }
+  static __device__ __forceinline__ uint32_t load4(const char* q, int nvalid) {
+    uint32_t a = (uint32_t)__cvta_generic_to_shared(q), lo, hi;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(lo) : "r"(a & ~3u));
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(hi) : "r"((a & ~3u) + 4u));          // past the stage buffer this is tabM: readable, masked below
+    uint32_t v = __funnelshift_r(lo, hi, (a & 3u) * 8u);
+    return nvalid >= 4 ? v : (nvalid <= 0 ? 0u : v & ((1u << (8 * nvalid)) - 1u));
+  }
+};
 
 // Serial slow path of a whole tile (thread 0): same outputs as the fast path, parsed from global memory.
 __device__ __noinline__ void tk_slow_tile(const AnnoView& A, const SamView& S, uint32_t capLines, long long vb, int a0, unsigned long long lineBase, bool firstTile, uint32_t* err) {
@@ -68,7 +101,7 @@ __device__ __noinline__ void tk_slow_tile(const AnnoView& A, const SamView& S, u
 }
 
 __global__ void __launch_bounds__(TK_THREADS, 4)
-k_tokenize_sam(AnnoView A, SamView S, uint32_t capLines, uint32_t nTiles, unsigned long long* status, uint32_t* ticket, unsigned long long* nlTotal, uint32_t* err) {
+k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamView S, uint32_t capLines, uint32_t nTiles, unsigned long long* status, uint32_t* ticket, unsigned long long* nlTotal, uint32_t* err) {
   extern __shared__ __align__(128) unsigned char tk_raw[];
   TokShared& sh = *reinterpret_cast<TokShared*>(tk_raw);
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -92,74 +125,59 @@ k_tokenize_sam(AnnoView A, SamView S, uint32_t capLines, uint32_t nTiles, unsign
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(tk_smem_addr(sh.stage + (c0 - v0))), "l"(base + c0), "r"(bytes), "r"(tk_smem_addr(&sh.bar)) : "memory");
   }
-  { uint32_t done = 0, bar = tk_smem_addr(&sh.bar);
+  { uint32_t done = 0, bar = tk_smem_addr(&sh.bar);                  // thread 0 waits for the copy, the others for thread 0 ...
+    if (tid == 0) while (!done) asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar) : "memory");
+    __syncthreads();
+    done = 0;                                                          // ... and then observe the completed phase themselves (acquire)
     while (!done) asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar) : "memory"); }
 
-  // ---- phase 1a: control-character mask per 16-byte piece
+  // ---- phase 1a: newline and tab masks per 16-byte piece
   const uint4* sv = reinterpret_cast<const uint4*>(sh.stage);
+  const int vnPos = 15 + a0;                                         // staged position of the virtual newline in front of text[0] (tile 0)
 #pragma unroll
   for (int k = 0; k < TK_PER_THREAD; k++) {
     uint32_t p = tid + k * TK_THREADS; uint4 q = sv[p];
-    uint32_t m = tk_ctrl4(q.x) | (tk_ctrl4(q.y) << 4) | (tk_ctrl4(q.z) << 8) | (tk_ctrl4(q.w) << 12);
+    uint32_t r0 = tk_marks4(q.x), r1 = tk_marks4(q.y), r2 = tk_marks4(q.z), r3 = tk_marks4(q.w);
+    uint32_t B = __byte_perm(__byte_perm(r0, r1, 0x0073), __byte_perm(r2, r3, 0x0073), 0x5410);   // top bytes of r0..r3
+    uint32_t tb = tk_nibbles16(B & 0x0F0F0F0Fu), nl = tk_nibbles16((B >> 4) & 0x0F0F0F0Fu);
     long long g0 = v0 + 16LL * p - a0;                               // text offset of the piece's byte 0
     if (g0 < 0 || g0 + 16 > (long long)S.len) {                      // piece straddles the text's ends: keep valid bytes only
       long long lo = g0 < 0 ? -g0 : 0, hi = (long long)S.len - g0;
       if (lo > 16) lo = 16; if (hi > 16) hi = 16; if (hi < 0) hi = 0;
-      m &= (hi > lo) ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+      uint32_t ok = (hi > lo) ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+      tb &= ok; nl &= ok;
     }
-    if (p == 0) m &= 0x8000u;                                        // lead-in: only the byte right before the tile matters
-    sh.ctrl[p] = (uint16_t)m;
+    if (p == 0) { nl &= 0x8000u; tb = 0; }                           // lead-in: only a newline right before the tile matters
+    if (tile == 0 && p == (uint32_t)(vnPos >> 4)) nl |= 1u << (vnPos & 15);
+    sh.tabM[p] = (uint16_t)tb; sh.nlM[p] = (uint16_t)nl;
   }
+  if (tid < 8) sh.tabM[TK_PIECES + tid] = 0;
   __syncthreads();
-  const int vnPos = 15 + a0;                                         // staged position of the virtual newline before text[0] (tile 0)
-  if (tile == 0 && tid == 0) sh.ctrl[vnPos >> 4] |= (uint16_t)(1u << (vnPos & 15));
-  if (tile == 0) __syncthreads();
 
-  // ---- phase 1b: classify, scan, emit
-  uint32_t tabM[TK_PER_THREAD / 2], nlM[TK_PER_THREAD / 2];          // two 16-bit piece masks per register
-  uint32_t nEv = 0, nNl = 0;
-  { uint4 cm = reinterpret_cast<const uint4*>(sh.ctrl)[tid]; uint32_t c[4] = {cm.x, cm.y, cm.z, cm.w};
-#pragma unroll
-    for (int h = 0; h < 4; h++) {
-      uint32_t m = c[h], tb = 0, nl = 0;
-      while (m) {
-        int bit = __ffs((int)m) - 1; m &= m - 1;
-        int pos = (int)(tid * TK_PER_THREAD + 2 * h) * 16 + bit;     // bit 16.. belongs to the next piece: same formula
-        char ch = sh.stage[pos]; bool forced = tile == 0 && pos == vnPos;
-        if (forced || ch == '\n') nl |= 1u << bit; else if (ch == '\t') tb |= 1u << bit;
-      }
-      tabM[h] = tb; nlM[h] = nl; nEv += __popc(tb | nl); nNl += __popc(nl);
-    } }
-  uint32_t packed = nEv | (nNl << 16), x = packed;
+  // ---- phase 1b: newline positions
+  uint32_t nlm[4]; { uint4 c = reinterpret_cast<const uint4*>(sh.nlM)[tid]; nlm[0] = c.x; nlm[1] = c.y; nlm[2] = c.z; nlm[3] = c.w; }   // pieces 8*tid .. 8*tid+7, two per register
+  uint32_t cnt = __popc(nlm[0]) + __popc(nlm[1]) + __popc(nlm[2]) + __popc(nlm[3]), x = cnt;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= (uint32_t)d) x += y; }
   if (lane == 31) sh.warpTot[warp] = x;
   __syncthreads();
-  uint32_t wbase = 0, tot = 0;
+  uint32_t wbase = 0, totNl = 0;
 #pragma unroll
-  for (int w = 0; w < TK_THREADS / 32; w++) { uint32_t v = sh.warpTot[w]; if (w < (int)warp) wbase += v; tot += v; }
-  uint32_t ex = wbase + x - packed;                                  // exclusive prefix: events (low 16), newlines (high 16)
-  uint32_t e = ex & 0xFFFFu, l = ex >> 16;
-  const uint32_t totEv = tot & 0xFFFFu, totNl = tot >> 16;
+  for (int w = 0; w < TK_THREADS / 32; w++) { uint32_t v = sh.warpTot[w]; if (w < (int)warp) wbase += v; totNl += v; }
+  uint32_t l = wbase + x - cnt;                                      // newlines before this thread's bytes
   // the newline at the tile's last owned byte starts the NEXT tile's first line
-  uint32_t lastBit = __shfl_sync(0xffffffffu, (nlM[3] >> 31) & 1u, (TK_FIRST_OV_THREAD - 1) & 31);
-  const bool fits = totEv <= (uint32_t)TK_EV_CAP && totNl <= (uint32_t)TK_NL_CAP;
+  uint32_t lastBit = __shfl_sync(0xffffffffu, (nlm[3] >> 31) & 1u, (TK_FIRST_OV_THREAD - 1) & 31);
+  const bool fits = totNl <= (uint32_t)TK_NL_CAP;
   unsigned long long* st = status + tile;
   if (tid == TK_FIRST_OV_THREAD) {
-    uint32_t own = l - lastBit; sh.nOwned = own; sh.nEv = totEv; sh.nNl = totNl;
+    uint32_t own = l - lastBit; sh.nOwned = own;
     *(volatile unsigned long long*)st = (tile == 0 ? TK_FLAG_PREFIX : TK_FLAG_AGG) | own;
   }
   if (fits) {
 #pragma unroll
     for (int h = 0; h < 4; h++) {
-      uint32_t m = tabM[h] | nlM[h];
-      while (m) {
-        int bit = __ffs((int)m) - 1; m &= m - 1;
-        uint32_t pos = (tid * TK_PER_THREAD + 2 * h) * 16 + bit, isNl = (nlM[h] >> bit) & 1u;
-        sh.ev[e] = (uint16_t)((pos << 1) | isNl);
-        if (isNl) sh.lineEv[l++] = (uint16_t)e;
-        e++;
-      }
+      uint32_t m = nlm[h];
+      while (m) { int bit = __ffs((int)m) - 1; m &= m - 1; sh.nlPos[l++] = (uint16_t)((tid * TK_PER_THREAD + 2 * h) * 16 + bit); }
     }
   }
   if (tid == TK_FIRST_OV_THREAD) {                                   // decoupled look-back
@@ -183,20 +201,18 @@ k_tokenize_sam(AnnoView A, SamView S, uint32_t capLines, uint32_t nTiles, unsign
   // ---- phase 2: one thread per owned line
   const bool reachesEof = v0 + TK_STAGE >= vEnd;
   for (uint32_t j = tid; j < nOwned; j += TK_THREADS) {
-    uint32_t evi = sh.lineEv[j]; int s = (int)(sh.ev[evi] >> 1) + 1;  // staged position of the line's first byte
+    int s = (int)sh.nlPos[j] + 1;                                    // staged position of the line's first byte
     unsigned long long k = lineBase + j; uint64_t g = (uint64_t)(v0 + s - a0);
     if (k <= capLines) S.lineOff[k] = g;
     if (g >= S.len) continue;                                        // the text's final newline opens no line
-    int n; int evEnd;
-    if (j + 1 < totNl) { evEnd = sh.lineEv[j + 1]; n = (int)(sh.ev[evEnd] >> 1) - s; }
-    else if (reachesEof) { evEnd = (int)totEv; n = (int)(vEnd - v0) - s; if (k + 1 <= capLines) S.lineOff[k + 1] = S.len + 1; }
-    else {                                                           // line runs past the overhang: generic decoder on global memory
+    int n = -1;
+    if (j + 1 < totNl) n = (int)sh.nlPos[j + 1] - s;
+    else if (reachesEof) { n = (int)(vEnd - v0) - s; if (k + 1 <= capLines) S.lineOff[k + 1] = S.len + 1; }
+    if (n < 0) {                                                     // line runs past the overhang: generic decoder on global memory
       uint64_t eg = g; while (eg < S.len && S.text[eg] != '\n') eg++;
       if (k < capLines) decode_record(A, S, (uint32_t)k, S.text + g, (int)(eg - g), err);
       if (eg == S.len && k + 1 <= capLines) S.lineOff[k + 1] = S.len + 1;
-      continue;
-    }
-    if (k < capLines) { EventTabs tabs{sh.ev, (int)evi + 1, evEnd, s}; decode_record_t(A, S, (uint32_t)k, sh.stage + s, n, tabs, err); }
+    } else if (k < capLines) { StageSrc src(sh.tabM, s, n); decode_record_t(A, S, (uint32_t)k, sh.stage + s, n, src, err); }
   }
 }
 

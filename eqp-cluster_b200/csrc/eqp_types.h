@@ -37,7 +37,7 @@ enum {
   DERR_INT = 17            // integer field does not parse
 };
 
-// reference-name dictionary slot: key = (fnv1a(name) & ~0xFFFF) | length, 0 = empty.  One 16-byte load yields everything lookup_ref needs.
+// reference-name dictionary slot: key = (name_hash(name) & ~0xFFFF) | length, 0 = empty.  One 16-byte load yields everything lookup_ref needs.
 struct alignas(16) DictEntry { uint64_t key; int32_t val; uint32_t off; };
 
 struct AnnoView {
