@@ -169,11 +169,18 @@ struct ScanSrc {
   static EQP_HD uint32_t load4(const char* q, int nvalid) { return name_group_bytes(q, nvalid); }
 };
 
+// One decoded line, before it is stored: parsing does not need the line's number, so the tokenizer kernel parses while the
+// line numbering (a chained scan over tiles) is still in flight.
+struct DecodedRec {
+  uint32_t code;                                                        // DERR_* of the first failed check, 0 = fine
+  uint32_t frag; int32_t flag, pos, pnext, ref, rnext; int nm, cigOff, cigLen, seqLen; uint8_t rf;
+};
+
 // One SAM line [p, p+n) (no '\n').  The text may live in shared or global memory.
 template <class Src>
-EQP_HD void decode_record_t(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, Src& src, uint32_t* err) {
+EQP_HD DecodedRec parse_record_t(const AnnoView& A, const char* p, int n, Src& src) {
   if (n > 0 && p[n - 1] == '\r') n--;
-  uint32_t code = DERR_NONE;                                            // first failed check, raised once at the end (single exit)
+  uint32_t code = DERR_NONE;                                            // first failed check (single exit)
   uint32_t frag = 0xFFFFFFFFu; uint8_t rf = 0;
   int32_t flag = 0, pos = 0, pnext = 0, ref = -1, rnext = -1; int nm = -1, cigOff = 0, cigLen = 0, seqLen = 0;
   if (n > 0 && p[0] != '@') {                                           // SamReader.java:173
@@ -252,12 +259,20 @@ EQP_HD void decode_record_t(const AnnoView& A, const SamView& S, uint32_t li, co
       }
     }
   }
-  if (code) { raise(err, code, li); frag = 0xFFFFFFFFu; rf = 0; }
-  S.frag[li] = frag; S.rf[li] = rf;
-  if (rf) {
-    S.flag[li] = (uint16_t)flag; S.ref[li] = ref; S.pos[li] = pos; S.rnext[li] = rnext; S.pnext[li] = pnext;
-    S.nm[li] = (int16_t)nm; S.cigOff[li] = (uint16_t)cigOff; S.cigLen[li] = (uint16_t)cigLen; S.seqLen[li] = (uint16_t)seqLen;
+  if (code) { frag = 0xFFFFFFFFu; rf = 0; }
+  return DecodedRec{code, frag, flag, pos, pnext, ref, rnext, nm, cigOff, cigLen, seqLen, rf};
+}
+EQP_HD void store_record(const SamView& S, uint32_t li, const DecodedRec& r, uint32_t* err) {
+  if (r.code) raise(err, r.code, li);
+  S.frag[li] = r.frag; S.rf[li] = r.rf;
+  if (r.rf) {
+    S.flag[li] = (uint16_t)r.flag; S.ref[li] = r.ref; S.pos[li] = r.pos; S.rnext[li] = r.rnext; S.pnext[li] = r.pnext;
+    S.nm[li] = (int16_t)r.nm; S.cigOff[li] = (uint16_t)r.cigOff; S.cigLen[li] = (uint16_t)r.cigLen; S.seqLen[li] = (uint16_t)r.seqLen;
   }
+}
+template <class Src>
+EQP_HD void decode_record_t(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, Src& src, uint32_t* err) {
+  store_record(S, li, parse_record_t(A, p, n, src), err);
 }
 
 EQP_HD void decode_record(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, uint32_t* err) {

@@ -33,7 +33,7 @@ struct TokShared {
   alignas(16) uint16_t nlM[TK_PIECES];
   uint16_t nlPos[TK_NL_CAP + 2];
   uint32_t warpTot[TK_THREADS / 32];
-  alignas(8) unsigned long long bar;
+  alignas(8) unsigned long long bar, barBase;                        // tile staged / lineBase published
   unsigned long long lineBase;
   uint32_t tile, nNl, nOwned;
 };
@@ -59,18 +59,15 @@ __device__ __forceinline__ uint32_t tk_nibbles16(uint32_t t) {        // t: nibb
 // Source for a line staged in shared memory: tabs from the tile's tab masks, 64 text bytes per 8-byte load; groups from two
 // aligned words and a funnel shift.
 struct StageSrc {
-  const unsigned long long* tabW;                                     // tab masks, one bit per staged byte
-  int s, lim, wi; unsigned long long word;                            // line start / end (staged positions), current mask word
-  __device__ __forceinline__ StageSrc(const uint16_t* tabM, int s_, int n) : tabW(reinterpret_cast<const unsigned long long*>(tabM)), s(s_), lim(s_ + n), wi(s_ >> 6) {
-    word = tabW[wi] & (~0ULL << (s & 63));
+  const uint32_t* tabW;                                               // tab masks, one bit per staged byte, 32 bytes of text per word
+  int s, lim, wi; uint32_t word;                                      // line start / end (staged positions), current mask word
+  __device__ __forceinline__ StageSrc(const uint16_t* tabM, int s_, int n) : tabW(reinterpret_cast<const uint32_t*>(tabM)), s(s_), lim(s_ + n), wi(s_ >> 5) {
+    word = tabW[wi] & (0xFFFFFFFFu << (s & 31));
   }
   __device__ __forceinline__ int next(const char*, int, int n) {
-    int res = n; bool go = true;
-    while (go) {
-      if (word) { int bit = __ffsll((long long)word) - 1; word &= word - 1; int q = (wi << 6) + bit - s; res = q < n ? q : n; go = false; }
-      else if (((wi + 1) << 6) >= lim) go = false;
-      else word = tabW[++wi];
-    }
+    while (!word && ((wi + 1) << 5) < lim) word = tabW[++wi];
+    int res = n;
+    if (word) { int q = (wi << 5) + (__ffs((int)word) - 1) - s; word &= word - 1; res = q < n ? q : n; }
     return res;
   }
   static __device__ __forceinline__ uint32_t load4(const char* q, int nvalid) {
@@ -112,6 +109,7 @@ k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamVi
   if (tid == 0) {
     sh.tile = atomicAdd(ticket, 1u);
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tk_smem_addr(&sh.bar)));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tk_smem_addr(&sh.barBase)));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -180,39 +178,60 @@ k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamVi
       while (m) { int bit = __ffs((int)m) - 1; m &= m - 1; sh.nlPos[l++] = (uint16_t)((tid * TK_PER_THREAD + 2 * h) * 16 + bit); }
     }
   }
-  if (tid == TK_FIRST_OV_THREAD) {                                   // decoupled look-back
+  __syncthreads();                                                   // nlPos[], nOwned complete
+  const uint32_t nOwned = sh.nOwned;
+  // Decoupled look-back by the last warp, 32 predecessors per step; the other warps already parse their lines and only wait
+  // (on an mbarrier) for the tile's first line number when they are about to store.
+  if (warp == TK_THREADS / 32 - 1) {
     unsigned long long sum = 0;
     if (tile) {
-      for (uint32_t i = tile; i-- > 0;) {
-        unsigned long long v;
-        do { v = *(volatile unsigned long long*)(status + i); } while (!(v >> 62));
-        sum += v & TK_VALUE_MASK;
-        if ((v >> 62) == 2) break;
+      long long i = (long long)tile - 1;
+      while (true) {
+        long long idx = i - lane; unsigned long long v = TK_FLAG_PREFIX;                    // in front of tile 0: prefix 0
+        if (idx >= 0) do { v = *(volatile unsigned long long*)(status + idx); } while (!(v >> 62));
+        uint32_t pm = __ballot_sync(0xffffffffu, (v >> 62) == 2);
+        uint32_t firstP = pm ? (uint32_t)(__ffs((int)pm) - 1) : 32u;
+        uint32_t c = lane <= firstP ? (uint32_t)(v & TK_VALUE_MASK) : 0u;
+        sum += __reduce_add_sync(0xffffffffu, c);
+        if (pm) break;
+        i -= 32;
       }
-      *(volatile unsigned long long*)st = TK_FLAG_PREFIX | (sum + sh.nOwned);
+      if (lane == 0) *(volatile unsigned long long*)st = TK_FLAG_PREFIX | (sum + nOwned);
     }
-    sh.lineBase = sum;
-    if (tile == nTiles - 1) *nlTotal = sum + sh.nOwned;
+    if (lane == 0) {
+      sh.lineBase = sum;
+      if (tile == nTiles - 1) *nlTotal = sum + nOwned;
+      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tk_smem_addr(&sh.barBase)) : "memory");
+    }
   }
-  __syncthreads();
-  const unsigned long long lineBase = sh.lineBase; const uint32_t nOwned = sh.nOwned;
-  if (!fits) { if (tid == 0) tk_slow_tile(A, S, capLines, vb, a0, lineBase, tile == 0, err); return; }
+  auto line_base = [&]() -> unsigned long long {                     // blocks until the look-back has finished
+    uint32_t done = 0, bar = tk_smem_addr(&sh.barBase);
+    while (!done) asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar) : "memory");
+    return *(volatile unsigned long long*)&sh.lineBase;
+  };
+  if (!fits) { if (tid == 0) tk_slow_tile(A, S, capLines, vb, a0, line_base(), tile == 0, err); return; }
 
   // ---- phase 2: one thread per owned line
   const bool reachesEof = v0 + TK_STAGE >= vEnd;
   for (uint32_t j = tid; j < nOwned; j += TK_THREADS) {
     int s = (int)sh.nlPos[j] + 1;                                    // staged position of the line's first byte
-    unsigned long long k = lineBase + j; uint64_t g = (uint64_t)(v0 + s - a0);
+    uint64_t g = (uint64_t)(v0 + s - a0);
+    int n = -1; bool eofLine = false;
+    if (j + 1 < totNl) n = (int)sh.nlPos[j + 1] - s;
+    else if (reachesEof) { n = (int)(vEnd - v0) - s; eofLine = true; }
+    DecodedRec rec{}; bool parsed = false;
+    if (g < S.len && n >= 0) { StageSrc src(sh.tabM, s, n); rec = parse_record_t(A, sh.stage + s, n, src); parsed = true; }
+    unsigned long long k = line_base() + j;
     if (k <= capLines) S.lineOff[k] = g;
     if (g >= S.len) continue;                                        // the text's final newline opens no line
-    int n = -1;
-    if (j + 1 < totNl) n = (int)sh.nlPos[j + 1] - s;
-    else if (reachesEof) { n = (int)(vEnd - v0) - s; if (k + 1 <= capLines) S.lineOff[k + 1] = S.len + 1; }
-    if (n < 0) {                                                     // line runs past the overhang: generic decoder on global memory
+    if (parsed) {
+      if (k < capLines) store_record(S, (uint32_t)k, rec, err);
+      if (eofLine && k + 1 <= capLines) S.lineOff[k + 1] = S.len + 1;
+    } else {                                                         // line runs past the overhang: generic decoder on global memory
       uint64_t eg = g; while (eg < S.len && S.text[eg] != '\n') eg++;
       if (k < capLines) decode_record(A, S, (uint32_t)k, S.text + g, (int)(eg - g), err);
       if (eg == S.len && k + 1 <= capLines) S.lineOff[k + 1] = S.len + 1;
-    } else if (k < capLines) { StageSrc src(sh.tabM, s, n); decode_record_t(A, S, (uint32_t)k, sh.stage + s, n, src, err); }
+    }
   }
 }
 
