@@ -81,6 +81,7 @@ def build_tools(force=False):
     emu_src = os.path.join(ROOT, "tests", "emu", "eqp_emu.cpp")
     if force or _newer(_glob(CSRC, (".h", ".hpp")) + [emu_src], EMU_BIN):
         _run(["g++", "-std=c++17", "-O2", "-o", EMU_BIN, emu_src, "-lz"])
+        _run(["g++", "-std=c++17", "-O2", "-DEQP_FLAT_SCAN=0", "-o", EMU_BIN + "_chain", emu_src, "-lz"])   # duplicate-chain walk for every fragment
     return WORLDGEN_BIN, EMU_BIN
 
 

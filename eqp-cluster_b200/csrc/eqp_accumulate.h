@@ -122,6 +122,15 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
     } else V.alnTail[a] = a;
     if (al.repr == a) { if ((al.flags & 6) == 4) right++; else left++; }   // ":r-" forms (WeightObject.java:859-865)
   }
+  // tag every hit with its representative (index within the fragment) and with the representative's half it merges into
+  // (combineExons pairs mate-swapped duplicates crosswise, WeightObjectAlignment.java:312-337): a22-a25 then read the
+  // fragment's hits as one flat range instead of walking duplicate chains
+  if (nA > 0xFFFFu) { raise(C.err, DERR_CAPACITY, C.base + slot); return; }
+  for (uint32_t a = a0; a < a1; a++) {
+    const Aln& al = V.alns[a]; if (al.hit0 == al.hit1) continue;
+    bool sw = al.repr != a && (al.flags & 32); uint16_t g = (uint16_t)(al.repr - a0);
+    for (uint32_t i = al.hit0; i < al.hit1; i++) { HitX& x = V.hx[i]; x.grp = g; if (sw) x.half = (uint8_t)(3 - x.half); }
+  }
   uint32_t a20 = (uint32_t)(left > right ? left : right);
   V.a20[slot] = a20;
   // final.wgt entry: BED weight (single-read, read index 1, n = a20) vs genome SAM weight, T+J entry as class arbiter
@@ -138,6 +147,9 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
 
 // ---- stage C: conforming features + accumulation for one run (mode)
 #define EQP_FS_CAP 160
+#ifndef EQP_FLAT_SCAN
+#define EQP_FLAT_SCAN 192              // hits of a fragment scanned flat per (representative, half, interval); beyond that the chain is walked
+#endif
 #define EQP_FT_CAP 320
 struct FeatSet { uint32_t id[EQP_FS_CAP]; uint32_t mask[EQP_FS_CAP]; int n; };
 EQP_HD bool fs_add(FeatSet& s, uint32_t id, uint32_t bit) {
@@ -146,31 +158,36 @@ EQP_HD bool fs_add(FeatSet& s, uint32_t id, uint32_t bit) {
   s.id[s.n] = id; s.mask[s.n] = bit; s.n++; return true;
 }
 
-// features of half `h` of representative alignment R (index r) with all merged duplicates folded in
-EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t a0, uint32_t a1, uint32_t r, int h,
+// features of half `h` of representative alignment R (index r) with all merged duplicates folded in.
+// The duplicates' hits follow R's in the fragment's hit range [.., hEnd) and carry (grp, half) of the representative half they
+// merge into, so "R first, then later duplicates in file order" is one forward scan with independent, mostly contiguous loads.
+EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t a0, uint32_t hEnd, uint32_t r, int h,
                           FeatSet& out, uint32_t frag) {
   const Aln& R = V.alns[r]; out.n = 0;
   int nIv = h == 1 ? R.nIv1 : R.nIv2; int maxField = h == 1 ? R.maxField1 : R.maxField2;
-  uint32_t r0 = h == 1 ? R.hit0 : R.split, r1 = h == 1 ? R.split : R.hit1;
+  uint32_t r0 = h == 1 ? R.hit0 : R.split; const uint16_t grp = (uint16_t)(r - a0);
   if (maxField >= 32) { raise(C.err, DERR_CAPACITY, frag); return; }
   FeatSet fs; fs.n = 0;
   for (int iv = 0; iv < nIv; iv++) {
-    int32_t chr, gs, ge; int field; half_interval(V, r0, r1, iv, chr, gs, ge, field);
-    int32_t exon[32]; uint8_t exGen[32]; int ne = 0;
-    for (uint32_t d = r; d != 0xFFFFFFFFu; d = V.alns[d].next) {          // R first, then later duplicates in file order
-      const Aln& D = V.alns[d];
-      int hd = (d != r && (D.flags & 32)) ? 3 - h : h;
-      uint32_t d0 = hd == 1 ? D.hit0 : D.split, d1 = hd == 1 ? D.split : D.hit1;
-      for (uint32_t i = d0; i < d1; i++) {
-        const HitX& x = V.hx[i];
-        if (!(x.flags & 1) || x.ivRank != iv || !(x.flags & (4 << mode))) continue;
-        int ex = A.rowExon[C.hits[i].row]; bool have = false;
-        for (int q = 0; q < ne; q++) if (exon[q] == ex) { have = true; break; }
-        if (have) continue;
-        if (ne >= 32) { raise(C.err, DERR_CAPACITY, frag); return; }
-        exon[ne] = ex; exGen[ne] = (x.flags & 2) ? 1 : 0; ne++;
+    int32_t gs = 0, ge = 0; int field = 0; bool haveIv = false;
+    int32_t exon[32]; uint8_t exGen[32]; int ne = 0; bool over = false;
+    auto visit = [&](const HitX& x) {
+      if (!haveIv) { gs = x.gs; ge = x.ge; field = x.ivField; haveIv = true; }   // R's own first record of the interval
+      if (x.flags & (4 << mode)) {
+        int ex = x.exon; bool have = false;
+        for (int q = 0; q < ne; q++) have |= exon[q] == ex;
+        if (!have) { if (ne >= 32) over = true; else { exon[ne] = ex; exGen[ne] = (x.flags & 2) ? 1 : 0; ne++; } }
+      }
+    };
+    if (hEnd - r0 <= EQP_FLAT_SCAN) {
+      for (uint32_t i = r0; i < hEnd; i++) { const HitX& x = V.hx[i]; if (x.grp == grp && x.half == h && (x.flags & 1) && x.ivRank == iv) visit(x); }
+    } else {                                                               // many alignments: walk the duplicate chain instead of the whole fragment
+      for (uint32_t d = r; d != 0xFFFFFFFFu; d = V.alns[d].next) {
+        const Aln& D = V.alns[d];
+        for (uint32_t i = D.hit0; i < D.hit1; i++) { const HitX& x = V.hx[i]; if (x.half == h && (x.flags & 1) && x.ivRank == iv) visit(x); }
       }
     }
+    if (over) { raise(C.err, DERR_CAPACITY, frag); return; }
     if (ne > 1) {                                                          // updateExonSet: keep max-overlap non-genomic exons
       int maxOv = 0;
       for (int q = 0; q < ne; q++) if (!exGen[q]) { int e = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = e - gs + 1; if (ov < 0) ov = 0; if (ov > maxOv) maxOv = ov; }
@@ -209,6 +226,7 @@ EQP_HD void fragment_count(const AnnoView& A, const ChunkView& C, const CountVie
   uint32_t a20 = V.a20[slot];
   if (a20 == 0) return;
   uint32_t frag = C.base + slot; uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1];
+  const uint32_t hEnd = C.hitCnt[C.blkOff[slot + 1]];                    // end of the fragment's hit range
   atomic_add_u64(&V.stats[mode * 3 + 0], 1);
   double w = 1.0 / (double)V.nFinal[slot];
   if (w > 1.0 / (double)a20) w = 1.0 / (double)a20;                      // ComputeCounts.java:762-764
@@ -219,8 +237,8 @@ EQP_HD void fragment_count(const AnnoView& A, const ChunkView& C, const CountVie
   for (uint32_t r = a0; r < a1; r++) {
     const Aln& R = V.alns[r]; if (R.hit0 == R.hit1 || R.repr != r) continue;
     s1.n = s2.n = 0;
-    if (R.flags & 2) half_features(A, C, V, P, mode, a0, a1, r, 1, s1, frag);
-    if (R.flags & 4) half_features(A, C, V, P, mode, a0, a1, r, 2, s2, frag);
+    if (R.flags & 2) half_features(A, C, V, P, mode, a0, hEnd, r, 1, s1, frag);
+    if (R.flags & 4) half_features(A, C, V, P, mode, a0, hEnd, r, 2, s2, frag);
     if (R.flags & 1) {                                                     // paired: gene run intersects, others unite (:325-335)
       if (mode == MODE_GENE) { int wn = 0; for (int i = 0; i < s1.n; i++) { bool in2 = false; for (int j = 0; j < s2.n; j++) if (s2.id[j] == s1.id[i]) { in2 = true; break; } if (in2) s1.id[wn++] = s1.id[i]; } s1.n = wn; }
       else for (int j = 0; j < s2.n; j++) { bool in1 = false; for (int i = 0; i < s1.n; i++) if (s1.id[i] == s2.id[j]) { in1 = true; break; } if (!in1) { if (s1.n >= EQP_FS_CAP) { raise(C.err, DERR_CAPACITY, frag); return; } s1.id[s1.n++] = s2.id[j]; } }

@@ -53,7 +53,7 @@ EQP_HD void build_half(const AnnoView& A, const ChunkView& C, const CountView& V
   for (uint32_t k = h0; k < h1; k++) {
     bool dup = false;
     if (k > h0) { RecKey a = rec_key(A, C, C.hits[k - 1]), b = rec_key(A, C, C.hits[k]); dup = rec_cmp(a, b) == 0; }
-    V.hx[k].flags = dup ? 0 : 1; V.hx[k].half = (uint8_t)half; V.hx[k].pad = 0;
+    V.hx[k].flags = dup ? 0 : 1; V.hx[k].half = (uint8_t)half; V.hx[k].grp = 0;
     if (!dup) n++;
   }
   const Block& b0 = C.blocks[C.hits[h0].block];
@@ -116,7 +116,7 @@ EQP_HD void build_half(const AnnoView& A, const ChunkView& C, const CountView& V
       int thr = P.overlap[m] < (exE - exS + 1) ? P.overlap[m] : (exE - exS + 1);
       if (c && h.overlap >= thr) conf |= (uint8_t)(4 << m);              // GenomicInterval.java:144
     }
-    x.gs = gs; x.ge = ge; x.chr = A.exChr[ex]; x.ivField = (int16_t)fieldIdx; x.exonLen = exE - exS + 1;
+    x.gs = gs; x.ge = ge; x.chr = A.exChr[ex]; x.ivField = (int16_t)fieldIdx; x.exon = ex;
     x.flags = (uint8_t)(1 | (genomic ? 2 : 0) | conf | (ivStrand == '-' ? 32 : 0));
     prevBlk = &b; prevExon = ex;
   }

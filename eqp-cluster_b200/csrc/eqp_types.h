@@ -98,9 +98,9 @@ struct HitX {                      // per hit, after the per-alignment sort/dedu
   int32_t chr;                     // chromosome index of the exon
   int16_t ivField;                 // field index of the (kept) interval this record belongs to
   uint16_t ivRank;                 // rank of that interval among the distinct intervals of its half
-  int32_t exonLen;
+  int32_t exon;                    // distinct-exon id of the hit's annotation row
   uint8_t flags;                   // bit0 valid, bit1 genomic row, bits2-4 conforming in gene/exon/junction run, bit5 interval strand '-'
-  uint8_t half; uint16_t pad;      // half: 1 or 2 (read index)
+  uint8_t half; uint16_t grp;      // half: 1 or 2 (read index; after a19 the half of the REPRESENTATIVE it merges into); grp: representative's index within the fragment
 };
 
 struct Aln {                       // one WeightObjectAlignment (a15-a19), 48 bytes

@@ -65,12 +65,12 @@ class World:
             run([self.tools["oracle"], "run", self.anno, c["dir"], c["layout"], o, "--quiet"] + list(flags))
         return o
 
-    def emu_run(self, name, flags=()):
+    def emu_run(self, name, flags=(), variant=""):
         """TEST-ONLY host emulation of the device functions (tests/emu): id -> value per mode + stats."""
         c = self.chunks[name]
-        o = os.path.join(c["dir"], "emu" + "".join(flags).replace("--", "_"))
+        o = os.path.join(c["dir"], "emu" + variant + "".join(flags).replace("--", "_"))
         os.makedirs(o, exist_ok=True)
-        run([self.tools["emu"], self.anno, c["dir"], "pe" if c["layout"] == "pe" else "se", o] + list(flags))
+        run([self.tools["emu"] + variant, self.anno, c["dir"], "pe" if c["layout"] == "pe" else "se", o] + list(flags))
         out = {}
         for m in ("gene", "exon", "junction"):
             out[m] = {}

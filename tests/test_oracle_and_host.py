@@ -53,6 +53,16 @@ def test_device_functions_match_oracle(world, name, seed, layout, spliced):
         assert_counts_match(got, want, what="%s %s" % (name, m))
 
 
+def test_duplicate_chain_walk_matches_oracle(world):
+    """a22-a25 read a fragment's hits flat up to EQP_FLAT_SCAN hits and walk the duplicate chains beyond: the chain path alone."""
+    c = world.chunk("pe_small", 1003, 1, 3000, "pe")
+    emu = world.emu_run("pe_small", variant="_chain")
+    for m in ("gene", "exon", "junction"):
+        want = read_cnt(os.path.join(c["oracle"], m + ".cnt"))
+        got = emu[m] if m == "junction" else {k: emu[m].get(k, 0.0) for k in want}
+        assert_counts_match(got, want, what="chain %s" % m)
+
+
 @pytest.mark.parametrize("flags", [("--unweighted",), ("--unambig",), ("--containment", "--nonsplice")])
 def test_device_functions_switches(world, flags):
     world.chunk("pe_small", 1003, 1, 3000, "pe")
