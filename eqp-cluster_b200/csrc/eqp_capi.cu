@@ -251,9 +251,9 @@ int eqp_debug_decode(eqp_ctx* ctx, const uint8_t* sam, size_t len, int misalign,
     CudaBackend be(ctx->stream, ctx->nSm);
     char* d = be.alloc<char>(len + 64); d += (16 - ((uintptr_t)d & 15)) % 16 + misalign;
     if (len) EQP_CUDA(cudaMemcpyAsync(d, sam, len, cudaMemcpyHostToDevice, ctx->stream));
-    uint32_t* err = be.alloc<uint32_t>(2); be.memset(err, 0, 8);
+    uint32_t* err = be.alloc<uint32_t>(4); be.memset(err, 0, 16);
     SamView S{}; uint8_t* proc = nullptr;
-    be.decode_fused(ctx->A, S, proc, d, len, err);
+    be.decode_fused(ctx->A, S, proc, d, len, err, err + 2);
     uint32_t h[2]; be.to_host(h, err, 8); *errCode = h[0]; *errDetail = h[1];
     size_t n = S.nLines;
     std::vector<uint64_t> lo(n + 1); std::vector<uint32_t> frag(n); std::vector<int32_t> ref(n), pos(n), pnext(n); std::vector<uint16_t> flag(n), co(n), cl(n), sl(n); std::vector<int16_t> nm(n); std::vector<uint8_t> rf(n);

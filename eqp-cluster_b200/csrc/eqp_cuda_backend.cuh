@@ -267,7 +267,7 @@ struct CudaBackend {
     S.flag = alloc<uint16_t>(cap); S.nm = alloc<int16_t>(cap); S.cigOff = alloc<uint16_t>(cap); S.cigLen = alloc<uint16_t>(cap); S.seqLen = alloc<uint16_t>(cap);
     S.rf = alloc<uint8_t>(cap); proc = alloc<uint8_t>(cap);
   }
-  void decode_fused(const AnnoView& A, SamView& S, uint8_t*& proc, const char* text, uint64_t len, uint32_t* err) {
+  void decode_fused(const AnnoView& A, SamView& S, uint8_t*& proc, const char* text, uint64_t len, uint32_t* err, uint32_t* fragMinMax) {
     S.text = text; S.len = len; S.nLines = 0;
     if (!len) { alloc_records(S, proc, 1); return; }
     static bool attr = false;
@@ -282,7 +282,7 @@ struct CudaBackend {
       memset(status, 0, (nTiles + 2) * 8);
       cudaEvent_t e0, e1; EQP_CUDA(cudaEventCreate(&e0)); EQP_CUDA(cudaEventCreate(&e1)); decEv.push_back({e0, e1});
       EQP_CUDA(cudaEventRecord(e0, stream));
-      k_tokenize_sam<<<(unsigned)nTiles, TK_THREADS, sizeof(TokShared), stream>>>(A, S, (uint32_t)cap, (uint32_t)nTiles, status, (uint32_t*)(status + nTiles + 1), status + nTiles, err); launches++;
+      k_tokenize_sam<<<(unsigned)nTiles, TK_THREADS, sizeof(TokShared), stream>>>(A, S, (uint32_t)cap, (uint32_t)nTiles, status, (uint32_t*)(status + nTiles + 1), status + nTiles, err, fragMinMax); launches++;
       EQP_CUDA(cudaGetLastError());
       EQP_CUDA(cudaEventRecord(e1, stream));
       unsigned long long tot = 0; to_host(&tot, status + nTiles, 8);

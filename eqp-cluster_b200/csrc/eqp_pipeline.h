@@ -71,18 +71,19 @@ struct Pipeline {
     scal = be.template alloc<uint32_t>(32); be.memset(scal, 0, 32 * sizeof(uint32_t));
     C.err = scal;
     const AnnoView A = this->A; const RunParams P = this->P;
-    // ---- a1/a2: line index + decode
+    // ---- a1/a2: line index + decode (+ the fragment id range of each input)
+    { uint32_t init[6] = {0xFFFFFFFFu, 0, 0xFFFFFFFFu, 0, 0xFFFFFFFFu, 0}; be.to_device(scal + 2, init, sizeof init); }
     for (int f = 0; f < 3; f++) {
-      if (BE::kFusedDecode) be.decode_fused(A, C.sam[f], C.proc[f], text[f], len[f], scal);   // one pass: line index + records
-      else { index_lines(f, text[f], len[f]); be.stage("line-index"); be.decode(A, C.sam[f], scal); }
+      uint32_t* mm = scal + 2 + 2 * f;
+      if (BE::kFusedDecode) be.decode_fused(A, C.sam[f], C.proc[f], text[f], len[f], scal, mm);   // one pass: line index + records + id range
+      else {
+        index_lines(f, text[f], len[f]); be.stage("line-index"); be.decode(A, C.sam[f], scal);
+        const SamView S = C.sam[f];
+        be.launch(S.nLines, [=] EQP_LAMBDA(uint64_t i) { if (S.rf[i] & RF_REC) { atomic_min_u32(mm, S.frag[i]); atomic_max_u32(mm + 1, S.frag[i]); } });
+      }
       be.stage("decode");
-      const SamView S = C.sam[f];                          // per-line decode_line(); CUDA backend uses the tiled shared-memory kernel
-      R.nRecords[f] = S.nLines;
+      R.nRecords[f] = C.sam[f].nLines;
     }
-    // fragment id range
-    { uint32_t init[6] = {0xFFFFFFFFu, 0, 0xFFFFFFFFu, 0, 0xFFFFFFFFu, 0}; be.to_device(scal + 2, init, sizeof init);
-      for (int f = 0; f < 3; f++) { const SamView S = C.sam[f]; uint32_t* mm = scal + 2 + 2 * f;
-        be.launch(S.nLines, [=] EQP_LAMBDA(uint64_t i) { if (S.rf[i] & RF_REC) { atomic_min_u32(mm, S.frag[i]); atomic_max_u32(mm + 1, S.frag[i]); } }); } }
     uint32_t h[8]; be.to_host(h, scal, sizeof h);
     if (h[0]) { R.err[0] = h[0]; R.err[1] = h[1]; return -1; }
     uint32_t lo = 0xFFFFFFFFu, hi = 0; bool anyRec = false;
@@ -204,9 +205,9 @@ struct Pipeline {
       be.stage("alignment-build");
       be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
       be.stage("fragment-weight");
-      be.fork();
-      for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) { be.branch(m); be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_count(A, C, V, P, m, perm[i]); }); }
-      be.join(); }
+      // the three counting runs of one fragment back to back in one thread: runs two and three find the fragment's alignments and
+      // hits in cache instead of paying the DRAM latency chain again (the runs were latency-bound as three concurrent kernels)
+      be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { uint32_t s = perm[i]; for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) fragment_count(A, C, V, P, m, s); }); }
     be.stage("fragment-count x3");
     // ---- results
     be.to_host(R.err, scal, 8);

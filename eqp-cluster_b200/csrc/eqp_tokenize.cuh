@@ -80,7 +80,7 @@ struct StageSrc {
 };
 
 // Serial slow path of a whole tile (thread 0): same outputs as the fast path, parsed from global memory.
-__device__ __noinline__ void tk_slow_tile(const AnnoView& A, const SamView& S, uint32_t capLines, long long vb, int a0, unsigned long long lineBase, bool firstTile, uint32_t* err) {
+__device__ __noinline__ void tk_slow_tile(const AnnoView& A, const SamView& S, uint32_t capLines, long long vb, int a0, unsigned long long lineBase, bool firstTile, uint32_t* err, uint32_t* fragMinMax) {
   unsigned long long k = lineBase;
   for (long long v = vb - 1; v < vb + TK_OWNED - 1; v++) {
     long long g = v - a0;
@@ -90,7 +90,7 @@ __device__ __noinline__ void tk_slow_tile(const AnnoView& A, const SamView& S, u
     if (k <= capLines) S.lineOff[k] = st;
     if (st < S.len) {
       uint64_t e = st; while (e < S.len && S.text[e] != '\n') e++;
-      if (k < capLines) decode_record(A, S, (uint32_t)k, S.text + st, (int)(e - st), err);
+      if (k < capLines) { decode_record(A, S, (uint32_t)k, S.text + st, (int)(e - st), err); if (S.rf[k] & RF_REC) { atomicMin(fragMinMax, S.frag[k]); atomicMax(fragMinMax + 1, S.frag[k]); } }
       if (e == S.len && k + 1 <= capLines) S.lineOff[k + 1] = S.len + 1;
     }
     k++;
@@ -98,7 +98,7 @@ __device__ __noinline__ void tk_slow_tile(const AnnoView& A, const SamView& S, u
 }
 
 __global__ void __launch_bounds__(TK_THREADS, 4)
-k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamView S, uint32_t capLines, uint32_t nTiles, unsigned long long* status, uint32_t* ticket, unsigned long long* nlTotal, uint32_t* err) {
+k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamView S, uint32_t capLines, uint32_t nTiles, unsigned long long* status, uint32_t* ticket, unsigned long long* nlTotal, uint32_t* err, uint32_t* fragMinMax) {
   extern __shared__ __align__(128) unsigned char tk_raw[];
   TokShared& sh = *reinterpret_cast<TokShared*>(tk_raw);
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -209,10 +209,11 @@ k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamVi
     while (!done) asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar) : "memory");
     return *(volatile unsigned long long*)&sh.lineBase;
   };
-  if (!fits) { if (tid == 0) tk_slow_tile(A, S, capLines, vb, a0, line_base(), tile == 0, err); return; }
+  if (!fits) { if (tid == 0) tk_slow_tile(A, S, capLines, vb, a0, line_base(), tile == 0, err, fragMinMax); return; }
 
   // ---- phase 2: one thread per owned line
   const bool reachesEof = v0 + TK_STAGE >= vEnd;
+  uint32_t fmin = 0xFFFFFFFFu, fmax = 0;                             // fragment id range of this thread's records
   for (uint32_t j = tid; j < nOwned; j += TK_THREADS) {
     int s = (int)sh.nlPos[j] + 1;                                    // staged position of the line's first byte
     uint64_t g = (uint64_t)(v0 + s - a0);
@@ -226,13 +227,16 @@ k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamVi
     if (g >= S.len) continue;                                        // the text's final newline opens no line
     if (parsed) {
       if (k < capLines) store_record(S, (uint32_t)k, rec, err);
+      if (rec.rf & RF_REC) { fmin = min(fmin, rec.frag); fmax = max(fmax, rec.frag); }
       if (eofLine && k + 1 <= capLines) S.lineOff[k + 1] = S.len + 1;
     } else {                                                         // line runs past the overhang: generic decoder on global memory
       uint64_t eg = g; while (eg < S.len && S.text[eg] != '\n') eg++;
-      if (k < capLines) decode_record(A, S, (uint32_t)k, S.text + g, (int)(eg - g), err);
+      if (k < capLines) { decode_record(A, S, (uint32_t)k, S.text + g, (int)(eg - g), err); if (S.rf[k] & RF_REC) { fmin = min(fmin, S.frag[k]); fmax = max(fmax, S.frag[k]); } }
       if (eg == S.len && k + 1 <= capLines) S.lineOff[k + 1] = S.len + 1;
     }
   }
+  fmin = __reduce_min_sync(0xffffffffu, fmin); fmax = __reduce_max_sync(0xffffffffu, fmax);
+  if (lane == 0 && fmin <= fmax) { atomicMin(fragMinMax, fmin); atomicMax(fragMinMax + 1, fmax); }
 }
 
 }  // namespace eqpb

@@ -30,7 +30,7 @@ struct HostBackend {
   }
   void stage(const char*) {}
   static const bool kFusedDecode = false;
-  void decode_fused(const AnnoView&, SamView&, uint8_t*&, const char*, uint64_t, uint32_t*) {}
+  void decode_fused(const AnnoView&, SamView&, uint8_t*&, const char*, uint64_t, uint32_t*, uint32_t*) {}
   void fork() {}
   void branch(int) {}
   void join() {}
