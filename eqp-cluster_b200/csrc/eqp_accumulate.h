@@ -10,6 +10,9 @@
 namespace eqpb {
 
 #define EQP_FIXED_SHIFT_D 38
+#ifndef EQP_FLAT_SCAN
+#define EQP_FLAT_SCAN 64               // fragments with up to this many hits are regrouped (fragment_weight) and streamed by the counting runs; larger ones walk the duplicate chains
+#endif
 EQP_HD int eqp_popc(uint32_t m) {
 #if defined(__CUDA_ARCH__)
   return __popc(m);
@@ -91,6 +94,8 @@ EQP_HD bool keys_equal(const CountView& V, const Aln& a, const Aln& b, bool& swa
   return halves_equal(V, a, h, b, h);
 }
 
+EQP_HD uint64_t hit_group_key(const HitX& x) { return ((uint64_t)((x.flags & 1) ? 0 : 1) << 40) | ((uint64_t)x.grp << 24) | ((uint64_t)x.half << 16) | x.ivRank; }
+
 // ---- stage B: dedupe, a20, final weight
 EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, uint32_t slot) {
   uint32_t b0 = C.blkOff[slot], b1 = C.blkOff[slot + 1];
@@ -131,6 +136,16 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
     bool sw = al.repr != a && (al.flags & 32); uint16_t g = (uint16_t)(al.repr - a0);
     for (uint32_t i = al.hit0; i < al.hit1; i++) { HitX& x = V.hx[i]; x.grp = g; if (sw) x.half = (uint8_t)(3 - x.half); }
   }
+  // small fragments: regroup the hits by (representative, half, interval), stable, dropped duplicates last: the counting runs
+  // then stream each fragment's hits once.  (hx is only indexed through Aln.hit0.. before this point; large fragments keep
+  // their order and walk the duplicate chains.)
+  { uint32_t h0 = C.hitCnt[b0], h1 = C.hitCnt[b1];
+    if (h1 - h0 <= EQP_FLAT_SCAN)
+      for (uint32_t i = h0 + 1; i < h1; i++) {
+        HitX cur = V.hx[i]; uint64_t ck = hit_group_key(cur); uint32_t j = i;
+        while (j > h0 && hit_group_key(V.hx[j - 1]) > ck) { V.hx[j] = V.hx[j - 1]; j--; }
+        if (j != i) V.hx[j] = cur;
+      } }
   uint32_t a20 = (uint32_t)(left > right ? left : right);
   V.a20[slot] = a20;
   // final.wgt entry: BED weight (single-read, read index 1, n = a20) vs genome SAM weight, T+J entry as class arbiter
@@ -147,9 +162,6 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
 
 // ---- stage C: conforming features + accumulation for one run (mode)
 #define EQP_FS_CAP 160
-#ifndef EQP_FLAT_SCAN
-#define EQP_FLAT_SCAN 192              // hits of a fragment scanned flat per (representative, half, interval); beyond that the chain is walked
-#endif
 #define EQP_FT_CAP 320
 struct FeatSet { uint32_t id[EQP_FS_CAP]; uint32_t mask[EQP_FS_CAP]; int n; };
 EQP_HD bool fs_add(FeatSet& s, uint32_t id, uint32_t bit) {
@@ -158,53 +170,38 @@ EQP_HD bool fs_add(FeatSet& s, uint32_t id, uint32_t bit) {
   s.id[s.n] = id; s.mask[s.n] = bit; s.n++; return true;
 }
 
-// features of half `h` of representative alignment R (index r) with all merged duplicates folded in.
-// The duplicates' hits follow R's in the fragment's hit range [.., hEnd) and carry (grp, half) of the representative half they
-// merge into, so "R first, then later duplicates in file order" is one forward scan with independent, mostly contiguous loads.
-EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t a0, uint32_t hEnd, uint32_t r, int h,
-                          FeatSet& out, uint32_t frag) {
-  const Aln& R = V.alns[r]; out.n = 0;
-  int nIv = h == 1 ? R.nIv1 : R.nIv2; int maxField = h == 1 ? R.maxField1 : R.maxField2;
-  uint32_t r0 = h == 1 ? R.hit0 : R.split; const uint16_t grp = (uint16_t)(r - a0);
-  if (maxField >= 32) { raise(C.err, DERR_CAPACITY, frag); return; }
-  FeatSet fs; fs.n = 0;
-  for (int iv = 0; iv < nIv; iv++) {
-    int32_t gs = 0, ge = 0; int field = 0; bool haveIv = false;
-    int32_t exon[32]; uint8_t exGen[32]; int ne = 0; bool over = false;
-    auto visit = [&](const HitX& x) {
-      if (!haveIv) { gs = x.gs; ge = x.ge; field = x.ivField; haveIv = true; }   // R's own first record of the interval
-      if (x.flags & (4 << mode)) {
-        int ex = x.exon; bool have = false;
-        for (int q = 0; q < ne; q++) have |= exon[q] == ex;
-        if (!have) { if (ne >= 32) over = true; else { exon[ne] = ex; exGen[ne] = (x.flags & 2) ? 1 : 0; ne++; } }
-      }
-    };
-    if (hEnd - r0 <= EQP_FLAT_SCAN) {
-      for (uint32_t i = r0; i < hEnd; i++) { const HitX& x = V.hx[i]; if (x.grp == grp && x.half == h && (x.flags & 1) && x.ivRank == iv) visit(x); }
-    } else {                                                               // many alignments: walk the duplicate chain instead of the whole fragment
-      for (uint32_t d = r; d != 0xFFFFFFFFu; d = V.alns[d].next) {
-        const Aln& D = V.alns[d];
-        for (uint32_t i = D.hit0; i < D.hit1; i++) { const HitX& x = V.hx[i]; if (x.half == h && (x.flags & 1) && x.ivRank == iv) visit(x); }
-      }
-    }
-    if (over) { raise(C.err, DERR_CAPACITY, frag); return; }
-    if (ne > 1) {                                                          // updateExonSet: keep max-overlap non-genomic exons
-      int maxOv = 0;
-      for (int q = 0; q < ne; q++) if (!exGen[q]) { int e = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = e - gs + 1; if (ov < 0) ov = 0; if (ov > maxOv) maxOv = ov; }
-      if (maxOv > 0) { int w = 0; for (int q = 0; q < ne; q++) { int e = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = e - gs + 1; if (ov < 0) ov = 0; if (exGen[q] || ov >= maxOv) { exon[w] = exon[q]; exGen[w] = exGen[q]; w++; } } ne = w; }
-    }
-    if (mode == MODE_EXON && P.unambiguous[mode] && ne >= 2) ne = 0;      // -U with genomicIntervalMode (:603-608)
-    for (int q = 0; q < ne; q++) {
-      int ex = exon[q]; uint32_t f0 = A.featOff[mode][ex], f1 = A.featOff[mode][ex + 1]; bool any = false;
-      for (uint32_t f = f0; f < f1; f++) {
-        uint32_t v = A.feat[mode][f]; uint32_t id = v & 0x7fffffffu;
-        if (mode == MODE_JUNCTION && !(v & 0x80000000u) && !V.junctionActive[id]) continue;   // row removed by the per-chunk map filter (a27)
-        any = true;
-        if (!fs_add(fs, id, 1u << field)) { raise(C.err, DERR_CAPACITY, frag); return; }
-      }
-      if (!any && !fs_add(fs, (uint32_t)A.nFeat[mode] + (uint32_t)ex, 1u << field)) { raise(C.err, DERR_CAPACITY, frag); return; }   // unknown exon: own pseudo id
-    }
+// One genomic interval of a half: its exon set (first-seen order) -> updateExonSet -> features with the interval's field bit.
+struct ExonSet { int32_t exon[32]; uint8_t gen[32]; int n; bool over; };
+EQP_HD void exon_add(ExonSet& e, const HitX& x) {
+  int ex = x.exon; bool have = false;
+  for (int q = 0; q < e.n; q++) have |= e.exon[q] == ex;
+  if (!have) { if (e.n >= 32) e.over = true; else { e.exon[e.n] = ex; e.gen[e.n] = (x.flags & 2) ? 1 : 0; e.n++; } }
+}
+EQP_HD bool interval_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, ExonSet& e, int32_t gs, int32_t ge, int field,
+                              FeatSet& fs, uint32_t frag) {
+  if (e.over) { raise(C.err, DERR_CAPACITY, frag); return false; }
+  int ne = e.n; int32_t* exon = e.exon; uint8_t* exGen = e.gen;
+  if (ne > 1) {                                                          // updateExonSet: keep max-overlap non-genomic exons
+    int maxOv = 0;
+    for (int q = 0; q < ne; q++) if (!exGen[q]) { int en = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = en - gs + 1; if (ov < 0) ov = 0; if (ov > maxOv) maxOv = ov; }
+    if (maxOv > 0) { int w = 0; for (int q = 0; q < ne; q++) { int en = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = en - gs + 1; if (ov < 0) ov = 0; if (exGen[q] || ov >= maxOv) { exon[w] = exon[q]; exGen[w] = exGen[q]; w++; } } ne = w; }
   }
+  if (mode == MODE_EXON && P.unambiguous[mode] && ne >= 2) ne = 0;      // -U with genomicIntervalMode (:603-608)
+  for (int q = 0; q < ne; q++) {
+    int ex = exon[q]; uint32_t f0 = A.featOff[mode][ex], f1 = A.featOff[mode][ex + 1]; bool any = false;
+    for (uint32_t f = f0; f < f1; f++) {
+      uint32_t v = A.feat[mode][f]; uint32_t id = v & 0x7fffffffu;
+      if (mode == MODE_JUNCTION && !(v & 0x80000000u) && !V.junctionActive[id]) continue;   // row removed by the per-chunk map filter (a27)
+      any = true;
+      if (!fs_add(fs, id, 1u << field)) { raise(C.err, DERR_CAPACITY, frag); return false; }
+    }
+    if (!any && !fs_add(fs, (uint32_t)A.nFeat[mode] + (uint32_t)ex, 1u << field)) { raise(C.err, DERR_CAPACITY, frag); return false; }   // unknown exon: own pseudo id
+  }
+  return true;
+}
+// field-coverage test of a half's candidate features (GenomicAlignment.java:570-712)
+EQP_HD void conforming_features(const FeatSet& fs, int mode, int maxField, FeatSet& out) {
+  out.n = 0;
   for (int i = 0; i < fs.n; i++) {
     uint32_t m = fs.mask[i]; bool okf;
     if (mode == MODE_GENE) okf = eqp_popc(m) >= maxField + 1;
@@ -212,6 +209,30 @@ EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView
     else okf = (m & (m >> 1)) != 0;                                       // two consecutive field indices (:679-701)
     if (okf) { out.id[out.n] = fs.id[i]; out.mask[out.n] = 0; out.n++; }
   }
+}
+
+// features of half `h` of representative alignment R (index r) with all merged duplicates folded in: duplicate-chain walk
+// (fragments with more than EQP_FLAT_SCAN hits; smaller ones are regrouped by fragment_weight and streamed, see fragment_count)
+EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t r, int h, FeatSet& out, uint32_t frag) {
+  const Aln& R = V.alns[r]; out.n = 0;
+  int nIv = h == 1 ? R.nIv1 : R.nIv2; int maxField = h == 1 ? R.maxField1 : R.maxField2;
+  if (maxField >= 32) { raise(C.err, DERR_CAPACITY, frag); return; }
+  if (mode == MODE_JUNCTION && nIv < 2) return;                            // a junction needs two consecutive fields (:679-701)
+  FeatSet fs; fs.n = 0;
+  for (int iv = 0; iv < nIv; iv++) {
+    int32_t gs = 0, ge = 0; int field = 0; bool haveIv = false; ExonSet e; e.n = 0; e.over = false;
+    for (uint32_t d = r; d != 0xFFFFFFFFu; d = V.alns[d].next) {          // R first, then later duplicates in file order
+      const Aln& D = V.alns[d];
+      for (uint32_t i = D.hit0; i < D.hit1; i++) {
+        const HitX& x = V.hx[i];
+        if (x.half != h || !(x.flags & 1) || x.ivRank != iv) continue;
+        if (!haveIv) { gs = x.gs; ge = x.ge; field = x.ivField; haveIv = true; }   // R's own first record of the interval
+        if (x.flags & (4 << mode)) exon_add(e, x);
+      }
+    }
+    if (!interval_features(A, C, V, P, mode, e, gs, ge, field, fs, frag)) return;
+  }
+  conforming_features(fs, mode, maxField, out);
 }
 
 EQP_HD void atomic_add_u64(unsigned long long* p, unsigned long long v) {
@@ -222,38 +243,77 @@ EQP_HD void atomic_add_u64(unsigned long long* p, unsigned long long v) {
 #endif
 }
 
-EQP_HD void fragment_count(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t slot) {
+// returns 0 = the fragment is no weight object, 1 = it added to a count, 2 = it was excluded (or aborted on a capacity error)
+EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t slot) {
   uint32_t a20 = V.a20[slot];
-  if (a20 == 0) return;
+  if (a20 == 0) return 0;
   uint32_t frag = C.base + slot; uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1];
   const uint32_t hEnd = C.hitCnt[C.blkOff[slot + 1]];                    // end of the fragment's hit range
-  atomic_add_u64(&V.stats[mode * 3 + 0], 1);
   double w = 1.0 / (double)V.nFinal[slot];
   if (w > 1.0 / (double)a20) w = 1.0 / (double)a20;                      // ComputeCounts.java:762-764
-  if (!(w >= P.weightThreshold)) { atomic_add_u64(&V.stats[mode * 3 + 2], 1); return; }
+  if (!(w >= P.weightThreshold)) return 2;
   double addW = P.unweighted ? 1.0 : w;
   uint32_t fid[EQP_FT_CAP]; uint16_t k1[EQP_FT_CAP], k2[EQP_FT_CAP]; int nf = 0;
-  FeatSet s1, s2;
-  for (uint32_t r = a0; r < a1; r++) {
-    const Aln& R = V.alns[r]; if (R.hit0 == R.hit1 || R.repr != r) continue;
-    s1.n = s2.n = 0;
-    if (R.flags & 2) half_features(A, C, V, P, mode, a0, hEnd, r, 1, s1, frag);
-    if (R.flags & 4) half_features(A, C, V, P, mode, a0, hEnd, r, 2, s2, frag);
-    if (R.flags & 1) {                                                     // paired: gene run intersects, others unite (:325-335)
-      if (mode == MODE_GENE) { int wn = 0; for (int i = 0; i < s1.n; i++) { bool in2 = false; for (int j = 0; j < s2.n; j++) if (s2.id[j] == s1.id[i]) { in2 = true; break; } if (in2) s1.id[wn++] = s1.id[i]; } s1.n = wn; }
-      else for (int j = 0; j < s2.n; j++) { bool in1 = false; for (int i = 0; i < s1.n; i++) if (s1.id[i] == s2.id[j]) { in1 = true; break; } if (!in1) { if (s1.n >= EQP_FS_CAP) { raise(C.err, DERR_CAPACITY, frag); return; } s1.id[s1.n++] = s2.id[j]; } }
+  FeatSet s1, s2; bool bad = false;
+  // one representative alignment done: paired -> gene run intersects the halves, the others unite them (:325-335); then count per feature
+  auto merge_alignment = [&](uint8_t flags) {
+    if (flags & 1) {
+      if (mode == MODE_GENE) { int wn = 0; for (int i = 0; i < s1.n; i++) { bool in2 = false; for (int j = 0; j < s2.n; j++) in2 |= s2.id[j] == s1.id[i]; if (in2) s1.id[wn++] = s1.id[i]; } s1.n = wn; }
+      else for (int j = 0; j < s2.n; j++) { bool in1 = false; for (int i = 0; i < s1.n; i++) in1 |= s1.id[i] == s2.id[j]; if (!in1) { if (s1.n >= EQP_FS_CAP) { bad = true; return; } s1.id[s1.n++] = s2.id[j]; } }
       s2.n = 0;
     }
     for (int side = 0; side < 2; side++) {
       FeatSet& s = side ? s2 : s1;
       for (int i = 0; i < s.n; i++) {
-        int q = 0; for (; q < nf; q++) if (fid[q] == s.id[i]) break;
-        if (q == nf) { if (nf >= EQP_FT_CAP) { raise(C.err, DERR_CAPACITY, frag); return; } fid[nf] = s.id[i]; k1[nf] = k2[nf] = 0; nf++; }
+        int q = 0; while (q < nf && fid[q] != s.id[i]) q++;
+        if (q == nf) { if (nf >= EQP_FT_CAP) { bad = true; return; } fid[nf] = s.id[i]; k1[nf] = k2[nf] = 0; nf++; }
         if (side) k2[q]++; else k1[q]++;
       }
     }
+  };
+  const uint32_t hBeg = C.hitCnt[C.blkOff[slot]];
+  if (hEnd - hBeg <= EQP_FLAT_SCAN) {
+    // hits regrouped by fragment_weight: (representative, half, interval) runs, representatives in file order
+    FeatSet fs; uint32_t i = hBeg;
+    while (i < hEnd && (V.hx[i].flags & 1) && !bad) {
+      const uint16_t g = V.hx[i].grp; const Aln& R = V.alns[a0 + g];
+      s1.n = s2.n = 0;
+      while (i < hEnd && (V.hx[i].flags & 1) && V.hx[i].grp == g && !bad) {
+        const int h = V.hx[i].half; int maxField = h == 1 ? R.maxField1 : R.maxField2;
+        if (maxField >= 32) { bad = true; break; }
+        fs.n = 0;
+        if (mode == MODE_JUNCTION && (h == 1 ? R.nIv1 : R.nIv2) < 2) {      // a junction needs two consecutive fields (:679-701): one interval cannot conform
+          while (i < hEnd && (V.hx[i].flags & 1) && V.hx[i].grp == g && V.hx[i].half == h) i++;
+          (h == 1 ? s1 : s2).n = 0; continue;
+        }
+        while (i < hEnd && !bad) {                                         // one interval per iteration
+          HitX x = V.hx[i];
+          if (!(x.flags & 1) || x.grp != g || x.half != h) break;
+          const int iv = x.ivRank; ExonSet e; e.n = 0; e.over = false;
+          const int32_t gs = x.gs, ge = x.ge; const int field = x.ivField;   // R's own first record of the interval
+          while (true) {
+            if (x.flags & (4 << mode)) exon_add(e, x);
+            if (++i >= hEnd) break;
+            x = V.hx[i];
+            if (!(x.flags & 1) || x.grp != g || x.half != h || x.ivRank != iv) break;
+          }
+          if (!interval_features(A, C, V, P, mode, e, gs, ge, field, fs, frag)) return 2;
+        }
+        conforming_features(fs, mode, maxField, h == 1 ? s1 : s2);
+      }
+      if (!bad) merge_alignment(R.flags);
+    }
+  } else {
+    for (uint32_t r = a0; r < a1 && !bad; r++) {
+      const Aln& R = V.alns[r]; if (R.hit0 == R.hit1 || R.repr != r) continue;
+      s1.n = s2.n = 0;
+      if (R.flags & 2) half_features(A, C, V, P, mode, r, 1, s1, frag);
+      if (R.flags & 4) half_features(A, C, V, P, mode, r, 2, s2, frag);
+      merge_alignment(R.flags);
+    }
   }
-  if (P.unambiguous[mode] && mode != MODE_EXON && nf >= 2) { atomic_add_u64(&V.stats[mode * 3 + 2], 1); return; }   // :371-382 returns 0
+  if (bad) { raise(C.err, DERR_CAPACITY, frag); return 2; }
+  if (P.unambiguous[mode] && mode != MODE_EXON && nf >= 2) return 2;   // :371-382 returns 0
   bool added = false;
   for (int q = 0; q < nf; q++) {
     int k = k1[q] > k2[q] ? k1[q] : k2[q];
@@ -262,7 +322,7 @@ EQP_HD void fragment_count(const AnnoView& A, const ChunkView& C, const CountVie
     if (c > 0) added = true;
     if (fid[q] < (uint32_t)A.nFeat[mode]) atomic_add_u64(&V.acc[mode][fid[q]], (unsigned long long)(c * (double)(1ULL << EQP_FIXED_SHIFT_D) + 0.5));
   }
-  atomic_add_u64(&V.stats[mode * 3 + (added ? 1 : 2)], 1);
+  return added ? 1 : 2;
 }
 
 }  // namespace eqpb

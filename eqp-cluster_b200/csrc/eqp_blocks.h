@@ -65,6 +65,14 @@ EQP_HD int cigar_segments(const char* cg, int n, F&& emit, int& sumRead, bool& b
   return seg;                                                           // number of segments (ciagrFieldNum)
 }
 
+// segments of one record: "<n>M" CIGARs were already reduced to n by the decoder (SamView::cigM), anything else is parsed from the text
+template <class F>
+EQP_HD int record_segments(const SamView& R, uint32_t li, F&& emit, int& sumRead, bool& badOp) {
+  uint16_t m = R.cigM[li];
+  if (m != 0xFFFFu) { badOp = false; sumRead = m; emit(0, 0, (int)m, (int)m, 0, 0); return 1; }
+  return cigar_segments(R.text + R.lineOff[li] + R.cigOff[li], R.cigLen[li], emit, sumRead, badOp);
+}
+
 // Pass 1 (count) and pass 2 (fill) over one fragment's combined record set.
 EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot, bool fill, uint32_t& nBlocksOut, uint32_t& nAlnOut) {
   SetDesc sd = C.setC[slot];
@@ -98,11 +106,10 @@ EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot
       for (int side = 0; side < 2; side++) {
         if (side == 1 && mateFile < 0) break;
         const SamView& R = side ? C.sam[mateFile] : S; uint32_t li = side ? mateLine : i;
-        const char* cg = R.text + R.lineOff[li] + R.cigOff[li];
         int bedStart = R.pos[li] - 1 > 0 ? R.pos[li] - 1 : 0;
         uint8_t ridx = (uint8_t)rec_flag_read_index(R, li), paired = (R.rf[li] & RF_HASMATE) ? 1 : 0, strand = (R.flag[li] & 16) ? '-' : '+';
         int sumRead; bool bad; uint32_t firstOfRec = nb;
-        int nSeg = cigar_segments(cg, R.cigLen[li], [&](int seg, int off, int refLen, int readLen, int insSoft, int del) {
+        int nSeg = record_segments(R, li, [&](int seg, int off, int refLen, int readLen, int insSoft, int del) {
           if (readLen <= 0) return;
           if (fill) {
             Block& b = C.blocks[bo + nb];
@@ -122,7 +129,7 @@ EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot
         if (side == 1 && mateFile < 0) break;
         const SamView& R = side ? C.sam[mateFile] : S; uint32_t li = side ? mateLine : i;
         int sumRead; bool bad;
-        cigar_segments(R.text + R.lineOff[li] + R.cigOff[li], R.cigLen[li], [&](int, int, int, int, int, int) {}, sumRead, bad);
+        record_segments(R, li, [&](int, int, int, int, int, int) {}, sumRead, bad);
         if (bad) raise(C.err, DERR_CIGAR_OP, C.base + slot);
         if (sumRead != R.seqLen[li]) raise(C.err, DERR_CIGAR_LEN, C.base + slot);
       }

@@ -264,7 +264,7 @@ struct CudaBackend {
   void alloc_records(SamView& S, uint8_t*& proc, uint64_t cap) {
     S.lineOff = alloc<uint64_t>(cap + 1);
     S.frag = alloc<uint32_t>(cap); S.ref = alloc<int32_t>(cap); S.pos = alloc<int32_t>(cap); S.rnext = alloc<int32_t>(cap); S.pnext = alloc<int32_t>(cap);
-    S.flag = alloc<uint16_t>(cap); S.nm = alloc<int16_t>(cap); S.cigOff = alloc<uint16_t>(cap); S.cigLen = alloc<uint16_t>(cap); S.seqLen = alloc<uint16_t>(cap);
+    S.flag = alloc<uint16_t>(cap); S.nm = alloc<int16_t>(cap); S.cigOff = alloc<uint16_t>(cap); S.cigLen = alloc<uint16_t>(cap); S.seqLen = alloc<uint16_t>(cap); S.cigM = alloc<uint16_t>(cap);
     S.rf = alloc<uint8_t>(cap); proc = alloc<uint8_t>(cap);
   }
   void decode_fused(const AnnoView& A, SamView& S, uint8_t*& proc, const char* text, uint64_t len, uint32_t* err, uint32_t* fragMinMax) {

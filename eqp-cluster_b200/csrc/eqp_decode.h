@@ -173,7 +173,7 @@ struct ScanSrc {
 // line numbering (a chained scan over tiles) is still in flight.
 struct DecodedRec {
   uint32_t code;                                                        // DERR_* of the first failed check, 0 = fine
-  uint32_t frag; int32_t flag, pos, pnext, ref, rnext; int nm, cigOff, cigLen, seqLen; uint8_t rf;
+  uint32_t frag; int32_t flag, pos, pnext, ref, rnext; int nm, cigOff, cigLen, seqLen; uint8_t rf; uint16_t cigM;
 };
 
 // One SAM line [p, p+n) (no '\n').  The text may live in shared or global memory.
@@ -182,7 +182,7 @@ EQP_HD DecodedRec parse_record_t(const AnnoView& A, const char* p, int n, Src& s
   if (n > 0 && p[n - 1] == '\r') n--;
   uint32_t code = DERR_NONE;                                            // first failed check (single exit)
   uint32_t frag = 0xFFFFFFFFu; uint8_t rf = 0;
-  int32_t flag = 0, pos = 0, pnext = 0, ref = -1, rnext = -1; int nm = -1, cigOff = 0, cigLen = 0, seqLen = 0;
+  int32_t flag = 0, pos = 0, pnext = 0, ref = -1, rnext = -1; int nm = -1, cigOff = 0, cigLen = 0, seqLen = 0; uint16_t cigM = 0xFFFFu;
   if (n > 0 && p[0] != '@') {                                           // SamReader.java:173
     int nt = 0, from = 0;                                                // the first 11 tabs, as scalars (an indexed array would live in local memory)
 #define EQP_TAB_STEP(i) int tab##i = n; if (nt == i) { int q = src.next(p, from, n); if (q < n) { tab##i = q; nt = i + 1; from = q + 1; } }
@@ -246,6 +246,9 @@ EQP_HD DecodedRec parse_record_t(const AnnoView& A, const char* p, int n, Src& s
       if (!code && !intsOk) code = DERR_INT;
       if (!code && riBad) code = DERR_READ_INDEX;
       cigOff = tab4 + 1; cigLen = tab5 - tab4 - 1;
+      { uint32_t v = 0; bool simple = cigLen >= 2 && cigLen <= 6 && p[cigOff + cigLen - 1] == 'M';       // "<n>M": the only block is [pos-1, pos-1+n)
+        for (int i = 0; i + 1 < cigLen && simple; i++) { uint32_t c = (uint32_t)(uint8_t)p[cigOff + i] - (uint32_t)'0'; simple = c <= 9u; v = v * 10 + c; }
+        cigM = (simple && v < 0xFFFFu) ? (uint16_t)v : (uint16_t)0xFFFFu; }
       seqLen = tab9 - tab8 - 1;
       int qualEnd = nt >= 11 ? tab10 : n, qualLen = qualEnd - tab9 - 1;
       if (!code && !(qualLen == 1 && p[tab9 + 1] == '*') && qualLen != seqLen) code = DERR_SEQ_QUAL;
@@ -260,14 +263,14 @@ EQP_HD DecodedRec parse_record_t(const AnnoView& A, const char* p, int n, Src& s
     }
   }
   if (code) { frag = 0xFFFFFFFFu; rf = 0; }
-  return DecodedRec{code, frag, flag, pos, pnext, ref, rnext, nm, cigOff, cigLen, seqLen, rf};
+  return DecodedRec{code, frag, flag, pos, pnext, ref, rnext, nm, cigOff, cigLen, seqLen, rf, cigM};
 }
 EQP_HD void store_record(const SamView& S, uint32_t li, const DecodedRec& r, uint32_t* err) {
   if (r.code) raise(err, r.code, li);
   S.frag[li] = r.frag; S.rf[li] = r.rf;
   if (r.rf) {
     S.flag[li] = (uint16_t)r.flag; S.ref[li] = r.ref; S.pos[li] = r.pos; S.rnext[li] = r.rnext; S.pnext[li] = r.pnext;
-    S.nm[li] = (int16_t)r.nm; S.cigOff[li] = (uint16_t)r.cigOff; S.cigLen[li] = (uint16_t)r.cigLen; S.seqLen[li] = (uint16_t)r.seqLen;
+    S.nm[li] = (int16_t)r.nm; S.cigOff[li] = (uint16_t)r.cigOff; S.cigLen[li] = (uint16_t)r.cigLen; S.seqLen[li] = (uint16_t)r.seqLen; S.cigM[li] = r.cigM;
   }
 }
 template <class Src>

@@ -14,18 +14,30 @@
 
 namespace eqpb {
 
+// Single-address reductions (every lane that calls passes the SAME p): the active lanes combine in the warp and one lane
+// issues the atomic.  Same-address atomics serialise in L2 (~0.85 clk per lane): 10^8 of them cost as much as a whole stage.
 EQP_HD void atomic_min_u32(uint32_t* p, uint32_t v) {
 #if defined(__CUDA_ARCH__)
-  atomicMin(p, v);
+  uint32_t m = __activemask(), r = __reduce_min_sync(m, v);
+  if ((threadIdx.x & 31) == (uint32_t)(__ffs((int)m) - 1)) atomicMin(p, r);
 #else
   if (v < *p) *p = v;
 #endif
 }
 EQP_HD void atomic_max_u32(uint32_t* p, uint32_t v) {
 #if defined(__CUDA_ARCH__)
-  atomicMax(p, v);
+  uint32_t m = __activemask(), r = __reduce_max_sync(m, v);
+  if ((threadIdx.x & 31) == (uint32_t)(__ffs((int)m) - 1)) atomicMax(p, r);
 #else
   if (v > *p) *p = v;
+#endif
+}
+EQP_HD void counter_add(unsigned long long* p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+  uint32_t m = __activemask(), r = __reduce_add_sync(m, v);
+  if (r && (threadIdx.x & 31) == (uint32_t)(__ffs((int)m) - 1)) atomicAdd(p, (unsigned long long)r);
+#else
+  *p += v;
 #endif
 }
 
@@ -63,7 +75,7 @@ struct Pipeline {
     S.frag = be.template alloc<uint32_t>(n); S.ref = be.template alloc<int32_t>(n); S.pos = be.template alloc<int32_t>(n);
     S.rnext = be.template alloc<int32_t>(n); S.pnext = be.template alloc<int32_t>(n); S.flag = be.template alloc<uint16_t>(n);
     S.nm = be.template alloc<int16_t>(n); S.cigOff = be.template alloc<uint16_t>(n); S.cigLen = be.template alloc<uint16_t>(n);
-    S.seqLen = be.template alloc<uint16_t>(n); S.rf = be.template alloc<uint8_t>(n); C.proc[f] = be.template alloc<uint8_t>(n);
+    S.seqLen = be.template alloc<uint16_t>(n); S.cigM = be.template alloc<uint16_t>(n); S.rf = be.template alloc<uint8_t>(n); C.proc[f] = be.template alloc<uint8_t>(n);
   }
 
   int run(const char* const text[3], const uint64_t len[3], ChunkResult& R) {
@@ -173,7 +185,7 @@ struct Pipeline {
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
     { const ChunkView C = this->C; unsigned long long* stats = V.stats;
       be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, false, nb, na); C.blkOff[s] = nb; C.alnOff[s] = na;
-        SetCursor c{0, 0xFFFFFFFFu}; int f; if (set_next(C, C.setC[s], (uint32_t)s, c, f)) atomic_add_u64(&stats[9], 1); }); }
+        SetCursor c{0, 0xFFFFFFFFu}; int f; counter_add(&stats[9], set_next(C, C.setC[s], (uint32_t)s, c, f) ? 1u : 0u); }); }
     be.scan(C.blkOff, N); be.scan(C.alnOff, N);
     be.to_host(&nBlocks, C.blkOff + N, 4); be.to_host(&nAln, C.alnOff + N, 4);
     C.blocks = be.template alloc<Block>((uint64_t)nBlocks + 1); C.hitCnt = be.template alloc<uint32_t>((uint64_t)nBlocks + 1);
@@ -207,7 +219,13 @@ struct Pipeline {
       be.stage("fragment-weight");
       // the three counting runs of one fragment back to back in one thread: runs two and three find the fragment's alignments and
       // hits in cache instead of paying the DRAM latency chain again (the runs were latency-bound as three concurrent kernels)
-      be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { uint32_t s = perm[i]; for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) fragment_count(A, C, V, P, m, s); }); }
+      be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) {
+        uint32_t s = perm[i];
+        for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) {
+          int r = fragment_count(A, C, V, P, m, s);                          // 0 not a weight object, 1 included, 2 excluded (ComputeCounts.java:986-989)
+          counter_add(&V.stats[m * 3 + 0], r ? 1u : 0u); counter_add(&V.stats[m * 3 + 1], r == 1 ? 1u : 0u); counter_add(&V.stats[m * 3 + 2], r == 2 ? 1u : 0u);
+        }
+      }); }
     be.stage("fragment-count x3");
     // ---- results
     be.to_host(R.err, scal, 8);

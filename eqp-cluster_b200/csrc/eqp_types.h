@@ -66,6 +66,7 @@ struct SamView {                   // one decoded SAM input (structure of arrays
   uint32_t nLines;
   uint32_t* frag; int32_t* ref; int32_t* pos; int32_t* rnext; int32_t* pnext;
   uint16_t* flag; int16_t* nm; uint16_t* cigOff; uint16_t* cigLen; uint16_t* seqLen;
+  uint16_t* cigM;                  // n when the CIGAR is exactly "<n>M" (the a10 stage then never touches the text), else 0xFFFF
   uint8_t* rf;                     // bit0 record (not header/empty), bit1 mapped, bit2 hasMate, bits3-4 readIndex
 };
 enum { RF_REC = 1, RF_MAPPED = 2, RF_HASMATE = 4 };
