@@ -90,7 +90,7 @@ struct eqp_ctx {
   std::unique_ptr<CudaBackend> be; std::unique_ptr<Pipeline<CudaBackend>> pl;
   ChunkResult R{}; bool haveChunk = false;
   unsigned long long* vec = nullptr; int64_t vecLen = 0;           // gene|exon|junction fixed-point vector of the last chunk
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr; cudaStream_t copyStream = nullptr;
   std::string err, debugText;
 };
 
@@ -167,8 +167,18 @@ int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, siz
     for (int f = 0; f < 3; f++) {
       if (on_device) { text[f] = (const char*)src[f]; continue; }
       char* d = ctx->be->alloc<char>(len[f] + 16);
-      if (len[f]) EQP_CUDA(cudaMemcpyAsync(d, src[f], len[f], cudaMemcpyHostToDevice, ctx->stream));
       text[f] = d;
+    }
+    if (!on_device) {
+      if (!ctx->copyStream) EQP_CUDA(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+      cudaEvent_t evAlloc; EQP_CUDA(cudaEventCreateWithFlags(&evAlloc, cudaEventDisableTiming));
+      EQP_CUDA(cudaEventRecord(evAlloc, ctx->stream)); EQP_CUDA(cudaStreamWaitEvent(ctx->copyStream, evAlloc, 0));   // the buffers are stream-ordered allocations of ctx->stream
+      for (int f = 0; f < 3; f++) {
+        if (len[f]) EQP_CUDA(cudaMemcpyAsync((void*)text[f], src[f], len[f], cudaMemcpyHostToDevice, ctx->copyStream));
+        EQP_CUDA(cudaEventCreateWithFlags(&ctx->be->inputReady[f], cudaEventDisableTiming));
+        EQP_CUDA(cudaEventRecord(ctx->be->inputReady[f], ctx->copyStream));
+      }
+      EQP_CUDA(cudaEventDestroy(evAlloc));
     }
     ctx->pl.reset(new Pipeline<CudaBackend>(*ctx->be, ctx->A, P));
     EQP_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
@@ -286,6 +296,7 @@ void eqp_destroy(eqp_ctx* ctx) {
   if (ctx->vec) cudaFree(ctx->vec);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->copyStream) cudaStreamDestroy(ctx->copyStream);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }

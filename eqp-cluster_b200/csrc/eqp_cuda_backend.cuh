@@ -267,8 +267,13 @@ struct CudaBackend {
     S.flag = alloc<uint16_t>(cap); S.nm = alloc<int16_t>(cap); S.cigOff = alloc<uint16_t>(cap); S.cigLen = alloc<uint16_t>(cap); S.seqLen = alloc<uint16_t>(cap); S.cigM = alloc<uint16_t>(cap);
     S.rf = alloc<uint8_t>(cap); proc = alloc<uint8_t>(cap);
   }
+  // host inputs: the H2D copy of each SAM text runs on its own stream; the tokenizer of input f starts when copy f has landed,
+  // so tokenizing T and J overlaps the copies of J and G
+  cudaEvent_t inputReady[3] = {nullptr, nullptr, nullptr}; int nextInput = 0;
   void decode_fused(const AnnoView& A, SamView& S, uint8_t*& proc, const char* text, uint64_t len, uint32_t* err, uint32_t* fragMinMax) {
     S.text = text; S.len = len; S.nLines = 0;
+    if (nextInput < 3 && inputReady[nextInput]) EQP_CUDA(cudaStreamWaitEvent(stream, inputReady[nextInput], 0));
+    nextInput++;
     if (!len) { alloc_records(S, proc, 1); return; }
     static bool attr = false;
     if (!attr) { EQP_CUDA(cudaFuncSetAttribute(k_tokenize_sam, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TokShared))); attr = true; }

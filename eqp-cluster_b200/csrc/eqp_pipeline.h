@@ -80,7 +80,7 @@ struct Pipeline {
 
   int run(const char* const text[3], const uint64_t len[3], ChunkResult& R) {
     be.stage(nullptr);
-    scal = be.template alloc<uint32_t>(32); be.memset(scal, 0, 32 * sizeof(uint32_t));
+    scal = be.template alloc<uint32_t>(128); be.memset(scal, 0, 128 * sizeof(uint32_t));
     C.err = scal;
     const AnnoView A = this->A; const RunParams P = this->P;
     // ---- a1/a2: line index + decode (+ the fragment id range of each input)
@@ -133,25 +133,26 @@ struct Pipeline {
       }); }
     be.stage("frag-stats");
     // ---- a5-a7: T+J weights, stage-1 selection, presence bounds, stage-2 selection, aux lookup table
-    uint32_t* bnd = scal + 8;                          // [0] firstT [1] firstJ [2] lastT [3] anyT [4] anyJ | [5] firstTJ [6] firstG [7] lastTJ [8] anyTJ [9] anyG
-    { uint32_t init[10] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0, 0, 0, 0xFFFFFFFFu, 0xFFFFFFFFu, 0, 0, 0}; be.to_device(bnd, init, sizeof init); }
+    // presence bounds of the inputs (first / last slot with a record, any record): known from the fragment id range of each file;
+    // those of the stage-1 output are reduced on the device, in a cache line of their own (nothing else reads or writes it meanwhile)
+    const bool anyT = h[2] != 0xFFFFFFFFu, anyJ = h[4] != 0xFFFFFFFFu, anyG = h[6] != 0xFFFFFFFFu;
+    const uint32_t firstT = anyT ? h[2] - C.base : 0xFFFFFFFFu, lastT = anyT ? h[3] - C.base : 0, firstJ = anyJ ? h[4] - C.base : 0xFFFFFFFFu, firstG = anyG ? h[6] - C.base : 0xFFFFFFFFu;
+    uint32_t* bnd = scal + 64;                         // [0] firstTJ [1] lastTJ [2] anyTJ
+    { uint32_t init[3] = {0xFFFFFFFFu, 0, 0}; be.to_device(bnd, init, sizeof init); }
     { const ChunkView C = this->C;
       be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
-        if (C.ff[FILE_T][s].bits & 1) { atomic_min_u32(bnd + 0, (uint32_t)s); atomic_max_u32(bnd + 2, (uint32_t)s); bnd[3] = 1; }
-        if (C.ff[FILE_J][s].bits & 1) { atomic_min_u32(bnd + 1, (uint32_t)s); bnd[4] = 1; }
-        if (C.ff[FILE_G][s].bits & 1) { atomic_min_u32(bnd + 6, (uint32_t)s); bnd[9] = 1; }
         C.stTJ[s] = combine_weights_ed(C.st[FILE_T][s], C.st[FILE_J][s], P.slack);
       });
       be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
         Side a = side_of_file(FILE_T, C.ff[FILE_T][s], C.st[FILE_T][s]), b = side_of_file(FILE_J, C.ff[FILE_J][s], C.st[FILE_J][s]);
-        SetDesc r = combine_stage(a, b, (uint32_t)s, bnd[0], bnd[1], bnd[2], bnd[3] != 0, bnd[4] != 0, P.slack, C.err, C.base + (uint32_t)s);
+        SetDesc r = combine_stage(a, b, (uint32_t)s, firstT, firstJ, lastT, anyT, anyJ, P.slack, C.err, C.base + (uint32_t)s);
         C.setTJ[s] = r;
-        if (sd_n(r)) { atomic_min_u32(bnd + 5, (uint32_t)s); atomic_max_u32(bnd + 7, (uint32_t)s); bnd[8] = 1; }
+        if (sd_n(r)) { atomic_min_u32(bnd + 0, (uint32_t)s); atomic_max_u32(bnd + 1, (uint32_t)s); bnd[2] = 1; }
       });
       be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
         FragFile ffs[3] = {C.ff[0][s], C.ff[1][s], C.ff[2][s]};
         Side a = side_of_set(C.setTJ[s], ffs, C.stTJ[s]), b = side_of_file(FILE_G, C.ff[FILE_G][s], C.st[FILE_G][s]);
-        C.setC[s] = combine_stage(a, b, (uint32_t)s, bnd[5], bnd[6], bnd[7], bnd[8] != 0, bnd[9] != 0, P.slack, C.err, C.base + (uint32_t)s);
+        C.setC[s] = combine_stage(a, b, (uint32_t)s, bnd[0], firstG, bnd[1], bnd[2] != 0, anyG, P.slack, C.err, C.base + (uint32_t)s);
       });
       // aux: first slot >= s with a T+J weight entry (FragmentEntryFactory.getNextFragmentEntry(query), :75-106)
       const uint32_t CH = 512; uint64_t nCh = ((uint64_t)N + CH - 1) / CH;
