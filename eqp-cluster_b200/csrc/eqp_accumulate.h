@@ -140,7 +140,9 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
   // then stream each fragment's hits once.  (hx is only indexed through Aln.hit0.. before this point; large fragments keep
   // their order and walk the duplicate chains.)
   { uint32_t h0 = C.hitCnt[b0], h1 = C.hitCnt[b1];
-    if (h1 - h0 <= EQP_FLAT_SCAN)
+    bool sorted = true; uint64_t prev = 0;
+    if (h1 - h0 <= EQP_FLAT_SCAN) for (uint32_t i = h0; i < h1; i++) { uint64_t k = hit_group_key(V.hx[i]); sorted &= k >= prev; prev = k; }   // independent loads
+    if (h1 - h0 <= EQP_FLAT_SCAN && !sorted)
       for (uint32_t i = h0 + 1; i < h1; i++) {
         HitX cur = V.hx[i]; uint64_t ck = hit_group_key(cur); uint32_t j = i;
         while (j > h0 && hit_group_key(V.hx[j - 1]) > ck) { V.hx[j] = V.hx[j - 1]; j--; }

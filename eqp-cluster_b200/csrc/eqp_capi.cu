@@ -2,6 +2,7 @@
 // There is no CPU path in this library: every compute entry point needs a CUDA device and fails with EQP_ERR_CUDA without one.
 #include <cstdio>
 #include <cstring>
+#include <chrono>
 #include <memory>
 #include "../../include/eqp_count.h"
 #include "eqp_cuda_backend.cuh"
@@ -154,8 +155,11 @@ int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, siz
   if (p->stranded) return fail(ctx, EQP_ERR_UNSUPPORTED, derr_text(DERR_STRANDED));
   memset(out, 0, sizeof *out);
   try {
+    auto wall = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double w0 = wall();
     EQP_CUDA(cudaSetDevice(ctx->device));
     ctx->haveChunk = false; ctx->pl.reset(); ctx->be.reset();        // frees the previous chunk's device buffers (stream-ordered)
+    double w1 = wall();
     ctx->be.reset(new CudaBackend(ctx->stream, ctx->nSm));
     RunParams P{};
     P.overlap[0] = p->gene_overlap; P.overlap[1] = p->exon_overlap; P.overlap[2] = p->junction_overlap;
@@ -181,6 +185,7 @@ int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, siz
       EQP_CUDA(cudaEventDestroy(evAlloc));
     }
     ctx->pl.reset(new Pipeline<CudaBackend>(*ctx->be, ctx->A, P));
+    double w2 = wall();
     EQP_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
     ctx->R = ChunkResult{};
     int rc = ctx->pl->run(text, len, ctx->R);
@@ -191,6 +196,7 @@ int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, siz
     EQP_CUDA(cudaEventRecord(ctx->ev1, ctx->stream)); EQP_CUDA(cudaEventSynchronize(ctx->ev1));
     float ms = 0; EQP_CUDA(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
     ctx->be->finish_timing(); ctx->be->report_stages();
+    if (ctx->be->timing) fprintf(stderr, "[eqp host ] release %.3f ms, setup %.3f ms, run (events %.3f) %.3f ms wall\n", w1 - w0, w2 - w1, ms, wall() - w2);
     if (rc) {
       char buf[512]; snprintf(buf, sizeof buf, "%s [code %u, detail %u]", derr_text(ctx->R.err[0]), ctx->R.err[0], ctx->R.err[1]);
       return fail(ctx, derr_class(ctx->R.err[0]), buf);

@@ -25,6 +25,13 @@ __global__ void __launch_bounds__(256) k_items(uint64_t n, F f) {
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
 }
 
+// same, compiled for at least MINB resident CTAs per SM: the latency-bound per-fragment stages trade registers for warps in flight
+template <int MINB, class F>
+__global__ void __launch_bounds__(256, MINB) k_items_occ(uint64_t n, F f) {
+  uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
+}
+
 // ---------------------------------------------------------------- scan (exclusive, in place, total at p[n])
 static const int SCAN_THREADS = 256, SCAN_ITEMS = 8, SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
@@ -224,6 +231,11 @@ struct CudaBackend {
   template <class F> void launch(uint64_t n, F f) {
     if (!n) return;
     k_items<<<grid_for(n, 256), 256, 0, stream>>>(n, f); launches++;
+    EQP_CUDA(cudaGetLastError());
+  }
+  template <int MINB, class F> void launch_occ(uint64_t n, F f) {
+    if (!n) return;
+    k_items_occ<MINB><<<grid_for(n, 256), 256, 0, stream>>>(n, f); launches++;
     EQP_CUDA(cudaGetLastError());
   }
   void scan(uint32_t* p, uint64_t n) {

@@ -216,7 +216,7 @@ struct Pipeline {
       be.stage("order");
       be.launch(nAln, [=] EQP_LAMBDA(uint64_t a) { alignment_build(A, C, V, P, (uint32_t)a); });
       be.stage("alignment-build");
-      be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
+      be.template launch_occ<4>(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
       be.stage("fragment-weight");
       // the three counting runs of one fragment back to back in one thread: runs two and three find the fragment's alignments and
       // hits in cache instead of paying the DRAM latency chain again (the runs were latency-bound as three concurrent kernels)

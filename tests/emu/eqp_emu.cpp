@@ -14,6 +14,7 @@ struct HostBackend {
   template <class T> T* alloc(uint64_t n) { void* p = calloc(n ? n : 1, sizeof(T)); allocs.push_back(p); return (T*)p; }
   void memset(void* p, int v, uint64_t bytes) { ::memset(p, v, bytes); }
   template <class F> void launch(uint64_t n, F f) { for (uint64_t i = 0; i < n; i++) f(i); }
+  template <int MINB, class F> void launch_occ(uint64_t n, F f) { launch(n, f); }
   void scan(uint32_t* p, uint64_t n) { uint32_t acc = 0; for (uint64_t i = 0; i < n; i++) { uint32_t v = p[i]; p[i] = acc; acc += v; } p[n] = acc; }
   void to_host(void* dst, const void* src, uint64_t bytes) { memcpy(dst, src, bytes); }
   void to_device(void* dst, const void* src, uint64_t bytes) { memcpy(dst, src, bytes); }
