@@ -166,39 +166,10 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
 #define EQP_FS_CAP 160
 #define EQP_FT_CAP 320
 struct FeatSet { uint32_t id[EQP_FS_CAP]; uint32_t mask[EQP_FS_CAP]; int n; };
-// Candidate features of one half with their field bits.  Small sets are searched linearly; from EQP_FS_HASH_AT entries on
-// (junction runs of reads in many-exon genes: every junction of every exon is a candidate) a 256-slot open-addressing index
-// over the same arrays takes over.
-#ifndef EQP_FS_HASH_AT
-#define EQP_FS_HASH_AT 12
-#endif
-struct FeatIndex : FeatSet { bool hashed; uint8_t slot[256]; };
-EQP_HD void fs_reset(FeatIndex& s) { s.n = 0; s.hashed = false; }
-EQP_HD uint32_t fs_hash(uint32_t id) { return (id * 2654435761u) >> 24; }
-EQP_HD bool fs_add(FeatIndex& s, uint32_t id, uint32_t bit) {
-  bool found = false, ok = true;
-  if (!s.hashed) {
-    for (int i = 0; i < s.n; i++) if (s.id[i] == id) { s.mask[i] |= bit; found = true; }
-    if (!found) {
-      if (s.n >= EQP_FS_CAP) ok = false;
-      else {
-        s.id[s.n] = id; s.mask[s.n] = bit; s.n++;
-        if (s.n == EQP_FS_HASH_AT) {
-          for (int k = 0; k < 256; k++) s.slot[k] = 0;
-          for (int i = 0; i < s.n; i++) { uint32_t h = fs_hash(s.id[i]); while (s.slot[h]) h = (h + 1) & 255u; s.slot[h] = (uint8_t)(i + 1); }
-          s.hashed = true;
-        }
-      }
-    }
-  } else {
-    uint32_t h = fs_hash(id);
-    while (s.slot[h] && !found) { int i = s.slot[h] - 1; if (s.id[i] == id) { s.mask[i] |= bit; found = true; } else h = (h + 1) & 255u; }
-    if (!found) {
-      if (s.n >= EQP_FS_CAP) ok = false;
-      else { s.id[s.n] = id; s.mask[s.n] = bit; s.n++; s.slot[h] = (uint8_t)s.n; }
-    }
-  }
-  return ok;
+EQP_HD bool fs_add(FeatSet& s, uint32_t id, uint32_t bit) {
+  for (int i = 0; i < s.n; i++) if (s.id[i] == id) { s.mask[i] |= bit; return true; }
+  if (s.n >= EQP_FS_CAP) return false;
+  s.id[s.n] = id; s.mask[s.n] = bit; s.n++; return true;
 }
 
 // One genomic interval of a half: its exon set (first-seen order) -> updateExonSet -> features with the interval's field bit.
@@ -209,7 +180,7 @@ EQP_HD void exon_add(ExonSet& e, const HitX& x) {
   if (!have) { if (e.n >= 32) e.over = true; else { e.exon[e.n] = ex; e.gen[e.n] = (x.flags & 2) ? 1 : 0; e.n++; } }
 }
 EQP_HD bool interval_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, ExonSet& e, int32_t gs, int32_t ge, int field,
-                              FeatIndex& fs, uint32_t frag) {
+                              FeatSet& fs, uint32_t frag) {
   if (e.over) { raise(C.err, DERR_CAPACITY, frag); return false; }
   int ne = e.n; int32_t* exon = e.exon; uint8_t* exGen = e.gen;
   if (ne > 1) {                                                          // updateExonSet: keep max-overlap non-genomic exons
@@ -249,7 +220,7 @@ EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView
   int nIv = h == 1 ? R.nIv1 : R.nIv2; int maxField = h == 1 ? R.maxField1 : R.maxField2;
   if (maxField >= 32) { raise(C.err, DERR_CAPACITY, frag); return; }
   if (mode == MODE_JUNCTION && nIv < 2) return;                            // a junction needs two consecutive fields (:679-701)
-  FeatIndex fs; fs_reset(fs);
+  FeatSet fs; fs.n = 0;
   for (int iv = 0; iv < nIv; iv++) {
     int32_t gs = 0, ge = 0; int field = 0; bool haveIv = false; ExonSet e; e.n = 0; e.over = false;
     for (uint32_t d = r; d != 0xFFFFFFFFu; d = V.alns[d].next) {          // R first, then later duplicates in file order
@@ -305,14 +276,14 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
   const uint32_t hBeg = C.hitCnt[C.blkOff[slot]];
   if (hEnd - hBeg <= EQP_FLAT_SCAN) {
     // hits regrouped by fragment_weight: (representative, half, interval) runs, representatives in file order
-    FeatIndex fs; uint32_t i = hBeg;
+    FeatSet fs; uint32_t i = hBeg;
     while (i < hEnd && (V.hx[i].flags & 1) && !bad) {
       const uint16_t g = V.hx[i].grp; const Aln& R = V.alns[a0 + g];
       s1.n = s2.n = 0;
       while (i < hEnd && (V.hx[i].flags & 1) && V.hx[i].grp == g && !bad) {
         const int h = V.hx[i].half; int maxField = h == 1 ? R.maxField1 : R.maxField2;
         if (maxField >= 32) { bad = true; break; }
-        fs_reset(fs);
+        fs.n = 0;
         if (mode == MODE_JUNCTION && (h == 1 ? R.nIv1 : R.nIv2) < 2) {      // a junction needs two consecutive fields (:679-701): one interval cannot conform
           while (i < hEnd && (V.hx[i].flags & 1) && V.hx[i].grp == g && V.hx[i].half == h) i++;
           (h == 1 ? s1 : s2).n = 0; continue;
