@@ -18,14 +18,16 @@
 
 namespace eqpb {
 
-static const int TK_THREADS = 256;
+static const int TK_THREADS = 128;                                   // a tile holds ~90 lines: more threads would only idle in phase 2
+static const int TK_MIN_CTAS = 5;                                    // per SM: 5 x 43 KB of shared memory
 static const int TK_PIECES = 2048;                                   // 16-byte pieces staged per tile
 static const int TK_STAGE = TK_PIECES * 16;                          // 32 KB
 static const int TK_OV_PIECES = 128;                                 // 2 KB overhang
 static const int TK_OWNED = (TK_PIECES - 1 - TK_OV_PIECES) * 16;     // 30,704 bytes of line starts per tile
-static const int TK_PER_THREAD = TK_PIECES / TK_THREADS;             // 8 pieces = 128 bytes
-static const int TK_NL_CAP = 2048;
-static const int TK_FIRST_OV_THREAD = (TK_PIECES - TK_OV_PIECES) / TK_PER_THREAD;   // 240
+static const int TK_PER_THREAD = TK_PIECES / TK_THREADS;             // 16 pieces = 256 bytes
+static const int TK_NL_CAP = 1024;
+static const int TK_FIRST_OV_THREAD = (TK_PIECES - TK_OV_PIECES) / TK_PER_THREAD;   // 120: first thread whose pieces are all overhang
+static_assert((TK_PIECES - TK_OV_PIECES) % TK_PER_THREAD == 0 && TK_PER_THREAD % 8 == 0 && (TK_FIRST_OV_THREAD & 31) != 0, "tile geometry");
 
 struct TokShared {
   alignas(128) char stage[TK_STAGE];
@@ -97,7 +99,7 @@ __device__ __noinline__ void tk_slow_tile(const AnnoView& A, const SamView& S, u
   }
 }
 
-__global__ void __launch_bounds__(TK_THREADS, 4)
+__global__ void __launch_bounds__(TK_THREADS, TK_MIN_CTAS)
 k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamView S, uint32_t capLines, uint32_t nTiles, unsigned long long* status, uint32_t* ticket, unsigned long long* nlTotal, uint32_t* err, uint32_t* fragMinMax) {
   extern __shared__ __align__(128) unsigned char tk_raw[];
   TokShared& sh = *reinterpret_cast<TokShared*>(tk_raw);
@@ -153,8 +155,13 @@ k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamVi
   __syncthreads();
 
   // ---- phase 1b: newline positions
-  uint32_t nlm[4]; { uint4 c = reinterpret_cast<const uint4*>(sh.nlM)[tid]; nlm[0] = c.x; nlm[1] = c.y; nlm[2] = c.z; nlm[3] = c.w; }   // pieces 8*tid .. 8*tid+7, two per register
-  uint32_t cnt = __popc(nlm[0]) + __popc(nlm[1]) + __popc(nlm[2]) + __popc(nlm[3]), x = cnt;
+  const int NW = TK_PER_THREAD / 2;                                  // two 16-bit piece masks per register
+  uint32_t nlm[NW]; uint32_t cnt = 0;
+#pragma unroll
+  for (int q = 0; q < NW / 4; q++) { uint4 c = reinterpret_cast<const uint4*>(sh.nlM)[tid * (NW / 4) + q]; nlm[4 * q] = c.x; nlm[4 * q + 1] = c.y; nlm[4 * q + 2] = c.z; nlm[4 * q + 3] = c.w; }
+#pragma unroll
+  for (int h = 0; h < NW; h++) cnt += __popc(nlm[h]);
+  uint32_t x = cnt;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= (uint32_t)d) x += y; }
   if (lane == 31) sh.warpTot[warp] = x;
@@ -164,7 +171,7 @@ k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamVi
   for (int w = 0; w < TK_THREADS / 32; w++) { uint32_t v = sh.warpTot[w]; if (w < (int)warp) wbase += v; totNl += v; }
   uint32_t l = wbase + x - cnt;                                      // newlines before this thread's bytes
   // the newline at the tile's last owned byte starts the NEXT tile's first line
-  uint32_t lastBit = __shfl_sync(0xffffffffu, (nlm[3] >> 31) & 1u, (TK_FIRST_OV_THREAD - 1) & 31);
+  uint32_t lastBit = __shfl_sync(0xffffffffu, (nlm[NW - 1] >> 31) & 1u, (TK_FIRST_OV_THREAD - 1) & 31);
   const bool fits = totNl <= (uint32_t)TK_NL_CAP;
   unsigned long long* st = status + tile;
   if (tid == TK_FIRST_OV_THREAD) {
@@ -173,7 +180,7 @@ k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamVi
   }
   if (fits) {
 #pragma unroll
-    for (int h = 0; h < 4; h++) {
+    for (int h = 0; h < NW; h++) {
       uint32_t m = nlm[h];
       while (m) { int bit = __ffs((int)m) - 1; m &= m - 1; sh.nlPos[l++] = (uint16_t)((tid * TK_PER_THREAD + 2 * h) * 16 + bit); }
     }
