@@ -14,11 +14,11 @@
 
 namespace eqpb {
 
-// Single-address reductions (every lane that calls passes the SAME p): the active lanes combine in the warp and one lane
-// issues the atomic.  Same-address atomics serialise in L2 (~0.85 clk per lane): 10^8 of them cost as much as a whole stage.
+// Single-address reductions: the active lanes that pass the same p (grouped with match.any: lanes of different loop iterations may
+// sit on the same instruction) combine in the warp and one lane issues the atomic.  Same-address atomics serialise in L2 (~0.85 clk per lane): 10^8 of them cost as much as a whole stage.
 EQP_HD void atomic_min_u32(uint32_t* p, uint32_t v) {
 #if defined(__CUDA_ARCH__)
-  uint32_t m = __activemask(), r = __reduce_min_sync(m, v);
+  uint32_t m = __match_any_sync(__activemask(), (unsigned long long)p), r = __reduce_min_sync(m, v);
   if ((threadIdx.x & 31) == (uint32_t)(__ffs((int)m) - 1)) atomicMin(p, r);
 #else
   if (v < *p) *p = v;
@@ -26,7 +26,7 @@ EQP_HD void atomic_min_u32(uint32_t* p, uint32_t v) {
 }
 EQP_HD void atomic_max_u32(uint32_t* p, uint32_t v) {
 #if defined(__CUDA_ARCH__)
-  uint32_t m = __activemask(), r = __reduce_max_sync(m, v);
+  uint32_t m = __match_any_sync(__activemask(), (unsigned long long)p), r = __reduce_max_sync(m, v);
   if ((threadIdx.x & 31) == (uint32_t)(__ffs((int)m) - 1)) atomicMax(p, r);
 #else
   if (v > *p) *p = v;
@@ -34,7 +34,7 @@ EQP_HD void atomic_max_u32(uint32_t* p, uint32_t v) {
 }
 EQP_HD void counter_add(unsigned long long* p, uint32_t v) {
 #if defined(__CUDA_ARCH__)
-  uint32_t m = __activemask(), r = __reduce_add_sync(m, v);
+  uint32_t m = __match_any_sync(__activemask(), (unsigned long long)p), r = __reduce_add_sync(m, v);
   if (r && (threadIdx.x & 31) == (uint32_t)(__ffs((int)m) - 1)) atomicAdd(p, (unsigned long long)r);
 #else
   *p += v;
