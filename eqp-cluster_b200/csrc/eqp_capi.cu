@@ -93,6 +93,9 @@ struct eqp_ctx {
   unsigned long long* vec = nullptr; int64_t vecLen = 0;           // gene|exon|junction fixed-point vector of the last chunk
   cudaEvent_t ev0 = nullptr, ev1 = nullptr; cudaStream_t copyStream = nullptr;
   std::string err, debugText;
+  std::vector<void*> pinned;
+  void pin(void* p, size_t bytes) { if (bytes && cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) pinned.push_back(p); else cudaGetLastError(); }
+  void unpin() { for (void* p : pinned) cudaHostUnregister(p); pinned.clear(); }
 };
 
 static thread_local std::string g_err;                              // errors raised before a ctx exists
@@ -139,6 +142,12 @@ int eqp_load_annotation(eqp_ctx* ctx, const eqp_annotation_files* f) {
     if (ctx->vec) { cudaFree(ctx->vec); ctx->vec = nullptr; }
     ctx->vecLen = (int64_t)ctx->A.nFeat[0] + ctx->A.nFeat[1] + ctx->A.nFeat[2];
     EQP_CUDA(cudaMalloc((void**)&ctx->vec, (size_t)(ctx->vecLen + 1) * 8)); EQP_CUDA(cudaMemset(ctx->vec, 0, (size_t)(ctx->vecLen + 1) * 8));
+    // result buffers: sized once per annotation and page-locked, so the per-chunk D2H of the count vectors runs at PCIe speed
+    ctx->unpin();
+    for (int m = 0; m < 3; m++) { ctx->R.fixed[m].assign((size_t)ctx->A.nFeat[m], 0); ctx->R.counts[m].assign((size_t)ctx->A.nFeat[m], 0.0); }
+    ctx->R.junctionActive.assign((size_t)ctx->A.nFeat[2], 0);
+    for (int m = 0; m < 3; m++) ctx->pin(ctx->R.fixed[m].data(), ctx->R.fixed[m].size() * 8);
+    ctx->pin(ctx->R.junctionActive.data(), ctx->R.junctionActive.size());
     ctx->annoLoaded = true; ctx->haveChunk = false; return EQP_OK;
   } catch (const AnnoError& ex) { return fail(ctx, ex.code == -5 ? EQP_ERR_UNSUPPORTED : ex.code == -1 ? EQP_ERR_ARG : EQP_ERR_IO, ex.what()); }
   catch (const CudaError& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
@@ -187,7 +196,7 @@ int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, siz
     ctx->pl.reset(new Pipeline<CudaBackend>(*ctx->be, ctx->A, P));
     double w2 = wall();
     EQP_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
-    ctx->R = ChunkResult{};
+    memset(ctx->R.stats, 0, sizeof ctx->R.stats); memset(ctx->R.err, 0, sizeof ctx->R.err); memset(ctx->R.nRecords, 0, sizeof ctx->R.nRecords);   // the count vectors keep their (page-locked) storage
     int rc = ctx->pl->run(text, len, ctx->R);
     if (rc == 0) {
       int64_t off = 0;
@@ -299,6 +308,7 @@ void eqp_destroy(eqp_ctx* ctx) {
   cudaSetDevice(ctx->device);
   ctx->pl.reset(); ctx->be.reset();
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  ctx->unpin();
   if (ctx->vec) cudaFree(ctx->vec);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);

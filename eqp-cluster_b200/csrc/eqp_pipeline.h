@@ -235,7 +235,8 @@ struct Pipeline {
     for (int m = 0; m < 3; m++) {
       R.fixed[m].resize(A.nFeat[m]); if (A.nFeat[m]) be.to_host(R.fixed[m].data(), V.acc[m], (uint64_t)A.nFeat[m] * 8);
       R.counts[m].resize(A.nFeat[m]);
-      for (int i = 0; i < A.nFeat[m]; i++) R.counts[m][i] = (double)R.fixed[m][i] / (double)(1ULL << EQP_FIXED_SHIFT_D);
+      { const double scale = 1.0 / (double)(1ULL << EQP_FIXED_SHIFT_D); const unsigned long long* fx = R.fixed[m].data(); double* out = R.counts[m].data();   // exact: power-of-two scale
+        for (int i = 0; i < A.nFeat[m]; i++) out[i] = (double)fx[i] * scale; }
     }
     R.junctionActive.resize(A.nFeat[2]); if (A.nFeat[2]) be.to_host(R.junctionActive.data(), V.junctionActive, A.nFeat[2]);
     return 0;
