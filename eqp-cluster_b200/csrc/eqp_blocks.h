@@ -77,21 +77,20 @@ EQP_HD int record_segments(const SamView& R, uint32_t li, F&& emit, int& sumRead
 EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot, bool fill, uint32_t& nBlocksOut, uint32_t& nAlnOut) {
   SetDesc sd = C.setC[slot];
   uint32_t nb = 0, na = 0; uint32_t bo = fill ? C.blkOff[slot] : 0;
-  SetCursor ci{0, 0xFFFFFFFFu}; int fi;
+  SetCursor ci{0, 0xFFFFFFFFu}; int fi; bool taken = false;             // taken: a record of this fragment was consumed as a mate (only then proc[] is read)
   while (set_next(C, sd, slot, ci, fi)) {
     const SamView& S = C.sam[fi]; uint32_t i = ci.line;
-    if (C.proc[fi][i]) continue;
-    C.proc[fi][i] = 1;
+    if (taken && C.proc[fi][i]) continue;
     int mateFile = -1; uint32_t mateLine = 0;
     if (S.rf[i] & RF_HASMATE) {                                          // findMate over the rest of the group
       SetCursor cj = ci; int fj;
       while (set_next(C, sd, slot, cj, fj)) {
-        if (C.proc[fj][cj.line]) continue;
+        if (taken && C.proc[fj][cj.line]) continue;
         const SamView& T = C.sam[fj];
         // isMate across inputs only needs the decoded fields
         int ia = rec_flag_read_index(S, i), ib = rec_flag_read_index(T, cj.line);
         if (ia != ib && ((S.rf[i] >> 5) & 3) == ((T.rf[cj.line] >> 5) & 3) && S.rnext[i] == T.ref[cj.line] && S.pnext[i] == T.pos[cj.line] &&
-            S.ref[i] == T.rnext[cj.line] && S.pos[i] == T.pnext[cj.line]) { mateFile = fj; mateLine = cj.line; C.proc[fj][cj.line] = 1; break; }
+            S.ref[i] == T.rnext[cj.line] && S.pos[i] == T.pnext[cj.line]) { mateFile = fj; mateLine = cj.line; C.proc[fj][cj.line] = 1; taken = true; break; }
       }
       if (mateFile >= 0) {
         const SamView& T = C.sam[mateFile];

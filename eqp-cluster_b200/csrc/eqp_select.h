@@ -15,10 +15,11 @@ EQP_HD bool is_mate(const SamView& S, uint32_t a, uint32_t b) {       // a.isMat
   return S.rnext[a] == S.ref[b] && S.pnext[a] == S.pos[b] && S.ref[a] == S.rnext[b] && S.pos[a] == S.pnext[b];
 }
 
-// a4 for one fragment of one file.  proc[] is a per-line scratch byte (zeroed by the caller).
+// a4 for one fragment of one file.  proc[] is a per-line scratch byte (zeroed by the caller), set for records consumed as mates.
 EQP_HD void fragment_stats(const AnnoView& A, const SamView& S, uint32_t first, uint32_t end, bool whitelist, uint8_t* proc,
                            FragStat& out, FragFile& ff, uint32_t* err, uint32_t fragId) {
   FragStat f{}; int ri = 1; bool hasMate = false, any = false, added = false; uint8_t bits = 0;
+  bool taken = false;                                                   // a record of this fragment was consumed as a mate: only then proc[] is read
   for (uint32_t i = first; i < end; i++) {
     uint8_t rf = S.rf[i];
     if (!(rf & RF_REC)) continue;
@@ -27,18 +28,17 @@ EQP_HD void fragment_stats(const AnnoView& A, const SamView& S, uint32_t first, 
     if (!(rf & RF_MAPPED)) continue;
     bits |= (idx == 1 ? 2 : 4);
     any = true;
-    if (proc[i]) continue;
+    if (taken && proc[i]) continue;
     int32_t ref = S.ref[i];
     bool ok = !whitelist || (ref >= 0 && (A.refFlags[ref] & 1));
     if (rf & RF_HASMATE) {
       uint32_t j = i + 1; bool found = false;
-      for (; j < end; j++) { if ((S.rf[j] & RF_MAPPED) && !proc[j] && is_mate(S, i, j)) { found = true; break; } }
+      for (; j < end; j++) { if ((S.rf[j] & RF_MAPPED) && !(taken && proc[j]) && is_mate(S, i, j)) { found = true; break; } }
       if (found) {
-        proc[i] = proc[j] = 1;
+        proc[j] = 1; taken = true;                                        // i itself is never visited again (searches only look forward)
         if (ok) { f.edPe += S.nm[i] + S.nm[j]; f.nPe++; hasMate = true; added = true; }
       }                                                                 // else dropped (SamProcessorFragmentEntry.java:192-197)
     } else {
-      proc[i] = 1;
       if (ok) {                                                          // FragmentEntry.add(SamRecord) :430-477
         hasMate = false; added = true;
         if (idx != ri) ri = 3;
