@@ -179,15 +179,43 @@ EQP_HD void exon_add(ExonSet& e, const HitX& x) {
   for (int q = 0; q < e.n; q++) have |= e.exon[q] == ex;
   if (!have) { if (e.n >= 32) e.over = true; else { e.exon[e.n] = ex; e.gen[e.n] = (x.flags & 2) ? 1 : 0; e.n++; } }
 }
-EQP_HD bool interval_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, ExonSet& e, int32_t gs, int32_t ge, int field,
-                              FeatSet& fs, uint32_t frag) {
-  if (e.over) { raise(C.err, DERR_CAPACITY, frag); return false; }
+// GenomicInterval.updateExonSet (GenomicInterval.java:479-523): among several exons keep the genomic ones and the non-genomic ones of maximal overlap
+EQP_HD int exon_filter(const AnnoView& A, ExonSet& e, int32_t gs, int32_t ge) {
   int ne = e.n; int32_t* exon = e.exon; uint8_t* exGen = e.gen;
-  if (ne > 1) {                                                          // updateExonSet: keep max-overlap non-genomic exons
+  if (ne > 1) {
     int maxOv = 0;
     for (int q = 0; q < ne; q++) if (!exGen[q]) { int en = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = en - gs + 1; if (ov < 0) ov = 0; if (ov > maxOv) maxOv = ov; }
     if (maxOv > 0) { int w = 0; for (int q = 0; q < ne; q++) { int en = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = en - gs + 1; if (ov < 0) ov = 0; if (exGen[q] || ov >= maxOv) { exon[w] = exon[q]; exGen[w] = exGen[q]; w++; } } ne = w; }
   }
+  e.n = ne; return ne;
+}
+// Junction run, a half with exactly two intervals of one exon each (the ordinary spliced read): a junction conforms iff it is a
+// candidate of both exons and the two fields are consecutive (:679-701), i.e. the intersection of the two exons' feature lists.
+// The lists are sorted by id when the annotation is loaded, so this is one merge instead of a set with field masks.
+// Returns false when the shape is different (the general path then handles the half).
+EQP_HD bool junction_pair(const AnnoView& A, const CountView& V, ExonSet& ea, int32_t gsa, int32_t gea, int fa, ExonSet& eb, int32_t gsb, int32_t geb, int fb, FeatSet& out, bool& overflow) {
+  if (ea.over || eb.over) return false;
+  if (exon_filter(A, ea, gsa, gea) != 1 || exon_filter(A, eb, gsb, geb) != 1) return false;   // the filter is idempotent: the general path may run it again
+  out.n = 0;
+  if (fa - fb != 1 && fb - fa != 1) return true;
+  const uint32_t* F = A.feat[MODE_JUNCTION]; const uint32_t* O = A.featOff[MODE_JUNCTION];
+  uint32_t i = O[ea.exon[0]], i1 = O[ea.exon[0] + 1], j = O[eb.exon[0]], j1 = O[eb.exon[0] + 1];
+  while (i < i1 && j < j1) {
+    uint32_t va = F[i], vb = F[j], ia = va & 0x7fffffffu, ib = vb & 0x7fffffffu;
+    if (ia < ib) i++; else if (ib < ia) j++;
+    else {
+      bool act = ((va & vb) >> 31) != 0 || V.junctionActive[ia] != 0;    // a row survives the chunk's map filter (a27) or is in the transcript map
+      bool pa = (va >> 31) || act, pb = (vb >> 31) || act;
+      if (pa && pb) { if (out.n >= EQP_FS_CAP) { overflow = true; return true; } out.id[out.n] = ia; out.mask[out.n] = 0; out.n++; }
+      i++; j++;
+    }
+  }
+  return true;
+}
+EQP_HD bool interval_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, ExonSet& e, int32_t gs, int32_t ge, int field,
+                              FeatSet& fs, uint32_t frag) {
+  if (e.over) { raise(C.err, DERR_CAPACITY, frag); return false; }
+  int ne = exon_filter(A, e, gs, ge); int32_t* exon = e.exon;
   if (mode == MODE_EXON && P.unambiguous[mode] && ne >= 2) ne = 0;      // -U with genomicIntervalMode (:603-608)
   for (int q = 0; q < ne; q++) {
     int ex = exon[q]; uint32_t f0 = A.featOff[mode][ex], f1 = A.featOff[mode][ex + 1]; bool any = false;
@@ -288,10 +316,12 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
           while (i < hEnd && (V.hx[i].flags & 1) && V.hx[i].grp == g && V.hx[i].half == h) i++;
           (h == 1 ? s1 : s2).n = 0; continue;
         }
+        const bool pairShape = mode == MODE_JUNCTION && (h == 1 ? R.nIv1 : R.nIv2) == 2;   // candidate for junction_pair()
+        ExonSet e2[2]; int32_t gs2[2], ge2[2]; int field2[2]; int nColl = 0;
         while (i < hEnd && !bad) {                                         // one interval per iteration
           HitX x = V.hx[i];
           if (!(x.flags & 1) || x.grp != g || x.half != h) break;
-          const int iv = x.ivRank; ExonSet e; e.n = 0; e.over = false;
+          const int iv = x.ivRank; ExonSet& e = e2[pairShape ? (nColl & 1) : 0]; e.n = 0; e.over = false;
           const int32_t gs = x.gs, ge = x.ge; const int field = x.ivField;   // R's own first record of the interval
           while (true) {
             if (x.flags & (4 << mode)) exon_add(e, x);
@@ -299,7 +329,13 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
             x = V.hx[i];
             if (!(x.flags & 1) || x.grp != g || x.half != h || x.ivRank != iv) break;
           }
-          if (!interval_features(A, C, V, P, mode, e, gs, ge, field, fs, frag)) return 2;
+          if (pairShape && nColl < 2) { gs2[nColl] = gs; ge2[nColl] = ge; field2[nColl] = field; nColl++; }
+          else if (!interval_features(A, C, V, P, mode, e, gs, ge, field, fs, frag)) return 2;
+        }
+        if (pairShape) {
+          bool done = nColl == 2 && junction_pair(A, V, e2[0], gs2[0], ge2[0], field2[0], e2[1], gs2[1], ge2[1], field2[1], h == 1 ? s1 : s2, bad);
+          if (done) continue;
+          for (int c = 0; c < nColl; c++) if (!interval_features(A, C, V, P, mode, e2[c], gs2[c], ge2[c], field2[c], fs, frag)) return 2;
         }
         conforming_features(fs, mode, maxField, h == 1 ? s1 : s2);
       }

@@ -209,7 +209,9 @@ struct AnnoHost {
         if (!have) v.push_back(f);
       }
       featOff[m].push_back(0);
-      for (auto& v : per) { for (auto x : v) feat[m].push_back(x); featOff[m].push_back((uint32_t)feat[m].size()); }
+      for (auto& v : per) {                                             // by feature id: the junction run intersects two lists by merging (junction_pair)
+        std::sort(v.begin(), v.end(), [](uint32_t a, uint32_t b) { return (a & 0x7fffffffu) < (b & 0x7fffffffu); });
+        for (auto x : v) feat[m].push_back(x); featOff[m].push_back((uint32_t)feat[m].size()); }
     }
     // ---- a27: which junction features does a reference id seen in the chunk keep alive?
     std::unordered_map<std::string, std::vector<std::string>> jjExt;    // internal junction id -> external ids
