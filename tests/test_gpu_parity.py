@@ -160,3 +160,36 @@ def test_chunk_vectors_add_up(world, ctx):
         ctx.accumulate(acc.data_ptr())
     got = acc.cpu().numpy().view(np.uint64)[:want.size]
     assert n == want.size + res.fixed["junction"].size and np.array_equal(got, want)
+
+
+def test_sample_files_from_the_reduced_vector(world, ctx, tmp_path):
+    """Writer step after the reduce (combine.write_sample_files) against `combineCounts.py -A` semantics applied to per-chunk
+    `.cnt` files (combine.combine_counts): same ids in the same order, values equal to 1e-9 (fp64 sum of chunk values vs exact
+    fixed-point sum)."""
+    import torch
+    cmb = eqp.combine
+    acc, files = None, {m: [] for m in eqp.MODES}
+    for c, (seed, first) in enumerate(((1021, 1), (1022, 20001))):
+        ch = world.chunk("sf_%d" % c, seed, first, 20000, "se")
+        res = ctx.count_chunk(*read_sams(ch["dir"], "se"))
+        if acc is None:
+            _, n = ctx.device_vector()
+            acc = torch.zeros(n, dtype=torch.int64, device="cuda")
+        ctx.accumulate(acc.data_ptr())
+        for m in eqp.MODES:                                              # chunk files as compute-counts writes them ("0" rows, junctions non-zero only)
+            p = os.path.join(str(tmp_path), "s-C%03d-%s.cnt" % (c + 1, m))
+            with open(p, "w") as f:
+                for i, v in zip(ctx.feature_ids[m], res.counts[m]):
+                    if v != 0 or m != "junction":
+                        f.write("%s\t%s\n" % (i, repr(float(v)) if v else "0"))
+            files[m].append(p)
+    paths = cmb.write_sample_files(ctx.feature_ids, acc.cpu().numpy(), os.path.join(str(tmp_path), "s"))
+    for m in eqp.MODES:
+        want = os.path.join(str(tmp_path), "want-%s.cnt" % m)
+        cmb.combine_counts(files[m], want, add_up=True)
+        w, g = open(want).read().splitlines(), open(paths[m]).read().splitlines()
+        assert [r.split("\t")[0] for r in w] == [r.split("\t")[0] for r in g], m
+        assert any(float(r.split("\t")[1]) > 0 for r in g), m
+        for rw, rg in zip(w, g):
+            a, b = float(rw.split("\t")[1]), float(rg.split("\t")[1])
+            assert abs(a - b) <= 1e-9 * max(a, b), (m, rw, rg)
