@@ -98,3 +98,28 @@ def test_write_counts_equals_add_up_of_chunk_files(tmp_path):
     assert [r.split("\t")[0] for r in w] == [r.split("\t")[0] for r in g]
     for rw, rg in zip(w, g):                                         # fp64 sum of chunk values vs exact fixed-point sum: same to 1e-9 (usually the same text)
         assert abs(float(rw.split("\t")[1]) - float(rg.split("\t")[1])) <= 1e-9 * float(rw.split("\t")[1])
+
+
+def test_fpkm_hand_traced(tmp_path):
+    """computeFpkm.py semantics traced by hand: lengths from the gene-length file first, then from the GTF (union of all rows
+    of the gene per chromosome), ids without any length dropped, reads summed per sample over chunk rows."""
+    fp = eqp.fpkm
+    cnt = put(tmp_path, "P-gene.cnt", "Id\tS1\tS2\nG1\t10.0\t0.0\nG2\t3.0\t6.0\nG3\t1.0\t1.0\nENST9\t1.0\t1.0\n")
+    lens = put(tmp_path, "lengths.txt", "Gene Id\tLength\nG1\t2000\n")
+    reads = put(tmp_path, "reads.txt", "Sample\tChunk\tAligned reads\nS1\tC001\t1500000\nS1\tC002\t500000\nS2\t4000000\n")
+    gtf = put(tmp_path, "a.gtf",
+              'chr1\tx\texon\t101\t200\t.\t+\t.\tgene_id "G2"; transcript_id "T1";\n'
+              'chr1\tx\texon\t151\t300\t.\t+\t.\tgene_id "G2"; transcript_id "T2";\n'          # overlaps the first: union 101-300 = 200
+              'chr1\tx\texon\t301\t400\t.\t+\t.\tgene_id "G2"; transcript_id "T2";\n'          # starts after 300: separate, +100
+              'chr2\tx\texon\t1\t50\t.\t+\t.\tgene_id "G2"; transcript_id "T3";\n')            # other chromosome: 50 < 300, ignored
+    out = os.path.join(str(tmp_path), "P-gene.fpkm")
+    fp.main(["-c", cnt, "-g", gtf, "-n", reads, "-o", out, "-l", lens])
+    # G1: 10 / 2.0 / 2.0 = 2.5 ; 0 ; G2: length 300 -> 3 / 0.3 / 2.0 = 5.0 ; 6 / 0.3 / 4.0 = 5.0 ; G3 and ENST9 have no length
+    assert open(out).read() == "Gene Id\tS1\tS2\nG1\t2.5\t0.0\nG2\t5.0\t5.0\n"
+    assert fp.union_length([(5, 9), (1, 5), (20, 29)]) == 9 + 10 and fp.union_length([]) == 0
+    fp.main(["-c", cnt, "-n", reads, "-o", out, "-l", lens, "-m", "-C", "S2"])
+    assert open(out).read() == "Gene Id\tMean control FPKM\nG1\t0.0\n"
+    lens2 = put(tmp_path, "lengths2.txt", "G1\t1000\nG2\t1000\nG3\t1000\nENST9\t1000\n")
+    fp.main(["-c", cnt, "-o", out, "-l", lens2])                         # no -n: normalised by the column sums (15 and 8)
+    rows = dict(r.split("\t", 1) for r in open(out).read().splitlines())
+    assert rows["G1"] == "%s\t0.0" % cmb.py2_float_str(10.0 / 1.0 / (15.0 / 1e6)) and rows["ENST9"].split("\t")[1] == "125000.0"
