@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstring>
 #include <chrono>
+#include <deque>
 #include <memory>
 #include "../../include/eqp_count.h"
 #include "eqp_cuda_backend.cuh"
@@ -94,6 +95,23 @@ struct eqp_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr; cudaStream_t copyStream = nullptr;
   std::string err, debugText;
   std::vector<void*> pinned;
+  // Host chunks whose H2D copy was started ahead of their eqp_count_chunk call (eqp_prefetch_chunk), oldest first; `current` = the
+  // device text (and copy-done events) of the chunk being counted.
+  struct HostChunk { const uint8_t* src[3]; size_t len[3]; char* dev[3]; cudaEvent_t ready[3]; };
+  std::deque<HostChunk> prefetched; HostChunk current{};
+  void retire(HostChunk& c, cudaStream_t s) {
+    for (int f = 0; f < 3; f++) { if (c.dev[f]) cudaFreeAsync(c.dev[f], s); if (c.ready[f]) cudaEventDestroy(c.ready[f]); }
+    c = HostChunk{};
+  }
+  void start_copy(HostChunk& c) {                                   // allocation + copy + event per input, all ordered on the copy stream
+    if (!copyStream) EQP_CUDA(cudaStreamCreateWithFlags(&copyStream, cudaStreamNonBlocking));
+    for (int f = 0; f < 3; f++) {
+      void* d = nullptr; EQP_CUDA(cudaMallocAsync(&d, c.len[f] + 16, copyStream)); c.dev[f] = (char*)d;
+      if (c.len[f]) EQP_CUDA(cudaMemcpyAsync(d, c.src[f], c.len[f], cudaMemcpyHostToDevice, copyStream));
+      EQP_CUDA(cudaEventCreateWithFlags(&c.ready[f], cudaEventDisableTiming));
+      EQP_CUDA(cudaEventRecord(c.ready[f], copyStream));
+    }
+  }
   void pin(void* p, size_t bytes) { if (bytes && cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) pinned.push_back(p); else cudaGetLastError(); }
   void unpin() { for (void* p : pinned) cudaHostUnregister(p); pinned.clear(); }
 };
@@ -177,21 +195,24 @@ int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, siz
     P.unambiguous[0] = P.unambiguous[1] = p->unambiguous ? 1 : 0; P.unambiguous[2] = 0;
     P.unweighted = p->unweighted ? 1 : 0; P.modes = (uint8_t)(p->modes & 7); P.weightThreshold = p->read_weight_threshold; P.slack = p->distance_slack;
     const uint8_t* src[3] = {t_sam, j_sam, g_sam}; uint64_t len[3] = {t_len, j_len, g_len}; const char* text[3];
-    for (int f = 0; f < 3; f++) {
-      if (on_device) { text[f] = (const char*)src[f]; continue; }
-      char* d = ctx->be->alloc<char>(len[f] + 16);
-      text[f] = d;
-    }
-    if (!on_device) {
-      if (!ctx->copyStream) EQP_CUDA(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
-      cudaEvent_t evAlloc; EQP_CUDA(cudaEventCreateWithFlags(&evAlloc, cudaEventDisableTiming));
-      EQP_CUDA(cudaEventRecord(evAlloc, ctx->stream)); EQP_CUDA(cudaStreamWaitEvent(ctx->copyStream, evAlloc, 0));   // the buffers are stream-ordered allocations of ctx->stream
-      for (int f = 0; f < 3; f++) {
-        if (len[f]) EQP_CUDA(cudaMemcpyAsync((void*)text[f], src[f], len[f], cudaMemcpyHostToDevice, ctx->copyStream));
-        EQP_CUDA(cudaEventCreateWithFlags(&ctx->be->inputReady[f], cudaEventDisableTiming));
-        EQP_CUDA(cudaEventRecord(ctx->be->inputReady[f], ctx->copyStream));
+    ctx->retire(ctx->current, ctx->stream);
+    if (on_device) { for (int f = 0; f < 3; f++) text[f] = (const char*)src[f]; }
+    else {
+      // host buffers: the copies run on the copy stream and the tokenizer of input f waits for copy f only, so tokenizing overlaps the
+      // later copies.  A chunk announced with eqp_prefetch_chunk is already on its way (or resident).
+      bool pre = false;
+      if (!ctx->prefetched.empty()) {
+        const eqp_ctx::HostChunk& q = ctx->prefetched.front(); pre = true;
+        for (int f = 0; f < 3; f++) pre = pre && q.src[f] == src[f] && q.len[f] == len[f];
+        if (pre) { ctx->current = q; ctx->prefetched.pop_front(); }
+        else {                                                      // not the announced chunk: the announcements are dropped, this chunk is copied now
+          EQP_CUDA(cudaStreamSynchronize(ctx->copyStream));
+          for (auto& c : ctx->prefetched) ctx->retire(c, ctx->copyStream);
+          ctx->prefetched.clear();
+        }
       }
-      EQP_CUDA(cudaEventDestroy(evAlloc));
+      if (!pre) { for (int f = 0; f < 3; f++) { ctx->current.src[f] = src[f]; ctx->current.len[f] = len[f]; } ctx->start_copy(ctx->current); }
+      for (int f = 0; f < 3; f++) { text[f] = ctx->current.dev[f]; ctx->be->inputReady[f] = ctx->current.ready[f]; }
     }
     ctx->pl.reset(new Pipeline<CudaBackend>(*ctx->be, ctx->A, P));
     double w2 = wall();
@@ -204,6 +225,7 @@ int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, siz
     }
     EQP_CUDA(cudaEventRecord(ctx->ev1, ctx->stream)); EQP_CUDA(cudaEventSynchronize(ctx->ev1));
     float ms = 0; EQP_CUDA(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    ctx->retire(ctx->current, ctx->stream);                         // the text is not needed once the results are on the host
     ctx->be->finish_timing(); ctx->be->report_stages();
     if (ctx->be->timing) fprintf(stderr, "[eqp host ] release %.3f ms, setup %.3f ms, run (events %.3f) %.3f ms wall\n", w1 - w0, w2 - w1, ms, wall() - w2);
     if (rc) {
@@ -221,6 +243,22 @@ int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, siz
     ctx->haveChunk = true; return EQP_OK;
   } catch (const CudaError& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
   catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+
+int eqp_prefetch_chunk(eqp_ctx* ctx, const uint8_t* t_sam, size_t t_len, const uint8_t* j_sam, size_t j_len, const uint8_t* g_sam, size_t g_len) {
+  if (!ctx) return fail(ctx, EQP_ERR_ARG, "eqp_prefetch_chunk: null context");
+  if ((t_len && !t_sam) || (j_len && !j_sam) || (g_len && !g_sam)) return fail(ctx, EQP_ERR_ARG, "eqp_prefetch_chunk: null SAM buffer with non-zero length");
+  if (ctx->prefetched.size() >= 2) return fail(ctx, EQP_ERR_ARG, "eqp_prefetch_chunk: two chunks are already in flight");
+  eqp_ctx::HostChunk c{};
+  try {
+    EQP_CUDA(cudaSetDevice(ctx->device));
+    c.src[0] = t_sam; c.src[1] = j_sam; c.src[2] = g_sam; c.len[0] = t_len; c.len[1] = j_len; c.len[2] = g_len;
+    ctx->start_copy(c);
+    ctx->prefetched.push_back(c); return EQP_OK;
+  } catch (const std::exception& ex) {
+    cudaGetLastError(); if (ctx->copyStream) { cudaStreamSynchronize(ctx->copyStream); ctx->retire(c, ctx->copyStream); }
+    return fail(ctx, EQP_ERR_CUDA, ex.what());
+  }
 }
 
 int64_t eqp_feature_count(eqp_ctx* ctx, int mode) { return (ctx && ctx->annoLoaded && mode >= 0 && mode < 3) ? (int64_t)ctx->H.featIds[mode].size() : -1; }
@@ -307,6 +345,8 @@ void eqp_destroy(eqp_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   ctx->pl.reset(); ctx->be.reset();
+  if (ctx->copyStream) cudaStreamSynchronize(ctx->copyStream);
+  ctx->retire(ctx->current, ctx->stream); for (auto& c : ctx->prefetched) ctx->retire(c, ctx->stream);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   ctx->unpin();
   if (ctx->vec) cudaFree(ctx->vec);

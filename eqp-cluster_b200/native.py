@@ -50,7 +50,7 @@ class Counts(C.Structure):
                 ("device_ms", C.c_double), ("dominant_kernel_ms", C.c_double), ("kernel_launches", C.c_int64)]
 
 
-EXPORTS = ("eqp_version", "eqp_default_params", "eqp_create", "eqp_load_annotation", "eqp_count_chunk", "eqp_feature_count",
+EXPORTS = ("eqp_version", "eqp_default_params", "eqp_create", "eqp_load_annotation", "eqp_count_chunk", "eqp_prefetch_chunk", "eqp_feature_count",
            "eqp_feature_id", "eqp_device_vector", "eqp_accumulate", "eqp_debug_fetch", "eqp_debug_decode", "eqp_last_error", "eqp_destroy")
 
 _lib = None
@@ -71,6 +71,8 @@ def load_library(path=None):
     lib.eqp_create.argtypes = [C.c_int, C.POINTER(vp)]
     lib.eqp_load_annotation.argtypes = [vp, C.POINTER(AnnotationFiles)]
     lib.eqp_count_chunk.argtypes = [vp, C.POINTER(Params), vp, C.c_size_t, vp, C.c_size_t, vp, C.c_size_t, C.c_int, C.POINTER(Counts)]
+    lib.eqp_prefetch_chunk.argtypes = [vp, vp, C.c_size_t, vp, C.c_size_t, vp, C.c_size_t]
+    lib.eqp_prefetch_chunk.restype = C.c_int
     lib.eqp_feature_count.argtypes = [vp, C.c_int]; lib.eqp_feature_count.restype = C.c_int64
     lib.eqp_feature_id.argtypes = [vp, C.c_int, C.c_int64]; lib.eqp_feature_id.restype = C.c_char_p
     lib.eqp_device_vector.argtypes = [vp, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
@@ -144,6 +146,7 @@ class CountContext:
         if rc:
             raise EqpError(rc, (self.lib.eqp_last_error(None) or b"").decode())
         self.feature_ids = None
+        self._prefetch_keep = []
 
     def _check(self, rc):
         if rc:
@@ -169,7 +172,15 @@ class CountContext:
         c = Counts()
         self._check(self.lib.eqp_count_chunk(self.h, C.byref(p), bufs[0][0], bufs[0][1], bufs[1][0], bufs[1][1], bufs[2][0], bufs[2][1],
                                               1 if on_device else 0, C.byref(c)))
+        if self._prefetch_keep and not on_device:
+            self._prefetch_keep.pop(0)
         return ChunkCounts(c, self.feature_ids) if fetch else c
+
+    def prefetch_chunk(self, t_sam, j_sam, g_sam):
+        """Start the H2D copy of a later chunk's host buffers; the count_chunk call with the same buffers picks it up."""
+        bufs = [_buf(x) for x in (t_sam, j_sam, g_sam)]
+        self._check(self.lib.eqp_prefetch_chunk(self.h, bufs[0][0], bufs[0][1], bufs[1][0], bufs[1][1], bufs[2][0], bufs[2][1]))
+        self._prefetch_keep.append(bufs)                                 # the host buffers must outlive the copy
 
     def device_vector(self):
         ptr, n = C.c_void_p(), C.c_int64()

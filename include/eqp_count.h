@@ -103,6 +103,15 @@ int  eqp_count_chunk(eqp_ctx* ctx, const eqp_params* params,
                      const uint8_t* t_sam, size_t t_len, const uint8_t* j_sam, size_t j_len,
                      const uint8_t* g_sam, size_t g_len, int on_device, eqp_counts* out);
 
+/* Double-buffered ingest: start the host-to-device copy of a LATER chunk's three SAM buffers now, on the
+ * copy stream, so that it overlaps the counting of the chunk before it.  Call it before the eqp_count_chunk of the previous
+ * chunk (that call blocks); the eqp_count_chunk(on_device = 0) that follows with the same pointers and lengths picks the copy up.
+ * At most two chunks may be announced; the host buffers must stay valid (and should be page-locked) until their chunk has been
+ * counted.  An announcement that does not match the next eqp_count_chunk call is dropped.  This replaces the
+ * `zcat file | java ...` hand-over of compute-intersection-bed-file.sh:644-662 for callers that hold several chunks in memory. */
+int  eqp_prefetch_chunk(eqp_ctx* ctx, const uint8_t* t_sam, size_t t_len, const uint8_t* j_sam, size_t j_len,
+                        const uint8_t* g_sam, size_t g_len);
+
 /* Feature ids, mode = 0 gene, 1 exon, 2 junction. */
 int64_t     eqp_feature_count(eqp_ctx* ctx, int mode);
 const char* eqp_feature_id(eqp_ctx* ctx, int mode, int64_t index);

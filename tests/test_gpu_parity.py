@@ -193,3 +193,25 @@ def test_sample_files_from_the_reduced_vector(world, ctx, tmp_path):
         for rw, rg in zip(w, g):
             a, b = float(rw.split("\t")[1]), float(rg.split("\t")[1])
             assert abs(a - b) <= 1e-9 * max(a, b), (m, rw, rg)
+
+
+def test_prefetched_chunks_give_the_same_counts(world, ctx):
+    """eqp_prefetch_chunk (double-buffered H2D): same bits as the blocking copy, in order; a non-matching announcement is dropped;
+    a third announcement is refused."""
+    a = read_sams(world.chunk("pf_a", 1031, 1, 20000, "se")["dir"], "se")
+    b = read_sams(world.chunk("pf_b", 1032, 20001, 15000, "se")["dir"], "se")
+    ra, rb = ctx.count_chunk(*a), ctx.count_chunk(*b)
+    keep = {m: (ra.fixed[m].copy(), rb.fixed[m].copy()) for m in eqp.MODES}
+    ctx.prefetch_chunk(*a)
+    ctx.prefetch_chunk(*b)
+    with pytest.raises(eqp.EqpError):
+        ctx.prefetch_chunk(*a)
+    pa = ctx.count_chunk(*a)
+    fa = {m: pa.fixed[m].copy() for m in eqp.MODES}
+    ctx.prefetch_chunk(*a)                                               # b is next in the queue, then a
+    pb = ctx.count_chunk(*b)
+    fb = {m: pb.fixed[m].copy() for m in eqp.MODES}
+    pb2 = ctx.count_chunk(*b)                                            # announced a, counted b: announcement dropped
+    for m in eqp.MODES:
+        assert np.array_equal(fa[m], keep[m][0]) and np.array_equal(fb[m], keep[m][1]) and np.array_equal(pb2.fixed[m], keep[m][1]), m
+    assert pa.number_mapped_reads == ra.number_mapped_reads and pb2.number_mapped_reads == rb.number_mapped_reads
