@@ -192,7 +192,7 @@ struct Pipeline {
     C.blocks = be.template alloc<Block>((uint64_t)nBlocks + 1); C.hitCnt = be.template alloc<uint32_t>((uint64_t)nBlocks + 1);
     C.alnBlk = be.template alloc<uint32_t>((uint64_t)nAln + 1); be.to_device(C.alnBlk + nAln, &nBlocks, 4);
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
-    { const ChunkView C = this->C; be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, nb, na); }); }
+    { const ChunkView C = this->C; be.template launch_occ<6>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, nb, na); }); }
     be.stage("blocks");
     // ---- a11: interval join (count, scan, fill)
     { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { C.hitCnt[b] = join_block(A, C.blocks[b], nullptr, (uint32_t)b); }); }
