@@ -177,26 +177,14 @@ __global__ void __launch_bounds__(LI_WARPS * 32) k_fill_line_offsets(const char*
 // ---------------------------------------------------------------- backend
 struct CudaBackend {
   cudaStream_t stream; int nSm;
-  cudaStream_t mainStream; cudaStream_t side[3] = {nullptr, nullptr, nullptr}; cudaEvent_t evFork = nullptr, evJoin[3] = {nullptr, nullptr, nullptr};
+  cudaStream_t mainStream;
   std::vector<void*> allocs;
-  cudaEvent_t evDec0 = nullptr, evDec1 = nullptr; float decodeMs = 0; long launches = 0; uint64_t bytesAllocated = 0;
+  float decodeMs = 0; long launches = 0; uint64_t bytesAllocated = 0;
 
-  explicit CudaBackend(cudaStream_t s, int sms) : stream(s), nSm(sms > 0 ? sms : EQP_NUM_SMS_DEFAULT), mainStream(s) {
-    EQP_CUDA(cudaEventCreateWithFlags(&evFork, cudaEventDisableTiming));
-    for (int i = 0; i < 3; i++) { EQP_CUDA(cudaStreamCreateWithFlags(&side[i], cudaStreamNonBlocking)); EQP_CUDA(cudaEventCreateWithFlags(&evJoin[i], cudaEventDisableTiming)); }
-    EQP_CUDA(cudaEventCreate(&evDec0)); EQP_CUDA(cudaEventCreate(&evDec1));
-  }
-  ~CudaBackend() {
-    finish_timing(); release(); if (evDec0) cudaEventDestroy(evDec0); if (evDec1) cudaEventDestroy(evDec1); if (evFork) cudaEventDestroy(evFork);
-    for (int i = 0; i < 3; i++) { if (evJoin[i]) cudaEventDestroy(evJoin[i]); if (side[i]) cudaStreamDestroy(side[i]); }
-  }
-  // Independent stages (the three counting runs) go to side streams so that their low-occupancy tails overlap.
-  void fork() { EQP_CUDA(cudaEventRecord(evFork, mainStream)); }
-  void branch(int i) { stream = side[i]; EQP_CUDA(cudaStreamWaitEvent(stream, evFork, 0)); }
-  void join() {
-    for (int i = 0; i < 3; i++) { EQP_CUDA(cudaEventRecord(evJoin[i], side[i])); EQP_CUDA(cudaStreamWaitEvent(mainStream, evJoin[i], 0)); }
-    stream = mainStream;
-  }
+  // No streams or other heavyweight driver objects are created per chunk: stream creation/destruction serialises on driver locks
+  // (tens of ms when another process, e.g. an nvidia-smi poll, holds them).
+  explicit CudaBackend(cudaStream_t s, int sms) : stream(s), nSm(sms > 0 ? sms : EQP_NUM_SMS_DEFAULT), mainStream(s) {}
+  ~CudaBackend() { finish_timing(); release(); }
   // EQP_STAGE_TIMING=1: CUDA-event time between consecutive stage() marks on the main stream, printed to stderr per chunk
   bool timing = getenv("EQP_STAGE_TIMING") != nullptr; std::vector<std::pair<const char*, cudaEvent_t>> marks;
   void stage(const char* name) {
