@@ -131,11 +131,17 @@ def write_counts(feature_ids, values, path, nonzero_only=False):
 
 
 def write_sample_files(feature_ids, vector, prefix, suffix=".cnt", shift=38, nonzero_junctions=True):
-    """Writer-rank step after sharding.reduce_vectors(): `vector` is the reduced gene||exon||junction fixed-point vector of one
-    sample (int64/uint64, 2^-shift reads), `feature_ids` = {mode: [ids]} in the vector's order (CountContext.feature_ids).
+    """Writer-rank step after the sample reduce: `vector` is the reduced gene||exon||junction vector of one sample, either WIDE
+    (2n entries: fraction limbs in 2^-shift reads, then integer limbs; include/eqp_count.h "sample level") or a plain chunk vector
+    (n entries, 2^-shift reads); `feature_ids` = {mode: [ids]} in the vector's order (CountContext.feature_ids).
     Writes <prefix>-gene<suffix>, -exon, -junction as process-samples.sh:1730-1748 would via combineCounts.py -A."""
     import numpy as np
-    v = np.asarray(vector).astype(np.uint64).astype(np.float64) / float(1 << shift)
+    n = sum(len(feature_ids[m]) for m in ("gene", "exon", "junction"))
+    raw = np.ascontiguousarray(vector).view(np.uint64)
+    if raw.size == 2 * n and n:
+        v = raw[n:].astype(np.float64) + raw[:n].astype(np.float64) / float(1 << shift)
+    else:
+        v = raw.astype(np.float64) / float(1 << shift)
     off, paths = 0, {}
     for mode in ("gene", "exon", "junction"):
         ids = feature_ids[mode]

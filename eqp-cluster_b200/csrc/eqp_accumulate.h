@@ -21,6 +21,89 @@ EQP_HD int eqp_popc(uint32_t m) {
 #endif
 }
 
+// ---- canonical alignment keys (a18).  The reference compares STRINGS: WeightObjectAlignment.setGenomicAlignmentString (:185-219) over
+// the per-half strings that GenomicAlignment.adjustGenomicAlignmentString (:873-887) rebuilds for every alignment: intervals as
+// "chr/start/end/" joined by ":".  A tr- interval prints "" outside the gene run (GenomicInterval.java:711-713), and because the rebuild
+// tests `alignmentString == ""` by identity, LEADING tr- intervals vanish together with their separator, later ones leave an empty token;
+// a half of tr- intervals only is the literal "" and switches the alignment string to plain concatenation (:201-215).
+// Here a half is its token list; keys are a hash of the same structure and equality is decided on the tokens themselves.
+struct TokCur { uint32_t s0, s1; int nIv, r; bool gene, started; };
+EQP_HD TokCur tok_begin(const Aln& a, int h, bool gene) {
+  TokCur c; c.s0 = h == 1 ? a.hit0 : a.split; c.s1 = h == 1 ? a.split : a.hit1; c.nIv = h == 1 ? a.nIv1 : a.nIv2; c.r = -1; c.gene = gene; c.started = false; return c;
+}
+static const int32_t TOK_EMPTY = (int32_t)0x80000000;
+EQP_HD bool tok_next(const CountView& V, TokCur& c, int32_t& chr, int32_t& gs, int32_t& ge) {
+  while (++c.r < c.nIv) {
+    for (uint32_t i = c.s0; i < c.s1; i++) {
+      const HitX& x = V.hx[i];
+      if (!(x.flags & 1) || x.ivRank != c.r) continue;
+      if (x.chr <= -2 && !c.gene) {
+        if (!c.started) break;                                              // leading tr- interval: dropped
+        chr = TOK_EMPTY; gs = ge = 0; return true;
+      }
+      c.started = true; chr = x.chr; gs = x.gs; ge = x.ge; return true;
+    }
+  }
+  return false;
+}
+EQP_HD bool half_lit(const Aln& a, int h, bool gene) { return !gene && ((a.tr >> (3 * (h - 1))) & 2); }   // string is the literal ""
+// 0 = "a-b" ordered by start (both halves, neither literal), 1 = "l-", 2 = "r-", 3 = concatenation
+EQP_HD int key_form(const Aln& a, bool gene) {
+  bool h1 = a.flags & 2, h2 = a.flags & 4;
+  if (h1 && h2 && !half_lit(a, 1, gene) && !half_lit(a, 2, gene)) return 0;
+  if (!h2) return 1;
+  if (!h1) return 2;
+  return 3;
+}
+EQP_HD uint64_t alignment_key(const CountView& V, const Aln& al, bool gene) {
+  const uint8_t fl = al.flags; const int form = key_form(al, gene);
+  uint64_t hsh = mix64(0x1234, (uint64_t)((fl & 1) ? 0 : (fl >> 3) & 3));    // alignmentBaseId: fragment id, or fragment id + /S1, /S2
+  hsh = mix64(hsh, (uint64_t)form);
+  const bool secondFirst = form == 0 && !(al.start1 <= al.start2);
+  for (int part = 0; part < 2; part++) {
+    int half = form == 0 ? (secondFirst ? 2 - part : 1 + part) : form == 1 ? 1 : form == 2 ? 2 : 1 + part;
+    if ((form == 1 || form == 2) && part == 1) break;
+    if (form == 0 && part == 1) hsh = mix64(hsh, 0xABCDEF00u);               // the "-" between the two halves
+    TokCur c = tok_begin(al, half, gene); int32_t chr, gs, ge;
+    while (tok_next(V, c, chr, gs, ge)) hsh = mix64(mix64(mix64(hsh, (uint64_t)(uint32_t)chr), (uint64_t)gs), (uint64_t)ge);
+  }
+  return hsh;
+}
+EQP_HD bool halves_equal(const CountView& V, const Aln& a, int ha, const Aln& b, int hb, bool gene) {
+  TokCur ca = tok_begin(a, ha, gene), cb = tok_begin(b, hb, gene);
+  while (true) {
+    int32_t c1, s1, e1, c2, s2, e2;
+    bool na = tok_next(V, ca, c1, s1, e1), nb = tok_next(V, cb, c2, s2, e2);
+    if (na != nb) return false;
+    if (!na) return true;
+    if (c1 != c2 || s1 != s2 || e1 != e2) return false;
+  }
+}
+// string equality of two WeightObjectAlignment keys; on success `swapped` tells how b's halves map onto a's
+EQP_HD bool keys_equal(const CountView& V, const Aln& a, uint64_t ka, const Aln& b, uint64_t kb, bool gene, bool& swapped) {
+  swapped = false;
+  if (ka != kb) return false;
+  if ((a.flags & 1) != (b.flags & 1)) return false;
+  if (!(a.flags & 1) && ((a.flags >> 3) & 3) != ((b.flags >> 3) & 3)) return false;
+  const int form = key_form(a, gene);
+  if (form != key_form(b, gene)) return false;
+  if (form == 0) {
+    bool sa = !(a.start1 <= a.start2), sb = !(b.start1 <= b.start2);     // which half is printed first
+    int a1 = sa ? 2 : 1, a2 = sa ? 1 : 2, b1 = sb ? 2 : 1, b2 = sb ? 1 : 2;
+    if (!halves_equal(V, a, a1, b, b1, gene) || !halves_equal(V, a, a2, b, b2, gene)) return false;
+    // combineExons (:312-337): straight pairing if ga1==ga1' and ga2==ga2', else the mate-swapped pairing
+    swapped = !(halves_equal(V, a, 1, b, 1, gene) && halves_equal(V, a, 2, b, 2, gene));
+    return true;
+  }
+  if (form == 1) return halves_equal(V, a, 1, b, 1, gene);
+  if (form == 2) return halves_equal(V, a, 2, b, 2, gene);
+  // concatenation: at most one half of each alignment has tokens
+  bool straight = halves_equal(V, a, 1, b, 1, gene) && halves_equal(V, a, 2, b, 2, gene);
+  if (straight) return true;
+  if (halves_equal(V, a, 1, b, 2, gene) && halves_equal(V, a, 2, b, 1, gene)) { swapped = true; return true; }
+  return false;
+}
+
 // ---- stage A (one alignment per item): sort the alignment's hits, build both halves, hash the canonical key
 EQP_HD void alignment_build(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, uint32_t a) {
   uint32_t b0 = C.alnBlk[a], b1 = C.alnBlk[a + 1];
@@ -39,99 +122,73 @@ EQP_HD void alignment_build(const AnnoView& A, const ChunkView& C, const CountVi
   uint8_t fl = fb.paired ? 1 : 0;
   for (uint32_t i = k; i < e; i++) if ((C.blocks[C.hits[i].block].paired ? 1 : 0) != (fl & 1)) raise(C.err, DERR_INCONSISTENT, frag);
   al.start1 = al.start2 = 0x7fffffff; al.nIv1 = al.nIv2 = 0; al.maxField1 = al.maxField2 = -1;
-  if (split > k) { build_half(A, C, V, P, k, split, 1, al.start1, al.nIv1, al.maxField1, frag); fl |= 2; }
-  if (e > split) { build_half(A, C, V, P, split, e, 2, al.start2, al.nIv2, al.maxField2, frag); fl |= 4; }
+  uint8_t tr1 = 0, tr2 = 0;
+  if (split > k) { build_half(A, C, V, P, k, split, 1, al.start1, al.nIv1, al.maxField1, tr1, frag); fl |= 2; }
+  if (e > split) { build_half(A, C, V, P, split, e, 2, al.start2, al.nIv2, al.maxField2, tr2, frag); fl |= 4; }
   if (!(fl & 1)) fl |= (uint8_t)(((fl & 2) ? 1 : 2) << 3);
   if (!(fl & 1) && (fl & 2) && (fl & 4)) raise(C.err, DERR_INCONSISTENT, frag);     // single-read alignment with both read indices
-  al.flags = fl;
-  // canonical key (strand slot is empty in the reference's strings: GenomicInterval never sets originalStrand)
-  bool both = (fl & 2) && (fl & 4); bool secondFirst = both && !(al.start1 <= al.start2);
-  uint64_t hsh = mix64(0x1234, (uint64_t)((fl & 1) ? 0 : (fl >> 3) & 3));
-  hsh = mix64(hsh, both ? 0 : (fl & 2) ? 1 : 2);
-  for (int part = 0; part < 2; part++) {
-    int half = both ? (secondFirst ? 2 - part : 1 + part) : ((fl & 2) ? 1 : 2);
-    if (!both && part == 1) break;
-    uint32_t s0 = half == 1 ? k : split, s1 = half == 1 ? split : e; int nIv = half == 1 ? al.nIv1 : al.nIv2;
-    hsh = mix64(hsh, 0xABCDEF00u + (uint64_t)nIv);
-    for (int r = 0; r < nIv; r++)
-      for (uint32_t i = s0; i < s1; i++) { const HitX& x = V.hx[i]; if ((x.flags & 1) && x.ivRank == r) { hsh = mix64(mix64(mix64(hsh, (uint64_t)x.chr), (uint64_t)x.gs), (uint64_t)x.ge); break; } }
-  }
-  al.key = hsh;
-}
-
-// interval r of a half: first valid record with that rank
-EQP_HD bool half_interval(const CountView& V, uint32_t s0, uint32_t s1, int r, int32_t& chr, int32_t& gs, int32_t& ge, int& field) {
-  for (uint32_t i = s0; i < s1; i++) { const HitX& x = V.hx[i]; if ((x.flags & 1) && x.ivRank == r) { chr = x.chr; gs = x.gs; ge = x.ge; field = x.ivField; return true; } }
-  return false;
-}
-EQP_HD bool halves_equal(const CountView& V, const Aln& a, int ha, const Aln& b, int hb) {
-  int na = ha == 1 ? a.nIv1 : a.nIv2, nb = hb == 1 ? b.nIv1 : b.nIv2;
-  if (na != nb) return false;
-  uint32_t a0 = ha == 1 ? a.hit0 : a.split, a1 = ha == 1 ? a.split : a.hit1, b0 = hb == 1 ? b.hit0 : b.split, b1 = hb == 1 ? b.split : b.hit1;
-  for (int r = 0; r < na; r++) {
-    int32_t c1, s1, e1, c2, s2, e2; int f;
-    half_interval(V, a0, a1, r, c1, s1, e1, f); half_interval(V, b0, b1, r, c2, s2, e2, f);
-    if (c1 != c2 || s1 != s2 || e1 != e2) return false;
-  }
-  return true;
-}
-// string equality of two WeightObjectAlignment keys; on success `swapped` tells how b's halves map onto a's
-EQP_HD bool keys_equal(const CountView& V, const Aln& a, const Aln& b, bool& swapped) {
-  swapped = false;
-  if (a.key != b.key) return false;
-  if ((a.flags & 1) != (b.flags & 1)) return false;
-  if (!(a.flags & 1) && ((a.flags >> 3) & 3) != ((b.flags >> 3) & 3)) return false;
-  if ((a.flags & 6) != (b.flags & 6)) return false;
-  if ((a.flags & 6) == 6) {
-    bool sa = !(a.start1 <= a.start2), sb = !(b.start1 <= b.start2);     // which half is printed first
-    int a1 = sa ? 2 : 1, a2 = sa ? 1 : 2, b1 = sb ? 2 : 1, b2 = sb ? 1 : 2;
-    if (!halves_equal(V, a, a1, b, b1) || !halves_equal(V, a, a2, b, b2)) return false;
-    // combineExons (:312-337): straight pairing if ga1==ga1' and ga2==ga2', else the mate-swapped pairing
-    swapped = !(halves_equal(V, a, 1, b, 1) && halves_equal(V, a, 2, b, 2));
-    return true;
-  }
-  int h = (a.flags & 2) ? 1 : 2;
-  return halves_equal(V, a, h, b, h);
+  al.flags = fl; al.tr = (uint8_t)(tr1 | (tr2 << 3)); al.pad[0] = al.pad[1] = 0;
+  al.key = alignment_key(V, al, false);
 }
 
 EQP_HD uint64_t hit_group_key(const HitX& x) { return ((uint64_t)((x.flags & 1) ? 0 : 1) << 40) | ((uint64_t)x.grp << 24) | ((uint64_t)x.half << 16) | x.ivRank; }
 
 // ---- stage B: dedupe, a20, final weight
-EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, uint32_t slot) {
-  uint32_t b0 = C.blkOff[slot], b1 = C.blkOff[slot + 1];
-  V.a20[slot] = 0; V.nFinal[slot] = 0;
-  if (b0 == b1 || C.hitCnt[b0] == C.hitCnt[b1]) return;
-  uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1];
-  int left = 0, right = 0; uint32_t nA = a1 - a0, cap = 2 * nA; uint32_t* tab = V.dedupTab + 2 * (uint64_t)a0;
+// a19 + a20 for one fragment: dedupe its alignments by key (first in file order is the representative, later ones are chained to it)
+// and count the representatives.  GENE = false: keys of the weight pass and of the exon / junction runs, state in Aln; GENE = true: keys
+// of the gene run, state in AlnG (only fragments with tr- exon hits need it: without a tr- interval the two keys are the same string).
+template <bool GENE>
+EQP_HD uint32_t dedupe_fragment(const CountView& V, uint32_t a0, uint32_t a1) {
+  int left = 0, right = 0; bool hasTr = false; uint32_t nA = a1 - a0, cap = 2 * nA; uint32_t* tab = V.dedupTab + 2 * (uint64_t)a0;
+  if (GENE) { for (uint32_t a = a0; a < a1; a++) { AlnG& g = V.alnG[a]; g.repr = a; g.next = 0xFFFFFFFFu; g.flags = 0; g.key = V.alns[a].hit0 == V.alns[a].hit1 ? 0 : alignment_key(V, V.alns[a], true); }
+    if (nA > 4) for (uint32_t s = 0; s < cap; s++) tab[s] = 0; }            // the table was used by the first dedupe
   for (uint32_t a = a0; a < a1; a++) {
     Aln& al = V.alns[a]; if (al.hit0 == al.hit1) continue;
-    al.repr = a;
+    const uint64_t key = GENE ? V.alnG[a].key : al.key;
+    if (!GENE) al.repr = a;
     uint32_t found = 0xFFFFFFFFu; bool sw = false;
     if (nA <= 4) {                                                         // tiny fragment: compare with the earlier representatives directly
       for (uint32_t p = a0; p < a; p++) {
-        const Aln& q = V.alns[p]; if (q.hit0 == q.hit1 || q.repr != p) continue;
-        if (keys_equal(V, q, al, sw)) { found = p; break; }
+        const Aln& q = V.alns[p]; if (q.hit0 == q.hit1 || (GENE ? V.alnG[p].repr : q.repr) != p) continue;
+        if (keys_equal(V, q, GENE ? V.alnG[p].key : q.key, al, key, GENE, sw)) { found = p; break; }
       }
     } else {                                                               // per-fragment open-addressing table of representatives (2 slots per alignment, zeroed)
-      uint32_t s = (uint32_t)(((al.key * 0x9E3779B97F4A7C15ULL) >> 32) % cap);
+      uint32_t s = (uint32_t)(((key * 0x9E3779B97F4A7C15ULL) >> 32) % cap);
       while (true) {
         uint32_t e = tab[s];
         if (!e) { tab[s] = a - a0 + 1; break; }
-        if (keys_equal(V, V.alns[a0 + e - 1], al, sw)) { found = a0 + e - 1; break; }   // insertion order along the probe path = file order: first equal key wins
+        const uint32_t p = a0 + e - 1;
+        if (keys_equal(V, V.alns[p], GENE ? V.alnG[p].key : V.alns[p].key, al, key, GENE, sw)) { found = p; break; }   // insertion order along the probe path = file order: first equal key wins
         s = s + 1 == cap ? 0 : s + 1;
       }
     }
     if (found != 0xFFFFFFFFu) {                                            // duplicate: append to the representative's chain (file order)
-      al.repr = found; if (sw) al.flags |= 32;
-      V.alns[V.alnTail[found]].next = a; V.alnTail[found] = a;
-    } else V.alnTail[a] = a;
-    if (al.repr == a) { if ((al.flags & 6) == 4) right++; else left++; }   // ":r-" forms (WeightObject.java:859-865)
+      if (GENE) { V.alnG[a].repr = found; if (sw) V.alnG[a].flags |= 32; V.alnG[V.alnTail[found]].next = a; }
+      else { al.repr = found; if (sw) al.flags |= 32; V.alns[V.alnTail[found]].next = a; }
+      V.alnTail[found] = a;
+    } else {
+      V.alnTail[a] = a;
+      // getNumGenomicAlignments (WeightObject.java:819-880): alignments of tr- intervals only are not counted but add one in total
+      const bool trAln = (!(al.flags & 2) || (al.tr & 2)) && (!(al.flags & 4) || (al.tr & 16));
+      if (trAln) hasTr = true; else if (key_form(al, GENE) == 2) right++; else left++;   // ":r-" forms (:859-865)
+    }
   }
+  return (uint32_t)(left > right ? left : right) + (hasTr ? 1u : 0u);
+}
+
+EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, uint32_t slot) {
+  uint32_t b0 = C.blkOff[slot], b1 = C.blkOff[slot + 1];
+  V.a20[slot] = 0; V.nFinal[slot] = 0;
+  if (b0 == b1 || C.hitCnt[b0] == C.hitCnt[b1]) return;
+  uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1]; const uint32_t nA = a1 - a0;
+  const uint32_t a20 = dedupe_fragment<false>(V, a0, a1);
   // tag every hit with its representative (index within the fragment) and with the representative's half it merges into
   // (combineExons pairs mate-swapped duplicates crosswise, WeightObjectAlignment.java:312-337): a22-a25 then read the
-  // fragment's hits as one flat range instead of walking duplicate chains
+  // fragment's hits as one flat range instead of walking duplicate chains.  Fragments with tr- exon hits are left untagged: their
+  // gene run has its own dedupe (fragment_weight_gene) and HitX::grp keeps the non-tr ordinal of the interval.
   if (nA > 0xFFFFu) { raise(C.err, DERR_CAPACITY, C.base + slot); return; }
-  for (uint32_t a = a0; a < a1; a++) {
+  const bool trFrag = C.slotTr[slot] != 0;
+  if (!trFrag) for (uint32_t a = a0; a < a1; a++) {
     const Aln& al = V.alns[a]; if (al.hit0 == al.hit1) continue;
     bool sw = al.repr != a && (al.flags & 32); uint16_t g = (uint16_t)(al.repr - a0);
     for (uint32_t i = al.hit0; i < al.hit1; i++) { HitX& x = V.hx[i]; x.grp = g; if (sw) x.half = (uint8_t)(3 - x.half); }
@@ -139,7 +196,7 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
   // small fragments: regroup the hits by (representative, half, interval), stable, dropped duplicates last: the counting runs
   // then stream each fragment's hits once.  (hx is only indexed through Aln.hit0.. before this point; large fragments keep
   // their order and walk the duplicate chains.)
-  { uint32_t h0 = C.hitCnt[b0], h1 = C.hitCnt[b1];
+  if (!trFrag) { uint32_t h0 = C.hitCnt[b0], h1 = C.hitCnt[b1];
     bool sorted = true; uint64_t prev = 0;
     if (h1 - h0 <= EQP_FLAT_SCAN) for (uint32_t i = h0; i < h1; i++) { uint64_t k = hit_group_key(V.hx[i]); sorted &= k >= prev; prev = k; }   // independent loads
     if (h1 - h0 <= EQP_FLAT_SCAN && !sorted)
@@ -148,7 +205,6 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
         while (j > h0 && hit_group_key(V.hx[j - 1]) > ck) { V.hx[j] = V.hx[j - 1]; j--; }
         if (j != i) V.hx[j] = cur;
       } }
-  uint32_t a20 = (uint32_t)(left > right ? left : right);
   V.a20[slot] = a20;
   // final.wgt entry: BED weight (single-read, read index 1, n = a20) vs genome SAM weight, T+J entry as class arbiter
   FragStat bed{}; bed.nSr1 = (uint16_t)(a20 > 65535 ? 65535 : a20); bed.flags = FS_EXISTS | (1 << 2);
@@ -160,6 +216,75 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
     if (cm == 1) n = a20; else if (cm == -1) n = (uint32_t)fe_n(g); else n = (int)a20 >= fe_n(g) ? a20 : (uint32_t)fe_n(g);
   }
   V.nFinal[slot] = n;
+}
+
+// second dedupe of a fragment with tr- exon hits, under the gene run's keys (a20 can differ between the runs)
+EQP_HD void fragment_weight_gene(const ChunkView& C, const CountView& V, uint32_t slot) {
+  if (V.a20[slot] == 0) { V.a20G[slot] = 0; return; }
+  V.a20G[slot] = dedupe_fragment<true>(V, C.alnOff[slot], C.alnOff[slot + 1]);
+}
+
+// ---- a17 for a fragment with a positive lengthDifference: WeightObject.adjustGenomicAlignments (:180-204) ->
+// WeightObjectAlignment.adjustGenomicAlignmentString (:266-300) -> GenomicInterval.adjustChrStartEnd (GenomicInterval.java:284-421).
+// A sequential sweep in file order, exactly as the reference runs it: every interval with a length difference is compared with every
+// interval of the same half of every other alignment and may be snapped onto it (or snap it).  An interval lives in the records that
+// carry its rank; its first record also owns the a17 state (IvAdj).  Keys are rebuilt afterwards.
+struct IvRef { uint32_t first; uint32_t s0, s1; uint16_t rank; int32_t refId; };
+EQP_HD bool iv_find(const CountView& V, uint32_t s0, uint32_t s1, int rank, uint32_t& first) {
+  for (uint32_t i = s0; i < s1; i++) { const HitX& x = V.hx[i]; if ((x.flags & 1) && x.ivRank == rank) { first = i; return true; } }
+  return false;
+}
+EQP_HD void iv_move(const CountView& V, const IvRef& x, int32_t gs, int32_t ge, int32_t ld) {
+  for (uint32_t i = x.s0; i < x.s1; i++) { HitX& h = V.hx[i]; if ((h.flags & 1) && h.ivRank == x.rank) { h.gs = gs; h.ge = ge; } }
+  V.ivAdj[x.first].ld = ld;
+}
+// GenomicInterval.adjustChrStartEnd(GenomicInterval) :284-358
+EQP_HD bool adjust_pair(const CountView& V, const IvRef& x0, const IvRef& y0) {
+  const IvRef* px = &x0; const IvRef* py = &y0;
+  { const HitX& hx = V.hx[px->first]; const HitX& hy = V.hx[py->first];
+    if (hx.chr != hy.chr) return false;
+    if (px->refId == py->refId) return false;
+    if (hx.gs == hy.gs && hx.ge == hy.ge) return false;
+    const int32_t xld = V.ivAdj[px->first].ld, yld = V.ivAdj[py->first].ld;
+    if (xld < yld || (xld == yld && hx.gs < hy.gs)) { const IvRef* t = px; px = py; py = t; } }   // the recursive call with swapped roles (:303-316)
+  const IvRef& x = *px; const IvRef& y = *py;
+  const HitX& hx = V.hx[x.first]; const HitX& hy = V.hx[y.first];
+  const int32_t xld = V.ivAdj[x.first].ld, yld = V.ivAdj[y.first].ld;
+  int32_t lx = hx.ge - hx.gs, ly = hy.ge - hy.gs; if (lx < 0) lx = -lx; if (ly < 0) ly = -ly;
+  int32_t d = V.ivAdj[y.first].orig - V.ivAdj[x.first].orig; if (d < 0) d = -d;
+  if (lx == ly && d <= xld && (xld > yld || (xld == yld && hx.gs > hy.gs))) { iv_move(V, x, hy.gs, hy.ge, yld); return true; }
+  return false;
+}
+EQP_HD void fragment_adjust(const AnnoView& A, const ChunkView& C, const CountView& V, uint32_t slot) {
+  uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1];
+  for (uint32_t a = a0; a < a1; a++) {                                     // a17 state of every interval
+    const Aln& al = V.alns[a];
+    for (uint32_t i = al.hit0; i < al.hit1; i++) { const HitX& x = V.hx[i]; if (x.flags & 1) { V.ivAdj[i].ld = record_ld(A, C, C.hits[i]); V.ivAdj[i].orig = x.gs; } }
+  }
+  for (uint32_t a = a0; a < a1; a++) {
+    const Aln& al = V.alns[a]; if (al.hit0 == al.hit1) continue;
+    const int32_t refA = A.bktRefId[C.blocks[C.hits[al.hit0].block].bucket];
+    for (int h = 1; h <= 2; h++) {
+      if (!(al.flags & (h == 1 ? 2 : 4))) continue;
+      IvRef x; x.s0 = h == 1 ? al.hit0 : al.split; x.s1 = h == 1 ? al.split : al.hit1; x.refId = refA;
+      const int nIv = h == 1 ? al.nIv1 : al.nIv2;
+      for (int r = 0; r < nIv; r++) {
+        if (!iv_find(V, x.s0, x.s1, r, x.first)) continue;
+        x.rank = (uint16_t)r;
+        if (V.ivAdj[x.first].ld == 0) continue;
+        for (uint32_t a2 = a0; a2 < a1; a2++) {
+          // The reference skips alignments whose string equals the (partly rebuilt) string of this one; for those adjust_pair cannot
+          // act anyway: it needs a different reference id and different coordinates of equal length within 3 bp, which two intervals
+          // of one read alignment never have.  The alignment itself is excluded by the reference-id test.
+          const Aln& bl = V.alns[a2]; if (bl.hit0 == bl.hit1 || !(bl.flags & (h == 1 ? 2 : 4))) continue;
+          IvRef y; y.s0 = h == 1 ? bl.hit0 : bl.split; y.s1 = h == 1 ? bl.split : bl.hit1; y.refId = A.bktRefId[C.blocks[C.hits[bl.hit0].block].bucket];
+          const int nIv2 = h == 1 ? bl.nIv1 : bl.nIv2;
+          for (int r2 = 0; r2 < nIv2; r2++) { if (!iv_find(V, y.s0, y.s1, r2, y.first)) continue; y.rank = (uint16_t)r2; adjust_pair(V, x, y); }
+        }
+      }
+    }
+  }
+  for (uint32_t a = a0; a < a1; a++) { Aln& al = V.alns[a]; if (al.hit0 != al.hit1) al.key = alignment_key(V, al, false); }
 }
 
 // ---- stage C: conforming features + accumulation for one run (mode)
@@ -204,8 +329,8 @@ EQP_HD bool junction_pair(const AnnoView& A, const CountView& V, ExonSet& ea, in
     uint32_t va = F[i], vb = F[j], ia = va & 0x7fffffffu, ib = vb & 0x7fffffffu;
     if (ia < ib) i++; else if (ib < ia) j++;
     else {
-      bool act = ((va & vb) >> 31) != 0 || V.junctionActive[ia] != 0;    // a row survives the chunk's map filter (a27) or is in the transcript map
-      bool pa = (va >> 31) || act, pb = (vb >> 31) || act;
+      // a row survives the chunk's map filter (a27) or is in the transcript map
+      bool pa = (va >> 31) || V.junctionActive[A.featAct ? A.featAct[i] : ia] != 0, pb = (vb >> 31) || V.junctionActive[A.featAct ? A.featAct[j] : ib] != 0;
       if (pa && pb) { if (out.n >= EQP_FS_CAP) { overflow = true; return true; } out.id[out.n] = ia; out.mask[out.n] = 0; out.n++; }
       i++; j++;
     }
@@ -217,15 +342,16 @@ EQP_HD bool interval_features(const AnnoView& A, const ChunkView& C, const Count
   if (e.over) { raise(C.err, DERR_CAPACITY, frag); return false; }
   int ne = exon_filter(A, e, gs, ge); int32_t* exon = e.exon;
   if (mode == MODE_EXON && P.unambiguous[mode] && ne >= 2) ne = 0;      // -U with genomicIntervalMode (:603-608)
+  const uint32_t bit = field >= 0 ? 1u << field : 0u;                   // a tr- record of the junction run has no field (:638-656)
   for (int q = 0; q < ne; q++) {
     int ex = exon[q]; uint32_t f0 = A.featOff[mode][ex], f1 = A.featOff[mode][ex + 1]; bool any = false;
     for (uint32_t f = f0; f < f1; f++) {
       uint32_t v = A.feat[mode][f]; uint32_t id = v & 0x7fffffffu;
-      if (mode == MODE_JUNCTION && !(v & 0x80000000u) && !V.junctionActive[id]) continue;   // row removed by the per-chunk map filter (a27)
+      if (mode == MODE_JUNCTION && !(v & 0x80000000u) && !V.junctionActive[A.featAct ? A.featAct[f] : id]) continue;   // row removed by the per-chunk map filter (a27)
       any = true;
-      if (!fs_add(fs, id, 1u << field)) { raise(C.err, DERR_CAPACITY, frag); return false; }
+      if (!fs_add(fs, id, bit)) { raise(C.err, DERR_CAPACITY, frag); return false; }
     }
-    if (!any && !fs_add(fs, (uint32_t)A.nFeat[mode] + (uint32_t)ex, 1u << field)) { raise(C.err, DERR_CAPACITY, frag); return false; }   // unknown exon: own pseudo id
+    if (!any && !fs_add(fs, (uint32_t)A.nFeat[mode] + (uint32_t)ex, bit)) { raise(C.err, DERR_CAPACITY, frag); return false; }   // unknown exon: own pseudo id
   }
   return true;
 }
@@ -242,21 +368,32 @@ EQP_HD void conforming_features(const FeatSet& fs, int mode, int maxField, FeatS
 }
 
 // features of half `h` of representative alignment R (index r) with all merged duplicates folded in: duplicate-chain walk
-// (fragments with more than EQP_FLAT_SCAN hits; smaller ones are regrouped by fragment_weight and streamed, see fragment_count)
-EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t r, int h, FeatSet& out, uint32_t frag) {
+// (fragments with more than EQP_FLAT_SCAN hits, and fragments with tr- exon hits; the others are regrouped by fragment_weight and
+// streamed, see fragment_count).  trFrag: the hits are untagged (HitX::half is the read index, HitX::grp the non-tr ordinal), the
+// gene run walks the AlnG chains, and outside the gene run duplicates pair their non-tr intervals by ordinal while tr- intervals keep
+// the representative's own exons only (GenomicAlignment.combineExons skips intervals that print "", :721-786).
+EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t r, int h, bool trFrag, FeatSet& out, uint32_t frag) {
   const Aln& R = V.alns[r]; out.n = 0;
   int nIv = h == 1 ? R.nIv1 : R.nIv2; int maxField = h == 1 ? R.maxField1 : R.maxField2;
   if (maxField >= 32) { raise(C.err, DERR_CAPACITY, frag); return; }
   if (mode == MODE_JUNCTION && nIv < 2) return;                            // a junction needs two consecutive fields (:679-701)
+  const bool useG = trFrag && mode == MODE_GENE;
+  const uint32_t r0 = h == 1 ? R.hit0 : R.split, r1 = h == 1 ? R.split : R.hit1;
   FeatSet fs; fs.n = 0;
   for (int iv = 0; iv < nIv; iv++) {
-    int32_t gs = 0, ge = 0; int field = 0; bool haveIv = false; ExonSet e; e.n = 0; e.over = false;
-    for (uint32_t d = r; d != 0xFFFFFFFFu; d = V.alns[d].next) {          // R first, then later duplicates in file order
+    int32_t gs = 0, ge = 0; int field = 0; bool haveIv = false, trIv = false; uint16_t ord = 0; ExonSet e; e.n = 0; e.over = false;
+    if (trFrag) { uint32_t f; if (iv_find(V, r0, r1, iv, f)) { trIv = V.hx[f].chr <= -2; ord = V.hx[f].grp; } }
+    for (uint32_t d = r; d != 0xFFFFFFFFu; d = useG ? V.alnG[d].next : V.alns[d].next) {          // R first, then later duplicates in file order
       const Aln& D = V.alns[d];
+      const bool sw = trFrag && d != r && ((useG ? V.alnG[d].flags : D.flags) & 32);
+      if (trFrag && d != r && trIv && !useG) break;
       for (uint32_t i = D.hit0; i < D.hit1; i++) {
         const HitX& x = V.hx[i];
-        if (x.half != h || !(x.flags & 1) || x.ivRank != iv) continue;
-        if (!haveIv) { gs = x.gs; ge = x.ge; field = x.ivField; haveIv = true; }   // R's own first record of the interval
+        if (!(x.flags & 1)) continue;
+        if ((sw ? 3 - x.half : x.half) != h) continue;
+        if (trFrag && d != r && !useG) { if (x.grp != ord) continue; }
+        else if (x.ivRank != iv) continue;
+        if (!haveIv) { gs = x.gs; ge = x.ge; field = mode == MODE_JUNCTION ? x.ivFieldJ : x.ivField; haveIv = true; }   // R's own first record of the interval
         if (x.flags & (4 << mode)) exon_add(e, x);
       }
     }
@@ -274,9 +411,12 @@ EQP_HD void atomic_add_u64(unsigned long long* p, unsigned long long v) {
 }
 
 // returns 0 = the fragment is no weight object, 1 = it added to a count, 2 = it was excluded (or aborted on a capacity error)
-EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t slot) {
-  uint32_t a20 = V.a20[slot];
-  if (a20 == 0) return 0;
+// wsum: the fragment's weightAdded (sum of its contributions, printed ids or not, ComputeCounts.java:772,849) in 2^-32 units
+EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t slot, uint64_t& wsum) {
+  wsum = 0;
+  const bool trFrag = C.slotTr[slot] != 0;
+  uint32_t a20 = trFrag && mode == MODE_GENE ? V.a20G[slot] : V.a20[slot];
+  if (V.a20[slot] == 0) return 0;
   uint32_t frag = C.base + slot; uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1];
   const uint32_t hEnd = C.hitCnt[C.blkOff[slot + 1]];                    // end of the fragment's hit range
   double w = 1.0 / (double)V.nFinal[slot];
@@ -302,7 +442,7 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
     }
   };
   const uint32_t hBeg = C.hitCnt[C.blkOff[slot]];
-  if (hEnd - hBeg <= EQP_FLAT_SCAN) {
+  if (hEnd - hBeg <= EQP_FLAT_SCAN && !trFrag) {
     // hits regrouped by fragment_weight: (representative, half, interval) runs, representatives in file order
     FeatSet fs; uint32_t i = hBeg;
     while (i < hEnd && (V.hx[i].flags & 1) && !bad) {
@@ -322,7 +462,7 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
           HitX x = V.hx[i];
           if (!(x.flags & 1) || x.grp != g || x.half != h) break;
           const int iv = x.ivRank; ExonSet& e = e2[pairShape ? (nColl & 1) : 0]; e.n = 0; e.over = false;
-          const int32_t gs = x.gs, ge = x.ge; const int field = x.ivField;   // R's own first record of the interval
+          const int32_t gs = x.gs, ge = x.ge; const int field = mode == MODE_JUNCTION ? x.ivFieldJ : x.ivField;   // R's own first record of the interval
           while (true) {
             if (x.flags & (4 << mode)) exon_add(e, x);
             if (++i >= hEnd) break;
@@ -342,11 +482,12 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
       if (!bad) merge_alignment(R.flags);
     }
   } else {
+    const bool useG = trFrag && mode == MODE_GENE;
     for (uint32_t r = a0; r < a1 && !bad; r++) {
-      const Aln& R = V.alns[r]; if (R.hit0 == R.hit1 || R.repr != r) continue;
+      const Aln& R = V.alns[r]; if (R.hit0 == R.hit1 || (useG ? V.alnG[r].repr : R.repr) != r) continue;
       s1.n = s2.n = 0;
-      if (R.flags & 2) half_features(A, C, V, P, mode, r, 1, s1, frag);
-      if (R.flags & 4) half_features(A, C, V, P, mode, r, 2, s2, frag);
+      if (R.flags & 2) half_features(A, C, V, P, mode, r, 1, trFrag, s1, frag);
+      if (R.flags & 4) half_features(A, C, V, P, mode, r, 2, trFrag, s2, frag);
       merge_alignment(R.flags);
     }
   }
@@ -358,6 +499,7 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
     double t = 0; for (int i = 0; i < k && t < 1.0; i++) t = t + addW;     // repeated addition (:100-111, :343); min(1, max(w1, w2)) (:427-428)
     double c = t < 1.0 ? t : 1.0;
     if (c > 0) added = true;
+    wsum += (uint64_t)(c * 4294967296.0 + 0.5);
     if (fid[q] < (uint32_t)A.nFeat[mode]) atomic_add_u64(&V.acc[mode][fid[q]], (unsigned long long)(c * (double)(1ULL << EQP_FIXED_SHIFT_D) + 0.5));
   }
   return added ? 1 : 2;

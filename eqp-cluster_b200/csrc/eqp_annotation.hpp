@@ -54,11 +54,16 @@ struct AnnoHost {
   std::string strPool; std::vector<uint32_t> refStrOff; std::vector<uint16_t> refStrLen; std::vector<uint8_t> refFlags;
   std::vector<uint32_t> refVerOff; std::vector<int32_t> refVerBucket;
   std::vector<uint32_t> refActOff; std::vector<int32_t> refAct;
-  std::vector<uint32_t> bktRowOff; std::vector<uint8_t> bktFlags;
+  std::vector<uint32_t> bktRowOff; std::vector<uint8_t> bktFlags; std::vector<int32_t> bktRefId;
   std::vector<int32_t> rowStart, rowEnd, rowMaxEnd, rowExon; std::vector<uint8_t> rowFlags;
   std::vector<int32_t> exChr, exStart, exEnd; std::vector<uint8_t> exStrand;
   std::vector<uint32_t> featOff[3], feat[3]; std::vector<std::string> featIds[3];
-  std::vector<std::string> chrNames, bucketNames;
+  std::vector<uint32_t> featAct; std::vector<std::string> actIds; int mapColumns[3] = {2, 2, 2};
+  // rows of the count file in print order (ComputeCounts.java:875-950): 2-column maps print every id of the map in TreeSet order,
+  // 3-column maps print one row per map line (file order; the junction map in the order filter-junction-map-files.sh:298-299 leaves it in)
+  struct OutRow { std::string id; int32_t feature; int32_t act; uint8_t always; };
+  std::vector<OutRow> outRows[3];
+  std::vector<std::string> chrNames, trChrNames, bucketNames;
 
   static std::string slurp(const char* path) {
     if (!path) throw AnnoError(-1, "annotation path is null");
@@ -131,9 +136,11 @@ struct AnnoHost {
         if (ei == exonIdx.end()) { ei = exonIdx.emplace(ks, (int32_t)exons.size()).first; exons.push_back(k); }
         rows[bi->second].push_back({atoi(t[1].c_str()), atoi(t[2].c_str()), ei->second, t[5].empty() ? '.' : t[5][0], fileIdx++});
       }); }
-    { std::set<std::string> chrs; for (auto& k : exons) if (!k.tr) chrs.insert(k.chr);
-      for (auto& c : chrs) { chrIdxTmp[c] = (int32_t)chrNames.size(); chrNames.push_back(c); } }
-    for (auto& k : exons) { exChr.push_back(k.tr ? -2 : chrIdxTmp[k.chr]); exStart.push_back(k.s); exEnd.push_back(k.e); exStrand.push_back((uint8_t)k.strand); }
+    { std::set<std::string> chrs, trs; for (auto& k : exons) (k.tr ? trs : chrs).insert(k.chr);
+      for (auto& c : chrs) { chrIdxTmp[c] = (int32_t)chrNames.size(); chrNames.push_back(c); }
+      for (auto& c : trs) { chrIdxTmp[c] = -2 - (int32_t)trChrNames.size(); trChrNames.push_back(c); } }
+    for (auto& k : exons) { exChr.push_back(chrIdxTmp[k.chr]); exStart.push_back(k.s); exEnd.push_back(k.e); exStrand.push_back((uint8_t)k.strand); }
+    std::unordered_map<std::string, int32_t> refIdTmp;
     bktRowOff.push_back(0);
     for (size_t b = 0; b < rows.size(); b++) {
       auto& v = rows[b];
@@ -141,6 +148,9 @@ struct AnnoHost {
       const std::string& name = bucketNames[b];
       bool inv = name.size() > 11 && name.compare(name.size() - 11, 11, ".inv-strand") == 0;
       bktFlags.push_back((name.find("junction") != std::string::npos ? 1 : 0) | (inv ? 2 : 0));
+      { bool genomicBucket = false; for (auto& x : v) genomicBucket |= !exons[x.exon].tr && exons[x.exon].chr == name;   // BedRecord.java:154-176
+        std::string rid = inv ? name.substr(0, name.size() - 11) : name; if (!genomicBucket) rid = stripVersion(rid);
+        bktRefId.push_back(refIdTmp.emplace(rid, (int32_t)refIdTmp.size()).first->second); }
       int maxEnd = 0;
       for (size_t i = 0; i < v.size(); i++) {
         maxEnd = std::max(maxEnd, v[i].e);
@@ -179,39 +189,64 @@ struct AnnoHost {
       while (dict[s].key) s = (s + 1) & dictMask;
       dict[s] = DictEntry{dict_key(h, (int)refNames[r].size()), r, refStrOff[r]};
     }
-    // ---- exon -> feature lists (2- or 3-column maps; 3-column maps are rejected for now)
+    // ---- exon -> feature lists.  2 columns: exon, feature id.  3 columns: exon, printed id, internal id (Exon.java:107-125): counted under
+    // the internal id, printed per map line under the printed id; the junction map's rows are switched on per chunk by their column-2 id
+    // (filter-junction-map-files.sh:286-296 filters `-I 1`), so the activation index of a junction row is the index of that id.
     const char* maps[3] = {geneMap, exonMap, junctionMap};
-    std::unordered_map<std::string, uint32_t> jFeatIdx;
+    std::unordered_map<std::string, uint32_t> jActIdx;
     for (int m = 0; m < 3; m++) {
-      std::string text = slurp(maps[m]); std::set<std::string> ids; std::vector<std::pair<std::string, std::string>> pairs;
-      std::set<std::pair<std::string, std::string>> always;
+      std::string text = slurp(maps[m]); std::set<std::string> ids, acts;
+      struct MapRow { std::string exon, printed, feat, line; bool always; };
+      std::vector<MapRow> rowsM; int columns = 2;
       auto readMap = [&](const std::string& txt, bool isAlways) {
         lines(txt, [&](const std::string& l) {
           auto t = tok(l, '\t'); if (t.empty()) throw AnnoError(-3, "No exon id found.");
           if (t[0] == "Exon Id") return;
           if (t.size() < 2) throw AnnoError(-3, "No count object for exon " + t[0] + " found on loading.");
-          if (t.size() > 2) throw AnnoError(-5, "3-column count object maps are not supported yet");
-          std::string k = keyStr(parseExon(t[0]));
-          ids.insert(t[1]); pairs.push_back({k, t[1]}); if (isAlways) always.insert({k, t[1]});
+          int fields = t.size() >= 3 ? 3 : 2;
+          // Exon.java:126-131 rejects a line with fewer columns than an earlier one; the opposite order passes the load and then fails in
+          // the 3-column writer ("No third column found", ComputeCounts.java:921-923): either way the run aborts
+          if (fields != columns && !rowsM.empty()) throw AnnoError(-3, fields < columns ? "Not all lines have " + std::to_string(columns) + " columns." : "No third column found for exon " + rowsM[0].exon + ".");
+          columns = fields;
+          rowsM.push_back({keyStr(parseExon(t[0])), t[1], fields == 3 ? t[2] : t[1], l, isAlways});
+          ids.insert(rowsM.back().feat); acts.insert(t[1]);
         });
       };
+      if (m == 2) readMap(slurp(junctionTranscriptMap), true);           // the filter puts these rows first (`cat` order is irrelevant: sort -u follows)
       readMap(text, false);
-      if (m == 2) readMap(slurp(junctionTranscriptMap), true);
+      mapColumns[m] = columns;
       featIds[m].assign(ids.begin(), ids.end());
       std::unordered_map<std::string, uint32_t> fidx; for (size_t i = 0; i < featIds[m].size(); i++) fidx[featIds[m][i]] = (uint32_t)i;
-      if (m == 2) jFeatIdx = fidx;
-      std::vector<std::vector<uint32_t>> per(exons.size());
-      for (auto& pr : pairs) {
-        auto ei = exonIdx.find(pr.first); if (ei == exonIdx.end()) continue;   // exon never reachable through the B file
-        uint32_t f = fidx[pr.second] | (m == 2 && always.count(pr) ? 0x80000000u : 0u);
+      if (m == 2) { actIds.assign(acts.begin(), acts.end()); for (size_t i = 0; i < actIds.size(); i++) jActIdx[actIds[i]] = (uint32_t)i; }
+      struct Ent { uint32_t f, act; };
+      std::vector<std::vector<Ent>> per(exons.size());
+      std::set<std::pair<std::string, std::string>> alwaysRows;
+      if (m == 2) for (auto& r : rowsM) if (r.always) alwaysRows.insert({r.exon, r.printed + "\t" + r.feat});
+      for (auto& r : rowsM) {
+        auto ei = exonIdx.find(r.exon); if (ei == exonIdx.end()) continue;   // exon never reachable through the B file
+        bool alw = m == 2 && alwaysRows.count({r.exon, r.printed + "\t" + r.feat});
+        uint32_t f = fidx[r.feat] | (alw ? 0x80000000u : 0u), act = m == 2 ? jActIdx[r.printed] : 0;
         auto& v = per[ei->second]; bool have = false;
-        for (auto& x : v) if ((x & 0x7fffffffu) == (f & 0x7fffffffu)) { x |= f; have = true; }
-        if (!have) v.push_back(f);
+        for (auto& x : v) if ((x.f & 0x7fffffffu) == (f & 0x7fffffffu) && x.act == act) { x.f |= f; have = true; }
+        if (!have) v.push_back({f, act});
       }
       featOff[m].push_back(0);
       for (auto& v : per) {                                             // by feature id: the junction run intersects two lists by merging (junction_pair)
-        std::sort(v.begin(), v.end(), [](uint32_t a, uint32_t b) { return (a & 0x7fffffffu) < (b & 0x7fffffffu); });
-        for (auto x : v) feat[m].push_back(x); featOff[m].push_back((uint32_t)feat[m].size()); }
+        std::stable_sort(v.begin(), v.end(), [](const Ent& a, const Ent& b) { return (a.f & 0x7fffffffu) < (b.f & 0x7fffffffu); });
+        for (auto& x : v) { feat[m].push_back(x.f); if (m == 2 && columns == 3) featAct.push_back(x.act); }
+        featOff[m].push_back((uint32_t)feat[m].size()); }
+      // print order
+      if (columns == 2) {
+        std::unordered_set<std::string> alwaysIds; for (auto& r : rowsM) if (r.always) alwaysIds.insert(r.feat);   // ids of exon_junction_transcript.map are in every filtered map
+        for (size_t i = 0; i < featIds[m].size(); i++) outRows[m].push_back({featIds[m][i], (int32_t)i, m == 2 ? (int32_t)jActIdx[featIds[m][i]] : 0, (uint8_t)(m != 2 || alwaysIds.count(featIds[m][i]) ? 1 : 0)});
+      }
+      else if (m != 2) { for (auto& r : rowsM) outRows[m].push_back({r.printed, (int32_t)fidx[r.feat], 0, 1}); }
+      else {                                                              // sort -u of whole lines, then a stable sort on the text from column 2 on
+        std::map<std::string, MapRow*> uniq; for (auto& r : rowsM) { auto it = uniq.find(r.line); if (it == uniq.end()) uniq[r.line] = &r; else if (r.always) it->second->always = true; }
+        std::vector<MapRow*> v; for (auto& kv : uniq) v.push_back(kv.second);
+        std::stable_sort(v.begin(), v.end(), [](const MapRow* a, const MapRow* b) { return a->line.substr(a->line.find('\t') + 1) < b->line.substr(b->line.find('\t') + 1); });
+        for (auto* r : v) outRows[m].push_back({r->printed, (int32_t)fidx[r->feat], (int32_t)jActIdx[r->printed], (uint8_t)(r->always ? 1 : 0)});
+      }
     }
     // ---- a27: which junction features does a reference id seen in the chunk keep alive?
     std::unordered_map<std::string, std::vector<std::string>> jjExt;    // internal junction id -> external ids
@@ -238,7 +273,7 @@ struct AnnoHost {
           }
           std::set<std::string> all = ext;
           for (auto& x : ext) { auto q = equiv.find(x); if (q != equiv.end()) all.insert(q->second.begin(), q->second.end()); }
-          for (auto& x : all) { auto f = jFeatIdx.find(x); if (f != jFeatIdx.end()) refAct.push_back((int32_t)f->second); }
+          for (auto& x : all) { auto f = jActIdx.find(x); if (f != jActIdx.end()) refAct.push_back((int32_t)f->second); }
         }
       }
       refActOff.push_back((uint32_t)refAct.size());
@@ -251,9 +286,10 @@ struct AnnoHost {
     v.refStrOff = refStrOff.data(); v.refStrLen = refStrLen.data(); v.refFlags = refFlags.data();
     v.refVerOff = refVerOff.data(); v.refVerBucket = refVerBucket.data(); v.refActOff = refActOff.data(); v.refAct = refAct.data();
     v.nRef = (int32_t)refStrOff.size();
-    v.bktRowOff = bktRowOff.data(); v.bktFlags = bktFlags.data(); v.nBucket = (int32_t)bktFlags.size();
+    v.bktRowOff = bktRowOff.data(); v.bktFlags = bktFlags.data(); v.bktRefId = bktRefId.data(); v.nBucket = (int32_t)bktFlags.size();
     v.rowStart = rowStart.data(); v.rowEnd = rowEnd.data(); v.rowMaxEnd = rowMaxEnd.data(); v.rowExon = rowExon.data(); v.rowFlags = rowFlags.data();
-    v.exChr = exChr.data(); v.exStart = exStart.data(); v.exEnd = exEnd.data(); v.exStrand = exStrand.data(); v.nExon = (int32_t)exChr.size();
+    v.exChr = exChr.data(); v.exStart = exStart.data(); v.exEnd = exEnd.data(); v.exStrand = exStrand.data(); v.nExon = (int32_t)exChr.size(); v.nTrChr = (int32_t)trChrNames.size();
+    v.featAct = featAct.empty() ? nullptr : featAct.data(); v.nAct = (int32_t)actIds.size();
     for (int m = 0; m < 3; m++) { v.featOff[m] = featOff[m].data(); v.feat[m] = feat[m].data(); v.nFeat[m] = (int32_t)featIds[m].size(); }
     return v;
   }

@@ -18,6 +18,7 @@ struct ChunkView {                 // everything the per-fragment stages read/wr
   uint32_t* alnBlk;                          // per alignment: its first block (nAln + 1 entries; blocks of an alignment are contiguous)
   Hit* hits;
   uint8_t* seenRef;                // a27: reference ids seen in combined SAM or junction SAM
+  uint8_t* slotTr; uint8_t* slotLd;  // per slot: the fragment has a tr- exon hit / an interval with a positive length difference (set by alignment_build)
   uint32_t* err;
 };
 
@@ -74,7 +75,8 @@ EQP_HD int record_segments(const SamView& R, uint32_t li, F&& emit, int& sumRead
 }
 
 // Pass 1 (count) and pass 2 (fill) over one fragment's combined record set.
-EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot, bool fill, uint32_t& nBlocksOut, uint32_t& nAlnOut) {
+// stranded: 0 = no, 1 = forward, 2 = backward: the block strand becomes the fragment strand (SamRecord.java:431-436,859-873)
+EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot, bool fill, int stranded, uint32_t& nBlocksOut, uint32_t& nAlnOut) {
   SetDesc sd = C.setC[slot];
   uint32_t nb = 0, na = 0; uint32_t bo = fill ? C.blkOff[slot] : 0;
   SetCursor ci{0, 0xFFFFFFFFu}; int fi; bool taken = false;             // taken: a record of this fragment was consumed as a mate (only then proc[] is read)
@@ -107,6 +109,7 @@ EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot
         const SamView& R = side ? C.sam[mateFile] : S; uint32_t li = side ? mateLine : i;
         int bedStart = R.pos[li] - 1 > 0 ? R.pos[li] - 1 : 0;
         uint8_t ridx = (uint8_t)rec_flag_read_index(R, li), paired = (R.rf[li] & RF_HASMATE) ? 1 : 0, strand = (R.flag[li] & 16) ? '-' : '+';
+        if (stranded && rf_read_index(R.rf[li]) != (stranded == 1 ? 1 : 2)) strand = strand == '+' ? '-' : '+';   // getFragmentStrand / getReverseFragmentStrand
         int sumRead; bool bad; uint32_t firstOfRec = nb;
         int nSeg = record_segments(R, li, [&](int seg, int off, int refLen, int readLen, int insSoft, int del) {
           if (readLen <= 0) return;
@@ -138,8 +141,10 @@ EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot
 }
 
 // a11 for one block: rows of the bucket overlapping [start,end) by >= 1 bp.
-EQP_HD uint32_t join_block(const AnnoView& A, const Block& b, Hit* out, uint32_t blockIdx) {
+// sameStrand: `bedtools intersect -s` (CIB:938-940 with BED_STRAND_SPECIFIC_OPTION): only rows on the block's strand
+EQP_HD uint32_t join_block(const AnnoView& A, const Block& b, Hit* out, uint32_t blockIdx, bool sameStrand) {
   if (b.bucket < 0) return 0;
+  const uint32_t wantStrand = b.strand == '+' ? 0u : 1u;
   int32_t lo = (int32_t)A.bktRowOff[b.bucket], hi = (int32_t)A.bktRowOff[b.bucket + 1];
   int32_t l = lo, h = hi;                                                // first row with start >= b.end
   while (l < h) { int32_t m = (l + h) >> 1; if (A.rowStart[m] < b.end) l = m + 1; else h = m; }
@@ -147,7 +152,7 @@ EQP_HD uint32_t join_block(const AnnoView& A, const Block& b, Hit* out, uint32_t
   for (int32_t k = l - 1; k >= lo; k--) {
     if (A.rowMaxEnd[k] <= b.start) break;
     int32_t re = A.rowEnd[k];
-    if (re > b.start) {
+    if (re > b.start && (!sameStrand || ((A.rowFlags[k] >> 1) & 3u) == wantStrand)) {
       int32_t ov = (re < b.end ? re : b.end) - (A.rowStart[k] > b.start ? A.rowStart[k] : b.start);
       if (ov >= 1) { if (out) { out[n].block = blockIdx; out[n].row = k; out[n].overlap = ov; } n++; }
     }

@@ -7,6 +7,7 @@
 #include <memory>
 #include "../../include/eqp_count.h"
 #include "eqp_cuda_backend.cuh"
+#include "eqp_nccl.h"
 
 using namespace eqpb;
 
@@ -27,31 +28,36 @@ template <class T> struct DevArray {
 struct AnnoDevice {
   DevArray<DictEntry> dict; DevArray<char> strPool; DevArray<uint32_t> refStrOff; DevArray<uint16_t> refStrLen;
   DevArray<uint8_t> refFlags; DevArray<uint32_t> refVerOff; DevArray<int32_t> refVerBucket; DevArray<uint32_t> refActOff; DevArray<int32_t> refAct;
-  DevArray<uint32_t> bktRowOff; DevArray<uint8_t> bktFlags; DevArray<int32_t> rowStart, rowEnd, rowMaxEnd, rowExon; DevArray<uint8_t> rowFlags;
+  DevArray<uint32_t> bktRowOff; DevArray<uint8_t> bktFlags; DevArray<int32_t> bktRefId; DevArray<uint32_t> featAct; DevArray<int32_t> rowStart, rowEnd, rowMaxEnd, rowExon; DevArray<uint8_t> rowFlags;
   DevArray<int32_t> exChr, exStart, exEnd; DevArray<uint8_t> exStrand; DevArray<uint32_t> featOff[3], feat[3];
   size_t bytes = 0;
   AnnoView upload(const AnnoHost& H) {
     AnnoView v = H.view();
     dict.upload(H.dict); strPool.upload(H.strPool.data(), H.strPool.size()); refStrOff.upload(H.refStrOff);
     refStrLen.upload(H.refStrLen); refFlags.upload(H.refFlags); refVerOff.upload(H.refVerOff); refVerBucket.upload(H.refVerBucket);
-    refActOff.upload(H.refActOff); refAct.upload(H.refAct); bktRowOff.upload(H.bktRowOff); bktFlags.upload(H.bktFlags);
+    refActOff.upload(H.refActOff); refAct.upload(H.refAct); bktRowOff.upload(H.bktRowOff); bktFlags.upload(H.bktFlags); bktRefId.upload(H.bktRefId); featAct.upload(H.featAct);
     rowStart.upload(H.rowStart); rowEnd.upload(H.rowEnd); rowMaxEnd.upload(H.rowMaxEnd); rowExon.upload(H.rowExon); rowFlags.upload(H.rowFlags);
     exChr.upload(H.exChr); exStart.upload(H.exStart); exEnd.upload(H.exEnd); exStrand.upload(H.exStrand);
     v.dict = dict.p; v.strPool = strPool.p; v.refStrOff = refStrOff.p; v.refStrLen = refStrLen.p; v.refFlags = refFlags.p;
     v.refVerOff = refVerOff.p; v.refVerBucket = refVerBucket.p; v.refActOff = refActOff.p; v.refAct = refAct.p;
-    v.bktRowOff = bktRowOff.p; v.bktFlags = bktFlags.p; v.rowStart = rowStart.p; v.rowEnd = rowEnd.p; v.rowMaxEnd = rowMaxEnd.p; v.rowExon = rowExon.p; v.rowFlags = rowFlags.p;
+    v.bktRowOff = bktRowOff.p; v.bktFlags = bktFlags.p; v.bktRefId = bktRefId.p; v.featAct = H.featAct.empty() ? nullptr : featAct.p; v.rowStart = rowStart.p; v.rowEnd = rowEnd.p; v.rowMaxEnd = rowMaxEnd.p; v.rowExon = rowExon.p; v.rowFlags = rowFlags.p;
     v.exChr = exChr.p; v.exStart = exStart.p; v.exEnd = exEnd.p; v.exStrand = exStrand.p;
     for (int m = 0; m < 3; m++) { featOff[m].upload(H.featOff[m]); feat[m].upload(H.feat[m]); v.featOff[m] = featOff[m].p; v.feat[m] = feat[m].p; }
     bytes = H.dict.size() * 16 + H.strPool.size() + H.refStrOff.size() * 7 + H.refVerOff.size() * 4 + H.refVerBucket.size() * 4 + H.refActOff.size() * 4 + H.refAct.size() * 4 +
-            H.bktRowOff.size() * 5 + H.rowStart.size() * 17 + H.exChr.size() * 13;
+            H.bktRowOff.size() * 9 + H.rowStart.size() * 17 + H.exChr.size() * 13 + H.featAct.size() * 4;
     for (int m = 0; m < 3; m++) bytes += (H.featOff[m].size() + H.feat[m].size()) * 4;
     return v;
   }
 };
 
-__global__ void k_add_u64(unsigned long long* __restrict__ dst, const unsigned long long* __restrict__ src, int64_t n) {
+// chunk vector (n elements, 2^-38 units) into a wide sample accumulator (2n elements): low 38 bits into the fraction limb, the rest into
+// the integer limb (include/eqp_count.h, "sample level")
+__global__ void k_add_wide(unsigned long long* __restrict__ dst, const unsigned long long* __restrict__ src, int64_t n) {
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] += src[i];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    unsigned long long v = src[i];
+    if (v) { dst[i] += v & ((1ull << EQP_FIXED_SHIFT_D) - 1); dst[n + i] += v >> EQP_FIXED_SHIFT_D; }
+  }
 }
 
 const char* derr_text(uint32_t code) {
@@ -65,21 +71,22 @@ const char* derr_text(uint32_t code) {
     case DERR_CIGAR_OP: return "unknown CIGAR operation (SamRecord.java:419-421)";
     case DERR_CIGAR_LEN: return "read length differs from the CIGAR's M+I+S (SamRecord.java:463-466)";
     case DERR_MATE_REF: return "Differing referenceName mate found (SamRecord.java:567-571)";
-    case DERR_TR_EXON: return "tr- transcript exon hit: not handled on the device yet";
-    case DERR_POS_LENDIFF: return "transcript exon longer than its genome exon: not handled on the device yet";
+    case DERR_TR_LENDIFF: return "an alignment has both a tr- exon record and a transcript/genome exon length difference: its coordinates differ between the junction run and the others (GenomicAlignment.java:233-234, BedRecord.java:417-452), not handled on the device";
+    case DERR_ACC_OVERFLOW: return "chunk has 2^26 or more fragments: a 64-bit fixed-point accumulator could overflow";
     case DERR_CAPACITY: return "a per-fragment device table overflowed";
     case DERR_GENOME_COORD: return "genomic record does not agree with its exon (BedRecord.java:669-673,683-687)";
     case DERR_INCONSISTENT: return "inconsistent records within one alignment (GenomicAlignment.java:123-148,245-300)";
     case DERR_BAD_JUNCTION_ID: return "junction reference id is not <gene>-junction-<i>-<j>:<l>:<r> (createExtendedJunctionIds.py:93-114)";
-    case DERR_STRANDED: return "strand-specific counting is not handled on the device yet";
+    case DERR_STRANDED: return "strand-specific direction must be 0 (none), 1 (forward) or 2 (backward)";
     case DERR_INT: return "integer SAM field does not parse";
     default: return "unknown device error";
   }
 }
 int derr_class(uint32_t code) {
   switch (code) {
-    case DERR_TR_EXON: case DERR_POS_LENDIFF: case DERR_STRANDED: return EQP_ERR_UNSUPPORTED;
-    case DERR_CAPACITY: return EQP_ERR_CAPACITY;
+    case DERR_TR_LENDIFF: return EQP_ERR_UNSUPPORTED;
+    case DERR_STRANDED: return EQP_ERR_ARG;
+    case DERR_CAPACITY: case DERR_ACC_OVERFLOW: return EQP_ERR_CAPACITY;
     default: return EQP_ERR_FORMAT;
   }
 }
@@ -112,6 +119,21 @@ struct eqp_ctx {
       EQP_CUDA(cudaEventRecord(c.ready[f], copyStream));
     }
   }
+  // streaming ingest (eqp_chunk_begin/feed/end): growing device text per input + a page-locked staging ring
+  static const int kStages = 4; static const size_t kStageBytes = 16u << 20;
+  struct Feed { bool active = false; char* dev[3] = {nullptr, nullptr, nullptr}; size_t len[3] = {0, 0, 0}, cap[3] = {0, 0, 0}; } feed;
+  uint8_t* stage[kStages] = {nullptr, nullptr, nullptr, nullptr}; cudaEvent_t stageFree[kStages] = {nullptr, nullptr, nullptr, nullptr}; int nextStage = 0;
+  void feed_reserve(int f, size_t want) {                           // grow on the copy stream: earlier pieces are copied over in stream order
+    if (want <= feed.cap[f]) return;
+    size_t cap = feed.cap[f] ? feed.cap[f] * 2 : (size_t)64 << 20; if (cap < want) cap = want;
+    void* d = nullptr; EQP_CUDA(cudaMallocAsync(&d, cap + 16, copyStream));
+    if (feed.len[f]) EQP_CUDA(cudaMemcpyAsync(d, feed.dev[f], feed.len[f], cudaMemcpyDeviceToDevice, copyStream));
+    if (feed.dev[f]) EQP_CUDA(cudaFreeAsync(feed.dev[f], copyStream));
+    feed.dev[f] = (char*)d; feed.cap[f] = cap;
+  }
+  void feed_drop() { for (int f = 0; f < 3; f++) { if (feed.dev[f]) cudaFreeAsync(feed.dev[f], copyStream ? copyStream : stream); } feed = Feed(); }
+  // NCCL communicator of this context (one rank per context)
+  nccl_comm_t comm = nullptr; int commRanks = 0, commRank = -1;
   void pin(void* p, size_t bytes) { if (bytes && cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) pinned.push_back(p); else cudaGetLastError(); }
   void unpin() { for (void* p : pinned) cudaHostUnregister(p); pinned.clear(); }
 };
@@ -141,7 +163,9 @@ int eqp_create(int device, eqp_ctx** out) {
     std::unique_ptr<eqp_ctx> c(new eqp_ctx); c->device = device;
     EQP_CUDA(cudaSetDevice(device));
     cudaDeviceProp prop; EQP_CUDA(cudaGetDeviceProperties(&prop, device)); c->nSm = prop.multiProcessorCount;
-    EQP_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    // a blocking stream: ordered against the legacy default stream, on which a caller (torch) typically prepares device-resident
+    // inputs and accumulators (include/eqp_count.h, eqp_accumulate)
+    EQP_CUDA(cudaStreamCreate(&c->stream));
     cudaMemPool_t pool; EQP_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
     uint64_t keep = ~0ULL; EQP_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));   // keep chunk buffers cached between chunks
     EQP_CUDA(cudaEventCreate(&c->ev0)); EQP_CUDA(cudaEventCreate(&c->ev1));
@@ -163,7 +187,7 @@ int eqp_load_annotation(eqp_ctx* ctx, const eqp_annotation_files* f) {
     // result buffers: sized once per annotation and page-locked, so the per-chunk D2H of the count vectors runs at PCIe speed
     ctx->unpin();
     for (int m = 0; m < 3; m++) { ctx->R.fixed[m].assign((size_t)ctx->A.nFeat[m], 0); ctx->R.counts[m].assign((size_t)ctx->A.nFeat[m], 0.0); }
-    ctx->R.junctionActive.assign((size_t)ctx->A.nFeat[2], 0);
+    ctx->R.junctionActive.assign((size_t)ctx->A.nAct, 0);
     for (int m = 0; m < 3; m++) ctx->pin(ctx->R.fixed[m].data(), ctx->R.fixed[m].size() * 8);
     ctx->pin(ctx->R.junctionActive.data(), ctx->R.junctionActive.size());
     ctx->annoLoaded = true; ctx->haveChunk = false; return EQP_OK;
@@ -174,73 +198,141 @@ int eqp_load_annotation(eqp_ctx* ctx, const eqp_annotation_files* f) {
 
 int64_t eqp_annotation_bytes(eqp_ctx* ctx) { return ctx && ctx->annoLoaded ? (int64_t)ctx->D.bytes : 0; }
 
+// Count the chunk whose three texts are in device memory (text/len); ready[f] (may be null) = event after which text f is complete.
+static int run_chunk(eqp_ctx* ctx, const eqp_params* p, const char* const text[3], const uint64_t len[3], cudaEvent_t const ready[3], eqp_counts* out) {
+  auto wall = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  double w0 = wall();
+  ctx->haveChunk = false; ctx->pl.reset(); ctx->be.reset();          // frees the previous chunk's device buffers (stream-ordered)
+  double w1 = wall();
+  ctx->be.reset(new CudaBackend(ctx->stream, ctx->nSm));
+  RunParams P{};
+  P.overlap[0] = p->gene_overlap; P.overlap[1] = p->exon_overlap; P.overlap[2] = p->junction_overlap;
+  P.spliceConforming[0] = P.spliceConforming[1] = p->nonsplice_conforming ? 0 : 1; P.spliceConforming[2] = 1;   // CC:932-935,959-960,1034-1035
+  P.containment[0] = p->containment ? 1 : 0; P.containment[1] = P.containment[2] = 0;
+  P.unambiguous[0] = P.unambiguous[1] = p->unambiguous ? 1 : 0; P.unambiguous[2] = 0;
+  P.unweighted = p->unweighted ? 1 : 0; P.modes = (uint8_t)(p->modes & 7); P.weightThreshold = p->read_weight_threshold; P.slack = p->distance_slack;
+  P.stranded = (uint8_t)p->stranded;
+  for (int f = 0; f < 3; f++) ctx->be->inputReady[f] = ready ? ready[f] : nullptr;
+  ctx->pl.reset(new Pipeline<CudaBackend>(*ctx->be, ctx->A, P));
+  double w2 = wall();
+  EQP_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+  memset(ctx->R.stats, 0, sizeof ctx->R.stats); memset(ctx->R.err, 0, sizeof ctx->R.err); memset(ctx->R.nRecords, 0, sizeof ctx->R.nRecords);   // the count vectors keep their (page-locked) storage
+  int rc = ctx->pl->run(text, len, ctx->R);
+  if (rc == 0) {
+    int64_t off = 0;
+    for (int m = 0; m < 3; m++) { if (ctx->A.nFeat[m]) EQP_CUDA(cudaMemcpyAsync(ctx->vec + off, ctx->pl->V.acc[m], (size_t)ctx->A.nFeat[m] * 8, cudaMemcpyDeviceToDevice, ctx->stream)); off += ctx->A.nFeat[m]; }
+  }
+  EQP_CUDA(cudaEventRecord(ctx->ev1, ctx->stream)); EQP_CUDA(cudaEventSynchronize(ctx->ev1));
+  float ms = 0; EQP_CUDA(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  ctx->retire(ctx->current, ctx->stream);                           // the text is not needed once the results are on the host
+  ctx->be->finish_timing(); ctx->be->report_stages();
+  if (ctx->be->timing) fprintf(stderr, "[eqp host ] release %.3f ms, setup %.3f ms, run (events %.3f) %.3f ms wall\n", w1 - w0, w2 - w1, ms, wall() - w2);
+  if (rc) {
+    char buf[512]; snprintf(buf, sizeof buf, "%s [code %u, detail %u]", derr_text(ctx->R.err[0]), ctx->R.err[0], ctx->R.err[1]);
+    return fail(ctx, derr_class(ctx->R.err[0]), buf);
+  }
+  const ChunkResult& R = ctx->R;
+  out->n_gene = ctx->A.nFeat[0]; out->n_exon = ctx->A.nFeat[1]; out->n_junction = ctx->A.nFeat[2]; out->n_junction_act = ctx->A.nAct;
+  out->gene = R.counts[0].data(); out->exon = R.counts[1].data(); out->junction = R.counts[2].data();
+  out->gene_fixed = (const uint64_t*)R.fixed[0].data(); out->exon_fixed = (const uint64_t*)R.fixed[1].data(); out->junction_fixed = (const uint64_t*)R.fixed[2].data();
+  out->junction_active = R.junctionActive.data();
+  out->number_mapped_reads = (int64_t)R.stats[9]; out->number_expressed_reads = (int64_t)R.stats[1];
+  for (int m = 0; m < 3; m++) { out->num_weight_objects[m] = (int64_t)R.stats[m * 3]; out->num_weight_objects_included[m] = (int64_t)R.stats[m * 3 + 1]; out->num_weight_objects_excluded[m] = (int64_t)R.stats[m * 3 + 2]; out->n_records[m] = R.nRecords[m];
+    out->sum_weights[m] = (double)R.stats[10 + m] / 4294967296.0; }
+  out->device_ms = ms; out->dominant_kernel_ms = ctx->be->decodeMs; out->kernel_launches = ctx->be->launches;
+  ctx->haveChunk = true; return EQP_OK;
+}
+
+static int check_params(eqp_ctx* ctx, const eqp_params* p) {
+  if (p->stranded < 0 || p->stranded > 2) return fail(ctx, EQP_ERR_ARG, derr_text(DERR_STRANDED));
+  return EQP_OK;
+}
+
 int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, size_t t_len, const uint8_t* j_sam, size_t j_len,
                     const uint8_t* g_sam, size_t g_len, int on_device, eqp_counts* out) {
   if (!ctx || !p || !out) return fail(ctx, EQP_ERR_ARG, "eqp_count_chunk: null argument");
   if (!ctx->annoLoaded) return fail(ctx, EQP_ERR_ARG, "eqp_count_chunk: call eqp_load_annotation first");
   if ((t_len && !t_sam) || (j_len && !j_sam) || (g_len && !g_sam)) return fail(ctx, EQP_ERR_ARG, "eqp_count_chunk: null SAM buffer with non-zero length");
-  if (p->stranded) return fail(ctx, EQP_ERR_UNSUPPORTED, derr_text(DERR_STRANDED));
+  if (ctx->feed.active) return fail(ctx, EQP_ERR_ARG, "eqp_count_chunk: a streamed chunk is open (eqp_chunk_begin without eqp_chunk_end)");
+  if (int rc = check_params(ctx, p)) return rc;
   memset(out, 0, sizeof *out);
   try {
-    auto wall = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
-    double w0 = wall();
     EQP_CUDA(cudaSetDevice(ctx->device));
-    ctx->haveChunk = false; ctx->pl.reset(); ctx->be.reset();        // frees the previous chunk's device buffers (stream-ordered)
-    double w1 = wall();
-    ctx->be.reset(new CudaBackend(ctx->stream, ctx->nSm));
-    RunParams P{};
-    P.overlap[0] = p->gene_overlap; P.overlap[1] = p->exon_overlap; P.overlap[2] = p->junction_overlap;
-    P.spliceConforming[0] = P.spliceConforming[1] = p->nonsplice_conforming ? 0 : 1; P.spliceConforming[2] = 1;   // CC:932-935,959-960,1034-1035
-    P.containment[0] = p->containment ? 1 : 0; P.containment[1] = P.containment[2] = 0;
-    P.unambiguous[0] = P.unambiguous[1] = p->unambiguous ? 1 : 0; P.unambiguous[2] = 0;
-    P.unweighted = p->unweighted ? 1 : 0; P.modes = (uint8_t)(p->modes & 7); P.weightThreshold = p->read_weight_threshold; P.slack = p->distance_slack;
     const uint8_t* src[3] = {t_sam, j_sam, g_sam}; uint64_t len[3] = {t_len, j_len, g_len}; const char* text[3];
     ctx->retire(ctx->current, ctx->stream);
-    if (on_device) { for (int f = 0; f < 3; f++) text[f] = (const char*)src[f]; }
-    else {
-      // host buffers: the copies run on the copy stream and the tokenizer of input f waits for copy f only, so tokenizing overlaps the
-      // later copies.  A chunk announced with eqp_prefetch_chunk is already on its way (or resident).
-      bool pre = false;
-      if (!ctx->prefetched.empty()) {
-        const eqp_ctx::HostChunk& q = ctx->prefetched.front(); pre = true;
-        for (int f = 0; f < 3; f++) pre = pre && q.src[f] == src[f] && q.len[f] == len[f];
-        if (pre) { ctx->current = q; ctx->prefetched.pop_front(); }
-        else {                                                      // not the announced chunk: the announcements are dropped, this chunk is copied now
-          EQP_CUDA(cudaStreamSynchronize(ctx->copyStream));
-          for (auto& c : ctx->prefetched) ctx->retire(c, ctx->copyStream);
-          ctx->prefetched.clear();
-        }
+    if (on_device) { for (int f = 0; f < 3; f++) text[f] = (const char*)src[f]; return run_chunk(ctx, p, text, len, nullptr, out); }
+    // host buffers: the copies run on the copy stream and the tokenizer of input f waits for copy f only, so tokenizing overlaps the
+    // later copies.  A chunk announced with eqp_prefetch_chunk is already on its way (or resident).
+    bool pre = false;
+    if (!ctx->prefetched.empty()) {
+      const eqp_ctx::HostChunk& q = ctx->prefetched.front(); pre = true;
+      for (int f = 0; f < 3; f++) pre = pre && q.src[f] == src[f] && q.len[f] == len[f];
+      if (pre) { ctx->current = q; ctx->prefetched.pop_front(); }
+      else {                                                      // not the announced chunk: the announcements are dropped, this chunk is copied now
+        EQP_CUDA(cudaStreamSynchronize(ctx->copyStream));
+        for (auto& c : ctx->prefetched) ctx->retire(c, ctx->copyStream);
+        ctx->prefetched.clear();
       }
-      if (!pre) { for (int f = 0; f < 3; f++) { ctx->current.src[f] = src[f]; ctx->current.len[f] = len[f]; } ctx->start_copy(ctx->current); }
-      for (int f = 0; f < 3; f++) { text[f] = ctx->current.dev[f]; ctx->be->inputReady[f] = ctx->current.ready[f]; }
     }
-    ctx->pl.reset(new Pipeline<CudaBackend>(*ctx->be, ctx->A, P));
-    double w2 = wall();
-    EQP_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
-    memset(ctx->R.stats, 0, sizeof ctx->R.stats); memset(ctx->R.err, 0, sizeof ctx->R.err); memset(ctx->R.nRecords, 0, sizeof ctx->R.nRecords);   // the count vectors keep their (page-locked) storage
-    int rc = ctx->pl->run(text, len, ctx->R);
-    if (rc == 0) {
-      int64_t off = 0;
-      for (int m = 0; m < 3; m++) { if (ctx->A.nFeat[m]) EQP_CUDA(cudaMemcpyAsync(ctx->vec + off, ctx->pl->V.acc[m], (size_t)ctx->A.nFeat[m] * 8, cudaMemcpyDeviceToDevice, ctx->stream)); off += ctx->A.nFeat[m]; }
+    if (!pre) { for (int f = 0; f < 3; f++) { ctx->current.src[f] = src[f]; ctx->current.len[f] = len[f]; } ctx->start_copy(ctx->current); }
+    for (int f = 0; f < 3; f++) text[f] = ctx->current.dev[f];
+    return run_chunk(ctx, p, text, len, ctx->current.ready, out);
+  } catch (const CudaError& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+  catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+
+int eqp_chunk_begin(eqp_ctx* ctx, size_t t_hint, size_t j_hint, size_t g_hint) {
+  if (!ctx) return fail(ctx, EQP_ERR_ARG, "eqp_chunk_begin: null context");
+  if (!ctx->annoLoaded) return fail(ctx, EQP_ERR_ARG, "eqp_chunk_begin: call eqp_load_annotation first");
+  try {
+    EQP_CUDA(cudaSetDevice(ctx->device));
+    if (!ctx->copyStream) EQP_CUDA(cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+    if (ctx->feed.active) ctx->feed_drop();                         // an abandoned stream
+    for (int k = 0; k < eqp_ctx::kStages; k++) if (!ctx->stage[k]) {
+      EQP_CUDA(cudaHostAlloc((void**)&ctx->stage[k], eqp_ctx::kStageBytes, cudaHostAllocDefault));
+      EQP_CUDA(cudaEventCreateWithFlags(&ctx->stageFree[k], cudaEventDisableTiming));
     }
-    EQP_CUDA(cudaEventRecord(ctx->ev1, ctx->stream)); EQP_CUDA(cudaEventSynchronize(ctx->ev1));
-    float ms = 0; EQP_CUDA(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
-    ctx->retire(ctx->current, ctx->stream);                         // the text is not needed once the results are on the host
-    ctx->be->finish_timing(); ctx->be->report_stages();
-    if (ctx->be->timing) fprintf(stderr, "[eqp host ] release %.3f ms, setup %.3f ms, run (events %.3f) %.3f ms wall\n", w1 - w0, w2 - w1, ms, wall() - w2);
-    if (rc) {
-      char buf[512]; snprintf(buf, sizeof buf, "%s [code %u, detail %u]", derr_text(ctx->R.err[0]), ctx->R.err[0], ctx->R.err[1]);
-      return fail(ctx, derr_class(ctx->R.err[0]), buf);
+    ctx->feed.active = true;
+    size_t hint[3] = {t_hint, j_hint, g_hint};
+    for (int f = 0; f < 3; f++) ctx->feed_reserve(f, hint[f] ? hint[f] : 1);
+    return EQP_OK;
+  } catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+
+int eqp_chunk_feed(eqp_ctx* ctx, int input, const uint8_t* buf, size_t len) {
+  if (!ctx || input < 0 || input > 2 || (len && !buf)) return fail(ctx, EQP_ERR_ARG, "eqp_chunk_feed: bad argument");
+  if (!ctx->feed.active) return fail(ctx, EQP_ERR_ARG, "eqp_chunk_feed: call eqp_chunk_begin first");
+  try {
+    EQP_CUDA(cudaSetDevice(ctx->device));
+    eqp_ctx::Feed& F = ctx->feed;
+    ctx->feed_reserve(input, F.len[input] + len);
+    for (size_t off = 0; off < len;) {
+      size_t piece = std::min(len - off, eqp_ctx::kStageBytes); int k = ctx->nextStage; ctx->nextStage = (k + 1) % eqp_ctx::kStages;
+      EQP_CUDA(cudaEventSynchronize(ctx->stageFree[k]));              // the copy that last used this staging buffer has finished
+      memcpy(ctx->stage[k], buf + off, piece);
+      EQP_CUDA(cudaMemcpyAsync(F.dev[input] + F.len[input], ctx->stage[k], piece, cudaMemcpyHostToDevice, ctx->copyStream));
+      EQP_CUDA(cudaEventRecord(ctx->stageFree[k], ctx->copyStream));
+      F.len[input] += piece; off += piece;
     }
-    const ChunkResult& R = ctx->R;
-    out->n_gene = ctx->A.nFeat[0]; out->n_exon = ctx->A.nFeat[1]; out->n_junction = ctx->A.nFeat[2];
-    out->gene = R.counts[0].data(); out->exon = R.counts[1].data(); out->junction = R.counts[2].data();
-    out->gene_fixed = (const uint64_t*)R.fixed[0].data(); out->exon_fixed = (const uint64_t*)R.fixed[1].data(); out->junction_fixed = (const uint64_t*)R.fixed[2].data();
-    out->junction_active = R.junctionActive.data();
-    out->number_mapped_reads = (int64_t)R.stats[9]; out->number_expressed_reads = (int64_t)R.stats[1];
-    for (int m = 0; m < 3; m++) { out->num_weight_objects[m] = (int64_t)R.stats[m * 3]; out->num_weight_objects_included[m] = (int64_t)R.stats[m * 3 + 1]; out->num_weight_objects_excluded[m] = (int64_t)R.stats[m * 3 + 2]; out->n_records[m] = R.nRecords[m]; }
-    out->device_ms = ms; out->dominant_kernel_ms = ctx->be->decodeMs; out->kernel_launches = ctx->be->launches;
-    ctx->haveChunk = true; return EQP_OK;
+    return EQP_OK;
+  } catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+
+int eqp_chunk_end(eqp_ctx* ctx, const eqp_params* p, eqp_counts* out) {
+  if (!ctx || !p || !out) return fail(ctx, EQP_ERR_ARG, "eqp_chunk_end: null argument");
+  if (!ctx->feed.active) return fail(ctx, EQP_ERR_ARG, "eqp_chunk_end: call eqp_chunk_begin first");
+  if (int rc = check_params(ctx, p)) return rc;
+  memset(out, 0, sizeof *out);
+  try {
+    EQP_CUDA(cudaSetDevice(ctx->device));
+    ctx->retire(ctx->current, ctx->stream);
+    eqp_ctx::HostChunk c{}; const char* text[3]; uint64_t len[3];
+    for (int f = 0; f < 3; f++) { c.dev[f] = ctx->feed.dev[f]; c.len[f] = ctx->feed.len[f]; text[f] = c.dev[f]; len[f] = c.len[f]; }
+    EQP_CUDA(cudaEventCreateWithFlags(&c.ready[0], cudaEventDisableTiming)); EQP_CUDA(cudaEventRecord(c.ready[0], ctx->copyStream));
+    ctx->feed = eqp_ctx::Feed();                                    // ownership of the device texts moves to `current` (freed when the chunk is done)
+    ctx->current = c;
+    cudaEvent_t ready[3] = {c.ready[0], nullptr, nullptr};          // one event after the last piece covers all three inputs
+    return run_chunk(ctx, p, text, len, ready, out);
   } catch (const CudaError& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
   catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
 }
@@ -267,6 +359,14 @@ const char* eqp_feature_id(eqp_ctx* ctx, int mode, int64_t i) {
   return ctx->H.featIds[mode][(size_t)i].c_str();
 }
 
+int eqp_map_columns(eqp_ctx* ctx, int mode) { return (ctx && ctx->annoLoaded && mode >= 0 && mode < 3) ? ctx->H.mapColumns[mode] : -1; }
+int64_t eqp_output_row_count(eqp_ctx* ctx, int mode) { return (ctx && ctx->annoLoaded && mode >= 0 && mode < 3) ? (int64_t)ctx->H.outRows[mode].size() : -1; }
+int eqp_get_output_row(eqp_ctx* ctx, int mode, int64_t i, eqp_output_row* out) {
+  if (!ctx || !out || !ctx->annoLoaded || mode < 0 || mode > 2 || i < 0 || i >= (int64_t)ctx->H.outRows[mode].size()) return fail(ctx, EQP_ERR_ARG, "eqp_get_output_row: bad argument");
+  const AnnoHost::OutRow& r = ctx->H.outRows[mode][(size_t)i];
+  out->id = r.id.c_str(); out->feature = r.feature; out->act = r.act; out->always = r.always; out->reserved = 0; return EQP_OK;
+}
+
 int eqp_device_vector(eqp_ctx* ctx, uint64_t** dev_ptr, int64_t* n) {
   if (!ctx || !dev_ptr || !n) return fail(ctx, EQP_ERR_ARG, "eqp_device_vector: null argument");
   if (!ctx->haveChunk) return fail(ctx, EQP_ERR_ARG, "eqp_device_vector: no chunk counted yet");
@@ -277,9 +377,70 @@ int eqp_accumulate(eqp_ctx* ctx, uint64_t* acc) {
   if (!ctx->haveChunk) return fail(ctx, EQP_ERR_ARG, "eqp_accumulate: no chunk counted yet");
   try {
     EQP_CUDA(cudaSetDevice(ctx->device));
-    if (ctx->vecLen) k_add_u64<<<ctx->nSm * 4, 256, 0, ctx->stream>>>((unsigned long long*)acc, ctx->vec, ctx->vecLen);
+    if (ctx->vecLen) k_add_wide<<<ctx->nSm * 4, 256, 0, ctx->stream>>>((unsigned long long*)acc, ctx->vec, ctx->vecLen);
     EQP_CUDA(cudaGetLastError()); EQP_CUDA(cudaStreamSynchronize(ctx->stream)); return EQP_OK;
   } catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+void eqp_wide_to_double(const uint64_t* wide, int64_t n, double* out) {
+  if (!wide || !out) return;
+  const double scale = 1.0 / (double)(1ULL << EQP_FIXED_SHIFT_D);
+  for (int64_t i = 0; i < n; i++) out[i] = (double)wide[n + i] + (double)wide[i] * scale;
+}
+
+// ---- NCCL inside the library (eqp_nccl.h)
+int eqp_comm_id(void* id_out) {
+  if (!id_out) return fail(nullptr, EQP_ERR_ARG, "eqp_comm_id: null argument");
+  NcclApi& N = nccl_api(); if (!N.load()) return fail(nullptr, EQP_ERR_NCCL, N.error);
+  nccl_unique_id id; int rc = N.GetUniqueId(&id);
+  if (rc != NCCL_SUCCESS) return fail(nullptr, EQP_ERR_NCCL, "ncclGetUniqueId: " + N.text(rc));
+  static_assert(sizeof id == EQP_COMM_ID_BYTES, "ncclUniqueId is 128 bytes");
+  memcpy(id_out, &id, sizeof id); return EQP_OK;
+}
+int eqp_comm_init(eqp_ctx* ctx, const void* id, int n_ranks, int rank) {
+  if (!ctx || !id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(ctx, EQP_ERR_ARG, "eqp_comm_init: bad argument");
+  NcclApi& N = nccl_api(); if (!N.load()) return fail(ctx, EQP_ERR_NCCL, N.error);
+  try {
+    EQP_CUDA(cudaSetDevice(ctx->device));
+    if (ctx->comm) { N.CommDestroy(ctx->comm); ctx->comm = nullptr; }
+    nccl_unique_id uid; memcpy(&uid, id, sizeof uid);
+    int rc = N.CommInitRank(&ctx->comm, n_ranks, uid, rank);
+    if (rc != NCCL_SUCCESS) { ctx->comm = nullptr; return fail(ctx, EQP_ERR_NCCL, "ncclCommInitRank: " + N.text(rc)); }
+    ctx->commRanks = n_ranks; ctx->commRank = rank; return EQP_OK;
+  } catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+int eqp_reduce_sample(eqp_ctx* ctx, uint64_t* acc, int root) {
+  if (!ctx || !acc) return fail(ctx, EQP_ERR_ARG, "eqp_reduce_sample: null argument");
+  if (!ctx->comm) return fail(ctx, EQP_ERR_ARG, "eqp_reduce_sample: call eqp_comm_init first");
+  if (root < 0 || root >= ctx->commRanks) return fail(ctx, EQP_ERR_ARG, "eqp_reduce_sample: root out of range");
+  if (!ctx->annoLoaded) return fail(ctx, EQP_ERR_ARG, "eqp_reduce_sample: call eqp_load_annotation first");
+  NcclApi& N = nccl_api();
+  try {
+    EQP_CUDA(cudaSetDevice(ctx->device));
+    int rc = N.Reduce(acc, acc, (size_t)ctx->vecLen * 2, NCCL_UINT64, NCCL_SUM, root, ctx->comm, ctx->stream);
+    if (rc != NCCL_SUCCESS) return fail(ctx, EQP_ERR_NCCL, "ncclReduce: " + N.text(rc));
+    EQP_CUDA(cudaStreamSynchronize(ctx->stream)); return EQP_OK;
+  } catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+int eqp_reduce_sample_local(eqp_ctx** ctxs, int n, uint64_t** accs, int root) {
+  if (!ctxs || !accs || n < 1 || root < 0 || root >= n) return fail(nullptr, EQP_ERR_ARG, "eqp_reduce_sample_local: bad argument");
+  for (int i = 0; i < n; i++) if (!ctxs[i] || !accs[i] || !ctxs[i]->annoLoaded || ctxs[i]->vecLen != ctxs[0]->vecLen) return fail(ctxs[0], EQP_ERR_ARG, "eqp_reduce_sample_local: contexts must hold the same annotation");
+  NcclApi& N = nccl_api(); if (!N.load()) return fail(ctxs[0], EQP_ERR_NCCL, N.error);
+  try {
+    bool have = true; for (int i = 0; i < n; i++) have = have && ctxs[i]->comm && ctxs[i]->commRanks == n && ctxs[i]->commRank == i;
+    if (!have) {                                                     // one communicator clique over this process's contexts, kept for later samples
+      std::vector<int> devs(n); std::vector<nccl_comm_t> comms(n);
+      for (int i = 0; i < n; i++) { devs[i] = ctxs[i]->device; if (ctxs[i]->comm) { N.CommDestroy(ctxs[i]->comm); ctxs[i]->comm = nullptr; } }
+      int rc = N.CommInitAll(comms.data(), n, devs.data());
+      if (rc != NCCL_SUCCESS) return fail(ctxs[0], EQP_ERR_NCCL, "ncclCommInitAll: " + N.text(rc));
+      for (int i = 0; i < n; i++) { ctxs[i]->comm = comms[i]; ctxs[i]->commRanks = n; ctxs[i]->commRank = i; }
+    }
+    int rc = N.GroupStart();
+    for (int i = 0; i < n && rc == NCCL_SUCCESS; i++) { EQP_CUDA(cudaSetDevice(ctxs[i]->device)); rc = N.Reduce(accs[i], accs[i], (size_t)ctxs[i]->vecLen * 2, NCCL_UINT64, NCCL_SUM, root, ctxs[i]->comm, ctxs[i]->stream); }
+    int rc2 = N.GroupEnd(); if (rc == NCCL_SUCCESS) rc = rc2;
+    if (rc != NCCL_SUCCESS) return fail(ctxs[0], EQP_ERR_NCCL, "ncclReduce (group): " + N.text(rc));
+    for (int i = 0; i < n; i++) { EQP_CUDA(cudaSetDevice(ctxs[i]->device)); EQP_CUDA(cudaStreamSynchronize(ctxs[i]->stream)); }
+    return EQP_OK;
+  } catch (const std::exception& ex) { return fail(ctxs[0], EQP_ERR_CUDA, ex.what()); }
 }
 
 int eqp_debug_fetch(eqp_ctx* ctx, const char* what, void* dst, size_t dstBytes, size_t* nWritten) {
@@ -345,7 +506,10 @@ void eqp_destroy(eqp_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   ctx->pl.reset(); ctx->be.reset();
+  if (ctx->comm && nccl_api().lib) { nccl_api().CommDestroy(ctx->comm); ctx->comm = nullptr; }
   if (ctx->copyStream) cudaStreamSynchronize(ctx->copyStream);
+  ctx->feed_drop();
+  for (int k = 0; k < eqp_ctx::kStages; k++) { if (ctx->stage[k]) cudaFreeHost(ctx->stage[k]); if (ctx->stageFree[k]) cudaEventDestroy(ctx->stageFree[k]); }
   ctx->retire(ctx->current, ctx->stream); for (auto& c : ctx->prefetched) ctx->retire(c, ctx->stream);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   ctx->unpin();

@@ -32,6 +32,13 @@ __global__ void __launch_bounds__(256, MINB) k_items_occ(uint64_t n, F f) {
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
 }
 
+// items [0, *count) with the count read on the device: work lists built by an earlier kernel, no host round trip
+template <class F>
+__global__ void __launch_bounds__(256) k_items_counted(const uint32_t* __restrict__ count, F f) {
+  uint64_t n = *count, stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
+}
+
 // ---------------------------------------------------------------- scan (exclusive, in place, total at p[n])
 static const int SCAN_THREADS = 256, SCAN_ITEMS = 8, SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
@@ -219,6 +226,11 @@ struct CudaBackend {
   template <class F> void launch(uint64_t n, F f) {
     if (!n) return;
     k_items<<<grid_for(n, 256), 256, 0, stream>>>(n, f); launches++;
+    EQP_CUDA(cudaGetLastError());
+  }
+  template <class F> void launch_counted(const uint32_t* count, uint64_t maxN, F f) {
+    if (!maxN) return;
+    k_items_counted<<<nSm * 2, 256, 0, stream>>>(count, f); launches++;
     EQP_CUDA(cudaGetLastError());
   }
   template <int MINB, class F> void launch_occ(uint64_t n, F f) {

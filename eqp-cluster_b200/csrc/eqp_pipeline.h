@@ -41,6 +41,26 @@ EQP_HD void counter_add(unsigned long long* p, uint32_t v) {
 #endif
 }
 
+// append to a work list (order irrelevant); rare events only
+EQP_HD void list_push(uint32_t* count, uint32_t* list, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+  list[atomicAdd(count, 1u)] = v;
+#else
+  list[(*count)++] = v;
+#endif
+}
+
+EQP_HD void counter_add64(unsigned long long* p, uint64_t v) {          // v < 2^42: two pieces that cannot wrap in a 32-lane sum
+#if defined(__CUDA_ARCH__)
+  uint32_t m = __match_any_sync(__activemask(), (unsigned long long)p);
+  uint32_t r0 = __reduce_add_sync(m, (uint32_t)(v & 0x3FFFFFu)), r1 = __reduce_add_sync(m, (uint32_t)(v >> 22));
+  unsigned long long r = (unsigned long long)r0 + ((unsigned long long)r1 << 22);
+  if (r && (threadIdx.x & 31) == (uint32_t)(__ffs((int)m) - 1)) atomicAdd(p, r);
+#else
+  *p += v;
+#endif
+}
+
 struct ChunkResult {
   std::vector<double> counts[3]; std::vector<unsigned long long> fixed[3]; std::vector<uint8_t> junctionActive;
   unsigned long long stats[16]; uint32_t nRecords[3]; uint32_t err[2];
@@ -108,6 +128,10 @@ struct Pipeline {
     C.stTJ = be.template alloc<FragStat>(N); C.setTJ = be.template alloc<SetDesc>(N); C.setC = be.template alloc<SetDesc>(N);
     C.auxSlot = be.template alloc<uint32_t>((uint64_t)N + 1); C.blkOff = be.template alloc<uint32_t>((uint64_t)N + 1); C.alnOff = be.template alloc<uint32_t>((uint64_t)N + 1);
     C.seenRef = be.template alloc<uint8_t>((uint64_t)A.nRef + 1); be.memset(C.seenRef, 0, (uint64_t)A.nRef + 1);
+    C.slotTr = be.template alloc<uint8_t>((uint64_t)N + 1); C.slotLd = be.template alloc<uint8_t>((uint64_t)N + 1);
+    be.memset(C.slotTr, 0, (uint64_t)N + 1); be.memset(C.slotLd, 0, (uint64_t)N + 1);
+    // one fragment adds at most 1.0 = 2^38 units to a feature, so a u64 accumulator holds 2^26 fragments' worth (include/eqp_count.h)
+    if ((uint64_t)N >= (1ull << 26)) { R.err[0] = DERR_ACC_OVERFLOW; R.err[1] = N; return -1; }
     be.stage("frag-range");
     // ---- fragment table: [first,end) line range per (file, slot); order check (CombineSamFiles.java:191-193)
     for (int f = 0; f < 3; f++) { const SamView S = C.sam[f]; FragFile* ff = C.ff[f]; uint32_t base = C.base; uint32_t* err = scal;
@@ -167,7 +191,7 @@ struct Pipeline {
     }
     be.stage("select");
     // ---- a27: reference ids seen (combined SAM + junction SAM) -> active junction features
-    V.junctionActive = be.template alloc<uint8_t>((uint64_t)A.nFeat[2] + 1); be.memset((void*)V.junctionActive, 0, (uint64_t)A.nFeat[2] + 1);
+    V.junctionActive = be.template alloc<uint8_t>((uint64_t)A.nAct + 1); be.memset((void*)V.junctionActive, 0, (uint64_t)A.nAct + 1);
     { const ChunkView C = this->C; uint8_t* act = (uint8_t*)V.junctionActive; const SamView J = C.sam[FILE_J];
       be.launch(J.nLines, [=] EQP_LAMBDA(uint64_t i) { if ((J.rf[i] & RF_REC) && J.ref[i] >= 0) C.seenRef[J.ref[i]] = 1; });
       be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
@@ -185,25 +209,30 @@ struct Pipeline {
     V.stats = be.template alloc<unsigned long long>(16); be.memset(V.stats, 0, 16 * sizeof(unsigned long long));
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
     { const ChunkView C = this->C; unsigned long long* stats = V.stats;
-      be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, false, nb, na); C.blkOff[s] = nb; C.alnOff[s] = na;
+      be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, false, P.stranded, nb, na); C.blkOff[s] = nb; C.alnOff[s] = na;
         SetCursor c{0, 0xFFFFFFFFu}; int f; counter_add(&stats[9], set_next(C, C.setC[s], (uint32_t)s, c, f) ? 1u : 0u); }); }
     be.scan(C.blkOff, N); be.scan(C.alnOff, N);
     be.to_host(&nBlocks, C.blkOff + N, 4); be.to_host(&nAln, C.alnOff + N, 4);
     C.blocks = be.template alloc<Block>((uint64_t)nBlocks + 1); C.hitCnt = be.template alloc<uint32_t>((uint64_t)nBlocks + 1);
     C.alnBlk = be.template alloc<uint32_t>((uint64_t)nAln + 1); be.to_device(C.alnBlk + nAln, &nBlocks, 4);
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
-    { const ChunkView C = this->C; be.template launch_occ<6>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, nb, na); }); }
+    { const ChunkView C = this->C; be.template launch_occ<6>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, P.stranded, nb, na); }); }
     be.stage("blocks");
     // ---- a11: interval join (count, scan, fill)
-    { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { C.hitCnt[b] = join_block(A, C.blocks[b], nullptr, (uint32_t)b); }); }
+    { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { C.hitCnt[b] = join_block(A, C.blocks[b], nullptr, (uint32_t)b, P.stranded != 0); }); }
     be.scan(C.hitCnt, nBlocks); be.to_host(&nHits, C.hitCnt + nBlocks, 4);
     C.hits = be.template alloc<Hit>((uint64_t)nHits + 1);
-    { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { join_block(A, C.blocks[b], C.hits + C.hitCnt[b], (uint32_t)b); }); }
+    { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { join_block(A, C.blocks[b], C.hits + C.hitCnt[b], (uint32_t)b, P.stranded != 0); }); }
     be.stage("join");
     // ---- a12-a25
     V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
     V.dedupTab = be.template alloc<uint32_t>(2 * (uint64_t)nAln + 2); be.memset(V.dedupTab, 0, (2 * (uint64_t)nAln + 2) * 4); V.alnTail = be.template alloc<uint32_t>((uint64_t)nAln + 1);
     V.a20 = be.template alloc<uint32_t>((uint64_t)N + 1); V.nFinal = be.template alloc<uint32_t>((uint64_t)N + 1);
+    V.ivAdj = be.template alloc<IvAdj>((uint64_t)nHits + 1);                // a17 scratch, touched for fragments with a positive length difference only
+    V.alnG = nullptr; V.a20G = nullptr;
+    if (A.nTrChr > 0) { V.alnG = be.template alloc<AlnG>((uint64_t)nAln + 1); V.a20G = be.template alloc<uint32_t>((uint64_t)N + 1); }
+    uint32_t* listLd = be.template alloc<uint32_t>((uint64_t)N + 1); uint32_t* listTr = be.template alloc<uint32_t>((uint64_t)N + 1);
+    uint32_t* listCnt = scal + 96; be.memset(listCnt, 0, 8);                // [0] fragments with a positive length difference, [1] with tr- exon hits
     for (int m = 0; m < 3; m++) { V.acc[m] = accOut[m] ? accOut[m] : be.template alloc<unsigned long long>((uint64_t)A.nFeat[m] + 1); be.memset(V.acc[m], 0, ((uint64_t)A.nFeat[m] + 1) * 8); }
     be.memset(V.a20, 0, ((uint64_t)N + 1) * 4); be.memset(V.nFinal, 0, ((uint64_t)N + 1) * 4);
     be.stage("alloc-a12");
@@ -216,15 +245,20 @@ struct Pipeline {
       be.stage("order");
       be.launch(nAln, [=] EQP_LAMBDA(uint64_t a) { alignment_build(A, C, V, P, (uint32_t)a); });
       be.stage("alignment-build");
+      // the rare shapes (transcript exon longer than its genome exon; tr- exons) go through work lists built on the device
+      be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { uint32_t s = perm[i]; if (C.slotLd[s]) list_push(listCnt, listLd, s); if (C.slotTr[s]) list_push(listCnt + 1, listTr, s); });
+      be.launch_counted(listCnt, N, [=] EQP_LAMBDA(uint64_t i) { fragment_adjust(A, C, V, listLd[i]); });                         // a17 before the dedupe
       be.template launch_occ<4>(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
+      if (V.alnG) be.launch_counted(listCnt + 1, N, [=] EQP_LAMBDA(uint64_t i) { fragment_weight_gene(C, V, listTr[i]); });      // gene-run keys of tr- fragments
       be.stage("fragment-weight");
       // the three counting runs of one fragment back to back in one thread: runs two and three find the fragment's alignments and
       // hits in cache instead of paying the DRAM latency chain again (the runs were latency-bound as three concurrent kernels)
       be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) {
         uint32_t s = perm[i];
         for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) {
-          int r = fragment_count(A, C, V, P, m, s);                          // 0 not a weight object, 1 included, 2 excluded (ComputeCounts.java:986-989)
+          uint64_t ws; int r = fragment_count(A, C, V, P, m, s, ws);       // 0 not a weight object, 1 included, 2 excluded (ComputeCounts.java:986-989)
           counter_add(&V.stats[m * 3 + 0], r ? 1u : 0u); counter_add(&V.stats[m * 3 + 1], r == 1 ? 1u : 0u); counter_add(&V.stats[m * 3 + 2], r == 2 ? 1u : 0u);
+          counter_add64(&V.stats[10 + m], ws);
         }
       }); }
     be.stage("fragment-count x3");
@@ -238,7 +272,7 @@ struct Pipeline {
       { const double scale = 1.0 / (double)(1ULL << EQP_FIXED_SHIFT_D); const unsigned long long* fx = R.fixed[m].data(); double* out = R.counts[m].data();   // exact: power-of-two scale
         for (int i = 0; i < A.nFeat[m]; i++) out[i] = (double)fx[i] * scale; }
     }
-    R.junctionActive.resize(A.nFeat[2]); if (A.nFeat[2]) be.to_host(R.junctionActive.data(), V.junctionActive, A.nFeat[2]);
+    R.junctionActive.resize(A.nAct); if (A.nAct) be.to_host(R.junctionActive.data(), V.junctionActive, A.nAct);
     return 0;
   }
 };

@@ -27,13 +27,14 @@ enum {
   DERR_CIGAR_OP = 7,       // unknown CIGAR operation (SamRecord.java:419-421)
   DERR_CIGAR_LEN = 8,      // read length != M+I+S (SamRecord.java:463-466)
   DERR_MATE_REF = 9,       // "Differing referenceName mate found" (SamRecord.java:567-571)
-  DERR_TR_EXON = 10,       // unsupported: tr- transcript exon hit
-  DERR_POS_LENDIFF = 11,   // unsupported: transcript exon longer than genome exon (a17 becomes effective)
+  DERR_TR_LENDIFF = 10,    // unsupported corner: one alignment has both a tr- exon record and a record with a length difference
+                           // (its field indices, hence its adapted coordinates, then differ between the junction run and the others)
+  DERR_ACC_OVERFLOW = 11,  // a fixed-point accumulator passed 2^62 (one feature took more than 2^24 reads' worth of weight)
   DERR_CAPACITY = 12,      // per-fragment table overflow
   DERR_GENOME_COORD = 13,  // BedRecord.java:669-673 / :683-687 self-checks
   DERR_INCONSISTENT = 14,  // GenomicAlignment.java consistency throws (:123-148, :245-300)
   DERR_BAD_JUNCTION_ID = 15,
-  DERR_STRANDED = 16,      // unsupported: strand-specific mode
+  DERR_STRANDED = 16,      // strand-specific mode: direction is neither forward (1) nor backward (2)
   DERR_INT = 17            // integer field does not parse
 };
 
@@ -50,14 +51,18 @@ struct AnnoView {
   int32_t nRef;
   // B index: buckets -> rows sorted by start
   const uint32_t* bktRowOff; const uint8_t* bktFlags;       // bit0 junction, bit1 .inv-strand
+  const int32_t* bktRefId;          // identity of the bucket's reference id after BedRecord.java:154-176 (.inv-strand and version stripped)
   int32_t nBucket;
   const int32_t* rowStart; const int32_t* rowEnd; const int32_t* rowMaxEnd; const int32_t* rowExon;
   const uint8_t* rowFlags;          // bit0 genomic row (bucket name == exon chromosome), bits1-2 row strand (0 '+', 1 '-', 2 other)
   // distinct exons
-  const int32_t* exChr; const int32_t* exStart; const int32_t* exEnd; const uint8_t* exStrand;   // exChr -2 = tr- exon
-  int32_t nExon;
+  const int32_t* exChr; const int32_t* exStart; const int32_t* exEnd; const uint8_t* exStrand;   // exChr <= -2: tr- exon of transcript -2 - exChr
+  int32_t nExon; int32_t nTrChr;    // nTrChr: number of distinct tr- chromosomes (0: the annotation has no tr- exons)
   // exon -> feature lists per mode; junction entries carry bit31 = "row also in exon_junction_transcript.map"
   const uint32_t* featOff[3]; const uint32_t* feat[3]; int32_t nFeat[3];
+  // 3-column junction map (Exon.java:107-125): a row is switched on by its column-2 id, counted under its column-3 id.
+  // featAct is parallel to feat[MODE_JUNCTION] (null: the activation index is the feature id); nAct = number of activation ids
+  const uint32_t* featAct; int32_t nAct;
 };
 
 struct SamView {                   // one decoded SAM input (structure of arrays, one entry per text line)
@@ -97,11 +102,14 @@ struct Hit { uint32_t block; int32_t row; int32_t overlap; };   // a11 output (1
 struct HitX {                      // per hit, after the per-alignment sort/dedupe (a12-a16), 24 bytes
   int32_t gs, ge;                  // genomic interval, 1-based closed
   int32_t chr;                     // chromosome index of the exon
-  int16_t ivField;                 // field index of the (kept) interval this record belongs to
+  int8_t ivField, ivFieldJ;        // field index of the (kept) interval this record belongs to; ivFieldJ: the same in the junction run, where
+                                   // tr- exon records do not take an index (-1, GenomicAlignment.java:233-234)
   uint16_t ivRank;                 // rank of that interval among the distinct intervals of its half
   int32_t exon;                    // distinct-exon id of the hit's annotation row
   uint8_t flags;                   // bit0 valid, bit1 genomic row, bits2-4 conforming in gene/exon/junction run, bit5 interval strand '-'
-  uint8_t half; uint16_t grp;      // half: 1 or 2 (read index; after a19 the half of the REPRESENTATIVE it merges into); grp: representative's index within the fragment
+  uint8_t half; uint16_t grp;      // half: 1 or 2 (read index; after a19 the half of the REPRESENTATIVE it merges into); grp: representative's index within the fragment.
+                                   // Fragments with a tr- exon hit are never tagged: half stays the read index and grp holds the interval's ordinal
+                                   // among the non-tr intervals of its half (0xFFFF for a tr- interval), see eqp_accumulate.h
 };
 
 struct Aln {                       // one WeightObjectAlignment (a15-a19), 48 bytes
@@ -110,8 +118,13 @@ struct Aln {                       // one WeightObjectAlignment (a15-a19), 48 by
   uint64_t key;
   int32_t start1, start2;          // GenomicAlignment.start per half
   uint16_t nIv1, nIv2; int16_t maxField1, maxField2;
-  uint8_t flags; uint8_t pad[3];   // bit0 paired, bit1 has half 1, bit2 has half 2, bits3-4 SR read index, bit5 halves swapped relative to repr
+  uint8_t flags;                   // bit0 paired, bit1 has half 1, bit2 has half 2, bits3-4 SR read index, bit5 halves swapped relative to repr
+  uint8_t tr;                      // per half h (shift 3*(h-1)): bit0 has a tr- interval, bit1 all intervals are tr-, i.e. its string is the literal "" outside the gene run
+  uint8_t pad[2];
   uint32_t next;                   // next alignment of the fragment with the same key (duplicate chain, file order), UINT32_MAX = end
 };
+
+// second dedupe of the alignments of a fragment with tr- exon hits: keys of the gene run, where tr- intervals are printed (GenomicInterval.java:711-713)
+struct AlnG { uint64_t key; uint32_t repr, next; uint8_t flags; uint8_t pad[7]; };   // flags bit5: halves swapped relative to repr
 
 }  // namespace eqpb

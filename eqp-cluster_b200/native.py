@@ -43,15 +43,22 @@ class Counts(C.Structure):
     _fields_ = [("n_gene", C.c_int64), ("n_exon", C.c_int64), ("n_junction", C.c_int64),
                 ("gene", C.POINTER(C.c_double)), ("exon", C.POINTER(C.c_double)), ("junction", C.POINTER(C.c_double)),
                 ("gene_fixed", C.POINTER(C.c_uint64)), ("exon_fixed", C.POINTER(C.c_uint64)), ("junction_fixed", C.POINTER(C.c_uint64)),
-                ("junction_active", C.POINTER(C.c_uint8)),
+                ("junction_active", C.POINTER(C.c_uint8)), ("n_junction_act", C.c_int64),
                 ("number_mapped_reads", C.c_int64), ("number_expressed_reads", C.c_int64),
                 ("num_weight_objects", C.c_int64 * 3), ("num_weight_objects_included", C.c_int64 * 3),
-                ("num_weight_objects_excluded", C.c_int64 * 3), ("n_records", C.c_int64 * 3),
+                ("num_weight_objects_excluded", C.c_int64 * 3), ("n_records", C.c_int64 * 3), ("sum_weights", C.c_double * 3),
                 ("device_ms", C.c_double), ("dominant_kernel_ms", C.c_double), ("kernel_launches", C.c_int64)]
 
 
-EXPORTS = ("eqp_version", "eqp_default_params", "eqp_create", "eqp_load_annotation", "eqp_count_chunk", "eqp_prefetch_chunk", "eqp_feature_count",
-           "eqp_feature_id", "eqp_device_vector", "eqp_accumulate", "eqp_debug_fetch", "eqp_debug_decode", "eqp_last_error", "eqp_destroy")
+class OutputRow(C.Structure):
+    _fields_ = [("id", C.c_char_p), ("feature", C.c_int64), ("act", C.c_int64), ("always", C.c_int32), ("reserved", C.c_int32)]
+
+
+EXPORTS = ("eqp_version", "eqp_default_params", "eqp_create", "eqp_load_annotation", "eqp_annotation_bytes", "eqp_count_chunk", "eqp_prefetch_chunk",
+           "eqp_feature_count", "eqp_feature_id", "eqp_map_columns", "eqp_output_row_count", "eqp_get_output_row", "eqp_device_vector", "eqp_accumulate",
+           "eqp_wide_to_double", "eqp_comm_id", "eqp_comm_init", "eqp_reduce_sample", "eqp_reduce_sample_local", "eqp_chunk_begin", "eqp_chunk_feed",
+           "eqp_chunk_end", "eqp_debug_fetch", "eqp_debug_decode", "eqp_last_error", "eqp_destroy")
+COMM_ID_BYTES = 128
 
 _lib = None
 
@@ -77,6 +84,17 @@ def load_library(path=None):
     lib.eqp_feature_id.argtypes = [vp, C.c_int, C.c_int64]; lib.eqp_feature_id.restype = C.c_char_p
     lib.eqp_device_vector.argtypes = [vp, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
     lib.eqp_accumulate.argtypes = [vp, vp]
+    lib.eqp_map_columns.argtypes = [vp, C.c_int]
+    lib.eqp_output_row_count.argtypes = [vp, C.c_int]; lib.eqp_output_row_count.restype = C.c_int64
+    lib.eqp_get_output_row.argtypes = [vp, C.c_int, C.c_int64, C.POINTER(OutputRow)]
+    lib.eqp_wide_to_double.argtypes = [vp, C.c_int64, vp]; lib.eqp_wide_to_double.restype = None
+    lib.eqp_comm_id.argtypes = [vp]
+    lib.eqp_comm_init.argtypes = [vp, vp, C.c_int, C.c_int]
+    lib.eqp_reduce_sample.argtypes = [vp, vp, C.c_int]
+    lib.eqp_reduce_sample_local.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(vp), C.c_int]
+    lib.eqp_chunk_begin.argtypes = [vp, C.c_size_t, C.c_size_t, C.c_size_t]
+    lib.eqp_chunk_feed.argtypes = [vp, C.c_int, vp, C.c_size_t]
+    lib.eqp_chunk_end.argtypes = [vp, C.POINTER(Params), C.POINTER(Counts)]
     lib.eqp_debug_fetch.argtypes = [vp, C.c_char_p, vp, C.c_size_t, C.POINTER(C.c_size_t)]
     lib.eqp_debug_decode.argtypes = [vp, vp, C.c_size_t, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     lib.eqp_last_error.argtypes = [vp]; lib.eqp_last_error.restype = C.c_char_p
@@ -113,13 +131,16 @@ def _buf(x):
 class ChunkCounts:
     """Host copy of one chunk's eqp_counts."""
 
-    def __init__(self, c, feature_ids):
+    def __init__(self, c, feature_ids, rows=None, columns=None):
+        self.output_rows, self.map_columns = rows, columns
+        self.sum_weights = list(c.sum_weights)
+
         def arr(ptr, n, dt):
             return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dt, copy=True) if n else np.zeros(0, dt)
         n = (c.n_gene, c.n_exon, c.n_junction)
         self.counts = {m: arr(getattr(c, m), n[i], np.float64) for i, m in enumerate(MODES)}
         self.fixed = {m: arr(getattr(c, m + "_fixed"), n[i], np.uint64) for i, m in enumerate(MODES)}
-        self.junction_active = arr(c.junction_active, n[2], np.uint8)
+        self.junction_active = arr(c.junction_active, c.n_junction_act, np.uint8)
         self.feature_ids = feature_ids
         self.number_mapped_reads = c.number_mapped_reads
         self.number_expressed_reads = c.number_expressed_reads
@@ -134,6 +155,20 @@ class ChunkCounts:
     def as_dict(self, mode, nonzero_only=False):
         ids, v = self.feature_ids[mode], self.counts[mode]
         return {ids[i]: float(v[i]) for i in range(len(ids)) if not nonzero_only or self.fixed[mode][i]}
+
+    def rows(self, mode, nonzero_only=None):
+        """(printed id, value) in the reference's print order (ComputeCounts.java:875-950): every row of the map for the gene and exon
+        runs, the rows of this chunk's filtered junction map for the junction run (non-zero ones only under -n, the default flow)."""
+        if nonzero_only is None:
+            nonzero_only = mode == "junction"
+        out, v, fx, act = [], self.counts[mode], self.fixed[mode], self.junction_active
+        for rid, feat, a, always in self.output_rows[mode]:
+            if mode == "junction" and not (always or act[a]):
+                continue
+            if nonzero_only and not fx[feat]:
+                continue
+            out.append((rid, float(v[feat])))
+        return out
 
 
 class CountContext:
@@ -156,11 +191,22 @@ class CountContext:
         paths = paths or annotation_paths(anno_dir, base, radius)
         f = AnnotationFiles(**{k: (v.encode() if v is not None else None) for k, v in paths.items()})
         self._check(self.lib.eqp_load_annotation(self.h, C.byref(f)))
-        self.feature_ids = {}
+        self.feature_ids, self.output_rows, self.map_columns = {}, {}, {}
+        row = OutputRow()
         for i, m in enumerate(MODES):
             n = self.lib.eqp_feature_count(self.h, i)
             self.feature_ids[m] = [self.lib.eqp_feature_id(self.h, i, k).decode() for k in range(n)]
+            self.map_columns[m] = self.lib.eqp_map_columns(self.h, i)
+            rows = []
+            for k in range(self.lib.eqp_output_row_count(self.h, i)):
+                self._check(self.lib.eqp_get_output_row(self.h, i, k, C.byref(row)))
+                rows.append((row.id.decode(), row.feature, row.act, row.always))
+            self.output_rows[m] = rows
         return self
+
+    @property
+    def vector_length(self):
+        return sum(len(self.feature_ids[m]) for m in MODES)
 
     @property
     def annotation_bytes(self):
@@ -174,7 +220,18 @@ class CountContext:
                                               1 if on_device else 0, C.byref(c)))
         if self._prefetch_keep and not on_device:
             self._prefetch_keep.pop(0)
-        return ChunkCounts(c, self.feature_ids) if fetch else c
+        return ChunkCounts(c, self.feature_ids, self.output_rows, self.map_columns) if fetch else c
+
+    def count_stream(self, pieces, params=None, hints=(0, 0, 0)):
+        """Streaming ingest (eqp_chunk_begin/feed/end): `pieces` yields (input, bytes) with input 0/1/2 = transcript/junction/genome."""
+        p = params or default_params()
+        self._check(self.lib.eqp_chunk_begin(self.h, *[int(h) for h in hints]))
+        for which, data in pieces:
+            addr, n, keep = _buf(data)
+            self._check(self.lib.eqp_chunk_feed(self.h, int(which), addr, n))
+        c = Counts()
+        self._check(self.lib.eqp_chunk_end(self.h, C.byref(p), C.byref(c)))
+        return ChunkCounts(c, self.feature_ids, self.output_rows, self.map_columns)
 
     def prefetch_chunk(self, t_sam, j_sam, g_sam):
         """Start the H2D copy of a later chunk's host buffers; the count_chunk call with the same buffers picks it up."""
@@ -188,7 +245,15 @@ class CountContext:
         return ptr.value, n.value
 
     def accumulate(self, device_ptr):
+        """Add the last chunk's vector into a WIDE (2 * vector_length uint64) device accumulator."""
         self._check(self.lib.eqp_accumulate(self.h, C.c_void_p(int(device_ptr))))
+
+    def comm_init(self, comm_id, n_ranks, rank):
+        self._check(self.lib.eqp_comm_init(self.h, comm_id, n_ranks, rank))
+
+    def reduce_sample(self, device_ptr, root=0):
+        """In-place ncclReduce(sum) of a wide accumulator onto `root`, NCCL called inside libeqpcount.so."""
+        self._check(self.lib.eqp_reduce_sample(self.h, C.c_void_p(int(device_ptr)), root))
 
     def debug_fetch(self, what, dtype):
         n = C.c_size_t()
@@ -206,6 +271,12 @@ class CountContext:
         rows = C.string_at(text, tlen.value).decode().splitlines() if tlen.value else []
         return rows, ec.value, ed.value
 
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
     def close(self):
         if self.h:
             self.lib.eqp_destroy(self.h)
@@ -216,3 +287,33 @@ class CountContext:
 
     def __exit__(self, *a):
         self.close()
+
+
+def comm_id():
+    """ncclGetUniqueId through the library: 128 bytes for rank 0 to ship to the other ranks."""
+    lib = load_library()
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    rc = lib.eqp_comm_id(buf)
+    if rc:
+        raise EqpError(rc, (lib.eqp_last_error(None) or b"").decode())
+    return buf.raw
+
+
+def reduce_sample_local(contexts, device_ptrs, root=0):
+    """One process, several GPUs: grouped ncclReduce over this process's contexts (eqp_reduce_sample_local)."""
+    lib = load_library()
+    n = len(contexts)
+    hs = (C.c_void_p * n)(*[c.h for c in contexts])
+    ps = (C.c_void_p * n)(*[C.c_void_p(int(p)) for p in device_ptrs])
+    rc = lib.eqp_reduce_sample_local(hs, n, ps, root)
+    if rc:
+        raise EqpError(rc, (lib.eqp_last_error(contexts[0].h) or b"").decode())
+
+
+def wide_to_double(wide):
+    """Host copy of a wide accumulator (2n uint64: fraction limbs, then integer limbs) -> n float64 (eqp_wide_to_double)."""
+    w = np.ascontiguousarray(wide).view(np.uint64)
+    n = w.size // 2
+    out = np.zeros(n, dtype=np.float64)
+    load_library().eqp_wide_to_double(w.ctypes.data, n, out.ctypes.data)
+    return out

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define EQP_ABI_VERSION 1
+#define EQP_ABI_VERSION 2
 
 enum {
   EQP_OK = 0,
@@ -29,8 +29,10 @@ enum {
   EQP_ERR_CUDA = -2,         /* no device, driver or allocation failure */
   EQP_ERR_IO = -3,           /* annotation file missing or malformed */
   EQP_ERR_FORMAT = -4,       /* input violates a check the reference aborts on */
-  EQP_ERR_UNSUPPORTED = -5,  /* valid for the reference, not yet handled on the device (DESIGN.md "out of scope") */
-  EQP_ERR_CAPACITY = -6      /* a per-fragment device table overflowed */
+  EQP_ERR_UNSUPPORTED = -5,  /* valid for the reference, not handled on the device (DESIGN.md "out of scope"): one corner, an alignment
+                                with both a tr- exon record and a transcript/genome exon length difference */
+  EQP_ERR_CAPACITY = -6,     /* a per-fragment device table overflowed, or a chunk has 2^26 or more fragments */
+  EQP_ERR_NCCL = -7          /* NCCL missing (libnccl.so.2 is loaded at run time) or a collective failed */
 };
 
 typedef struct eqp_ctx eqp_ctx;
@@ -54,7 +56,7 @@ typedef struct eqp_annotation_files {
  * (compute-counts.sh:932-935,959-960,1034-1035); replaces the UtilLib statics (UtilLib.java:101-226). */
 typedef struct eqp_params {
   int32_t paired_end;            /* informational: layout is read from the SAM flags */
-  int32_t stranded;              /* -s: 0 none (only 0 is supported on the device in this round) */
+  int32_t stranded;              /* -s <direction>: 0 none, 1 forward, 2 backward (compute-counts.sh:372-387; ConvertSamBed -S, bedtools -s, ComputeCounts -s) */
   int32_t gene_overlap;          /* 1 */
   int32_t exon_overlap;          /* -E, default 5  (compute-counts.sh:136) */
   int32_t junction_overlap;      /* -J, default 8  (compute-counts.sh:137,391-401) */
@@ -73,16 +75,18 @@ typedef struct eqp_params {
  * `*_fixed` are the exact accumulators: value = fixed / 2^EQP_FIXED_SHIFT.  They are what eqp_reduce adds. */
 #define EQP_FIXED_SHIFT 38
 typedef struct eqp_counts {
-  int64_t n_gene, n_exon, n_junction;
+  int64_t n_gene, n_exon, n_junction;        /* distinct count-object ids per map (column 2, or column 3 of a 3-column map) */
   const double* gene; const double* exon; const double* junction;
   const uint64_t* gene_fixed; const uint64_t* exon_fixed; const uint64_t* junction_fixed;
-  const uint8_t* junction_active;            /* 1 = id survives filter-junction-map-files.sh for this chunk */
+  const uint8_t* junction_active;            /* n_junction_act flags: 1 = the column-2 id survives filter-junction-map-files.sh for this chunk */
+  int64_t n_junction_act;                    /* == n_junction for a 2-column junction map */
   int64_t number_mapped_reads;               /* NUMBER_MAPPED_READS=   (ConvertSamBed.java:266) */
   int64_t number_expressed_reads;            /* NUMBER_EXPRESSED_READS= (ComputeCounts.java:991-993, gene run) */
   int64_t num_weight_objects[3];             /* per mode: gene, exon, junction (ComputeCounts.java:986-989) */
   int64_t num_weight_objects_included[3];
   int64_t num_weight_objects_excluded[3];
   int64_t n_records[3];                      /* SAM records decoded per input: transcript, junction, genome */
+  double  sum_weights[3];                    /* "Sum of weights contributing to count objects" per run (ComputeCounts.java:989) */
   double  device_ms;                         /* first kernel launch -> counts ready, CUDA events */
   double  dominant_kernel_ms;                /* the SAM decode kernel, summed over the three inputs */
   int64_t kernel_launches;
@@ -116,11 +120,51 @@ int  eqp_prefetch_chunk(eqp_ctx* ctx, const uint8_t* t_sam, size_t t_len, const 
 int64_t     eqp_feature_count(eqp_ctx* ctx, int mode);
 const char* eqp_feature_id(eqp_ctx* ctx, int mode, int64_t index);
 
-/* Device pointer + length (uint64 elements) of the concatenated gene|exon|junction fixed-point vector of the
- * last chunk — what a sample-level NCCL sum reduces (replaces `combineCounts.py -A`, combineCounts.py:199-210). */
-int  eqp_device_vector(eqp_ctx* ctx, uint64_t** dev_ptr, int64_t* n_elements);
-/* Add the last chunk's vector into a caller-owned device accumulator of the same length (multi-chunk samples). */
-int  eqp_accumulate(eqp_ctx* ctx, uint64_t* dev_accumulator);
+/* Rows of a count file in the reference's print order (ComputeCounts.java:875-950).  2-column map: one row per id, sorted
+ * (TreeSet order).  3-column map (Exon.java:107-125): one row per map line, printed id = column 2, value = the count of
+ * the column-3 id; the junction map's lines in the order filter-junction-map-files.sh:298-299 leaves them in.  A junction row
+ * is part of this chunk's filtered map iff `always` (it is in exon_junction_transcript.map) or junction_active[act] is set.
+ * eqp_map_columns tells the writer which zero to print: "0" (2 columns) or "0.0" (3 columns). */
+typedef struct eqp_output_row { const char* id; int64_t feature; int64_t act; int32_t always; int32_t reserved; } eqp_output_row;
+int     eqp_map_columns(eqp_ctx* ctx, int mode);
+int64_t eqp_output_row_count(eqp_ctx* ctx, int mode);
+int     eqp_get_output_row(eqp_ctx* ctx, int mode, int64_t index, eqp_output_row* out);
+
+/* ---- sample level: the sum over a sample's chunks (replaces `combineCounts.py -A`, combineCounts.py:199-210) ----
+ * A chunk vector is the concatenated gene|exon|junction accumulators, n = n_gene + n_exon + n_junction uint64 in 2^-38
+ * units.  One chunk cannot overflow them (a fragment adds at most 1.0 to a feature and eqp_count_chunk refuses chunks of
+ * 2^26 or more fragments), but a sample can: 2^26 = 67.1 M fragments' worth on ONE feature wraps a u64.  A sample
+ * accumulator is therefore WIDE: 2n uint64, element i = fraction limb (sum of the chunks' low 38 bits), element n + i =
+ * integer limb (sum of the chunks' bits 38..63); value_i = acc[n + i] + acc[i] / 2^38.  Plain integer sums, so NCCL's
+ * reduction order cannot change a bit, and the limbs hold 2^26 chunks. */
+int  eqp_device_vector(eqp_ctx* ctx, uint64_t** dev_ptr, int64_t* n_elements);       /* the last chunk's vector (n elements) */
+/* Add the last chunk's vector into a caller-owned, zero-initialised WIDE device accumulator (2n elements).  The add runs on
+ * the context's stream after the chunk's counting; work the caller queued on the legacy default stream (torch's default) is
+ * ordered before it, work on any other stream must be synchronised by the caller first.  Returns when the add has finished. */
+int  eqp_accumulate(eqp_ctx* ctx, uint64_t* dev_accumulator_wide);
+/* Host helper: wide accumulator (host copy, 2n elements) -> n doubles. */
+void eqp_wide_to_double(const uint64_t* wide, int64_t n, double* out);
+
+/* The reduce itself, with NCCL called inside the library (libnccl.so.2, loaded at run time), so that a host that cannot
+ * call torch.distributed — the Java mains — gets the combine-counts replacement.  One process per GPU:
+ *   rank 0: eqp_comm_id(id) -> ship the 128 bytes to the other ranks (file, socket, MPI ...);
+ *   every rank: eqp_comm_init(ctx, id, n_ranks, rank) once; then per sample eqp_reduce_sample(ctx, acc_wide, root):
+ *   in-place ncclReduce(sum, uint64) of the 2n elements onto `root`, ordered after this context's pending work.
+ * One process driving several GPUs (threads of one JVM): eqp_reduce_sample_local over that process's contexts. */
+#define EQP_COMM_ID_BYTES 128
+int  eqp_comm_id(void* id_out);
+int  eqp_comm_init(eqp_ctx* ctx, const void* id, int n_ranks, int rank);
+int  eqp_reduce_sample(eqp_ctx* ctx, uint64_t* dev_accumulator_wide, int root);
+int  eqp_reduce_sample_local(eqp_ctx** ctxs, int n, uint64_t** dev_accumulators_wide, int root);
+
+/* ---- streaming ingest: feed the three SAM texts piecewise while they are inflated (compute-intersection-bed-file.sh:644-662
+ * pipes `zcat` into the Java mains; a host need not hold 45 GB of text).  begin -> any number of feed calls per input, in
+ * text order per input, inputs interleaved freely -> end counts what was fed.  feed copies `len` host bytes through a
+ * page-locked staging ring and returns as soon as `buf` may be reused; the device buffers grow as needed (`*_hint` bytes
+ * are reserved up front, 0 = unknown). */
+int  eqp_chunk_begin(eqp_ctx* ctx, size_t t_hint, size_t j_hint, size_t g_hint);
+int  eqp_chunk_feed(eqp_ctx* ctx, int input /* 0 transcript, 1 junction, 2 genome */, const uint8_t* buf, size_t len);
+int  eqp_chunk_end(eqp_ctx* ctx, const eqp_params* params, eqp_counts* out);
 
 /* Debug/parity taps: copy a device intermediate of the last chunk to the host.
  * what: "weights:<T|J|G|TJ|final>", "selection", "blocks", "hits", "a20".  Layouts are documented in DESIGN.md. */

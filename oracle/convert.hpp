@@ -24,8 +24,11 @@ inline VersionTable load_transcript_versions(sv transcriptBed) {
 
 // ---- a10: SamRecord.computeBedEntries (J/sam-source/SamRecord.java:316-475) + BedEntry (:76-88)
 struct BedBlock { int start, end, score; std::string extra; char strand; };   // extra = "-L..-I..-D..-F..-.."
-inline std::vector<BedBlock> compute_bed_entries(const SamRec& r, int& bedEntryNum, const std::string& fragForErr) {
+// strandDir: 0 = none, 1 = `-S forward` (getFragmentStrand, SamRecord.java:859-865), 2 = `-S backward` (getReverseFragmentStrand, :867-873)
+inline std::vector<BedBlock> compute_bed_entries(const SamRec& r, int& bedEntryNum, const std::string& fragForErr, int strandDir = 0) {
   std::vector<BedBlock> out;
+  char strand = r.strand;                                                   // :431-436
+  if (strandDir && r.readIndex != (strandDir == 1 ? 1 : 2)) strand = strand == '+' ? '-' : '+';
   int bedStart = std::max(0, r.pos - 1);
   // split at [0-9]+N; then [0-9]+[A-Z=] tokens inside each segment
   struct Seg { int m = 0, ins = 0, del = 0, soft = 0, hard = 0; int intron = 0; };
@@ -54,7 +57,7 @@ inline std::vector<BedBlock> compute_bed_entries(const SamRec& r, int& bedEntryN
     if (readLen > 0) {
       char buf[96];
       snprintf(buf, sizeof buf, "-L%d-I%d-D%d-F%d-%d", readLen, s.ins + s.soft, s.del, k, nSeg - 1);
-      out.push_back({start, start + refLen, bedEntryNum, buf, r.strand});
+      out.push_back({start, start + refLen, bedEntryNum, buf, strand});
       bedEntryNum++;
     }
     sumRef += refLen; sumRead += readLen; sumIntron += s.intron;
@@ -67,7 +70,7 @@ inline std::vector<BedBlock> compute_bed_entries(const SamRec& r, int& bedEntryN
 
 // ---- a9: ConvertSamBed.main + SamProcessorBed.processSamRecords (:152-204) + SamRecord.printBedRecords (:484-573)
 struct ConvertStats { long mappedFragments = 0; };
-inline std::string convert_sam_bed(sv sam, const VersionTable* versions, ConvertStats* st = nullptr) {
+inline std::string convert_sam_bed(sv sam, const VersionTable* versions, ConvertStats* st = nullptr, int strandDir = 0) {
   std::string out; int bedEntryNum = 0;                                     // static SamRecord.bedEntryNum (:41)
   for_each_mapped_group(sam, [&](std::vector<SamRec>& recs) {
     if (st) st->mappedFragments++;
@@ -81,9 +84,9 @@ inline std::string convert_sam_bed(sv sam, const VersionTable* versions, Convert
       const SamRec* mate = nullptr;
       if (s.hasMate()) { int j = find_mate(recs, i, processed); if (j >= 0) mate = &recs[j]; }
       auto name = [&](const SamRec& x) { return fragId + (x.hasMate() ? "/P" : "/S") + std::to_string(x.flagReadIndex()); };
-      auto be = compute_bed_entries(s, bedEntryNum, name(s));
+      auto be = compute_bed_entries(s, bedEntryNum, name(s), strandDir);
       std::vector<BedBlock> mbe;
-      if (mate) mbe = compute_bed_entries(*mate, bedEntryNum, name(*mate));
+      if (mate) mbe = compute_bed_entries(*mate, bedEntryNum, name(*mate), strandDir);
       std::vector<std::string> one{std::string(s.rname)};
       const std::vector<std::string>* ids = &one;
       if (versions) { auto it = versions->find(std::string(s.rname)); if (it != versions->end()) ids = &it->second; }

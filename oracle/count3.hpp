@@ -41,6 +41,10 @@ struct WOA {                                           // J/bed-source/WeightObj
   bool isTrAlignment() const { return (!ga1 || ga1->isTrAlignment()) && (!ga2 || ga2->isTrAlignment()); }        // :514-528
 };
 
+// test instrumentation: how often the shapes of SURVEY.md 8d were actually exercised (printed into stats.txt)
+struct ShapeCounters { long snaps = 0, trRecords = 0, posLdRecords = 0; };
+inline ShapeCounters& shape_counters() { static ShapeCounters c; return c; }
+
 // GenomicInterval.adjustChrStartEnd(GenomicInterval) :284-358
 inline bool adjust_pair(GInterval& x, GInterval& y, const Params& p) {
   if (x.chr != y.chr) return false;
@@ -51,7 +55,7 @@ inline bool adjust_pair(GInterval& x, GInterval& y, const Params& p) {
     return false;
   }
   if (std::abs(x.end - x.start) == std::abs(y.end - y.start) && std::abs(y.origStart - x.origStart) <= x.ld) {
-    if (x.ld > y.ld || (x.ld == y.ld && x.start > y.start)) { x.start = y.start; x.end = y.end; x.ld = y.ld; return true; }
+    if (x.ld > y.ld || (x.ld == y.ld && x.start > y.start)) { x.start = y.start; x.end = y.end; x.ld = y.ld; shape_counters().snaps++; return true; }
   }
   return false;
 }

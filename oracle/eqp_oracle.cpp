@@ -45,14 +45,14 @@ static std::string filter_junction_map(sv refIds, sv exonJunction, sv exonJuncti
 
 int main(int argc, char** argv) {
   if (argc < 6 || strcmp(argv[1], "run")) {
-    fprintf(stderr, "usage: eqp_oracle run <annodir> <chunkdir> <se|pe> <outdir> [--stranded] [--unweighted] [--unambig] [--containment] [--nonsplice] [--no-adjust-shortcut] [--quiet]\n");
+    fprintf(stderr, "usage: eqp_oracle run <annodir> <chunkdir> <se|pe> <outdir> [--stranded=forward|backward] [--unweighted] [--unambig] [--containment] [--nonsplice] [--no-adjust-shortcut] [--quiet]\n");
     return 2;
   }
   std::string anno = argv[2], chunk = argv[3], lay = argv[4], outd = argv[5];
-  bool stranded = false, unweighted = false, unambig = false, containment = false, nonsplice = false, noShortcut = false, quiet = false;
+  int strandDir = 0; bool stranded = false, unweighted = false, unambig = false, containment = false, nonsplice = false, noShortcut = false, quiet = false;
   for (int i = 6; i < argc; i++) {
     std::string a = argv[i];
-    if (a == "--stranded") stranded = true; else if (a == "--unweighted") unweighted = true; else if (a == "--unambig") unambig = true;
+    if (a == "--stranded=forward") { stranded = true; strandDir = 1; } else if (a == "--stranded=backward") { stranded = true; strandDir = 2; } else if (a == "--unweighted") unweighted = true; else if (a == "--unambig") unambig = true;
     else if (a == "--containment") containment = true; else if (a == "--nonsplice") nonsplice = true;
     else if (a == "--no-adjust-shortcut") noShortcut = true; else if (a == "--quiet") quiet = true;
   }
@@ -72,7 +72,7 @@ int main(int argc, char** argv) {
     std::string samTJ = combine_sam_files(T, J, wT, wJ);
     std::string samC = combine_sam_files(samTJ, G, wTJ, wG);
     ConvertStats cs;
-    std::string bed = convert_sam_bed(samC, &versions, &cs);
+    std::string bed = convert_sam_bed(samC, &versions, &cs, strandDir);       // ConvertSamBed -S <direction> (CIB:366,912)
     std::string inter = intersect_wo(bed, B, stranded);
     std::string wBed = compute_read_weights(inter);
     std::string wFinal = combine_read_weight_files(wBed, wG, &wTJ, false);
@@ -94,8 +94,8 @@ int main(int argc, char** argv) {
     write_file(outd + "/reference.ids", refIds); write_file(outd + "/exon_junction_filtered.map", fmap);
     write_file(outd + "/gene.cnt", cg); write_file(outd + "/exon.cnt", ce); write_file(outd + "/junction.cnt", cj);
     char buf[512];
-    snprintf(buf, sizeof buf, "NUMBER_MAPPED_READS=%ld\nNUMBER_EXPRESSED_READS=%ld\nNUM_WEIGHT_OBJECTS=%ld\nORACLE_SECONDS=%.6f\n",
-             cs.mappedFragments, rg.stats.included, rg.stats.numWeightObjects, secs);
+    snprintf(buf, sizeof buf, "NUMBER_MAPPED_READS=%ld\nNUMBER_EXPRESSED_READS=%ld\nNUM_WEIGHT_OBJECTS=%ld\nORACLE_SECONDS=%.6f\nSHAPE_SNAPS=%ld\nSUM_WEIGHTS_GENE=%.4f\nSUM_WEIGHTS_EXON=%.4f\nSUM_WEIGHTS_JUNCTION=%.4f\n",
+             cs.mappedFragments, rg.stats.included, rg.stats.numWeightObjects, secs, shape_counters().snaps, rg.stats.sumObjectWeight, re.stats.sumObjectWeight, rj.stats.sumObjectWeight);
     write_file(outd + "/stats.txt", buf);
     if (!quiet) fputs(buf, stdout);
     return 0;

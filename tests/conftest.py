@@ -34,14 +34,16 @@ def tools():
 class World:
     """A seeded synthetic world: annotation dir + chunks, each with the oracle's outputs."""
 
-    def __init__(self, tools, root, anno_seed=76, n_genes=300):
+    def __init__(self, tools, root, anno_seed=76, n_genes=300, knobs=()):
+        """knobs: worldgen annotation-shape settings ("ld=0.2", "tr=0.2", ...; tools/worldgen.cpp); the defaults are the SURVEY 8d mix."""
         self.tools, self.root = tools, str(root)
         self.anno = os.path.join(self.root, "anno")
         os.makedirs(self.anno, exist_ok=True)
-        run([tools["worldgen"], "anno", self.anno, str(anno_seed), str(n_genes)])
+        run([tools["worldgen"], "anno", self.anno, str(anno_seed), str(n_genes)] + list(knobs))
         self.chunks = {}
 
-    def chunk(self, name, seed, first, n, layout, spliced=None):
+    def chunk(self, name, seed, first, n, layout, spliced=None, flags=()):
+        """flags: oracle switches the base run of this chunk uses (e.g. --stranded=forward)."""
         if name in self.chunks:
             return self.chunks[name]
         d = os.path.join(self.root, name)
@@ -51,8 +53,8 @@ class World:
         if spliced is not None:
             cmd.append(str(spliced))
         run(cmd)
-        run([self.tools["oracle"], "run", self.anno, d, layout, o, "--quiet"])
-        self.chunks[name] = {"dir": d, "oracle": o, "layout": layout, "n": n}
+        run([self.tools["oracle"], "run", self.anno, d, layout, o, "--quiet"] + list(flags))
+        self.chunks[name] = {"dir": d, "oracle": o, "layout": layout, "n": n, "flags": tuple(flags)}
         return self.chunks[name]
 
 
@@ -77,13 +79,55 @@ class World:
             for line in open(os.path.join(o, m + ".tsv")):
                 k, fx, v = line.rstrip("\n").split("\t")
                 out[m][k] = float(v)
+            out[m + "_rows"] = [(l.split("\t")[0], float(l.rstrip("\n").split("\t")[1])) for l in open(os.path.join(o, m + ".rows"))]
         out["stats"] = read_stats(os.path.join(o, "stats.txt"))
+        out["weights"] = {l.split()[0]: (int(l.split()[1]), int(l.split()[2])) for l in open(os.path.join(o, "weights.tsv"))}
         return out
 
 
 @pytest.fixture(scope="session")
 def world(tools, tmp_path_factory):
     return World(tools, tmp_path_factory.mktemp("world"))
+
+
+SHAPES = {                                  # one dense world per annotation shape of SURVEY 8d, and the mix
+    "ld": ("ld=0.3", "tr=0", "inv=0", "ver2=0"),                       # transcript exon longer / shorter than its genome exon (a13, a17)
+    "tr": ("tr=0.3", "ld=0", "inv=0", "ver2=0"),                       # tr- filler exons (a12, a16, a18, a20)
+    "trlong": ("tr=0.3", "trlong=1", "ld=0", "inv=0", "ver2=0"),       # fillers longer than a read: halves and alignments of tr- intervals only
+    "inv": ("inv=0.3", "ld=0", "tr=0", "ver2=0"),                      # .inv-strand references (a12)
+    "ver2": ("ver2=0.5", "ld=0", "tr=0", "inv=0"),                     # transcripts listed under two versioned ids (a8, a9)
+    "map3": ("map3=1",),                                               # 3-column junction maps (a24, a26)
+    "mixed": ("ld=0.2", "tr=0.2", "trlong=0.3", "inv=0.1", "ver2=0.2"),
+}
+
+
+@pytest.fixture(scope="session")
+def shape_worlds(tools, tmp_path_factory):
+    cache = {}
+
+    def get(shape):
+        if shape not in cache:
+            cache[shape] = World(tools, tmp_path_factory.mktemp("world_" + shape), knobs=SHAPES[shape])
+        return cache[shape]
+    return get
+
+
+def read_rows(path):
+    return [(l.split("\t")[0], float(l.rstrip("\n").split("\t")[1])) for l in open(path)]
+
+
+def assert_rows_match(got, want, rel=1e-9, exact=False, what=""):
+    """Count-file rows in print order: same ids in the same order, values equal (exact) or within 1e-9 relative."""
+    assert [r[0] for r in got] == [r[0] for r in want], "%s: row ids differ (%d vs %d rows)" % (what, len(got), len(want))
+    bad = [(g, w) for g, w in zip(got, want) if g[1] != w[1] and (exact or abs(g[1] - w[1]) > rel * max(abs(g[1]), abs(w[1])))]
+    assert not bad, "%s: %d mismatches, first %s" % (what, len(bad), bad[:5])
+
+
+def read_weights(oracle_dir):
+    """{fragment: (a20 of the weight pass, n of final.wgt)} from the oracle's bed.wgt / final.wgt."""
+    bed = {l.split("\t")[0]: int(l.split("\t")[1]) for l in open(os.path.join(oracle_dir, "bed.wgt"))}
+    fin = {l.split("\t")[0]: int(l.split("\t")[1]) for l in open(os.path.join(oracle_dir, "final.wgt"))}
+    return {f: (n, fin[f]) for f, n in bed.items()}
 
 
 def read_sams(chunk_dir, layout):

@@ -15,6 +15,7 @@ struct HostBackend {
   void memset(void* p, int v, uint64_t bytes) { ::memset(p, v, bytes); }
   template <class F> void launch(uint64_t n, F f) { for (uint64_t i = 0; i < n; i++) f(i); }
   template <int MINB, class F> void launch_occ(uint64_t n, F f) { launch(n, f); }
+  template <class F> void launch_counted(const uint32_t* count, uint64_t, F f) { for (uint64_t i = 0; i < *count; i++) f(i); }
   void scan(uint32_t* p, uint64_t n) { uint32_t acc = 0; for (uint64_t i = 0; i < n; i++) { uint32_t v = p[i]; p[i] = acc; acc += v; } p[n] = acc; }
   void to_host(void* dst, const void* src, uint64_t bytes) { memcpy(dst, src, bytes); }
   void to_device(void* dst, const void* src, uint64_t bytes) { memcpy(dst, src, bytes); }
@@ -87,6 +88,8 @@ int main(int argc, char** argv) {
       else if (!strcmp(argv[i], "--unambig")) P.unambiguous[0] = P.unambiguous[1] = 1;
       else if (!strcmp(argv[i], "--containment")) P.containment[0] = 1;
       else if (!strcmp(argv[i], "--nonsplice")) P.spliceConforming[0] = P.spliceConforming[1] = 0;
+      else if (!strcmp(argv[i], "--stranded=forward")) P.stranded = 1;
+      else if (!strcmp(argv[i], "--stranded=backward")) P.stranded = 2;
     }
     P.modes = 7; P.weightThreshold = 0.01; P.slack = 0.25;
     HostBackend be; Pipeline<HostBackend> pl(be, H.view(), P);
@@ -103,6 +106,16 @@ int main(int argc, char** argv) {
       }
       fclose(f);
     }
+    // the count files' rows in print order (ComputeCounts.java:875-950): gene and exon print every row, the junction run (-n) non-zero rows of the filtered map
+    for (int m = 0; m < 3; m++) {
+      FILE* f = fopen((outd + "/" + names[m] + ".rows").c_str(), "w");
+      for (auto& r : H.outRows[m]) {
+        if (m == 2 && !(r.always || R.junctionActive[r.act])) continue;
+        if (m == 2 && R.fixed[m][r.feature] == 0) continue;
+        fprintf(f, "%s\t%.17g\n", r.id.c_str(), R.counts[m][r.feature]);
+      }
+      fclose(f);
+    }
     { FILE* f = fopen((outd + "/weights.tsv").c_str(), "w");
       for (uint32_t s = 0; s < pl.C.nSlots; s++) if (pl.V.a20[s]) fprintf(f, "F%09u\t%u\t%u\n", pl.C.base + s, pl.V.a20[s], pl.V.nFinal[s]);
       fclose(f); }
@@ -116,7 +129,8 @@ int main(int argc, char** argv) {
       }
       fclose(f); }
     { FILE* f = fopen((outd + "/stats.txt").c_str(), "w");
-      fprintf(f, "NUMBER_MAPPED_READS=%llu\nNUMBER_EXPRESSED_READS=%llu\nNUM_WEIGHT_OBJECTS=%llu\nBLOCKS=%u\nHITS=%u\nALIGNMENTS=%u\n", R.stats[9], R.stats[1], R.stats[0], pl.nBlocks, pl.nHits, pl.nAln);
+      fprintf(f, "NUMBER_MAPPED_READS=%llu\nNUMBER_EXPRESSED_READS=%llu\nNUM_WEIGHT_OBJECTS=%llu\nBLOCKS=%u\nHITS=%u\nALIGNMENTS=%u\nSUM_WEIGHTS_GENE=%.4f\nSUM_WEIGHTS_EXON=%.4f\nSUM_WEIGHTS_JUNCTION=%.4f\n", R.stats[9], R.stats[1], R.stats[0], pl.nBlocks, pl.nHits, pl.nAln,
+              (double)R.stats[10] / 4294967296.0, (double)R.stats[11] / 4294967296.0, (double)R.stats[12] / 4294967296.0);
       fclose(f); }
     return 0;
   } catch (const std::exception& e) { fprintf(stderr, "ERROR: %s\n", e.what()); return 1; }

@@ -91,7 +91,8 @@ def test_library_exports_every_declared_symbol():
     assert set(eqp.EXPORTS) <= declared
     for sym in declared:
         assert hasattr(lib, sym), "libeqpcount.so does not export " + sym
-    assert lib.eqp_version() == 1
+    assert lib.eqp_version() == 2
+    assert declared <= set(eqp.EXPORTS) | {"eqp_ctx"}, declared - set(eqp.EXPORTS)      # the ctypes binding covers the whole header
 
 
 def test_params_struct_layout_and_defaults():

@@ -14,9 +14,18 @@
 //   read-ordered, unaligned reads present (flag 4), NM:i/AS:i tags, no NH.
 //
 // Usage:
-//   worldgen anno  <outdir> <seed> <n_genes>
+//   worldgen anno  <outdir> <seed> <n_genes> [key=value ...]
 //   worldgen reads <annodir> <outdir> <seed> <first_frag> <n_frags> <se|pe> [spliced_frac]
 // `reads` re-derives the world from <annodir>/world.seed so annotation and reads agree.
+// Annotation shape knobs (SURVEY.md 8d "Ensembl76-shaped"; defaults in Knobs):
+//   ld=F     fraction of transcripts with one exon whose transcript length differs from its genome length by +-1..3 bp
+//            (BedRecord.java:417-452; a positive difference makes GenomicInterval.adjustChrStartEnd effective, :284-421)
+//   tr=F     fraction of transcripts carrying a `tr-` filler exon between two exons (Exon.java:230-301, GenomicAlignment.java:233-234)
+//   trlong=F fraction of those fillers that are longer than a read (a read half can then consist of the filler alone)
+//   inv=F    fraction of transcripts listed as <id>.inv-strand (BedRecord.java:154-161)
+//   ver=F    fraction of transcripts with a versioned id <id>.<n>; ver2=F fraction with TWO versioned ids (ConvertSamBed.java:47-98)
+//   scaf=N   number of scaffolds (in genome.fa.fai) next to the chromosomes
+//   map3=0|1 write the junction maps with 3 columns: exon, printed id, internal id (Exon.java:107-125)
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -48,7 +57,14 @@ struct Rng {                         // splitmix64: reproducible across platform
 };
 
 struct GExon { int s, e; };                           // 1-based closed genome coords
-struct Transcript { int gene; std::vector<int> ex; int len; std::string id; };
+struct Transcript {
+  int gene; std::vector<int> ex; int len; std::string id;
+  std::vector<int> tl;                                // transcript-space length of each exon (tl[i] - genome length = lengthDifference)
+  int fillAfter = -1, fillLen = 0; bool fillInMap = false;   // tr- filler exon after ex[fillAfter] (genomic order), its length, listed in exon_gene.map
+  bool inv = false;                                   // listed as <id>.inv-strand: the transcript runs against its exons' strand
+  std::vector<std::string> names;                     // column-1 names in the BED files (versioned ids); SAM RNAME is `id`
+};
+struct Knobs { double ld = 0.005, tr = 0.01, trlong = 0.0, inv = 0.002, ver = 0.7, ver2 = 0.02; int scaf = 150, map3 = 0; };
 struct JRef {                                         // one junction reference
   int gene; int a, b;                                 // exon indices (genomic order), a<b
   std::vector<int> pex, ps, pe;                       // pieces: exon idx, genome start/end
@@ -63,6 +79,7 @@ struct Gene {
   double expr;
 };
 struct World {
+  Knobs k;
   std::vector<std::string> chrs; std::vector<int> chrLen; int nWhite;
   std::vector<Gene> genes; std::vector<Transcript> trs; std::vector<JRef> jrs;
   std::vector<double> cumExpr;
@@ -77,17 +94,20 @@ static std::string fmt(const char* f, ...) {
 
 static void build_world(World& w, uint64_t seed, int nGenes) {
   Rng r(seed);
-  int nChr = std::max(2, std::min(25, nGenes / 40 + 2));
-  for (int c = 0; c < nChr; c++) {
+  int nMain = std::max(2, std::min(25, nGenes / 40 + 2));
+  for (int c = 0; c < nMain; c++) {
     w.chrs.push_back(c < 22 ? fmt("chr%d", c + 1) : c == 22 ? "chrX" : c == 23 ? "chrY" : "chrM");
     w.chrLen.push_back(0);
   }
+  int nScaf = std::max(0, std::min(w.k.scaf, nGenes / 20));
+  for (int c = 0; c < nScaf; c++) { w.chrs.push_back(fmt("KI27%04d.1", c + 1)); w.chrLen.push_back(0); }
+  int nChr = nMain + nScaf;
   w.chrs.push_back("GL000191.1"); w.chrLen.push_back(0);
   w.nWhite = nChr + 1;                                // the decoy used for repeat copies is NOT in genome.fa.fai
   std::vector<int> cursor(w.chrs.size(), 10000), lastOnChr(w.chrs.size(), -1);
   for (int g = 0; g < nGenes; g++) {
     Gene G; G.id = fmt("ENSG%011d", g + 1);
-    G.chr = (r.uni() < 0.01) ? nChr : r.below(nChr);
+    { double u = r.uni(); G.chr = u < 0.01 ? nChr : (u < 0.03 && nScaf > 0) ? nMain + r.below(nScaf) : r.below(nMain); }
     G.strand = (r.uni() < 0.5) ? '+' : '-';
     int nEx = 1 + std::min(29, (int)(-8.0 * std::log(r.uni() + 1e-12)));
     // 8% of genes overlap the previous gene on the chromosome (shared region, maybe shared exon)
@@ -115,11 +135,31 @@ static void build_world(World& w, uint64_t seed, int nGenes) {
       for (int k = 0; k < nEx; k++)
         if (t == 0 || nEx == 1 || r.uni() < 0.8) T.ex.push_back(k);
       if (T.ex.empty()) T.ex.push_back(r.below(nEx));
-      for (int k : T.ex) T.len += G.ex[k].e - G.ex[k].s + 1;
       bool dup = false;
       for (int ti : G.tr) if (w.trs[ti].ex == T.ex) dup = true;
       if (dup) continue;
+      for (int k : T.ex) T.tl.push_back(G.ex[k].e - G.ex[k].s + 1);
+      Rng q(seed * 7919ULL + (uint64_t)w.trs.size() * 104729ULL + 17);   // own stream: the knobs do not disturb the gene layout
+      if (q.uni() < w.k.tr && T.ex.size() >= 2) {      // tr- filler exon between two exons of the transcript
+        T.fillAfter = q.below((int)T.ex.size() - 1);
+        T.fillLen = q.uni() < w.k.trlong ? 110 + q.below(60) : 5 + q.below(26);
+        T.fillInMap = q.uni() < 0.5;
+      }
+      // one exon whose transcript length differs by +-1..3 bp; not together with a filler: an alignment with both a tr- record and a
+      // length difference gets different coordinates in the junction run (the device reports DERR_TR_LENDIFF)
+      if (q.uni() < w.k.ld && T.fillAfter < 0) {
+        int i = q.below((int)T.ex.size()); int d = (1 + q.below(3)) * (q.uni() < 0.5 ? 1 : -1);
+        if (T.tl[i] + d >= 15) T.tl[i] += d;
+      }
+      T.inv = q.uni() < w.k.inv;
+      for (int l : T.tl) T.len += l;
+      T.len += T.fillLen;
       T.id = fmt("ENST%011d", (int)w.trs.size() + 1);
+      { double u = q.uni(); int v = 1 + q.below(9);
+        if (u < w.k.ver2) { T.names.push_back(T.id + fmt(".%d", v)); T.names.push_back(T.id + fmt(".%d", v + 1)); }
+        else if (u < w.k.ver2 + w.k.ver) T.names.push_back(T.id + fmt(".%d", v));
+        else T.names.push_back(T.id);
+        if (T.inv) for (auto& n : T.names) n += ".inv-strand"; }
       G.tr.push_back((int)w.trs.size());
       w.trs.push_back(T);
     }
@@ -162,6 +202,9 @@ static void build_world(World& w, uint64_t seed, int nGenes) {
 static std::string exon_key(const World& w, const Gene& G, int k) {     // map key (no gene prefix)
   return fmt("%s/%d/%d/%c", w.chrs[G.chr].c_str(), G.ex[k].s, G.ex[k].e, G.strand);
 }
+static std::string tr_name(const Transcript& T) {                      // chromosome part of the transcript's tr- exon ids
+  std::string n = T.names[0]; size_t p = n.find(".inv-strand"); if (p != std::string::npos) n.resize(p); return n;
+}
 static FILE* xopen(const std::string& p, const char* m) {
   FILE* f = fopen(p.c_str(), m);
   if (!f) { fprintf(stderr, "worldgen: cannot open %s\n", p.c_str()); exit(1); }
@@ -170,21 +213,35 @@ static FILE* xopen(const std::string& p, const char* m) {
 
 static void write_annotation(const World& w, const std::string& dir, uint64_t seed, int nGenes) {
   const std::string base = dir + "/ensembl_rna_hs";
-  FILE* fs = xopen(dir + "/world.seed", "w"); fprintf(fs, "%llu %d\n", (unsigned long long)seed, nGenes); fclose(fs);
+  FILE* fs = xopen(dir + "/world.seed", "w");
+  fprintf(fs, "%llu %d %.17g %.17g %.17g %.17g %.17g %.17g %d %d\n", (unsigned long long)seed, nGenes, w.k.ld, w.k.tr, w.k.trlong, w.k.inv, w.k.ver, w.k.ver2, w.k.scaf, w.k.map3);
+  fclose(fs);
   FILE* fai = xopen(dir + "/genome.fa.fai", "w");
   for (int c = 0; c < w.nWhite; c++) fprintf(fai, "%s\t%d\t0\t60\t61\n", w.chrs[c].c_str(), w.chrLen[c]);
   fclose(fai);
   FILE* bed = xopen(base + fmt("_%d_combined_exons.bed", RADIUS), "w");
   FILE* tbed = xopen(base + "_transcript_exons.bed", "w");
-  // transcript rows: exons in transcript (5'->3') order, transcript coordinates, 0-based half-open
+  // transcript rows: exons in transcript (5'->3') order, transcript coordinates, 0-based half-open.  An .inv-strand transcript
+  // runs against its exons' strand (BedRecord.java:154-161 inverts the exon strand for the mapping, the exon id keeps it).
   for (auto& T : w.trs) {
-    const Gene& G = w.genes[T.gene]; int off = 0; int n = (int)T.ex.size();
-    for (int i = 0; i < n; i++) {
-      int k = G.strand == '+' ? T.ex[i] : T.ex[n - 1 - i];
-      int len = G.ex[k].e - G.ex[k].s + 1;
-      fprintf(bed, "%s\t%d\t%d\t%s/%s\t0\t%c\n", T.id.c_str(), off, off + len, G.id.c_str(), exon_key(w, G, k).c_str(), G.strand);
-      fprintf(tbed, "%s\t%d\t%d\t%s/%s\t0\t%c\n", T.id.c_str(), off, off + len, G.id.c_str(), exon_key(w, G, k).c_str(), G.strand);
-      off += len;
+    const Gene& G = w.genes[T.gene]; int n = (int)T.ex.size();
+    bool flip = (G.strand == '-') != T.inv;
+    for (const std::string& name : T.names) {
+      int off = 0;
+      for (int i = 0; i < n; i++) {
+        int gi = flip ? n - 1 - i : i; int k = T.ex[gi]; int len = T.tl[gi];
+        if (flip && T.fillAfter == gi) {                 // filler sits between ex[fillAfter] and ex[fillAfter + 1] (genomic order)
+          fprintf(bed, "%s\t%d\t%d\t%s/tr-%s/%d/%d/%c\t0\t%c\n", name.c_str(), off, off + T.fillLen, G.id.c_str(), tr_name(T).c_str(), off + 1, off + T.fillLen, G.strand, G.strand);
+          off += T.fillLen;
+        }
+        fprintf(bed, "%s\t%d\t%d\t%s/%s\t0\t%c\n", name.c_str(), off, off + len, G.id.c_str(), exon_key(w, G, k).c_str(), G.strand);
+        fprintf(tbed, "%s\t%d\t%d\t%s/%s\t0\t%c\n", name.c_str(), off, off + len, G.id.c_str(), exon_key(w, G, k).c_str(), G.strand);
+        off += len;
+        if (!flip && T.fillAfter == gi) {
+          fprintf(bed, "%s\t%d\t%d\t%s/tr-%s/%d/%d/%c\t0\t%c\n", name.c_str(), off, off + T.fillLen, G.id.c_str(), tr_name(T).c_str(), off + 1, off + T.fillLen, G.strand, G.strand);
+          off += T.fillLen;
+        }
+      }
     }
   }
   // junction rows: pieces in genome order, junction coordinates
@@ -217,16 +274,29 @@ static void write_annotation(const World& w, const std::string& dir, uint64_t se
     fprintf(eg, "%s\t%s\n", key.c_str(), G.id.c_str());
     fprintf(ee, "%s\tENSE%011d\n", key.c_str(), ++exonNo);
   }
+  for (auto& T : w.trs) if (T.fillAfter >= 0 && T.fillInMap) {       // tr- exon ids of half the fillers are known to the gene map
+    const Gene& G = w.genes[T.gene]; int n = (int)T.ex.size(); bool flip = (G.strand == '-') != T.inv; int off = 0;
+    for (int i = 0; i < n; i++) {
+      int gi = flip ? n - 1 - i : i;
+      if (flip && T.fillAfter == gi) break;
+      off += T.tl[gi];
+      if (!flip && T.fillAfter == gi) break;
+    }
+    fprintf(eg, "tr-%s/%d/%d/%c\t%s\n", tr_name(T).c_str(), off + 1, off + T.fillLen, G.strand, G.id.c_str());
+  }
   fclose(eg); fclose(ee);
   FILE* ej = xopen(base + "_exon_junction.map", "w"); FILE* ejt = xopen(base + "_exon_junction_transcript.map", "w");
   FILE* jj = xopen(base + fmt("_%d_junction_junction_coordinate.map", RADIUS), "w");
   FILE* eq = xopen(base + "_equivalent_junctions.map", "w");
   std::vector<std::pair<std::string, std::string>> extByCoord;         // (coord w/o strand, ext id)
+  int jNo = 0;
   for (auto& J : w.jrs) {
     const Gene& G = w.genes[J.gene];
+    std::string tail = J.ext;                                          // 3-column variant: exon, printed id, internal id (Exon.java:107-125)
+    if (w.k.map3) tail += fmt("\tJI%08d", ++jNo);
     for (int k : {J.a, J.b}) {
-      fprintf(ej, "%s\t%s\n", exon_key(w, G, k).c_str(), J.ext.c_str());
-      if (J.annotated) fprintf(ejt, "%s\t%s\n", exon_key(w, G, k).c_str(), J.ext.c_str());
+      fprintf(ej, "%s\t%s\n", exon_key(w, G, k).c_str(), tail.c_str());
+      if (J.annotated) fprintf(ejt, "%s\t%s\n", exon_key(w, G, k).c_str(), tail.c_str());
     }
     fprintf(jj, "%s-junction-%02d-%02d:%s:%d:%d\t%s\n", G.id.c_str(), J.a + 1, J.b + 1, w.chrs[G.chr].c_str(), G.ex[J.a].e, G.ex[J.b].s, J.ext.c_str());
     extByCoord.push_back({fmt("%s_%d_%d", w.chrs[G.chr].c_str(), G.ex[J.a].e, G.ex[J.b].s), J.ext});
@@ -242,37 +312,48 @@ static void write_annotation(const World& w, const std::string& dir, uint64_t se
 
 // ---------------------------------------------------------------- read placement
 struct Blk { int ex, gs, ge; };                       // exon idx, genome start/end (1-based closed)
-struct Place { int gene, tr, go; std::vector<Blk> b; };   // go: offset in genomic-order transcript coords
+struct Place { int gene, tr, go; std::vector<Blk> b; bool clean; };   // go: offset in genomic-order transcript coords; clean: no filler, no length difference touched
 
-// Footprint of `span` reference bases at genomic-order offset `go` of transcript T.
+// Footprint of `span` transcript bases at genomic-order offset `go` of transcript T.  An exon whose transcript length differs from
+// its genome length by d carries its extra (d > 0) / missing (d < 0) bases at its genomic start.
 static bool place(const World& w, int ti, int go, int span, Place& P) {
   const Transcript& T = w.trs[ti]; const Gene& G = w.genes[T.gene];
   if (go < 0 || go + span > T.len) return false;
-  P.gene = T.gene; P.tr = ti; P.go = go; P.b.clear();
-  int off = 0, need = span;
-  for (int k : T.ex) {
-    int len = G.ex[k].e - G.ex[k].s + 1;
-    if (go < off + len && need > 0) {
-      int s = G.ex[k].s + std::max(0, go - off);
-      int e = std::min(G.ex[k].e, s + need - 1);
-      P.b.push_back({k, s, e}); need -= e - s + 1;
+  P.gene = T.gene; P.tr = ti; P.go = go; P.b.clear(); P.clean = true;
+  int off = 0, need = span, cur = go;
+  for (size_t i = 0; i < T.ex.size(); i++) {
+    int k = T.ex[i]; int glen = G.ex[k].e - G.ex[k].s + 1, tl = T.tl[i], d = tl - glen;
+    if (cur < off + tl && need > 0) {
+      int x0 = cur - off, take = std::min(need, tl - x0);
+      int a = std::max(0, std::min(glen - 1, x0 - d)), z = std::max(0, std::min(glen - 1, x0 + take - 1 - d));
+      P.b.push_back({k, G.ex[k].s + a, G.ex[k].s + z});
+      if (d != 0) P.clean = false;
+      need -= take; cur += take;
     }
-    off += len;
+    off += tl;
+    if (T.fillAfter == (int)i) {
+      if (cur < off + T.fillLen && need > 0) { int take = std::min(need, off + T.fillLen - cur); need -= take; cur += take; P.clean = false; }
+      off += T.fillLen;
+    }
   }
   return need == 0;
 }
 // Offset of the same genomic footprint in another transcript of the gene, or -1.
-static int iso_offset(const World& w, int ti, const Place& P) {
+static int iso_offset(const World& w, int ti, const Place& P, int span) {
   const Transcript& T = w.trs[ti]; const Gene& G = w.genes[T.gene];
+  if (ti == P.tr) return P.go;
+  if (!P.clean) return -1;
   int off = 0; size_t j = 0; int res = -1;
   for (size_t i = 0; i < T.ex.size(); i++) {
-    int k = T.ex[i]; int len = G.ex[k].e - G.ex[k].s + 1;
+    int k = T.ex[i]; int glen = G.ex[k].e - G.ex[k].s + 1;
     if (j < P.b.size() && k == P.b[j].ex) {
-      if (j == 0) res = off + (P.b[0].gs - G.ex[k].s);
+      if (j == 0) { res = off + (P.b[0].gs - G.ex[k].s) + (T.tl[i] - glen); if (res < off) return -1; }
       j++;
-      if (j == P.b.size()) return res;
+      if (j == P.b.size()) return res + span <= T.len ? res : -1;
+      if (T.fillAfter == (int)i) return -1;              // a filler separates the two exons in this transcript
     } else if (j > 0) return -1;                       // blocks must sit in consecutive exons
-    off += len;
+    off += T.tl[i];
+    if (T.fillAfter == (int)i) off += T.fillLen;
   }
   return -1;
 }
@@ -331,11 +412,13 @@ struct MateAlns { std::vector<Aln> t, j, g; };
 static void locus_alns(const World& w, const Place& P, int span, int rv, bool boundaryJ, int nm, MateAlns& M) {
   const Gene& G = w.genes[P.gene]; int gflip = (G.strand == '-');
   for (int ti : G.tr) {
-    int off = iso_offset(w, ti, P);
+    int off = iso_offset(w, ti, P, span);
     if (off < 0) continue;
-    int o = gflip ? w.trs[ti].len - off - span : off;
-    M.t.push_back({w.trs[ti].id, o + 1, rv, nm});
+    int tflip = gflip ^ (w.trs[ti].inv ? 1 : 0);
+    int o = tflip ? w.trs[ti].len - off - span : off;
+    M.t.push_back({w.trs[ti].id, o + 1, rv ^ (w.trs[ti].inv ? 1 : 0), nm});
   }
+  if (!P.clean) return;                                // the genome and the junction references do not contain this sequence
   if (P.b.size() == 1) M.g.push_back({w.chrs[G.chr], P.b[0].gs, rv ^ gflip, nm});
   int nb = 0;
   for (int ji : G.jr) {
@@ -459,7 +542,7 @@ static void gen_reads(const World& w, const std::string& dir, uint64_t seed, int
       if (r.uni() < 0.01) {                            // highly repetitive: many genome-only copies
         int extra = 21 + r.below(100);
         for (int e = 0; e < extra; e++) {
-          Place P; if (!random_place(w, r, span[0], P) || P.b.size() != 1) continue;
+          Place P; if (!random_place(w, r, span[0], P) || P.b.size() != 1 || !P.clean) continue;
           bool decoy = r.uni() < 0.1;                    // exercises the -c whitelist (ComputeReadWeightsSam.java:168-172)
           M[0].g.push_back({decoy ? std::string("GL000999.1_decoy") : w.chrs[w.genes[P.gene].chr], P.b[0].gs, r.below(2), 1 + r.below(2)});
         }
@@ -482,19 +565,28 @@ static void gen_reads(const World& w, const std::string& dir, uint64_t seed, int
 int main(int argc, char** argv) {
   if (argc >= 5 && !strcmp(argv[1], "anno")) {
     World w; uint64_t seed = strtoull(argv[3], 0, 10); int ng = atoi(argv[4]);
+    for (int i = 5; i < argc; i++) {
+      const char* eq = strchr(argv[i], '='); std::string key(argv[i], eq ? eq - argv[i] : strlen(argv[i])); double v = eq ? atof(eq + 1) : 0;
+      if (key == "ld") w.k.ld = v; else if (key == "tr") w.k.tr = v; else if (key == "trlong") w.k.trlong = v; else if (key == "inv") w.k.inv = v;
+      else if (key == "ver") w.k.ver = v; else if (key == "ver2") w.k.ver2 = v; else if (key == "scaf") w.k.scaf = (int)v; else if (key == "map3") w.k.map3 = (int)v;
+      else { fprintf(stderr, "worldgen: unknown knob %s\n", argv[i]); return 2; }
+    }
     build_world(w, seed, ng); write_annotation(w, argv[2], seed, ng);
-    fprintf(stderr, "worldgen: %zu genes, %zu transcripts, %zu junction references\n", w.genes.size(), w.trs.size(), w.jrs.size());
+    size_t nLd = 0, nTr = 0, nInv = 0, nV2 = 0;
+    for (auto& T : w.trs) { const Gene& G = w.genes[T.gene]; for (size_t i = 0; i < T.ex.size(); i++) if (T.tl[i] != G.ex[T.ex[i]].e - G.ex[T.ex[i]].s + 1) { nLd++; break; } nTr += T.fillAfter >= 0; nInv += T.inv; nV2 += T.names.size() > 1; }
+    fprintf(stderr, "worldgen: %zu genes, %zu transcripts (%zu with a length difference, %zu with a tr- exon, %zu inv-strand, %zu with two versions), %zu junction references, %zu reference sequences\n",
+            w.genes.size(), w.trs.size(), nLd, nTr, nInv, nV2, w.jrs.size(), w.chrs.size());
     return 0;
   }
   if (argc >= 8 && !strcmp(argv[1], "reads")) {
-    unsigned long long seed; int ng;
+    unsigned long long seed; int ng; World w;
     FILE* fs = xopen(std::string(argv[2]) + "/world.seed", "r");
-    if (fscanf(fs, "%llu %d", &seed, &ng) != 2) return 1;
+    if (fscanf(fs, "%llu %d %lf %lf %lf %lf %lf %lf %d %d", &seed, &ng, &w.k.ld, &w.k.tr, &w.k.trlong, &w.k.inv, &w.k.ver, &w.k.ver2, &w.k.scaf, &w.k.map3) != 10) return 1;
     fclose(fs);
-    World w; build_world(w, seed, ng);
+    build_world(w, seed, ng);
     gen_reads(w, argv[3], strtoull(argv[4], 0, 10), atoi(argv[5]), atoi(argv[6]), !strcmp(argv[7], "pe"), argc > 8 ? atof(argv[8]) : 0.0);
     return 0;
   }
-  fprintf(stderr, "usage: worldgen anno <outdir> <seed> <n_genes> | reads <annodir> <outdir> <seed> <first_frag> <n_frags> <se|pe> [spliced_frac]\n");
+  fprintf(stderr, "usage: worldgen anno <outdir> <seed> <n_genes> [ld=F tr=F trlong=F inv=F ver=F ver2=F scaf=N map3=0|1] | reads <annodir> <outdir> <seed> <first_frag> <n_frags> <se|pe> [spliced_frac]\n");
   return 2;
 }
