@@ -7,4 +7,4 @@ from . import sharding  # noqa: F401
 from . import combine  # noqa: F401
 from . import fpkm  # noqa: F401
 from .native import (CountContext, ChunkCounts, EqpError, Params, default_params, annotation_paths, load_library,  # noqa: F401
-                     EXPORTS, MODES, EQP_FIXED_SHIFT)
+                     EXPORTS, MODES, EQP_FIXED_SHIFT, comm_id, reduce_sample_local, wide_to_double)

@@ -61,7 +61,7 @@ def build_cli(force=False):
     srcs = _glob(os.path.join(PKG_DIR, "host"), (".cpp", ".hpp")) + [os.path.join(ROOT, "include", "eqp_count.h")]
     if force or _newer(srcs, CLI_PATH):
         os.makedirs(LIB_DIR, exist_ok=True)
-        _run(["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "include"), "-o", CLI_PATH, src, "-ldl", "-lz"])
+        _run(["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "include"), "-o", CLI_PATH, src, "-ldl", "-lz", "-lpthread"])
     return CLI_PATH
 
 

@@ -458,6 +458,14 @@ int eqp_debug_fetch(eqp_ctx* ctx, const char* what, void* dst, size_t dstBytes, 
   else if (w == "selection") { src = pl.C.setC; bytes = N * sizeof(SetDesc); }
   else if (w == "blocks") { src = pl.C.blocks; bytes = (size_t)pl.nBlocks * sizeof(Block); }
   else if (w == "hits") { src = pl.C.hits; bytes = (size_t)pl.nHits * sizeof(Hit); }
+  else if (w == "anno:buckets" || w == "anno:rows") {                      // host-side annotation tables, to decode the `blocks` / `hits` taps
+    std::string names; std::vector<int32_t> se;
+    if (w == "anno:buckets") { for (auto& n : ctx->H.bucketNames) { names += n; names += '\n'; } bytes = names.size(); }
+    else { se.resize(ctx->H.rowStart.size() * 2); for (size_t i = 0; i < ctx->H.rowStart.size(); i++) { se[2 * i] = ctx->H.rowStart[i]; se[2 * i + 1] = ctx->H.rowEnd[i]; } bytes = se.size() * 4; }
+    *nWritten = bytes; if (!dst) return EQP_OK;
+    if (dstBytes < bytes) return fail(ctx, EQP_ERR_ARG, "eqp_debug_fetch: buffer too small");
+    memcpy(dst, w == "anno:buckets" ? (const void*)names.data() : (const void*)se.data(), bytes); return EQP_OK;
+  }
   else return fail(ctx, EQP_ERR_ARG, "eqp_debug_fetch: unknown tap " + w);
   if (w == "meta") { bytes = sizeof meta; *nWritten = bytes; if (!dst) return EQP_OK; if (dstBytes < bytes) return fail(ctx, EQP_ERR_ARG, "eqp_debug_fetch: buffer too small"); memcpy(dst, meta, bytes); return EQP_OK; }
   *nWritten = bytes;

@@ -9,6 +9,8 @@
 #include <dlfcn.h>
 #include <sys/stat.h>
 #include <cstdint>
+#include <mutex>
+#include <thread>
 #include <vector>
 #include "eqp_count.h"
 #include "host_util.hpp"
@@ -75,7 +77,8 @@ int main(int argc, char** argv) {
     if (libPath.empty()) libPath = here + "/libeqpcount.so";
     void* lib = dlopen(libPath.c_str(), RTLD_NOW | RTLD_LOCAL);
     if (!lib) { fprintf(stderr, "ERROR: cannot load %s: %s (there is no CPU fallback)\n", libPath.c_str(), dlerror()); return 1; }
-    FN(eqp_create) FN(eqp_load_annotation) FN(eqp_count_chunk) FN(eqp_feature_count) FN(eqp_feature_id) FN(eqp_last_error) FN(eqp_destroy)
+    FN(eqp_create) FN(eqp_load_annotation) FN(eqp_chunk_begin) FN(eqp_chunk_feed) FN(eqp_chunk_end) FN(eqp_map_columns) FN(eqp_output_row_count) FN(eqp_get_output_row)
+    FN(eqp_last_error) FN(eqp_destroy)
     eqp_ctx* ctx = nullptr;
     if (p_eqp_create(device, &ctx)) { fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(nullptr)); return 1; }
     std::string ex = project + "/exon-pipeline-files", bed = ex + "/bed-files/" + fileBase, map = ex + "/map-files/" + fileBase, R = std::to_string(radius);
@@ -84,10 +87,24 @@ int main(int argc, char** argv) {
                 f7 = pick(map + "_equivalent_junctions.map"), f8 = ex + "/genome-files/genome.fa.fai";
     eqp_annotation_files af{f0.c_str(), f1.c_str(), f2.c_str(), f3.c_str(), f4.c_str(), f5.c_str(), f6.c_str(), f7.c_str(), f8.c_str()};
     if (p_eqp_load_annotation(ctx, &af)) { fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(ctx)); return 1; }
-    std::string T = read_maybe_gz(tPath), J = read_maybe_gz(jPath), G = read_maybe_gz(gPath);   // what `zcat` feeds the Java mains (CIB:644-662)
+    // `zcat <file> | java ...` (CIB:644-662) becomes: one inflate thread per input, each feeding the device through eqp_chunk_feed as the
+    // text comes out of zlib, so inflating, the host-to-device copies and (for the later inputs) each other overlap.  The context is not
+    // thread-safe: feed calls are serialised by a mutex (they only copy into a page-locked staging buffer and queue an async copy).
+    if (p_eqp_chunk_begin(ctx, 0, 0, 0)) { fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(ctx)); return 1; }
+    { std::mutex mu; std::string failed; const std::string* paths[3] = {&tPath, &jPath, &gPath}; std::vector<std::thread> th;
+      for (int f = 0; f < 3; f++) th.emplace_back([&, f] {
+        try {
+          stream_maybe_gz(*paths[f], [&](const char* buf, size_t n) {
+            std::lock_guard<std::mutex> lk(mu);
+            if (failed.empty() && p_eqp_chunk_feed(ctx, f, (const uint8_t*)buf, n)) failed = p_eqp_last_error(ctx);
+            return failed.empty();
+          });
+        } catch (const std::exception& e) { std::lock_guard<std::mutex> lk(mu); if (failed.empty()) failed = e.what(); }
+      });
+      for (auto& t : th) t.join();
+      if (!failed.empty()) { fprintf(stderr, "ERROR: %s\n", failed.c_str()); return 1; } }
     eqp_counts C;
-    if (p_eqp_count_chunk(ctx, &P, (const uint8_t*)T.data(), T.size(), (const uint8_t*)J.data(), J.size(), (const uint8_t*)G.data(), G.size(), 0, &C)) {
-      fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(ctx)); return 1; }
+    if (p_eqp_chunk_end(ctx, &P, &C)) { fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(ctx)); return 1; }
     printf("NUMBER_MAPPED_READS=%lld\n", (long long)C.number_mapped_reads);                      // ConvertSamBed.java:266, CIB:975-976
     const char* names[3] = {"gene", "exon", "junction"}; const double* vec[3] = {C.gene, C.exon, C.junction};
     const uint64_t* fx[3] = {C.gene_fixed, C.exon_fixed, C.junction_fixed};
@@ -95,14 +112,20 @@ int main(int argc, char** argv) {
       if (!(P.modes & (1 << m))) continue;
       std::string path = outBase + "-" + names[m] + ".cnt";
       FILE* f = fopen(path.c_str(), "w"); if (!f) { fprintf(stderr, "ERROR: cannot write %s\n", path.c_str()); return 1; }
-      int64_t n = p_eqp_feature_count(ctx, m); bool nonZeroOnly = m == 2 && nonZeroJunctions;            // ComputeCounts -n (CC:1034-1037)
-      for (int64_t k = 0; k < n; k++) {                                                                  // TreeSet order; "0" when absent (ComputeCounts.java:877-897)
-        if (fx[m][k] == 0) { if (!nonZeroOnly) fprintf(f, "%s\t0\n", p_eqp_feature_id(ctx, m, k)); continue; }
-        fprintf(f, "%s\t%s\n", p_eqp_feature_id(ctx, m, k), java_double(vec[m][k]).c_str());
+      // rows in the reference's print order (ComputeCounts.java:875-950): 2-column map = ids in TreeSet order, "0" when absent; 3-column map =
+      // one row per map line under its column-2 id, "0.0" when absent; -n (the junction run under -nj, CC:1034-1037) drops the zero rows
+      int64_t n = p_eqp_output_row_count(ctx, m); bool nonZeroOnly = m == 2 && nonZeroJunctions; const char* zero = p_eqp_map_columns(ctx, m) == 3 ? "0.0" : "0";
+      for (int64_t k = 0; k < n; k++) {
+        eqp_output_row r; if (p_eqp_get_output_row(ctx, m, k, &r)) { fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(ctx)); return 1; }
+        if (m == 2 && !(r.always || C.junction_active[r.act])) continue;                                 // not in this chunk's filtered junction map (a27)
+        if (fx[m][r.feature] == 0) { if (!nonZeroOnly) fprintf(f, "%s\t%s\n", r.id, zero); continue; }
+        fprintf(f, "%s\t%s\n", r.id, java_double(vec[m][r.feature]).c_str());
       }
       fclose(f);
-      printf("Num weight objects in BED file: %lld (%lld included, %lld excluded) [%s]\n", (long long)C.num_weight_objects[m], (long long)C.num_weight_objects_included[m],
-             (long long)C.num_weight_objects_excluded[m], names[m]);
+      double nw = (double)C.num_weight_objects[m];                                                       // ComputeCounts.java:986-989
+      fprintf(stderr, "Num weight objects in BED file: %lld, num weight objects included: %lld (%.2f%%), num weight objects excluded: %lld (%.2f%%).\n", (long long)C.num_weight_objects[m],
+              (long long)C.num_weight_objects_included[m], C.num_weight_objects_included[m] * 100.0 / nw, (long long)C.num_weight_objects_excluded[m], C.num_weight_objects_excluded[m] * 100.0 / nw);
+      fprintf(stderr, "Sum of weights contributing to count objects: %.2f\n", C.sum_weights[m]);
     }
     if (P.modes & 1) printf("NUMBER_EXPRESSED_READS=%lld\n", (long long)C.number_expressed_reads);        // ComputeCounts.java:991-993
     p_eqp_destroy(ctx);

@@ -23,6 +23,18 @@ inline std::string read_maybe_gz(const std::string& path) {
   return out;
 }
 
+// Same, piecewise: fn(buf, n) is called with consecutive pieces of the inflated text; it returns false to stop.
+template <class F>
+inline void stream_maybe_gz(const std::string& path, F&& fn, size_t piece = (size_t)8 << 20) {
+  gzFile f = gzopen(path.c_str(), "rb");
+  if (!f) throw std::runtime_error("File " + path + " not found.");
+  gzbuffer(f, 1 << 20);
+  std::string buf(piece, '\0'); int n;
+  while ((n = gzread(f, &buf[0], (unsigned)buf.size())) > 0) if (!fn(buf.data(), (size_t)n)) break;
+  bool bad = n < 0; gzclose(f);
+  if (bad) throw std::runtime_error("Problem reading " + path);
+}
+
 // java.lang.Double.toString: shortest digits that round-trip (JDK >= 19 exactly; older JDKs print the same digits except in
 // rare cases where they emit one digit more), decimal notation for 1e-3 <= |d| < 1e7, else computerised scientific notation.
 inline std::string java_double(double d) {

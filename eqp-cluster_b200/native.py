@@ -263,6 +263,12 @@ class CountContext:
             self._check(self.lib.eqp_debug_fetch(self.h, what.encode(), out.ctypes.data, out.nbytes, C.byref(n)))
         return out
 
+    def bucket_names(self):
+        return self.debug_fetch("anno:buckets", np.uint8).tobytes().decode().split("\n")[:-1]
+
+    def row_table(self):
+        return self.debug_fetch("anno:rows", np.int32).reshape(-1, 2)
+
     def debug_decode(self, sam, misalign=0):
         """Run only the tokenizer kernel on one SAM text: (rows, err_code, err_detail); rows as `eqp_emu decode` prints them."""
         addr, n, keep = _buf(sam)

@@ -167,7 +167,8 @@ int  eqp_chunk_feed(eqp_ctx* ctx, int input /* 0 transcript, 1 junction, 2 genom
 int  eqp_chunk_end(eqp_ctx* ctx, const eqp_params* params, eqp_counts* out);
 
 /* Debug/parity taps: copy a device intermediate of the last chunk to the host.
- * what: "weights:<T|J|G|TJ|final>", "selection", "blocks", "hits", "a20".  Layouts are documented in DESIGN.md. */
+ * what: "weights:<T|J|G|TJ|final>", "selection", "blocks", "hits", "a20", "meta"; "anno:buckets" (newline-separated reference names in
+ * bucket order) and "anno:rows" (int32 start,end per B row) decode the bucket / row indices.  Layouts are documented in DESIGN.md. */
 int  eqp_debug_fetch(eqp_ctx* ctx, const char* what, void* dst, size_t dst_bytes, size_t* n_written);
 
 /* Test tap for the a1/a2 tokenizer kernel alone: decodes one SAM text, placed `misalign` (0-15) bytes after a 16-byte boundary in

@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 import eqp_cluster_b200 as eqp
-from conftest import GOLDEN, assert_counts_match, read_cnt, read_sams, read_stats
+from conftest import GOLDEN, SHAPES, assert_counts_match, assert_rows_match, read_cnt, read_rows, read_sams, read_stats, read_weights
 
 pytestmark = pytest.mark.gpu
 
@@ -26,13 +26,19 @@ def check_chunk(ctx, chunk, oracle_dir, params=None, exact=False):
     assert res.number_expressed_reads == int(st["NUMBER_EXPRESSED_READS"])
     assert res.num_weight_objects[0] == int(st["NUM_WEIGHT_OBJECTS"])
     assert res.kernel_launches > 0 and res.device_ms > 0
-    for m in eqp.MODES:
-        want = read_cnt(os.path.join(oracle_dir, m + ".cnt"))
-        got = res.as_dict(m, nonzero_only=(m == "junction"))
-        if m != "junction":
-            assert set(got) == set(want), m                           # every id of the map is printed (ComputeCounts.java:877-897)
-        assert_counts_match(got, want, exact=exact, what=m)
+    for i, m in enumerate(eqp.MODES):
+        # rows in print order: every id of the map for gene / exon (ComputeCounts.java:877-897), the non-zero rows of the filtered junction map
+        assert_rows_match(res.rows(m), read_rows(os.path.join(oracle_dir, m + ".cnt")), exact=exact, what=m)
+        assert abs(res.sum_weights[i] - float(st["SUM_WEIGHTS_" + m.upper()])) <= 0.01, m    # ComputeCounts.java:989
     return res
+
+
+def check_weights(ctx, oracle_dir):
+    """a20 of the weight pass and the final.wgt entry of every fragment in the intersection, against bed.wgt / final.wgt."""
+    base = int(ctx.debug_fetch("meta", np.uint32)[0])
+    a20, nfinal = ctx.debug_fetch("a20", np.uint32), ctx.debug_fetch("weights:final", np.uint32)
+    got = {"F%09d" % (base + s): (int(a20[s]), int(nfinal[s])) for s in np.nonzero(a20)[0]}
+    assert got == read_weights(oracle_dir)
 
 
 @pytest.mark.parametrize("name,seed,layout,spliced,n", [
@@ -41,6 +47,32 @@ def check_chunk(ctx, chunk, oracle_dir, params=None, exact=False):
 def test_counts_match_oracle(world, ctx, name, seed, layout, spliced, n):
     c = world.chunk(name, seed, 1, n, layout, spliced)
     check_chunk(ctx, c, c["oracle"])
+
+
+@pytest.mark.parametrize("layout,seed", [("se", 1001), ("pe", 1003)])
+@pytest.mark.parametrize("shape", sorted(SHAPES))
+def test_annotation_shapes(shape_worlds, shape, layout, seed):
+    """One dense world per shape of SURVEY 8d (length differences / a17, tr- exons, long tr- fillers, .inv-strand, two versions,
+    3-column junction map) and their mix: counts, statistics and per-fragment weights against the oracle."""
+    w = shape_worlds(shape)
+    c = w.chunk(layout, seed, 1, 6000, layout)
+    with eqp.CountContext(0).load_annotation(w.anno) as cx:
+        check_chunk(cx, c, c["oracle"])
+        check_weights(cx, c["oracle"])
+        assert cx.map_columns["junction"] == (3 if shape == "map3" else 2)
+
+
+@pytest.mark.parametrize("direction,code", [("forward", 1), ("backward", 2)])
+@pytest.mark.parametrize("layout,seed", [("se", 1001), ("pe", 1003)])
+def test_strand_specific_mode(shape_worlds, layout, seed, direction, code):
+    w = shape_worlds("mixed")
+    c = w.chunk(layout, seed, 1, 6000, layout)
+    o = w.oracle_run(layout, ("--stranded=" + direction,))
+    p = eqp.default_params()
+    p.stranded = code
+    with eqp.CountContext(0).load_annotation(w.anno) as cx:
+        check_chunk(cx, c, o, params=p)
+        check_weights(cx, o)
 
 
 def test_weight_intermediates_match_oracle(world, ctx):
@@ -130,10 +162,10 @@ def test_errors_are_reported_not_swallowed(world, ctx):
     with pytest.raises(eqp.EqpError):
         ctx.count_chunk(t.replace(b"F000000007", b"Q000000007"), j, g)  # SamReader.java:157
     p = eqp.default_params()
-    p.stranded = 1
+    p.stranded = 3
     with pytest.raises(eqp.EqpError) as e:
         ctx.count_chunk(t, j, g, params=p)
-    assert e.value.code == -5
+    assert e.value.code == -1
 
 
 def test_chunk_vectors_add_up(world, ctx):
@@ -150,16 +182,37 @@ def test_chunk_vectors_add_up(world, ctx):
         k = s.find(b"\nF%09d" % frag)
         return (s, b"") if k < 0 else (s[:k + 1], s[k + 1:])
     halves = [split(s, 20001) for s in sams]
-    n = None
-    acc = None
+    n = ctx.vector_length
+    acc = eqp.sharding.wide_zeros(n, device="cuda")
+    torch.cuda.synchronize()
     for h in (0, 1):
         ctx.count_chunk(*[x[h] for x in halves])
-        if acc is None:
-            _, n = ctx.device_vector()
-            acc = torch.zeros(n, dtype=torch.int64, device="cuda")
+        assert ctx.device_vector()[1] == n
         ctx.accumulate(acc.data_ptr())
-    got = acc.cpu().numpy().view(np.uint64)[:want.size]
-    assert n == want.size + res.fixed["junction"].size and np.array_equal(got, want)
+    wide = acc.cpu().numpy().view(np.uint64)
+    got = (wide[n:] << np.uint64(38)) + wide[:n]                         # limbs back to one 2^-38 word (no overflow at this size)
+    assert n == want.size + res.fixed["junction"].size and np.array_equal(got[:want.size], want)
+    assert np.array_equal(eqp.wide_to_double(wide)[:want.size], want.astype(np.float64) / float(1 << 38))
+    # the reduce with NCCL called inside the library: a one-rank communicator on this GPU (the multi-rank run is tools/cohort.py)
+    ctx.comm_init(eqp.comm_id(), 1, 0)
+    ctx.reduce_sample(acc.data_ptr(), root=0)
+    assert np.array_equal(acc.cpu().numpy().view(np.uint64), wide)
+
+
+def test_wide_accumulator_does_not_wrap(world, ctx):
+    """A feature that collects more than 2^26 reads' worth of weight over the chunks of a sample wraps a single 2^-38 word; the wide
+    accumulator (fraction limb + integer limb) holds it."""
+    import torch
+    c = world.chunk("se_small", 1001, 1, 3000, "se")
+    res = ctx.count_chunk(*read_sams(c["dir"], "se"))
+    n = ctx.vector_length
+    acc = eqp.sharding.wide_zeros(n, device="cuda")
+    k = int(np.argmax(res.fixed["gene"]))
+    top = float(res.counts["gene"][k])
+    acc[n + k] = (1 << 27)                                                # as if earlier chunks had put 134 M reads on the top gene
+    torch.cuda.synchronize()
+    ctx.accumulate(acc.data_ptr())
+    assert eqp.wide_to_double(acc.cpu().numpy())[k] == float(1 << 27) + top
 
 
 def test_sample_files_from_the_reduced_vector(world, ctx, tmp_path):
@@ -173,8 +226,8 @@ def test_sample_files_from_the_reduced_vector(world, ctx, tmp_path):
         ch = world.chunk("sf_%d" % c, seed, first, 20000, "se")
         res = ctx.count_chunk(*read_sams(ch["dir"], "se"))
         if acc is None:
-            _, n = ctx.device_vector()
-            acc = torch.zeros(n, dtype=torch.int64, device="cuda")
+            acc = eqp.sharding.wide_zeros(ctx.vector_length, device="cuda")
+            torch.cuda.synchronize()
         ctx.accumulate(acc.data_ptr())
         for m in eqp.MODES:                                              # chunk files as compute-counts writes them ("0" rows, junctions non-zero only)
             p = os.path.join(str(tmp_path), "s-C%03d-%s.cnt" % (c + 1, m))
@@ -215,3 +268,96 @@ def test_prefetched_chunks_give_the_same_counts(world, ctx):
     for m in eqp.MODES:
         assert np.array_equal(fa[m], keep[m][0]) and np.array_equal(fb[m], keep[m][1]) and np.array_equal(pb2.fixed[m], keep[m][1]), m
     assert pa.number_mapped_reads == ra.number_mapped_reads and pb2.number_mapped_reads == rb.number_mapped_reads
+
+
+def test_streamed_chunk_gives_the_same_counts(world, ctx):
+    """eqp_chunk_begin / feed / end: the three texts fed piecewise and interleaved (as three inflate threads would) count to the same bits."""
+    c = world.chunk("se_mid", 1011, 1, 40000, "se")
+    sams = read_sams(c["dir"], "se")
+    ref = ctx.count_chunk(*sams)
+
+    def pieces():
+        step, offs = 3_000_001, [0, 0, 0]
+        while any(offs[f] < len(sams[f]) for f in range(3)):
+            for f in (2, 0, 1):
+                if offs[f] < len(sams[f]):
+                    yield f, sams[f][offs[f]:offs[f] + step]
+                    offs[f] += step
+    got = ctx.count_stream(pieces())
+    for m in eqp.MODES:
+        assert np.array_equal(ref.fixed[m], got.fixed[m]), m
+    assert got.number_mapped_reads == ref.number_mapped_reads
+    empty = ctx.count_stream(iter(()))
+    assert empty.number_mapped_reads == 0
+
+
+BLOCK = np.dtype([("bucket", "<i4"), ("start", "<i4"), ("end", "<i4"), ("L", "<u2"), ("I", "<u2"), ("D", "<u2"), ("seg", "u1"), ("maxSeg", "u1"),
+                  ("aln", "<u4"), ("readIdx", "u1"), ("paired", "u1"), ("strand", "u1"), ("pad", "u1"), ("slot", "<u4")])
+HIT = np.dtype([("block", "<u4"), ("row", "<i4"), ("overlap", "<i4")])
+
+
+def test_selection_blocks_and_join_taps(world, ctx):
+    """The intermediates behind the counts, against the oracle's files: which records survive the two CombineSamFiles runs
+    (`selection` tap vs combined.sam), the BED6 blocks (`blocks` tap vs combined.bed, a8-a10), and the join (`hits` tap vs
+    intersection.bed, a11) — the latter is the device's bucketed binary search against a file the oracle wrote and
+    tests/test_shapes.py::test_join_against_brute_force checks against an O(|A| x |B|) restatement."""
+    c = world.chunk("pe_small", 1003, 1, 3000, "pe")
+    sams = read_sams(c["dir"], "pe")
+    ctx.count_chunk(*sams)
+    meta = ctx.debug_fetch("meta", np.uint32)
+    base, n_slots = int(meta[0]), int(meta[1])
+    # --- selection: per slot up to 4 parts (file, read-index filter); expand to the multiset of mapped+unmapped lines the reference prints
+    sel = ctx.debug_fetch("selection", np.uint32)
+    by_frag = [{}, {}, {}]
+    for f in range(3):
+        for line in sams[f].split(b"\n"):
+            if line and not line.startswith(b"@"):
+                by_frag[f].setdefault(int(line[1:10]), []).append(line)
+
+    def read_index(line):
+        flag = int(line.split(b"\t")[1])
+        return 1 if not flag & 1 or flag & 64 or not flag & 128 else 2
+    got = []
+    for s in range(n_slots):
+        v = int(sel[s])
+        for k in range((v >> 16) & 7):
+            f, flt = (v >> (4 * k)) & 3, (v >> (4 * k + 2)) & 3
+            got += [l for l in by_frag[f].get(base + s, []) if not flt or read_index(l) == flt]
+    want = [l for l in open(os.path.join(c["oracle"], "combined.sam"), "rb").read().split(b"\n") if l and not l.startswith(b"@")]
+    assert got == want
+    # --- blocks: (reference name, start, end, L, I, D, seg, maxSeg, P/S + read index, strand) per fragment, alignment ids relabelled (SURVEY H10)
+    blk = ctx.debug_fetch("blocks", BLOCK)
+    names = ctx.bucket_names()
+    gb = sorted((base + int(b["slot"]), names[b["bucket"]], int(b["start"]), int(b["end"]), int(b["L"]), int(b["I"]), int(b["D"]), int(b["seg"]), int(b["maxSeg"]),
+                 ("P" if b["paired"] else "S") + str(int(b["readIdx"])), chr(b["strand"])) for b in blk)
+    wb = []
+    for l in open(os.path.join(c["oracle"], "combined.bed")):
+        t = l.rstrip("\n").split("\t")
+        nm = t[3]
+        frag = int(nm[1:10])
+        L, I, D = (int(nm.split("-" + k)[1].split("-")[0]) for k in ("L", "I", "D"))
+        seg, rest = nm.split("-F")[1].split("-")
+        wb.append((frag, t[0], int(t[1]), int(t[2]), L, I, D, int(seg), int(rest.split("/")[0]), rest.split("/")[1], t[5]))
+    versionless = [x for x in wb if x[1] in set(names)]                   # references without rows in the B file produce no device blocks
+    assert gb == sorted(versionless) and len(gb) > 3000
+    # --- hits: (block coordinates, B row coordinates, overlap) against intersection.bed
+    hits = ctx.debug_fetch("hits", HIT)
+    rows = ctx.row_table()
+    gh = sorted((names[blk[h["block"]]["bucket"]], int(blk[h["block"]]["start"]), int(blk[h["block"]]["end"]), base + int(blk[h["block"]]["slot"]),
+                 int(rows[h["row"]][0]), int(rows[h["row"]][1]), int(h["overlap"])) for h in hits)
+    wh = sorted((t[0], int(t[1]), int(t[2]), int(t[3][1:10]), int(t[7]), int(t[8]), int(t[12])) for t in (l.rstrip("\n").split("\t") for l in open(os.path.join(c["oracle"], "intersection.bed"))))
+    assert gh == wh and len(gh) > 5000
+
+
+@pytest.mark.parametrize("layout,seed", [("se", 1001), ("pe", 1003)])
+def test_parity_at_bench_annotation_scale(tools, tmp_path_factory, layout, seed):
+    """400,000 reads on the 60,000-gene annotation bench.py uses (SURVEY 8d shape mix at its default rates): what
+    tools/parity_large.py runs at 1 M reads, sized so that the oracle needs about a minute per layout."""
+    from conftest import World
+    w = test_parity_at_bench_annotation_scale.__dict__.setdefault("world", None) or World(tools, tmp_path_factory.mktemp("world60k"), n_genes=60000)
+    test_parity_at_bench_annotation_scale.world = w
+    c = w.chunk(layout, seed, 1, 400000, layout)
+    cx = test_parity_at_bench_annotation_scale.__dict__.get("ctx") or eqp.CountContext(0).load_annotation(w.anno)
+    test_parity_at_bench_annotation_scale.ctx = cx
+    check_chunk(cx, c, c["oracle"])
+    check_weights(cx, c["oracle"])
