@@ -55,7 +55,7 @@ EQP_HD int key_form(const Aln& a, bool gene) {
   if (!h1) return 2;
   return 3;
 }
-EQP_HD uint64_t alignment_key(const CountView& V, const Aln& al, bool gene) {
+EQP_HD_CALL uint64_t alignment_key(const CountView& V, const Aln& al, bool gene) {
   const uint8_t fl = al.flags; const int form = key_form(al, gene);
   uint64_t hsh = mix64(0x1234, (uint64_t)((fl & 1) ? 0 : (fl >> 3) & 3));    // alignmentBaseId: fragment id, or fragment id + /S1, /S2
   hsh = mix64(hsh, (uint64_t)form);
@@ -69,7 +69,7 @@ EQP_HD uint64_t alignment_key(const CountView& V, const Aln& al, bool gene) {
   }
   return hsh;
 }
-EQP_HD bool halves_equal(const CountView& V, const Aln& a, int ha, const Aln& b, int hb, bool gene) {
+EQP_HD_CALL bool halves_equal(const CountView& V, const Aln& a, int ha, const Aln& b, int hb, bool gene) {
   TokCur ca = tok_begin(a, ha, gene), cb = tok_begin(b, hb, gene);
   while (true) {
     int32_t c1, s1, e1, c2, s2, e2;
@@ -80,7 +80,7 @@ EQP_HD bool halves_equal(const CountView& V, const Aln& a, int ha, const Aln& b,
   }
 }
 // string equality of two WeightObjectAlignment keys; on success `swapped` tells how b's halves map onto a's
-EQP_HD bool keys_equal(const CountView& V, const Aln& a, uint64_t ka, const Aln& b, uint64_t kb, bool gene, bool& swapped) {
+EQP_HD_CALL bool keys_equal(const CountView& V, const Aln& a, uint64_t ka, const Aln& b, uint64_t kb, bool gene, bool& swapped) {
   swapped = false;
   if (ka != kb) return false;
   if ((a.flags & 1) != (b.flags & 1)) return false;

@@ -94,7 +94,7 @@ int derr_class(uint32_t code) {
 }  // namespace
 
 struct eqp_ctx {
-  int device = 0; int nSm = 0; cudaStream_t stream = nullptr;
+  int device = 0; int nSm = 0; size_t totalMem = 0; cudaStream_t stream = nullptr;
   AnnoHost H; AnnoDevice D; AnnoView A{}; bool annoLoaded = false;
   std::unique_ptr<CudaBackend> be; std::unique_ptr<Pipeline<CudaBackend>> pl;
   ChunkResult R{}; bool haveChunk = false;
@@ -162,7 +162,7 @@ int eqp_create(int device, eqp_ctx** out) {
   try {
     std::unique_ptr<eqp_ctx> c(new eqp_ctx); c->device = device;
     EQP_CUDA(cudaSetDevice(device));
-    cudaDeviceProp prop; EQP_CUDA(cudaGetDeviceProperties(&prop, device)); c->nSm = prop.multiProcessorCount;
+    cudaDeviceProp prop; EQP_CUDA(cudaGetDeviceProperties(&prop, device)); c->nSm = prop.multiProcessorCount; c->totalMem = prop.totalGlobalMem;
     // a blocking stream: ordered against the legacy default stream, on which a caller (torch) typically prepares device-resident
     // inputs and accumulators (include/eqp_count.h, eqp_accumulate)
     EQP_CUDA(cudaStreamCreate(&c->stream));
@@ -341,6 +341,12 @@ int eqp_prefetch_chunk(eqp_ctx* ctx, const uint8_t* t_sam, size_t t_len, const u
   if (!ctx) return fail(ctx, EQP_ERR_ARG, "eqp_prefetch_chunk: null context");
   if ((t_len && !t_sam) || (j_len && !j_sam) || (g_len && !g_sam)) return fail(ctx, EQP_ERR_ARG, "eqp_prefetch_chunk: null SAM buffer with non-zero length");
   if (ctx->prefetched.size() >= 2) return fail(ctx, EQP_ERR_ARG, "eqp_prefetch_chunk: two chunks are already in flight");
+  { // never let announced texts crowd out the counting stage: resident texts + its work buffers (about half a text) must fit the device
+    size_t resident = t_len + j_len + g_len, largest = resident;
+    for (auto& c : ctx->prefetched) { size_t b = c.len[0] + c.len[1] + c.len[2]; resident += b; largest = std::max(largest, b); }
+    { size_t b = ctx->current.len[0] + ctx->current.len[1] + ctx->current.len[2]; if (ctx->current.dev[0]) { resident += b; largest = std::max(largest, b); } }
+    if ((double)resident + 0.6 * (double)largest > 0.92 * (double)ctx->totalMem)
+      return fail(ctx, EQP_ERR_CAPACITY, "eqp_prefetch_chunk: the announced chunk does not fit next to the resident ones (count a chunk first)"); }
   eqp_ctx::HostChunk c{};
   try {
     EQP_CUDA(cudaSetDevice(ctx->device));

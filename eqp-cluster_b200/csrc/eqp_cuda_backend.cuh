@@ -1,5 +1,5 @@
 // CUDA backend of the chunk pipeline (sm_100a): stream-ordered allocation, the generic per-item launcher,
-// a three-phase exclusive scan, the SAM line-index kernels and the tiled shared-memory SAM decode kernel.
+// a three-phase exclusive scan, the work-class ordering and the launch of the one-pass SAM tokenizer (eqp_tokenize.cuh).
 // The per-item logic lives in the eqp_*.h headers; this file owns how it is mapped to the machine.
 #pragma once
 #include <cuda_runtime.h>
@@ -19,21 +19,22 @@ struct CudaError : std::runtime_error { CudaError(const std::string& m) : std::r
 static const int EQP_NUM_SMS_DEFAULT = 148;
 
 // ---------------------------------------------------------------- generic per-item kernel
-template <class F>
+// Tag: an empty struct named after the pipeline stage (eqp_pipeline.h), so that profiler listings read k_items<eqpb::st::blocks_fill, ...>
+template <class Tag, class F>
 __global__ void __launch_bounds__(256) k_items(uint64_t n, F f) {
   uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
 }
 
 // same, compiled for at least MINB resident CTAs per SM: the latency-bound per-fragment stages trade registers for warps in flight
-template <int MINB, class F>
+template <class Tag, int MINB, class F>
 __global__ void __launch_bounds__(256, MINB) k_items_occ(uint64_t n, F f) {
   uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
 }
 
 // items [0, *count) with the count read on the device: work lists built by an earlier kernel, no host round trip
-template <class F>
+template <class Tag, class F>
 __global__ void __launch_bounds__(256) k_items_counted(const uint32_t* __restrict__ count, F f) {
   uint64_t n = *count, stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) f(i);
@@ -123,64 +124,6 @@ __global__ void __launch_bounds__(ORD_THREADS) k_order_scatter(const uint32_t* _
   }
 }
 
-// ---------------------------------------------------------------- line index
-// One warp per LINE_TILE (1024 B) tile: 16-byte loads, per-byte compare with '\n', warp reduction.
-static const int LI_WARPS = 8;
-__device__ __forceinline__ uint32_t nl_mask16(uint4 v) {                // bit k set iff byte k == '\n'
-  uint32_t w[4] = {v.x, v.y, v.z, v.w}; uint32_t m = 0;
-#pragma unroll
-  for (int q = 0; q < 4; q++) {
-    uint32_t x = w[q] ^ 0x0a0a0a0au;                                     // zero bytes mark newlines
-    uint32_t z = ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu); // 0x80 in every zero byte (exact, no carries across bytes)
-    m |= (((z >> 7) & 1u) | ((z >> 14) & 2u) | ((z >> 21) & 4u) | ((z >> 28) & 8u)) << (4 * q);
-  }
-  return m;
-}
-__global__ void __launch_bounds__(LI_WARPS * 32) k_count_newlines(const char* __restrict__ text, uint64_t len, uint64_t nTiles, uint32_t* __restrict__ cnt) {
-  uint64_t t = (uint64_t)blockIdx.x * LI_WARPS + (threadIdx.x >> 5); uint32_t lane = threadIdx.x & 31;
-  if (t >= nTiles) return;
-  uint64_t b = t * LINE_TILE; uint32_t c = 0;
-  if (b + LINE_TILE <= len && (((uintptr_t)(text + b)) & 15) == 0) {
-    const uint4* q = reinterpret_cast<const uint4*>(text + b);
-#pragma unroll
-    for (int k = 0; k < (int)(LINE_TILE / 512); k++) c += __popc(nl_mask16(__ldg(q + k * 32 + lane)));
-  } else {
-    uint64_t e = b + LINE_TILE < len ? b + LINE_TILE : len;
-    for (uint64_t i = b + lane; i < e; i += 32) c += text[i] == '\n';
-  }
-  c = __reduce_add_sync(0xffffffffu, c);
-  if (lane == 0) cnt[t] = c;
-}
-// cnt[] now holds exclusive tile offsets; write lineOff[k] = byte after the k-th newline (k >= 1), lineOff[0] = 0.
-__global__ void __launch_bounds__(LI_WARPS * 32) k_fill_line_offsets(const char* __restrict__ text, uint64_t len, uint64_t nTiles, const uint32_t* __restrict__ cnt,
-                                                                     uint64_t* __restrict__ lineOff, uint32_t nLines, int lastIsNewline) {
-  uint64_t t = (uint64_t)blockIdx.x * LI_WARPS + (threadIdx.x >> 5); uint32_t lane = threadIdx.x & 31;
-  if (t >= nTiles) return;
-  uint64_t b = t * LINE_TILE, e = b + LINE_TILE < len ? b + LINE_TILE : len; uint32_t k = cnt[t];
-  if (t == 0 && lane == 0) lineOff[0] = 0;
-  if (e == len && !lastIsNewline && lane == 0) lineOff[nLines] = len + 1;
-  if (b + LINE_TILE <= len && (((uintptr_t)(text + b)) & 15) == 0) {
-    const uint4* q = reinterpret_cast<const uint4*>(text + b);
-#pragma unroll
-    for (int r = 0; r < (int)(LINE_TILE / 512); r++) {
-      uint32_t m = nl_mask16(__ldg(q + r * 32 + lane)); uint32_t c = __popc(m);
-      uint32_t x = c;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= (uint32_t)d) x += y; }
-      uint32_t mine = k + x - c; uint64_t base = b + (uint64_t)r * 512 + lane * 16;
-      while (m) { int bit = __ffs(m) - 1; m &= m - 1; lineOff[++mine] = base + bit + 1; }
-      k += __shfl_sync(0xffffffffu, x, 31);
-    }
-  } else {
-    for (uint64_t i0 = b; i0 < e; i0 += 32) {
-      uint64_t i = i0 + lane; bool nl = i < e && text[i] == '\n';
-      uint32_t bal = __ballot_sync(0xffffffffu, nl);
-      if (nl) lineOff[k + __popc(bal & ((1u << lane) - 1)) + 1] = i + 1;
-      k += __popc(bal);
-    }
-  }
-}
-
 // ---------------------------------------------------------------- backend
 struct CudaBackend {
   cudaStream_t stream; int nSm;
@@ -223,19 +166,19 @@ struct CudaBackend {
     uint64_t g = (n + threads - 1) / threads, cap = (uint64_t)nSm * 32;  // grid-stride beyond 32 CTAs per SM
     return (int)(g < cap ? (g ? g : 1) : cap);
   }
-  template <class F> void launch(uint64_t n, F f) {
+  template <class Tag = st::misc, class F> void launch(uint64_t n, F f) {
     if (!n) return;
-    k_items<<<grid_for(n, 256), 256, 0, stream>>>(n, f); launches++;
+    k_items<Tag><<<grid_for(n, 256), 256, 0, stream>>>(n, f); launches++;
     EQP_CUDA(cudaGetLastError());
   }
-  template <class F> void launch_counted(const uint32_t* count, uint64_t maxN, F f) {
+  template <class Tag = st::misc, class F> void launch_counted(const uint32_t* count, uint64_t maxN, F f) {
     if (!maxN) return;
-    k_items_counted<<<nSm * 2, 256, 0, stream>>>(count, f); launches++;
+    k_items_counted<Tag><<<nSm * 2, 256, 0, stream>>>(count, f); launches++;
     EQP_CUDA(cudaGetLastError());
   }
-  template <int MINB, class F> void launch_occ(uint64_t n, F f) {
+  template <class Tag, int MINB, class F> void launch_occ(uint64_t n, F f) {
     if (!n) return;
-    k_items_occ<MINB><<<grid_for(n, 256), 256, 0, stream>>>(n, f); launches++;
+    k_items_occ<Tag, MINB><<<grid_for(n, 256), 256, 0, stream>>>(n, f); launches++;
     EQP_CUDA(cudaGetLastError());
   }
   void scan(uint32_t* p, uint64_t n) {
@@ -258,17 +201,6 @@ struct CudaBackend {
     k_order_scatter<<<nBlocks, ORD_THREADS, 0, stream>>>(key, n, hist, nBlocks, perm, nKeep); launches++;
     EQP_CUDA(cudaGetLastError());
     return nKeep;
-  }
-  // line index: counts per LINE_TILE tile, then offsets (Pipeline::index_lines calls these instead of the generic lambdas)
-  void count_newlines(const char* text, uint64_t len, uint64_t nTiles, uint32_t* cnt) {
-    if (!nTiles) return;
-    k_count_newlines<<<(unsigned)((nTiles + LI_WARPS - 1) / LI_WARPS), LI_WARPS * 32, 0, stream>>>(text, len, nTiles, cnt); launches++;
-    EQP_CUDA(cudaGetLastError());
-  }
-  void fill_line_offsets(const char* text, uint64_t len, uint64_t nTiles, const uint32_t* cnt, uint64_t* lineOff, uint32_t nLines, char last) {
-    if (!nTiles) return;
-    k_fill_line_offsets<<<(unsigned)((nTiles + LI_WARPS - 1) / LI_WARPS), LI_WARPS * 32, 0, stream>>>(text, len, nTiles, cnt, lineOff, nLines, last == '\n'); launches++;
-    EQP_CUDA(cudaGetLastError());
   }
   // a1/a2 in one pass (eqp_tokenize.cuh): allocates the line index + record SoA of `S`, launches the tokenizer, returns with S.nLines set.
   // The number of lines is only known afterwards, so the tables are sized for len/160 lines and the pass is repeated when that was too small.
@@ -308,10 +240,10 @@ struct CudaBackend {
       S.nLines = (uint32_t)lines;
       if (lines <= cap) return;
       cap = lines;                                                          // tables were too small (average line under 160 bytes): once more, exact
+      for (int k = 0; k < 14; k++) { EQP_CUDA(cudaFreeAsync(allocs.back(), stream)); allocs.pop_back(); }   // the first attempt's 14 tables go back to the pool now
     }
     throw CudaError("line count changed between two passes over the same text");
   }
-  void decode(const AnnoView&, const SamView&, uint32_t*) {}
   void finish_timing() {
     for (auto& p : decEv) { float ms = 0; if (cudaEventElapsedTime(&ms, p.first, p.second) == cudaSuccess) decodeMs += ms; cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     decEv.clear();

@@ -61,6 +61,11 @@ EQP_HD void counter_add64(unsigned long long* p, uint64_t v) {          // v < 2
 #endif
 }
 
+// stage tags: they only name the kernels (profiler listings)
+namespace st { struct misc; struct frag_table; struct frag_stats; struct select_tj_weights; struct select_stage1; struct select_stage2; struct seen_refs; struct junction_active;
+               struct blocks_count; struct blocks_fill; struct join_count; struct join_fill; struct work_class; struct alignment_build; struct work_lists; struct fragment_adjust;
+               struct fragment_weight; struct fragment_weight_gene; struct fragment_count; }
+
 struct ChunkResult {
   std::vector<double> counts[3]; std::vector<unsigned long long> fixed[3]; std::vector<uint8_t> junctionActive;
   unsigned long long stats[16]; uint32_t nRecords[3]; uint32_t err[2];
@@ -79,6 +84,7 @@ struct Pipeline {
 
   Pipeline(BE& b, const AnnoView& a, const RunParams& p) : be(b), A(a), P(p) {}
 
+  // line index of the host emulation (tests/emu); the CUDA backend builds it inside the tokenizer kernel
   void index_lines(int f, const char* text, uint64_t len) {
     SamView& S = C.sam[f]; S.text = text; S.len = len;
     uint64_t nTiles = (len + LINE_TILE - 1) / LINE_TILE;
@@ -107,8 +113,8 @@ struct Pipeline {
     { uint32_t init[6] = {0xFFFFFFFFu, 0, 0xFFFFFFFFu, 0, 0xFFFFFFFFu, 0}; be.to_device(scal + 2, init, sizeof init); }
     for (int f = 0; f < 3; f++) {
       uint32_t* mm = scal + 2 + 2 * f;
-      if (BE::kFusedDecode) be.decode_fused(A, C.sam[f], C.proc[f], text[f], len[f], scal, mm);   // one pass: line index + records + id range
-      else {
+      if constexpr (BE::kFusedDecode) be.decode_fused(A, C.sam[f], C.proc[f], text[f], len[f], scal, mm);   // CUDA: one pass, line index + records + id range
+      else {                                                             // host emulation (tests/emu): line index, then the per-line decoder
         index_lines(f, text[f], len[f]); be.stage("line-index"); be.decode(A, C.sam[f], scal);
         const SamView S = C.sam[f];
         be.launch(S.nLines, [=] EQP_LAMBDA(uint64_t i) { if (S.rf[i] & RF_REC) { atomic_min_u32(mm, S.frag[i]); atomic_max_u32(mm + 1, S.frag[i]); } });
@@ -135,7 +141,7 @@ struct Pipeline {
     be.stage("frag-range");
     // ---- fragment table: [first,end) line range per (file, slot); order check (CombineSamFiles.java:191-193)
     for (int f = 0; f < 3; f++) { const SamView S = C.sam[f]; FragFile* ff = C.ff[f]; uint32_t base = C.base; uint32_t* err = scal;
-      be.launch(S.nLines, [=] EQP_LAMBDA(uint64_t i) {
+      be.template launch<st::frag_table>(S.nLines, [=] EQP_LAMBDA(uint64_t i) {
         if (!(S.rf[i] & RF_REC)) return;
         uint32_t fr = S.frag[i];
         uint64_t pi = i, ni = i + 1;                                     // nearest record lines around i (header / empty lines skipped)
@@ -150,7 +156,7 @@ struct Pipeline {
     // ---- a3/a4: per-fragment statistics in each input
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
     { const ChunkView C = this->C;
-      be.launch((uint64_t)N * 3, [=] EQP_LAMBDA(uint64_t k) {
+      be.template launch<st::frag_stats>((uint64_t)N * 3, [=] EQP_LAMBDA(uint64_t k) {
         int f = (int)(k / N); uint32_t s = (uint32_t)(k % N); FragFile ff = C.ff[f][s]; FragStat st{};
         fragment_stats(A, C.sam[f], ff.first, ff.end, f == FILE_G, C.proc[f], st, ff, C.err, C.base + s);
         C.st[f][s] = st; C.ff[f][s].bits = ff.bits;
@@ -164,16 +170,16 @@ struct Pipeline {
     uint32_t* bnd = scal + 64;                         // [0] firstTJ [1] lastTJ [2] anyTJ
     { uint32_t init[3] = {0xFFFFFFFFu, 0, 0}; be.to_device(bnd, init, sizeof init); }
     { const ChunkView C = this->C;
-      be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
+      be.template launch<st::select_tj_weights>(N, [=] EQP_LAMBDA(uint64_t s) {
         C.stTJ[s] = combine_weights_ed(C.st[FILE_T][s], C.st[FILE_J][s], P.slack);
       });
-      be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
+      be.template launch<st::select_stage1>(N, [=] EQP_LAMBDA(uint64_t s) {
         Side a = side_of_file(FILE_T, C.ff[FILE_T][s], C.st[FILE_T][s]), b = side_of_file(FILE_J, C.ff[FILE_J][s], C.st[FILE_J][s]);
         SetDesc r = combine_stage(a, b, (uint32_t)s, firstT, firstJ, lastT, anyT, anyJ, P.slack, C.err, C.base + (uint32_t)s);
         C.setTJ[s] = r;
         if (sd_n(r)) { atomic_min_u32(bnd + 0, (uint32_t)s); atomic_max_u32(bnd + 1, (uint32_t)s); bnd[2] = 1; }
       });
-      be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
+      be.template launch<st::select_stage2>(N, [=] EQP_LAMBDA(uint64_t s) {
         FragFile ffs[3] = {C.ff[0][s], C.ff[1][s], C.ff[2][s]};
         Side a = side_of_set(C.setTJ[s], ffs, C.stTJ[s]), b = side_of_file(FILE_G, C.ff[FILE_G][s], C.st[FILE_G][s]);
         C.setC[s] = combine_stage(a, b, (uint32_t)s, bnd[0], firstG, bnd[1], bnd[2] != 0, anyG, P.slack, C.err, C.base + (uint32_t)s);
@@ -194,12 +200,12 @@ struct Pipeline {
     V.junctionActive = be.template alloc<uint8_t>((uint64_t)A.nAct + 1); be.memset((void*)V.junctionActive, 0, (uint64_t)A.nAct + 1);
     { const ChunkView C = this->C; uint8_t* act = (uint8_t*)V.junctionActive; const SamView J = C.sam[FILE_J];
       be.launch(J.nLines, [=] EQP_LAMBDA(uint64_t i) { if ((J.rf[i] & RF_REC) && J.ref[i] >= 0) C.seenRef[J.ref[i]] = 1; });
-      be.launch(N, [=] EQP_LAMBDA(uint64_t s) {
+      be.template launch<st::seen_refs>(N, [=] EQP_LAMBDA(uint64_t s) {
         SetDesc sd = C.setC[s];
         for (int k = 0; k < sd_n(sd); k++) { int f = sd_file(sd, k), flt = sd_filter(sd, k); FragFile ff = C.ff[f][s];
           for (uint32_t i = ff.first; i < ff.end; i++) { uint8_t rf = C.sam[f].rf[i]; if ((rf & RF_REC) && (!flt || rf_read_index(rf) == flt) && C.sam[f].ref[i] >= 0) C.seenRef[C.sam[f].ref[i]] = 1; } }
       });
-      be.launch((uint64_t)A.nRef, [=] EQP_LAMBDA(uint64_t r) {
+      be.template launch<st::junction_active>((uint64_t)A.nRef, [=] EQP_LAMBDA(uint64_t r) {
         if (!C.seenRef[r]) return;
         if (A.refFlags[r] & 2) raise(C.err, DERR_BAD_JUNCTION_ID, (uint32_t)r);
         for (uint32_t k = A.refActOff[r]; k < A.refActOff[r + 1]; k++) act[A.refAct[k]] = 1;
@@ -209,20 +215,20 @@ struct Pipeline {
     V.stats = be.template alloc<unsigned long long>(16); be.memset(V.stats, 0, 16 * sizeof(unsigned long long));
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
     { const ChunkView C = this->C; unsigned long long* stats = V.stats;
-      be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, false, P.stranded, nb, na); C.blkOff[s] = nb; C.alnOff[s] = na;
+      be.template launch<st::blocks_count>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, false, P.stranded, nb, na); C.blkOff[s] = nb; C.alnOff[s] = na;
         SetCursor c{0, 0xFFFFFFFFu}; int f; counter_add(&stats[9], set_next(C, C.setC[s], (uint32_t)s, c, f) ? 1u : 0u); }); }
     be.scan(C.blkOff, N); be.scan(C.alnOff, N);
     be.to_host(&nBlocks, C.blkOff + N, 4); be.to_host(&nAln, C.alnOff + N, 4);
     C.blocks = be.template alloc<Block>((uint64_t)nBlocks + 1); C.hitCnt = be.template alloc<uint32_t>((uint64_t)nBlocks + 1);
     C.alnBlk = be.template alloc<uint32_t>((uint64_t)nAln + 1); be.to_device(C.alnBlk + nAln, &nBlocks, 4);
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
-    { const ChunkView C = this->C; be.template launch_occ<6>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, P.stranded, nb, na); }); }
+    { const ChunkView C = this->C; be.template launch_occ<st::blocks_fill, 6>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, P.stranded, nb, na); }); }
     be.stage("blocks");
     // ---- a11: interval join (count, scan, fill)
-    { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { C.hitCnt[b] = join_block(A, C.blocks[b], nullptr, (uint32_t)b, P.stranded != 0); }); }
+    { const ChunkView C = this->C; be.template launch<st::join_count>(nBlocks, [=] EQP_LAMBDA(uint64_t b) { C.hitCnt[b] = join_block(A, C.blocks[b], nullptr, (uint32_t)b, P.stranded != 0); }); }
     be.scan(C.hitCnt, nBlocks); be.to_host(&nHits, C.hitCnt + nBlocks, 4);
     C.hits = be.template alloc<Hit>((uint64_t)nHits + 1);
-    { const ChunkView C = this->C; be.launch(nBlocks, [=] EQP_LAMBDA(uint64_t b) { join_block(A, C.blocks[b], C.hits + C.hitCnt[b], (uint32_t)b, P.stranded != 0); }); }
+    { const ChunkView C = this->C; be.template launch<st::join_fill>(nBlocks, [=] EQP_LAMBDA(uint64_t b) { join_block(A, C.blocks[b], C.hits + C.hitCnt[b], (uint32_t)b, P.stranded != 0); }); }
     be.stage("join");
     // ---- a12-a25
     V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
@@ -239,21 +245,21 @@ struct Pipeline {
     // fragments with hits, ordered by descending hit-count class (stable within a class): warps of the thread-per-fragment stages get
     // fragments of similar cost while neighbouring lanes still touch neighbouring memory
     uint32_t* work = be.template alloc<uint32_t>((uint64_t)N + 1); uint32_t* perm = be.template alloc<uint32_t>((uint64_t)N + 1);
-    { const ChunkView C = this->C; be.launch(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t h = C.hitCnt[C.blkOff[s + 1]] - C.hitCnt[C.blkOff[s]]; uint32_t c = 0; while (h) { c++; h >>= 1; } work[s] = c; }); }   // class = 1 + floor(log2(hits)): coarse, so neighbouring slots stay neighbours
+    { const ChunkView C = this->C; be.template launch<st::work_class>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t h = C.hitCnt[C.blkOff[s + 1]] - C.hitCnt[C.blkOff[s]]; uint32_t c = 0; while (h) { c++; h >>= 1; } work[s] = c; }); }   // class = 1 + floor(log2(hits)): coarse, so neighbouring slots stay neighbours
     uint32_t nWork = be.order_by_work(work, N, perm);
     { const ChunkView C = this->C; const CountView V = this->V;
       be.stage("order");
-      be.launch(nAln, [=] EQP_LAMBDA(uint64_t a) { alignment_build(A, C, V, P, (uint32_t)a); });
+      be.template launch<st::alignment_build>(nAln, [=] EQP_LAMBDA(uint64_t a) { alignment_build(A, C, V, P, (uint32_t)a); });
       be.stage("alignment-build");
       // the rare shapes (transcript exon longer than its genome exon; tr- exons) go through work lists built on the device
-      be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) { uint32_t s = perm[i]; if (C.slotLd[s]) list_push(listCnt, listLd, s); if (C.slotTr[s]) list_push(listCnt + 1, listTr, s); });
-      be.launch_counted(listCnt, N, [=] EQP_LAMBDA(uint64_t i) { fragment_adjust(A, C, V, listLd[i]); });                         // a17 before the dedupe
-      be.template launch_occ<4>(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
-      if (V.alnG) be.launch_counted(listCnt + 1, N, [=] EQP_LAMBDA(uint64_t i) { fragment_weight_gene(C, V, listTr[i]); });      // gene-run keys of tr- fragments
+      be.template launch<st::work_lists>(nWork, [=] EQP_LAMBDA(uint64_t i) { uint32_t s = perm[i]; if (C.slotLd[s]) list_push(listCnt, listLd, s); if (C.slotTr[s]) list_push(listCnt + 1, listTr, s); });
+      be.template launch_counted<st::fragment_adjust>(listCnt, N, [=] EQP_LAMBDA(uint64_t i) { fragment_adjust(A, C, V, listLd[i]); });                         // a17 before the dedupe
+      be.template launch_occ<st::fragment_weight, 4>(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
+      if (V.alnG) be.template launch_counted<st::fragment_weight_gene>(listCnt + 1, N, [=] EQP_LAMBDA(uint64_t i) { fragment_weight_gene(C, V, listTr[i]); });      // gene-run keys of tr- fragments
       be.stage("fragment-weight");
       // the three counting runs of one fragment back to back in one thread: runs two and three find the fragment's alignments and
       // hits in cache instead of paying the DRAM latency chain again (the runs were latency-bound as three concurrent kernels)
-      be.launch(nWork, [=] EQP_LAMBDA(uint64_t i) {
+      be.template launch<st::fragment_count>(nWork, [=] EQP_LAMBDA(uint64_t i) {
         uint32_t s = perm[i];
         for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) {
           uint64_t ws; int r = fragment_count(A, C, V, P, m, s, ws);       // 0 not a weight object, 1 included, 2 excluded (ComputeCounts.java:986-989)

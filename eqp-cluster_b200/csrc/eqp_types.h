@@ -6,8 +6,10 @@
 
 #if defined(__CUDACC__)
 #define EQP_HD __host__ __device__ __forceinline__
+#define EQP_HD_CALL __host__ __device__ __noinline__      // real calls: keeps the callers' register allocation small
 #else
 #define EQP_HD inline
+#define EQP_HD_CALL inline
 #endif
 
 namespace eqpb {

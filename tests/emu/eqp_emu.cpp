@@ -13,9 +13,9 @@ struct HostBackend {
   std::vector<void*> allocs;
   template <class T> T* alloc(uint64_t n) { void* p = calloc(n ? n : 1, sizeof(T)); allocs.push_back(p); return (T*)p; }
   void memset(void* p, int v, uint64_t bytes) { ::memset(p, v, bytes); }
-  template <class F> void launch(uint64_t n, F f) { for (uint64_t i = 0; i < n; i++) f(i); }
-  template <int MINB, class F> void launch_occ(uint64_t n, F f) { launch(n, f); }
-  template <class F> void launch_counted(const uint32_t* count, uint64_t, F f) { for (uint64_t i = 0; i < *count; i++) f(i); }
+  template <class Tag = st::misc, class F> void launch(uint64_t n, F f) { for (uint64_t i = 0; i < n; i++) f(i); }
+  template <class Tag, int MINB, class F> void launch_occ(uint64_t n, F f) { for (uint64_t i = 0; i < n; i++) f(i); }
+  template <class Tag = st::misc, class F> void launch_counted(const uint32_t* count, uint64_t, F f) { for (uint64_t i = 0; i < *count; i++) f(i); }
   void scan(uint32_t* p, uint64_t n) { uint32_t acc = 0; for (uint64_t i = 0; i < n; i++) { uint32_t v = p[i]; p[i] = acc; acc += v; } p[n] = acc; }
   void to_host(void* dst, const void* src, uint64_t bytes) { memcpy(dst, src, bytes); }
   void to_device(void* dst, const void* src, uint64_t bytes) { memcpy(dst, src, bytes); }
