@@ -82,6 +82,7 @@ def build_tools(force=False):
     if force or _newer(_glob(CSRC, (".h", ".hpp")) + [emu_src], EMU_BIN):
         _run(["g++", "-std=c++17", "-O2", "-o", EMU_BIN, emu_src, "-lz"])
         _run(["g++", "-std=c++17", "-O2", "-DEQP_FLAT_SCAN=0", "-o", EMU_BIN + "_chain", emu_src, "-lz"])   # duplicate-chain walk for every fragment
+        _run(["g++", "-std=c++17", "-O2", "-DEQP_FS_SMALL=2", "-DEQP_FT_SMALL=3", "-o", EMU_BIN + "_retry", emu_src, "-lz"])   # tiny small tables: most fragments take the large-table retry
     return WORLDGEN_BIN, EMU_BIN
 
 

@@ -32,10 +32,10 @@ EQP_HD TokCur tok_begin(const Aln& a, int h, bool gene) {
   TokCur c; c.s0 = h == 1 ? a.hit0 : a.split; c.s1 = h == 1 ? a.split : a.hit1; c.nIv = h == 1 ? a.nIv1 : a.nIv2; c.r = -1; c.gene = gene; c.started = false; return c;
 }
 static const int32_t TOK_EMPTY = (int32_t)0x80000000;
-EQP_HD bool tok_next(const CountView& V, TokCur& c, int32_t& chr, int32_t& gs, int32_t& ge) {
+EQP_HD bool tok_next(const HitX* hx, TokCur& c, int32_t& chr, int32_t& gs, int32_t& ge) {
   while (++c.r < c.nIv) {
     for (uint32_t i = c.s0; i < c.s1; i++) {
-      const HitX& x = V.hx[i];
+      const HitX& x = hx[i];
       if (!(x.flags & 1) || x.ivRank != c.r) continue;
       if (x.chr <= -2 && !c.gene) {
         if (!c.started) break;                                              // leading tr- interval: dropped
@@ -55,7 +55,8 @@ EQP_HD int key_form(const Aln& a, bool gene) {
   if (!h1) return 2;
   return 3;
 }
-EQP_HD_CALL uint64_t alignment_key(const CountView& V, const Aln& al, bool gene) {
+// (the real calls take the hit table, not the view: a by-reference struct argument would force the caller to copy its kernel parameters to local memory)
+EQP_HD_CALL uint64_t alignment_key(const HitX* hx, const Aln& al, bool gene) {
   const uint8_t fl = al.flags; const int form = key_form(al, gene);
   uint64_t hsh = mix64(0x1234, (uint64_t)((fl & 1) ? 0 : (fl >> 3) & 3));    // alignmentBaseId: fragment id, or fragment id + /S1, /S2
   hsh = mix64(hsh, (uint64_t)form);
@@ -65,22 +66,22 @@ EQP_HD_CALL uint64_t alignment_key(const CountView& V, const Aln& al, bool gene)
     if ((form == 1 || form == 2) && part == 1) break;
     if (form == 0 && part == 1) hsh = mix64(hsh, 0xABCDEF00u);               // the "-" between the two halves
     TokCur c = tok_begin(al, half, gene); int32_t chr, gs, ge;
-    while (tok_next(V, c, chr, gs, ge)) hsh = mix64(mix64(mix64(hsh, (uint64_t)(uint32_t)chr), (uint64_t)gs), (uint64_t)ge);
+    while (tok_next(hx, c, chr, gs, ge)) hsh = mix64(mix64(mix64(hsh, (uint64_t)(uint32_t)chr), (uint64_t)gs), (uint64_t)ge);
   }
   return hsh;
 }
-EQP_HD_CALL bool halves_equal(const CountView& V, const Aln& a, int ha, const Aln& b, int hb, bool gene) {
+EQP_HD_CALL bool halves_equal(const HitX* hx, const Aln& a, int ha, const Aln& b, int hb, bool gene) {
   TokCur ca = tok_begin(a, ha, gene), cb = tok_begin(b, hb, gene);
   while (true) {
     int32_t c1, s1, e1, c2, s2, e2;
-    bool na = tok_next(V, ca, c1, s1, e1), nb = tok_next(V, cb, c2, s2, e2);
+    bool na = tok_next(hx, ca, c1, s1, e1), nb = tok_next(hx, cb, c2, s2, e2);
     if (na != nb) return false;
     if (!na) return true;
     if (c1 != c2 || s1 != s2 || e1 != e2) return false;
   }
 }
 // string equality of two WeightObjectAlignment keys; on success `swapped` tells how b's halves map onto a's
-EQP_HD_CALL bool keys_equal(const CountView& V, const Aln& a, uint64_t ka, const Aln& b, uint64_t kb, bool gene, bool& swapped) {
+EQP_HD_CALL bool keys_equal(const HitX* hx, const Aln& a, uint64_t ka, const Aln& b, uint64_t kb, bool gene, bool& swapped) {
   swapped = false;
   if (ka != kb) return false;
   if ((a.flags & 1) != (b.flags & 1)) return false;
@@ -90,17 +91,17 @@ EQP_HD_CALL bool keys_equal(const CountView& V, const Aln& a, uint64_t ka, const
   if (form == 0) {
     bool sa = !(a.start1 <= a.start2), sb = !(b.start1 <= b.start2);     // which half is printed first
     int a1 = sa ? 2 : 1, a2 = sa ? 1 : 2, b1 = sb ? 2 : 1, b2 = sb ? 1 : 2;
-    if (!halves_equal(V, a, a1, b, b1, gene) || !halves_equal(V, a, a2, b, b2, gene)) return false;
+    if (!halves_equal(hx, a, a1, b, b1, gene) || !halves_equal(hx, a, a2, b, b2, gene)) return false;
     // combineExons (:312-337): straight pairing if ga1==ga1' and ga2==ga2', else the mate-swapped pairing
-    swapped = !(halves_equal(V, a, 1, b, 1, gene) && halves_equal(V, a, 2, b, 2, gene));
+    swapped = !(halves_equal(hx, a, 1, b, 1, gene) && halves_equal(hx, a, 2, b, 2, gene));
     return true;
   }
-  if (form == 1) return halves_equal(V, a, 1, b, 1, gene);
-  if (form == 2) return halves_equal(V, a, 2, b, 2, gene);
+  if (form == 1) return halves_equal(hx, a, 1, b, 1, gene);
+  if (form == 2) return halves_equal(hx, a, 2, b, 2, gene);
   // concatenation: at most one half of each alignment has tokens
-  bool straight = halves_equal(V, a, 1, b, 1, gene) && halves_equal(V, a, 2, b, 2, gene);
+  bool straight = halves_equal(hx, a, 1, b, 1, gene) && halves_equal(hx, a, 2, b, 2, gene);
   if (straight) return true;
-  if (halves_equal(V, a, 1, b, 2, gene) && halves_equal(V, a, 2, b, 1, gene)) { swapped = true; return true; }
+  if (halves_equal(hx, a, 1, b, 2, gene) && halves_equal(hx, a, 2, b, 1, gene)) { swapped = true; return true; }
   return false;
 }
 
@@ -128,7 +129,7 @@ EQP_HD void alignment_build(const AnnoView& A, const ChunkView& C, const CountVi
   if (!(fl & 1)) fl |= (uint8_t)(((fl & 2) ? 1 : 2) << 3);
   if (!(fl & 1) && (fl & 2) && (fl & 4)) raise(C.err, DERR_INCONSISTENT, frag);     // single-read alignment with both read indices
   al.flags = fl; al.tr = (uint8_t)(tr1 | (tr2 << 3)); al.pad[0] = al.pad[1] = 0;
-  al.key = alignment_key(V, al, false);
+  al.key = alignment_key(V.hx, al, false);
 }
 
 EQP_HD uint64_t hit_group_key(const HitX& x) { return ((uint64_t)((x.flags & 1) ? 0 : 1) << 40) | ((uint64_t)x.grp << 24) | ((uint64_t)x.half << 16) | x.ivRank; }
@@ -140,7 +141,7 @@ EQP_HD uint64_t hit_group_key(const HitX& x) { return ((uint64_t)((x.flags & 1) 
 template <bool GENE>
 EQP_HD uint32_t dedupe_fragment(const CountView& V, uint32_t a0, uint32_t a1) {
   int left = 0, right = 0; bool hasTr = false; uint32_t nA = a1 - a0, cap = 2 * nA; uint32_t* tab = V.dedupTab + 2 * (uint64_t)a0;
-  if (GENE) { for (uint32_t a = a0; a < a1; a++) { AlnG& g = V.alnG[a]; g.repr = a; g.next = 0xFFFFFFFFu; g.flags = 0; g.key = V.alns[a].hit0 == V.alns[a].hit1 ? 0 : alignment_key(V, V.alns[a], true); }
+  if (GENE) { for (uint32_t a = a0; a < a1; a++) { AlnG& g = V.alnG[a]; g.repr = a; g.next = 0xFFFFFFFFu; g.flags = 0; g.key = V.alns[a].hit0 == V.alns[a].hit1 ? 0 : alignment_key(V.hx, V.alns[a], true); }
     if (nA > 4) for (uint32_t s = 0; s < cap; s++) tab[s] = 0; }            // the table was used by the first dedupe
   for (uint32_t a = a0; a < a1; a++) {
     Aln& al = V.alns[a]; if (al.hit0 == al.hit1) continue;
@@ -150,7 +151,7 @@ EQP_HD uint32_t dedupe_fragment(const CountView& V, uint32_t a0, uint32_t a1) {
     if (nA <= 4) {                                                         // tiny fragment: compare with the earlier representatives directly
       for (uint32_t p = a0; p < a; p++) {
         const Aln& q = V.alns[p]; if (q.hit0 == q.hit1 || (GENE ? V.alnG[p].repr : q.repr) != p) continue;
-        if (keys_equal(V, q, GENE ? V.alnG[p].key : q.key, al, key, GENE, sw)) { found = p; break; }
+        if (keys_equal(V.hx, q, GENE ? V.alnG[p].key : q.key, al, key, GENE, sw)) { found = p; break; }
       }
     } else {                                                               // per-fragment open-addressing table of representatives (2 slots per alignment, zeroed)
       uint32_t s = (uint32_t)(((key * 0x9E3779B97F4A7C15ULL) >> 32) % cap);
@@ -158,7 +159,7 @@ EQP_HD uint32_t dedupe_fragment(const CountView& V, uint32_t a0, uint32_t a1) {
         uint32_t e = tab[s];
         if (!e) { tab[s] = a - a0 + 1; break; }
         const uint32_t p = a0 + e - 1;
-        if (keys_equal(V, V.alns[p], GENE ? V.alnG[p].key : V.alns[p].key, al, key, GENE, sw)) { found = p; break; }   // insertion order along the probe path = file order: first equal key wins
+        if (keys_equal(V.hx, V.alns[p], GENE ? V.alnG[p].key : V.alns[p].key, al, key, GENE, sw)) { found = p; break; }   // insertion order along the probe path = file order: first equal key wins
         s = s + 1 == cap ? 0 : s + 1;
       }
     }
@@ -284,16 +285,23 @@ EQP_HD void fragment_adjust(const AnnoView& A, const ChunkView& C, const CountVi
       }
     }
   }
-  for (uint32_t a = a0; a < a1; a++) { Aln& al = V.alns[a]; if (al.hit0 != al.hit1) al.key = alignment_key(V, al, false); }
+  for (uint32_t a = a0; a < a1; a++) { Aln& al = V.alns[a]; if (al.hit0 != al.hit1) al.key = alignment_key(V.hx, al, false); }
 }
 
 // ---- stage C: conforming features + accumulation for one run (mode)
+// Per-fragment tables live in local memory; their size decides how much of the L1/L2 a resident thread claims.  Almost every fragment
+// needs a handful of entries, so the counting kernel is compiled twice: SMALL tables for all fragments, and the few that overflow them
+// are handed (through a device work list) to a second launch with the LARGE tables, whose overflow is the DERR_CAPACITY error.
 #define EQP_FS_CAP 160
 #define EQP_FT_CAP 320
-struct FeatSet { uint32_t id[EQP_FS_CAP]; uint32_t mask[EQP_FS_CAP]; int n; };
-EQP_HD bool fs_add(FeatSet& s, uint32_t id, uint32_t bit) {
+#ifndef EQP_FS_SMALL
+#define EQP_FS_SMALL 24
+#define EQP_FT_SMALL 32
+#endif
+template <int CAP> struct FeatSetT { static const int cap = CAP; uint32_t id[CAP]; uint32_t mask[CAP]; int n; };
+template <class FS> EQP_HD bool fs_add(FS& s, uint32_t id, uint32_t bit) {
   for (int i = 0; i < s.n; i++) if (s.id[i] == id) { s.mask[i] |= bit; return true; }
-  if (s.n >= EQP_FS_CAP) return false;
+  if (s.n >= FS::cap) return false;
   s.id[s.n] = id; s.mask[s.n] = bit; s.n++; return true;
 }
 
@@ -318,7 +326,8 @@ EQP_HD int exon_filter(const AnnoView& A, ExonSet& e, int32_t gs, int32_t ge) {
 // candidate of both exons and the two fields are consecutive (:679-701), i.e. the intersection of the two exons' feature lists.
 // The lists are sorted by id when the annotation is loaded, so this is one merge instead of a set with field masks.
 // Returns false when the shape is different (the general path then handles the half).
-EQP_HD bool junction_pair(const AnnoView& A, const CountView& V, ExonSet& ea, int32_t gsa, int32_t gea, int fa, ExonSet& eb, int32_t gsb, int32_t geb, int fb, FeatSet& out, bool& overflow) {
+template <class FS>
+EQP_HD bool junction_pair(const AnnoView& A, const CountView& V, ExonSet& ea, int32_t gsa, int32_t gea, int fa, ExonSet& eb, int32_t gsb, int32_t geb, int fb, FS& out, bool& overflow) {
   if (ea.over || eb.over) return false;
   if (exon_filter(A, ea, gsa, gea) != 1 || exon_filter(A, eb, gsb, geb) != 1) return false;   // the filter is idempotent: the general path may run it again
   out.n = 0;
@@ -331,15 +340,18 @@ EQP_HD bool junction_pair(const AnnoView& A, const CountView& V, ExonSet& ea, in
     else {
       // a row survives the chunk's map filter (a27) or is in the transcript map
       bool pa = (va >> 31) || V.junctionActive[A.featAct ? A.featAct[i] : ia] != 0, pb = (vb >> 31) || V.junctionActive[A.featAct ? A.featAct[j] : ib] != 0;
-      if (pa && pb) { if (out.n >= EQP_FS_CAP) { overflow = true; return true; } out.id[out.n] = ia; out.mask[out.n] = 0; out.n++; }
+      if (pa && pb) { if (out.n >= FS::cap) { overflow = true; return true; } out.id[out.n] = ia; out.mask[out.n] = 0; out.n++; }
       i++; j++;
     }
   }
   return true;
 }
+// returns false when a table overflowed
+template <class FS>
 EQP_HD bool interval_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, ExonSet& e, int32_t gs, int32_t ge, int field,
-                              FeatSet& fs, uint32_t frag) {
-  if (e.over) { raise(C.err, DERR_CAPACITY, frag); return false; }
+                              FS& fs, uint32_t frag) {
+  (void)C; (void)frag;
+  if (e.over) return false;
   int ne = exon_filter(A, e, gs, ge); int32_t* exon = e.exon;
   if (mode == MODE_EXON && P.unambiguous[mode] && ne >= 2) ne = 0;      // -U with genomicIntervalMode (:603-608)
   const uint32_t bit = field >= 0 ? 1u << field : 0u;                   // a tr- record of the junction run has no field (:638-656)
@@ -349,14 +361,15 @@ EQP_HD bool interval_features(const AnnoView& A, const ChunkView& C, const Count
       uint32_t v = A.feat[mode][f]; uint32_t id = v & 0x7fffffffu;
       if (mode == MODE_JUNCTION && !(v & 0x80000000u) && !V.junctionActive[A.featAct ? A.featAct[f] : id]) continue;   // row removed by the per-chunk map filter (a27)
       any = true;
-      if (!fs_add(fs, id, bit)) { raise(C.err, DERR_CAPACITY, frag); return false; }
+      if (!fs_add(fs, id, bit)) return false;
     }
-    if (!any && !fs_add(fs, (uint32_t)A.nFeat[mode] + (uint32_t)ex, bit)) { raise(C.err, DERR_CAPACITY, frag); return false; }   // unknown exon: own pseudo id
+    if (!any && !fs_add(fs, (uint32_t)A.nFeat[mode] + (uint32_t)ex, bit)) return false;   // unknown exon: own pseudo id
   }
   return true;
 }
 // field-coverage test of a half's candidate features (GenomicAlignment.java:570-712)
-EQP_HD void conforming_features(const FeatSet& fs, int mode, int maxField, FeatSet& out) {
+template <class FS>
+EQP_HD void conforming_features(const FS& fs, int mode, int maxField, FS& out) {
   out.n = 0;
   for (int i = 0; i < fs.n; i++) {
     uint32_t m = fs.mask[i]; bool okf;
@@ -372,14 +385,16 @@ EQP_HD void conforming_features(const FeatSet& fs, int mode, int maxField, FeatS
 // streamed, see fragment_count).  trFrag: the hits are untagged (HitX::half is the read index, HitX::grp the non-tr ordinal), the
 // gene run walks the AlnG chains, and outside the gene run duplicates pair their non-tr intervals by ordinal while tr- intervals keep
 // the representative's own exons only (GenomicAlignment.combineExons skips intervals that print "", :721-786).
-EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t r, int h, bool trFrag, FeatSet& out, uint32_t frag) {
+// returns false when a table overflowed
+template <class FS>
+EQP_HD bool half_features(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t r, int h, bool trFrag, FS& out, uint32_t frag) {
   const Aln& R = V.alns[r]; out.n = 0;
   int nIv = h == 1 ? R.nIv1 : R.nIv2; int maxField = h == 1 ? R.maxField1 : R.maxField2;
-  if (maxField >= 32) { raise(C.err, DERR_CAPACITY, frag); return; }
-  if (mode == MODE_JUNCTION && nIv < 2) return;                            // a junction needs two consecutive fields (:679-701)
+  if (maxField >= 32) return false;
+  if (mode == MODE_JUNCTION && nIv < 2) return true;                       // a junction needs two consecutive fields (:679-701)
   const bool useG = trFrag && mode == MODE_GENE;
   const uint32_t r0 = h == 1 ? R.hit0 : R.split, r1 = h == 1 ? R.split : R.hit1;
-  FeatSet fs; fs.n = 0;
+  FS fs; fs.n = 0;
   for (int iv = 0; iv < nIv; iv++) {
     int32_t gs = 0, ge = 0; int field = 0; bool haveIv = false, trIv = false; uint16_t ord = 0; ExonSet e; e.n = 0; e.over = false;
     if (trFrag) { uint32_t f; if (iv_find(V, r0, r1, iv, f)) { trIv = V.hx[f].chr <= -2; ord = V.hx[f].grp; } }
@@ -397,9 +412,10 @@ EQP_HD void half_features(const AnnoView& A, const ChunkView& C, const CountView
         if (x.flags & (4 << mode)) exon_add(e, x);
       }
     }
-    if (!interval_features(A, C, V, P, mode, e, gs, ge, field, fs, frag)) return;
+    if (!interval_features(A, C, V, P, mode, e, gs, ge, field, fs, frag)) return false;
   }
   conforming_features(fs, mode, maxField, out);
+  return true;
 }
 
 EQP_HD void atomic_add_u64(unsigned long long* p, unsigned long long v) {
@@ -411,8 +427,12 @@ EQP_HD void atomic_add_u64(unsigned long long* p, unsigned long long v) {
 }
 
 // returns 0 = the fragment is no weight object, 1 = it added to a count, 2 = it was excluded (or aborted on a capacity error)
+// FS_CAP / FT_CAP: table sizes (see EQP_FS_SMALL); with small tables an overflow returns -1 and the caller queues the fragment for the large ones.
 // wsum: the fragment's weightAdded (sum of its contributions, printed ids or not, ComputeCounts.java:772,849) in 2^-32 units
+template <int FS_CAP, int FT_CAP>
 EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, int mode, uint32_t slot, uint64_t& wsum) {
+  typedef FeatSetT<FS_CAP> FeatSet;
+  const bool retry = FS_CAP < EQP_FS_CAP;                                  // an overflow is not final
   wsum = 0;
   const bool trFrag = C.slotTr[slot] != 0;
   uint32_t a20 = trFrag && mode == MODE_GENE ? V.a20G[slot] : V.a20[slot];
@@ -423,20 +443,20 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
   if (w > 1.0 / (double)a20) w = 1.0 / (double)a20;                      // ComputeCounts.java:762-764
   if (!(w >= P.weightThreshold)) return 2;
   double addW = P.unweighted ? 1.0 : w;
-  uint32_t fid[EQP_FT_CAP]; uint16_t k1[EQP_FT_CAP], k2[EQP_FT_CAP]; int nf = 0;
+  uint32_t fid[FT_CAP]; uint16_t k1[FT_CAP], k2[FT_CAP]; int nf = 0;
   FeatSet s1, s2; bool bad = false;
   // one representative alignment done: paired -> gene run intersects the halves, the others unite them (:325-335); then count per feature
   auto merge_alignment = [&](uint8_t flags) {
     if (flags & 1) {
       if (mode == MODE_GENE) { int wn = 0; for (int i = 0; i < s1.n; i++) { bool in2 = false; for (int j = 0; j < s2.n; j++) in2 |= s2.id[j] == s1.id[i]; if (in2) s1.id[wn++] = s1.id[i]; } s1.n = wn; }
-      else for (int j = 0; j < s2.n; j++) { bool in1 = false; for (int i = 0; i < s1.n; i++) in1 |= s1.id[i] == s2.id[j]; if (!in1) { if (s1.n >= EQP_FS_CAP) { bad = true; return; } s1.id[s1.n++] = s2.id[j]; } }
+      else for (int j = 0; j < s2.n; j++) { bool in1 = false; for (int i = 0; i < s1.n; i++) in1 |= s1.id[i] == s2.id[j]; if (!in1) { if (s1.n >= FS_CAP) { bad = true; return; } s1.id[s1.n++] = s2.id[j]; } }
       s2.n = 0;
     }
     for (int side = 0; side < 2; side++) {
       FeatSet& s = side ? s2 : s1;
       for (int i = 0; i < s.n; i++) {
         int q = 0; while (q < nf && fid[q] != s.id[i]) q++;
-        if (q == nf) { if (nf >= EQP_FT_CAP) { bad = true; return; } fid[nf] = s.id[i]; k1[nf] = k2[nf] = 0; nf++; }
+        if (q == nf) { if (nf >= FT_CAP) { bad = true; return; } fid[nf] = s.id[i]; k1[nf] = k2[nf] = 0; nf++; }
         if (side) k2[q]++; else k1[q]++;
       }
     }
@@ -470,12 +490,13 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
             if (!(x.flags & 1) || x.grp != g || x.half != h || x.ivRank != iv) break;
           }
           if (pairShape && nColl < 2) { gs2[nColl] = gs; ge2[nColl] = ge; field2[nColl] = field; nColl++; }
-          else if (!interval_features(A, C, V, P, mode, e, gs, ge, field, fs, frag)) return 2;
+          else if (!interval_features(A, C, V, P, mode, e, gs, ge, field, fs, frag)) bad = true;
         }
         if (pairShape) {
           bool done = nColl == 2 && junction_pair(A, V, e2[0], gs2[0], ge2[0], field2[0], e2[1], gs2[1], ge2[1], field2[1], h == 1 ? s1 : s2, bad);
           if (done) continue;
-          for (int c = 0; c < nColl; c++) if (!interval_features(A, C, V, P, mode, e2[c], gs2[c], ge2[c], field2[c], fs, frag)) return 2;
+          for (int c = 0; c < nColl && !bad; c++) if (!interval_features(A, C, V, P, mode, e2[c], gs2[c], ge2[c], field2[c], fs, frag)) bad = true;
+          if (bad) break;
         }
         conforming_features(fs, mode, maxField, h == 1 ? s1 : s2);
       }
@@ -486,12 +507,12 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
     for (uint32_t r = a0; r < a1 && !bad; r++) {
       const Aln& R = V.alns[r]; if (R.hit0 == R.hit1 || (useG ? V.alnG[r].repr : R.repr) != r) continue;
       s1.n = s2.n = 0;
-      if (R.flags & 2) half_features(A, C, V, P, mode, r, 1, trFrag, s1, frag);
-      if (R.flags & 4) half_features(A, C, V, P, mode, r, 2, trFrag, s2, frag);
-      merge_alignment(R.flags);
+      if (R.flags & 2) bad |= !half_features(A, C, V, P, mode, r, 1, trFrag, s1, frag);
+      if ((R.flags & 4) && !bad) bad |= !half_features(A, C, V, P, mode, r, 2, trFrag, s2, frag);
+      if (!bad) merge_alignment(R.flags);
     }
   }
-  if (bad) { raise(C.err, DERR_CAPACITY, frag); return 2; }
+  if (bad) { if (retry) return -1; raise(C.err, DERR_CAPACITY, frag); return 2; }
   if (P.unambiguous[mode] && mode != MODE_EXON && nf >= 2) return 2;   // :371-382 returns 0
   bool added = false;
   for (int q = 0; q < nf; q++) {

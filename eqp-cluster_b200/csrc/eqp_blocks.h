@@ -141,8 +141,11 @@ EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot
 }
 
 // a11 for one block: rows of the bucket overlapping [start,end) by >= 1 bp.
-// sameStrand: `bedtools intersect -s` (CIB:938-940 with BED_STRAND_SPECIFIC_OPTION): only rows on the block's strand
-EQP_HD uint32_t join_block(const AnnoView& A, const Block& b, Hit* out, uint32_t blockIdx, bool sameStrand) {
+// sameStrand: `bedtools intersect -s` (CIB:938-940 with BED_STRAND_SPECIFIC_OPTION): only rows on the block's strand.
+// The rows are walked from the last candidate down; with `out` the hits are stored in ASCENDING row order (nOut = the count of the first
+// pass), which is the order BedRecord.compareTo wants for the records of one block (rows are sorted by start, end, strand, file order),
+// so that the per-alignment sort of alignment_build finds them sorted.
+EQP_HD uint32_t join_block(const AnnoView& A, const Block& b, Hit* out, uint32_t nOut, uint32_t blockIdx, bool sameStrand) {
   if (b.bucket < 0) return 0;
   const uint32_t wantStrand = b.strand == '+' ? 0u : 1u;
   int32_t lo = (int32_t)A.bktRowOff[b.bucket], hi = (int32_t)A.bktRowOff[b.bucket + 1];
@@ -154,7 +157,7 @@ EQP_HD uint32_t join_block(const AnnoView& A, const Block& b, Hit* out, uint32_t
     int32_t re = A.rowEnd[k];
     if (re > b.start && (!sameStrand || ((A.rowFlags[k] >> 1) & 3u) == wantStrand)) {
       int32_t ov = (re < b.end ? re : b.end) - (A.rowStart[k] > b.start ? A.rowStart[k] : b.start);
-      if (ov >= 1) { if (out) { out[n].block = blockIdx; out[n].row = k; out[n].overlap = ov; } n++; }
+      if (ov >= 1) { if (out) { Hit& o = out[nOut - 1 - n]; o.block = blockIdx; o.row = k; o.overlap = ov; } n++; }
     }
   }
   return n;

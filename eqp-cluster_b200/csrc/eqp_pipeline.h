@@ -41,6 +41,13 @@ EQP_HD void counter_add(unsigned long long* p, uint32_t v) {
 #endif
 }
 
+EQP_HD uint32_t atomic_inc_u32(uint32_t* p) {
+#if defined(__CUDA_ARCH__)
+  return atomicAdd(p, 1u);
+#else
+  return (*p)++;
+#endif
+}
 // append to a work list (order irrelevant); rare events only
 EQP_HD void list_push(uint32_t* count, uint32_t* list, uint32_t v) {
 #if defined(__CUDA_ARCH__)
@@ -64,7 +71,7 @@ EQP_HD void counter_add64(unsigned long long* p, uint64_t v) {          // v < 2
 // stage tags: they only name the kernels (profiler listings)
 namespace st { struct misc; struct frag_table; struct frag_stats; struct select_tj_weights; struct select_stage1; struct select_stage2; struct seen_refs; struct junction_active;
                struct blocks_count; struct blocks_fill; struct join_count; struct join_fill; struct work_class; struct alignment_build; struct work_lists; struct fragment_adjust;
-               struct fragment_weight; struct fragment_weight_gene; struct fragment_count; }
+               struct fragment_weight; struct fragment_weight_gene; struct fragment_count; struct fragment_count_large; }
 
 struct ChunkResult {
   std::vector<double> counts[3]; std::vector<unsigned long long> fixed[3]; std::vector<uint8_t> junctionActive;
@@ -225,10 +232,10 @@ struct Pipeline {
     { const ChunkView C = this->C; be.template launch_occ<st::blocks_fill, 6>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, P.stranded, nb, na); }); }
     be.stage("blocks");
     // ---- a11: interval join (count, scan, fill)
-    { const ChunkView C = this->C; be.template launch<st::join_count>(nBlocks, [=] EQP_LAMBDA(uint64_t b) { C.hitCnt[b] = join_block(A, C.blocks[b], nullptr, (uint32_t)b, P.stranded != 0); }); }
+    { const ChunkView C = this->C; be.template launch<st::join_count>(nBlocks, [=] EQP_LAMBDA(uint64_t b) { C.hitCnt[b] = join_block(A, C.blocks[b], nullptr, 0, (uint32_t)b, P.stranded != 0); }); }
     be.scan(C.hitCnt, nBlocks); be.to_host(&nHits, C.hitCnt + nBlocks, 4);
     C.hits = be.template alloc<Hit>((uint64_t)nHits + 1);
-    { const ChunkView C = this->C; be.template launch<st::join_fill>(nBlocks, [=] EQP_LAMBDA(uint64_t b) { join_block(A, C.blocks[b], C.hits + C.hitCnt[b], (uint32_t)b, P.stranded != 0); }); }
+    { const ChunkView C = this->C; be.template launch<st::join_fill>(nBlocks, [=] EQP_LAMBDA(uint64_t b) { join_block(A, C.blocks[b], C.hits + C.hitCnt[b], C.hitCnt[b + 1] - C.hitCnt[b], (uint32_t)b, P.stranded != 0); }); }
     be.stage("join");
     // ---- a12-a25
     V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
@@ -245,7 +252,13 @@ struct Pipeline {
     // fragments with hits, ordered by descending hit-count class (stable within a class): warps of the thread-per-fragment stages get
     // fragments of similar cost while neighbouring lanes still touch neighbouring memory
     uint32_t* work = be.template alloc<uint32_t>((uint64_t)N + 1); uint32_t* perm = be.template alloc<uint32_t>((uint64_t)N + 1);
-    { const ChunkView C = this->C; be.template launch<st::work_class>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t h = C.hitCnt[C.blkOff[s + 1]] - C.hitCnt[C.blkOff[s]]; uint32_t c = 0; while (h) { c++; h >>= 1; } work[s] = c; }); }   // class = 1 + floor(log2(hits)): coarse, so neighbouring slots stay neighbours
+    // work key: small fragments (at most 15 alignments and 15 hits) are binned by their exact (alignments, hits) pair, so that the lanes of a warp
+    // run the same trip counts in the per-fragment loops; larger ones by 1 + floor(log2(hits)).  Bins keep slot order: neighbouring lanes still touch
+    // neighbouring memory.  Keys sort descending: the expensive fragments start first.
+    { const ChunkView C = this->C; be.template launch<st::work_class>(N, [=] EQP_LAMBDA(uint64_t s) {
+        uint32_t h = C.hitCnt[C.blkOff[s + 1]] - C.hitCnt[C.blkOff[s]], na = C.alnOff[s + 1] - C.alnOff[s], key = 0;
+        if (h) { if (h <= 15 && na <= 14) key = (na << 4) | h; else { uint32_t c = 0, x = h; while (x) { c++; x >>= 1; } key = 240 + (c < 15 ? c : 15); } }
+        work[s] = key; }); }
     uint32_t nWork = be.order_by_work(work, N, perm);
     { const ChunkView C = this->C; const CountView V = this->V;
       be.stage("order");
@@ -258,14 +271,26 @@ struct Pipeline {
       if (V.alnG) be.template launch_counted<st::fragment_weight_gene>(listCnt + 1, N, [=] EQP_LAMBDA(uint64_t i) { fragment_weight_gene(C, V, listTr[i]); });      // gene-run keys of tr- fragments
       be.stage("fragment-weight");
       // the three counting runs of one fragment back to back in one thread: runs two and three find the fragment's alignments and
-      // hits in cache instead of paying the DRAM latency chain again (the runs were latency-bound as three concurrent kernels)
+      // hits in cache instead of paying the DRAM latency chain again (the runs were latency-bound as three concurrent kernels).
+      // First launch: small per-thread tables; (fragment, run) pairs that overflow them are queued for a second launch with the large tables.
+      uint32_t* bigCnt = listCnt + 2; uint32_t* bigList = listLd;        // the a17 list is consumed by now; N + 1 entries hold 3 runs of N/3 fragments at least (overflow beyond is an error)
+      be.memset(bigCnt, 0, 4);
+      auto tally = [=] EQP_LAMBDA(int m, int r, uint64_t ws) {             // 0 not a weight object, 1 included, 2 excluded (ComputeCounts.java:986-989)
+        counter_add(&V.stats[m * 3 + 0], r ? 1u : 0u); counter_add(&V.stats[m * 3 + 1], r == 1 ? 1u : 0u); counter_add(&V.stats[m * 3 + 2], r == 2 ? 1u : 0u);
+        counter_add64(&V.stats[10 + m], ws);
+      };
       be.template launch<st::fragment_count>(nWork, [=] EQP_LAMBDA(uint64_t i) {
         uint32_t s = perm[i];
         for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) {
-          uint64_t ws; int r = fragment_count(A, C, V, P, m, s, ws);       // 0 not a weight object, 1 included, 2 excluded (ComputeCounts.java:986-989)
-          counter_add(&V.stats[m * 3 + 0], r ? 1u : 0u); counter_add(&V.stats[m * 3 + 1], r == 1 ? 1u : 0u); counter_add(&V.stats[m * 3 + 2], r == 2 ? 1u : 0u);
-          counter_add64(&V.stats[10 + m], ws);
+          uint64_t ws; int r = fragment_count<EQP_FS_SMALL, EQP_FT_SMALL>(A, C, V, P, m, s, ws);
+          if (r < 0) { uint32_t k = atomic_inc_u32(bigCnt); if (k < N) bigList[k] = s * 4u + (uint32_t)m; else raise(C.err, DERR_CAPACITY, C.base + s); r = 0; ws = 0; }
+          tally(m, r, ws);
         }
+      });
+      be.template launch_counted<st::fragment_count_large>(bigCnt, N, [=] EQP_LAMBDA(uint64_t i) {
+        uint32_t s = bigList[i] >> 2; int m = (int)(bigList[i] & 3u);
+        uint64_t ws; int r = fragment_count<EQP_FS_CAP, EQP_FT_CAP>(A, C, V, P, m, s, ws);
+        tally(m, r, ws);
       }); }
     be.stage("fragment-count x3");
     // ---- results

@@ -45,12 +45,16 @@ static const unsigned long long TK_FLAG_AGG = 1ULL << 62, TK_FLAG_PREFIX = 2ULL 
 __device__ __forceinline__ uint32_t tk_smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // 4 text bytes -> top byte of the result: bits 24-27 = bytes equal to '\t', bits 28-31 = bytes equal to '\n' (exact compares).
-// c holds a marker at bit 3 (tab) / bit 7 (newline) of each byte; the multiply moves marker k of byte k to bit 24+k / 28+k
-// (all 32 partial-product positions are distinct, so nothing carries).
+// '\t' = 0x09 and '\n' = 0x0a are the bytes b with (b ^ 8) in {1, 2}: x = w ^ 0x08080808, a byte of x below 4 (and without its top bit)
+// is one of 0x08..0x0b, bit 0 / bit 1 of x then tell tab / newline (0x0b has both and counts as neither).  (x | 0x80) - 4 cannot
+// borrow across bytes.  The multiply moves the marker of byte k (bit 3 for tab, bit 7 for newline) to bit 24+k / 28+k: all 32
+// partial-product positions are distinct, so nothing carries.
 __device__ __forceinline__ uint32_t tk_marks4(uint32_t w) {
-  uint32_t xn = w ^ 0x0a0a0a0au, xt = w ^ 0x09090909u;
-  uint32_t zn = ~(((xn & 0x7f7f7f7fu) + 0x7f7f7f7fu) | xn | 0x7f7f7f7fu);
-  uint32_t zt = ~(((xt & 0x7f7f7f7fu) + 0x7f7f7f7fu) | xt | 0x7f7f7f7fu);
+  uint32_t x = w ^ 0x08080808u;
+  uint32_t t = (x | 0x80808080u) - 0x04040404u;                        // top bit of a byte clear <=> its low 7 bits are below 4
+  uint32_t m = ~(t | x) & 0x80808080u;
+  uint32_t a = x << 7, b = x << 6;                                      // bit 0 / bit 1 of every byte at its top bit
+  uint32_t zt = m & a & ~b, zn = m & b & ~a;
   return (zn | (zt >> 4)) * 0x00204081u;
 }
 // four bytes (hi nibble = newline bits, lo nibble = tab bits, one byte per text word) -> 16-bit masks

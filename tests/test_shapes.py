@@ -54,6 +54,20 @@ def test_switches_on_the_mixed_world(shape_worlds, flags):
     check_emu(w, "pe", flags)
 
 
+@pytest.mark.parametrize("variant", ["_chain", "_retry"])
+def test_alternate_paths_on_the_mixed_world(shape_worlds, variant):
+    """The duplicate-chain walk for every fragment (EQP_FLAT_SCAN=0) and the large-table retry of the counting kernel (small tables of
+    2 / 3 entries): the paths that only big fragments take in the product build, forced for all."""
+    w = shape_worlds("mixed")
+    c = w.chunk("pe", 1003, 1, 6000, "pe")
+    emu = w.emu_run("pe", variant=variant)
+    for m in ("gene", "exon", "junction"):
+        assert_rows_match(emu[m + "_rows"], read_rows(os.path.join(c["oracle"], m + ".cnt")), what="%s %s" % (variant, m))
+    st = read_stats(os.path.join(c["oracle"], "stats.txt"))
+    for k in ("NUMBER_EXPRESSED_READS", "NUM_WEIGHT_OBJECTS"):
+        assert emu["stats"][k] == st[k], k
+
+
 def test_default_world_has_the_survey_mix(world):
     """The default world (what bench.py counts, scaled down) carries every shape at the SURVEY 8d rates."""
     bed = open(os.path.join(world.anno, "ensembl_rna_hs_100_combined_exons.bed")).read()
