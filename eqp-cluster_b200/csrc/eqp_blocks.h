@@ -157,7 +157,11 @@ EQP_HD uint32_t join_block(const AnnoView& A, const Block& b, Hit* out, uint32_t
     int32_t re = A.rowEnd[k];
     if (re > b.start && (!sameStrand || ((A.rowFlags[k] >> 1) & 3u) == wantStrand)) {
       int32_t ov = (re < b.end ? re : b.end) - (A.rowStart[k] > b.start ? A.rowStart[k] : b.start);
+#ifdef EQP_VAR_DESC_HITS
+      if (ov >= 1) { if (out) { Hit& o = out[n]; o.block = blockIdx; o.row = k; o.overlap = ov; } n++; }
+#else
       if (ov >= 1) { if (out) { Hit& o = out[nOut - 1 - n]; o.block = blockIdx; o.row = k; o.overlap = ov; } n++; }
+#endif
     }
   }
   return n;

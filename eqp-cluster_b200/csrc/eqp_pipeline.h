@@ -257,7 +257,13 @@ struct Pipeline {
     // neighbouring memory.  Keys sort descending: the expensive fragments start first.
     { const ChunkView C = this->C; be.template launch<st::work_class>(N, [=] EQP_LAMBDA(uint64_t s) {
         uint32_t h = C.hitCnt[C.blkOff[s + 1]] - C.hitCnt[C.blkOff[s]], na = C.alnOff[s + 1] - C.alnOff[s], key = 0;
-        if (h) { if (h <= 15 && na <= 14) key = (na << 4) | h; else { uint32_t c = 0, x = h; while (x) { c++; x >>= 1; } key = 240 + (c < 15 ? c : 15); } }
+#ifdef EQP_VAR_COARSE_KEYS
+        if (h) { uint32_t c = 0, x = h; while (x) { c++; x >>= 1; } key = c; }
+        if (0)
+#else
+        if (h)
+#endif
+        { if (h <= 15 && na <= 14) key = (na << 4) | h; else { uint32_t c = 0, x = h; while (x) { c++; x >>= 1; } key = 240 + (c < 15 ? c : 15); } }
         work[s] = key; }); }
     uint32_t nWork = be.order_by_work(work, N, perm);
     { const ChunkView C = this->C; const CountView V = this->V;

@@ -6,7 +6,11 @@
 
 #if defined(__CUDACC__)
 #define EQP_HD __host__ __device__ __forceinline__
+#ifdef EQP_VAR_INLINE_KEYS
+#define EQP_HD_CALL __host__ __device__ __forceinline__
+#else
 #define EQP_HD_CALL __host__ __device__ __noinline__      // real calls: keeps the callers' register allocation small
+#endif
 #else
 #define EQP_HD inline
 #define EQP_HD_CALL inline

@@ -64,11 +64,12 @@ _lib = None
 
 
 def load_library(path=None):
-    """dlopen libeqpcount.so (building it in-tree if needed) and declare the prototypes of include/eqp_count.h."""
+    """dlopen libeqpcount.so (building it in-tree if needed) and declare the prototypes of include/eqp_count.h.
+    `path` (or $EQP_LIB) names another build of the library: tools/variants.py times several builds side by side."""
     global _lib
     if _lib is not None and path is None:
         return _lib
-    path = path or _build.LIB_PATH
+    path = path or os.environ.get("EQP_LIB") or _build.LIB_PATH
     if not os.path.exists(path):
         _build.build_library()
     lib = C.CDLL(path)
@@ -100,7 +101,8 @@ def load_library(path=None):
     lib.eqp_last_error.argtypes = [vp]; lib.eqp_last_error.restype = C.c_char_p
     lib.eqp_destroy.argtypes = [vp]; lib.eqp_destroy.restype = None
     lib.eqp_annotation_bytes.argtypes = [vp]; lib.eqp_annotation_bytes.restype = C.c_int64
-    _lib = lib
+    if _lib is None:
+        _lib = lib
     return lib
 
 
@@ -174,8 +176,8 @@ class ChunkCounts:
 class CountContext:
     """One eqp_ctx: bound to one GPU, one chunk in flight (include/eqp_count.h)."""
 
-    def __init__(self, device=0):
-        self.lib = load_library()
+    def __init__(self, device=0, lib_path=None):
+        self.lib = load_library(lib_path)
         self.h = C.c_void_p()
         rc = self.lib.eqp_create(device, C.byref(self.h))
         if rc:

@@ -1,0 +1,85 @@
+#!/usr/bin/env python
+"""variants.py — A/B timing of several builds of libeqpcount.so on ONE generated chunk (development tool).
+
+  python tools/variants.py build  name=-DFLAG1,-DFLAG2 ...     compile eqp-cluster_b200/lib/variants/libeqpcount_<name>.so (here, no GPU needed)
+  python tools/variants.py run [--reads N] [--layout se|pe]     on the GPU box: generate one chunk, then for every variant (and the product
+                                                                library) count it 1 + 3 times from device-resident text and print the stage times
+"""
+import glob
+import json
+import os
+import subprocess
+import sys
+import tempfile
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+VDIR = os.path.join(ROOT, "eqp-cluster_b200", "lib", "variants")
+
+
+def main():
+    import eqp_cluster_b200 as eqp
+    b = eqp.build
+    if sys.argv[1] == "build":
+        os.makedirs(VDIR, exist_ok=True)
+        for spec in sys.argv[2:]:
+            name, _, flags = spec.partition("=")
+            out = os.path.join(VDIR, "libeqpcount_%s.so" % name)
+            b._run([b.nvcc_path()] + b.NVCC_FLAGS + [f for f in flags.split(",") if f] + ["-o", out, os.path.join(b.CSRC, "eqp_capi.cu"), "-lz"])
+            print("built", out)
+        return
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("cmd")
+    ap.add_argument("--reads", type=int, default=25_000_000)
+    ap.add_argument("--layout", default="se")
+    ap.add_argument("--genes", type=int, default=60000)
+    args = ap.parse_args()
+    import torch
+    sys.path.insert(0, ROOT)
+    import bench
+    work = os.path.join(tempfile.gettempdir(), "eqp_variants")
+    os.makedirs(work, exist_ok=True)
+    b.build_tools()
+    anno = bench.make_annotation(b, work, args.genes)
+    dirs = bench.generate_blocks(b, anno, os.path.join(work, "chunk"), 1001, 1, args.reads, args.layout, os.cpu_count() or 1)
+    host = bench.load_blocks_pinned(torch, dirs, args.layout)
+    dev = [h.cuda() for h in host]
+    torch.cuda.synchronize()
+    dargs = [(d.data_ptr(), d.numel()) for d in dev]
+    libs = [("product", b.LIB_PATH)] + [(os.path.basename(p)[12:-3], p) for p in sorted(glob.glob(os.path.join(VDIR, "libeqpcount_*.so")))]
+    for name, path in libs:
+        r, w = os.pipe()
+        saved = os.dup(2)
+        ctx = eqp.CountContext(0, path).load_annotation(anno)
+        ctx.count_chunk(*dargs, on_device=True, fetch=False)
+        os.environ["EQP_STAGE_TIMING"] = "1"
+        ms = []
+        os.dup2(w, 2)
+        try:
+            for _ in range(3):
+                ms.append(ctx.count_chunk(*dargs, on_device=True, fetch=False).device_ms)
+        finally:
+            os.dup2(saved, 2)
+            os.close(w)
+            os.environ.pop("EQP_STAGE_TIMING", None)
+        text = os.read(r, 1 << 20).decode(errors="replace")
+        os.close(r)
+        import re
+        runs, cur = [], {}
+        for line in text.splitlines():
+            m = re.match(r"\[eqp stage\] (.+?)\s+([\d.]+) ms", line)
+            if not m:
+                continue
+            if m.group(1) == "total":
+                runs.append(cur)
+                cur = {}
+            else:
+                cur[m.group(1)] = cur.get(m.group(1), 0.0) + float(m.group(2))
+        best = {k: round(min(r[k] for r in runs if k in r), 2) for k in (runs[0] if runs else {})}
+        print(json.dumps({"variant": name, "device_ms": [round(x, 2) for x in ms], "stages_min_ms": best}), flush=True)
+        ctx.close()
+
+
+if __name__ == "__main__":
+    main()
