@@ -211,7 +211,8 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
   FragStat bed{}; bed.nSr1 = (uint16_t)(a20 > 65535 ? 65535 : a20); bed.flags = FS_EXISTS | (1 << 2);
   const FragStat& g = C.st[FILE_G][slot];
   uint32_t n = a20;
-  if (g.flags & FS_EXISTS) {
+  if (P.genomic) n = (uint32_t)fe_n(C.st[FILE_T][slot]);                  // ComputeCounts -w <ComputeReadWeightsSam output> (compute-genomic-counts.sh:1000-1010)
+  else if (g.flags & FS_EXISTS) {
     uint32_t ax = C.auxSlot[slot]; int cm = 0;
     if (ax != 0xFFFFFFFFu) cm = fe_cmp_mult(C.stTJ[ax], g);               // aux.compareMultiplicity(entry2), CombineReadWeightFiles.java:192-195
     if (cm == 1) n = a20; else if (cm == -1) n = (uint32_t)fe_n(g); else n = (int)a20 >= fe_n(g) ? a20 : (uint32_t)fe_n(g);

@@ -12,6 +12,7 @@ struct RunParams {                 // eqp_params, device form
   uint8_t spliceConforming[3], containment[3], unambiguous[3];
   uint8_t unweighted; uint8_t modes;
   uint8_t stranded;                // 0 none, 1 forward, 2 backward (compute-counts.sh:372-387)
+  uint8_t genomic;                 // the one input is a genomic aligner's SAM (compute-genomic-counts.sh): weights = its own alignment counts
   double weightThreshold, slack;
 };
 

@@ -91,8 +91,10 @@ EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot
         const SamView& T = C.sam[fj];
         // isMate across inputs only needs the decoded fields
         int ia = rec_flag_read_index(S, i), ib = rec_flag_read_index(T, cj.line);
-        if (ia != ib && ((S.rf[i] >> 5) & 3) == ((T.rf[cj.line] >> 5) & 3) && S.rnext[i] == T.ref[cj.line] && S.pnext[i] == T.pos[cj.line] &&
-            S.ref[i] == T.rnext[cj.line] && S.pos[i] == T.pnext[cj.line]) { mateFile = fj; mateLine = cj.line; C.proc[fj][cj.line] = 1; taken = true; break; }
+        bool mate = (S.hi && S.hi[i] >= 0) ? (T.hi && T.hi[cj.line] == S.hi[i])      // hit index decides alone (SamRecord.java:658-660)
+                  : (ia != ib && ((S.rf[i] >> 5) & 3) == ((T.rf[cj.line] >> 5) & 3) && S.rnext[i] == T.ref[cj.line] && S.pnext[i] == T.pos[cj.line] &&
+                     S.ref[i] == T.rnext[cj.line] && S.pos[i] == T.pnext[cj.line]);
+        if (mate) { mateFile = fj; mateLine = cj.line; C.proc[fj][cj.line] = 1; taken = true; break; }
       }
       if (mateFile >= 0) {
         const SamView& T = C.sam[mateFile];

@@ -211,8 +211,10 @@ static int run_chunk(eqp_ctx* ctx, const eqp_params* p, const char* const text[3
   P.containment[0] = p->containment ? 1 : 0; P.containment[1] = P.containment[2] = 0;
   P.unambiguous[0] = P.unambiguous[1] = p->unambiguous ? 1 : 0; P.unambiguous[2] = 0;
   P.unweighted = p->unweighted ? 1 : 0; P.modes = (uint8_t)(p->modes & 7); P.weightThreshold = p->read_weight_threshold; P.slack = p->distance_slack;
-  P.stranded = (uint8_t)p->stranded;
+  P.stranded = (uint8_t)p->stranded; P.genomic = p->genomic_input ? 1 : 0;
+  if (P.genomic) P.modes &= 3;
   for (int f = 0; f < 3; f++) ctx->be->inputReady[f] = ready ? ready[f] : nullptr;
+  ctx->be->wantHi = P.genomic != 0;
   ctx->pl.reset(new Pipeline<CudaBackend>(*ctx->be, ctx->A, P));
   double w2 = wall();
   EQP_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
@@ -245,6 +247,7 @@ static int run_chunk(eqp_ctx* ctx, const eqp_params* p, const char* const text[3
 
 static int check_params(eqp_ctx* ctx, const eqp_params* p) {
   if (p->stranded < 0 || p->stranded > 2) return fail(ctx, EQP_ERR_ARG, derr_text(DERR_STRANDED));
+  if (p->genomic_input && (p->modes & 4)) return fail(ctx, EQP_ERR_UNSUPPORTED, "genomic_input: the junction run of compute-genomic-counts.sh (map filtered through ExtractSplicedExonExonIds and a GTF, :1210-1290) is not built; ask for modes 1 | 2");
   return EQP_OK;
 }
 
@@ -255,6 +258,7 @@ int eqp_count_chunk(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_sam, siz
   if ((t_len && !t_sam) || (j_len && !j_sam) || (g_len && !g_sam)) return fail(ctx, EQP_ERR_ARG, "eqp_count_chunk: null SAM buffer with non-zero length");
   if (ctx->feed.active) return fail(ctx, EQP_ERR_ARG, "eqp_count_chunk: a streamed chunk is open (eqp_chunk_begin without eqp_chunk_end)");
   if (int rc = check_params(ctx, p)) return rc;
+  if (p->genomic_input && (j_len || g_len)) return fail(ctx, EQP_ERR_ARG, "genomic_input: the one SAM goes into the first input, the other two stay empty");
   memset(out, 0, sizeof *out);
   try {
     EQP_CUDA(cudaSetDevice(ctx->device));

@@ -210,7 +210,9 @@ struct CudaBackend {
     S.frag = alloc<uint32_t>(cap); S.ref = alloc<int32_t>(cap); S.pos = alloc<int32_t>(cap); S.rnext = alloc<int32_t>(cap); S.pnext = alloc<int32_t>(cap);
     S.flag = alloc<uint16_t>(cap); S.nm = alloc<int16_t>(cap); S.cigOff = alloc<uint16_t>(cap); S.cigLen = alloc<uint16_t>(cap); S.seqLen = alloc<uint16_t>(cap); S.cigM = alloc<uint16_t>(cap);
     S.rf = alloc<uint8_t>(cap); proc = alloc<uint8_t>(cap);
+    S.hi = wantHi ? alloc<int32_t>(cap) : nullptr;
   }
+  bool wantHi = false;                                                    // genomic-aligner input: keep the HI:i: hit indices
   // host inputs: the H2D copy of each SAM text runs on its own stream; the tokenizer of input f starts when copy f has landed,
   // so tokenizing T and J overlaps the copies of J and G
   cudaEvent_t inputReady[3] = {nullptr, nullptr, nullptr}; int nextInput = 0;
@@ -240,7 +242,7 @@ struct CudaBackend {
       S.nLines = (uint32_t)lines;
       if (lines <= cap) return;
       cap = lines;                                                          // tables were too small (average line under 160 bytes): once more, exact
-      for (int k = 0; k < 14; k++) { EQP_CUDA(cudaFreeAsync(allocs.back(), stream)); allocs.pop_back(); }   // the first attempt's 14 tables go back to the pool now
+      for (int k = 0; k < 14 + (wantHi ? 1 : 0); k++) { EQP_CUDA(cudaFreeAsync(allocs.back(), stream)); allocs.pop_back(); }   // the first attempt's tables go back to the pool now
     }
     throw CudaError("line count changed between two passes over the same text");
   }

@@ -139,11 +139,12 @@ EQP_HD int colon_count(const char* p, int a, int b) {
   return cnt;
 }
 
-// General tag-block scan (any token shape): field count with the reference's rule, first [nN]M:i:<digits>, HI:i: at a token start.
-// Returns false when an HI tag is present.  Only reached for lines whose tags are not all of the form XX:T:value.
-EQP_HD bool tags_general(const char* p, int t0, int n, int& fields, int& nm) {
-  fields = 11; nm = -1; int k = t0; bool colon = false, any = k < n, noHi = true;
-  for (; k < n && noHi; k++) {
+// General tag-block scan (any token shape): field count with the reference's rule, first [nN]M:i:<digits>, HI:i: at a token start
+// (hiAt = offset of its value, the last such token wins as in the reference's loop).  Only reached for lines whose tags are not all of the
+// form XX:T:value.
+EQP_HD void tags_general(const char* p, int t0, int n, int& fields, int& nm, int& hiAt) {
+  fields = 11; nm = -1; int k = t0; bool colon = false, any = k < n;
+  for (; k < n; k++) {
     char c = p[k];
     if (c == '\t') { if (!colon) fields++; colon = false; any = k + 1 < n; }
     else if (c == ':') {
@@ -155,12 +156,11 @@ EQP_HD bool tags_general(const char* p, int t0, int n, int& fields, int& nm) {
           while (d < n && p[d] >= '0' && p[d] <= '9' && v <= 30000) { v = v * 10 + (p[d] - '0'); d++; dig = true; }
           if (dig) nm = v;
         }
-        if (c1 == 'I' && c0 == 'H' && (k - 2 == t0 || p[k - 3] == '\t')) noHi = false;
+        if (c1 == 'I' && c0 == 'H' && (k - 2 == t0 || p[k - 3] == '\t')) hiAt = k + 3;
       }
     }
   }
-  if (noHi && any && !colon) fields++;                                   // last token (a trailing empty token is not one)
-  return noHi;
+  if (any && !colon) fields++;                                           // last token (a trailing empty token is not one)
 }
 
 // Source for text in any memory: tabs by search, groups byte by byte (never reads outside [p, p+n)).
@@ -174,6 +174,7 @@ struct ScanSrc {
 struct DecodedRec {
   uint32_t code;                                                        // DERR_* of the first failed check, 0 = fine
   uint32_t frag; int32_t flag, pos, pnext, ref, rnext; int nm, cigOff, cigLen, seqLen; uint8_t rf; uint16_t cigM;
+  int32_t hi; uint8_t hasHi;                                            // HI:i: tag (hit index), SamRecord.java:233-240
 };
 
 // One SAM line [p, p+n) (no '\n').  The text may live in shared or global memory.
@@ -183,6 +184,7 @@ EQP_HD DecodedRec parse_record_t(const AnnoView& A, const char* p, int n, Src& s
   uint32_t code = DERR_NONE;                                            // first failed check (single exit)
   uint32_t frag = 0xFFFFFFFFu; uint8_t rf = 0;
   int32_t flag = 0, pos = 0, pnext = 0, ref = -1, rnext = -1; int nm = -1, cigOff = 0, cigLen = 0, seqLen = 0; uint16_t cigM = 0xFFFFu;
+  int32_t hiVal = -1; int hiAt = -1;
   if (n > 0 && p[0] != '@') {                                           // SamReader.java:173
     int nt = 0, from = 0;                                                // the first 11 tabs, as scalars (an indexed array would live in local memory)
 #define EQP_TAB_STEP(i) int tab##i = n; if (nt == i) { int q = src.next(p, from, n); if (q < n) { tab##i = q; nt = i + 1; from = q + 1; } }
@@ -199,7 +201,7 @@ EQP_HD DecodedRec parse_record_t(const AnnoView& A, const char* p, int n, Src& s
       // (no field increment), the NM regex can only match at the token start and HI:i: is a plain prefix test.  "Every token has
       // ':' at offsets 2 and 4 and the block holds exactly two ':' per token" is that shape for all tokens at once.
       const uint32_t NMI = 'n' | ('M' << 8) | (':' << 16) | ((uint32_t)'i' << 24), HII = 'H' | ('I' << 8) | (':' << 16) | ((uint32_t)'i' << 24);
-      fields = 11; bool odd = false, hi = false; int t = from, nTok = 0;
+      fields = 11; bool odd = false; int t = from, nTok = 0;
       while (t < n && !odd) {
         int te = src.next(p, t, n), len = te - t;
         uint32_t w = Src::load4(p + t, len);
@@ -210,13 +212,16 @@ EQP_HD DecodedRec parse_record_t(const AnnoView& A, const char* p, int n, Src& s
             while (d < te && p[d] >= '0' && p[d] <= '9' && v <= 30000) { v = v * 10 + (p[d] - '0'); d++; dig = true; }
             if (dig) nm = v;
           }
-          hi |= w == HII;
+          if (w == HII) hiAt = t + 5;
           t = te + 1;
         } else odd = true;
       }
       if (!odd && colon_count(p, from, n) != 2 * nTok) odd = true;
-      if (odd) hi = !tags_general(p, from, n, fields, nm);
-      if (hi) code = DERR_FIELDS;                                        // HI:i: changes isMate (SamRecord.java:658-660): not produced by bowtie2
+      if (odd) { hiAt = -1; tags_general(p, from, n, fields, nm, hiAt); }
+      if (hiAt >= 0) {                                                    // new Integer(token.substring(5)): the rest of the token must be an integer
+        int e = hiAt; while (e < n && p[e] != '\t') e++;
+        if (!parse_int(p + hiAt, e - hiAt, hiVal)) code = DERR_INT;
+      }
     }
     if (!code && (fields < 11 || fields > 12)) code = DERR_FIELDS;
     if (!code) {
@@ -263,10 +268,12 @@ EQP_HD DecodedRec parse_record_t(const AnnoView& A, const char* p, int n, Src& s
     }
   }
   if (code) { frag = 0xFFFFFFFFu; rf = 0; }
-  return DecodedRec{code, frag, flag, pos, pnext, ref, rnext, nm, cigOff, cigLen, seqLen, rf, cigM};
+  return DecodedRec{code, frag, flag, pos, pnext, ref, rnext, nm, cigOff, cigLen, seqLen, rf, cigM, hiVal, (uint8_t)(hiAt >= 0 ? 1 : 0)};
 }
 EQP_HD void store_record(const SamView& S, uint32_t li, const DecodedRec& r, uint32_t* err) {
   if (r.code) raise(err, r.code, li);
+  else if (r.hasHi && !S.hi) raise(err, DERR_FIELDS, li);                // HI:i: changes isMate (SamRecord.java:658-660): only accepted from a genomic aligner's SAM
+  if (S.hi) S.hi[li] = r.rf ? r.hi : -1;
   S.frag[li] = r.frag; S.rf[li] = r.rf;
   if (r.rf) {
     S.flag[li] = (uint16_t)r.flag; S.ref[li] = r.ref; S.pos[li] = r.pos; S.rnext[li] = r.rnext; S.pnext[li] = r.pnext;

@@ -109,6 +109,7 @@ struct Pipeline {
     S.rnext = be.template alloc<int32_t>(n); S.pnext = be.template alloc<int32_t>(n); S.flag = be.template alloc<uint16_t>(n);
     S.nm = be.template alloc<int16_t>(n); S.cigOff = be.template alloc<uint16_t>(n); S.cigLen = be.template alloc<uint16_t>(n);
     S.seqLen = be.template alloc<uint16_t>(n); S.cigM = be.template alloc<uint16_t>(n); S.rf = be.template alloc<uint8_t>(n); C.proc[f] = be.template alloc<uint8_t>(n);
+    S.hi = P.genomic ? be.template alloc<int32_t>(n) : nullptr;
   }
 
   int run(const char* const text[3], const uint64_t len[3], ChunkResult& R) {

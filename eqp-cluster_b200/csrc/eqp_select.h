@@ -10,6 +10,7 @@ namespace eqpb {
 EQP_HD int rec_flag_read_index(const SamView& S, uint32_t i) { uint8_t rf = S.rf[i]; return flag_read_index(S.flag[i], (rf >> 5) & 3, rf_read_index(rf)); }
 
 EQP_HD bool is_mate(const SamView& S, uint32_t a, uint32_t b) {       // a.isMate(b); same fragment is given
+  if (S.hi && S.hi[a] >= 0) return S.hi[b] == S.hi[a];                   // hit index decides alone (SamRecord.java:658-660)
   if (rec_flag_read_index(S, a) == rec_flag_read_index(S, b)) return false;
   if (((S.rf[a] >> 5) & 3) != ((S.rf[b] >> 5) & 3)) return false;      // originalQueryName equality (/1 vs /2 names never mate)
   return S.rnext[a] == S.ref[b] && S.pnext[a] == S.pos[b] && S.ref[a] == S.rnext[b] && S.pos[a] == S.pnext[b];

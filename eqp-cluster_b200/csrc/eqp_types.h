@@ -79,6 +79,8 @@ struct SamView {                   // one decoded SAM input (structure of arrays
   uint16_t* flag; int16_t* nm; uint16_t* cigOff; uint16_t* cigLen; uint16_t* seqLen;
   uint16_t* cigM;                  // n when the CIGAR is exactly "<n>M" (the a10 stage then never touches the text), else 0xFFFF
   uint8_t* rf;                     // bit0 record (not header/empty), bit1 mapped, bit2 hasMate, bits3-4 readIndex
+  int32_t* hi;                     // HI:i: hit index (-1: none), SamRecord.java:233-240; null unless the input comes from a genomic aligner
+                                   // (compute-genomic-counts.sh) — bowtie2 writes no HI tag and the default flow rejects one
 };
 enum { RF_REC = 1, RF_MAPPED = 2, RF_HASMATE = 4 };
 EQP_HD int rf_read_index(uint8_t rf) { return (rf >> 3) & 3; }

@@ -36,7 +36,7 @@ class Params(C.Structure):
     _fields_ = [("paired_end", C.c_int32), ("stranded", C.c_int32), ("gene_overlap", C.c_int32), ("exon_overlap", C.c_int32),
                 ("junction_overlap", C.c_int32), ("read_weight_threshold", C.c_double), ("unweighted", C.c_int32),
                 ("unambiguous", C.c_int32), ("containment", C.c_int32), ("nonsplice_conforming", C.c_int32),
-                ("distance_slack", C.c_double), ("modes", C.c_int32), ("reserved", C.c_int32)]
+                ("distance_slack", C.c_double), ("modes", C.c_int32), ("genomic_input", C.c_int32)]
 
 
 class Counts(C.Structure):

@@ -67,7 +67,9 @@ typedef struct eqp_params {
   int32_t nonsplice_conforming;  /* -N (gene and exon runs) */
   double  distance_slack;        /* CombineSamFiles -s, default 0.25 */
   int32_t modes;                 /* bit0 gene, bit1 exon, bit2 junction */
-  int32_t reserved;
+  int32_t genomic_input;         /* 1: t_sam is the name-sorted SAM of a spliced GENOME aligner (compute-genomic-counts.sh:1040-1058,1126-1152): N
+                                    CIGARs, HI:i hit indices (SamRecord.java:658-660), weights = that SAM's own alignment counts; j_sam / g_sam
+                                    empty, modes 1 | 2; the context's combined_exons_bed is <base>_genome_exons.bed (or any B file with genome rows) */
 } eqp_params;
 
 /* Results of one chunk.  Vectors are indexed by the rank of the feature id in the map's sorted id set

@@ -43,8 +43,47 @@ static std::string filter_junction_map(sv refIds, sv exonJunction, sv exonJuncti
   std::string out; for (auto& s : v) out += s + "\n"; return out;
 }
 
+// compute-genomic-counts.sh:1040-1058,1126-1152 — one SAM of a spliced genome aligner: ComputeReadWeightsSam (no -c) for the weights,
+// ConvertSamBed (no -T) | bedtools intersect -b <base>_genome_exons.bed, then ComputeCounts -g / -e with that weight file.  The junction
+// run of that script filters its map through ExtractSplicedExonExonIds and a GTF (:1210-1290) and is not part of this restatement.
+static int run_genomic(int argc, char** argv) {
+  std::string anno = argv[2], samPath = argv[3], outd = argv[4];
+  int strandDir = 0; bool stranded = false, unweighted = false, unambig = false, containment = false, nonsplice = false, quiet = false;
+  for (int i = 5; i < argc; i++) {
+    std::string a = argv[i];
+    if (a == "--stranded=forward") { stranded = true; strandDir = 1; } else if (a == "--stranded=backward") { stranded = true; strandDir = 2; }
+    else if (a == "--unweighted") unweighted = true; else if (a == "--unambig") unambig = true; else if (a == "--containment") containment = true;
+    else if (a == "--nonsplice") nonsplice = true; else if (a == "--quiet") quiet = true;
+  }
+  try {
+    const std::string base = anno + "/ensembl_rna_hs";
+    std::string G = read_file(samPath), bFile = read_file(base + "_genome_exons.bed");
+    FeatureTable ftGene, ftExon; ftGene.load(read_file(base + "_exon_gene.map")); ftExon.load(read_file(base + "_exon_exon.map"));
+    BIndex B(bFile);
+    auto t0 = std::chrono::steady_clock::now();
+    std::string wG = compute_read_weights_sam(G, nullptr);
+    ConvertStats cs;
+    std::string bed = convert_sam_bed(G, nullptr, &cs, strandDir);
+    std::string inter = intersect_wo(bed, B, stranded);
+    Params pg; pg.mode = MODE_GENE; pg.stranded = stranded; pg.useReadWeights = !unweighted; pg.excludeAmbiguous = unambig; pg.containment = containment; pg.spliceConforming = !nonsplice;
+    Params pe = pg; pe.mode = MODE_EXON; pe.overlapThreshold = 5; pe.containment = false;
+    CountResult rg = compute_counts(inter, wG, ftGene, pg), re = compute_counts(inter, wG, ftExon, pe);
+    double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    write_file(outd + "/genomic-sam.wgt", wG); write_file(outd + "/combined.bed", bed); write_file(outd + "/intersection.bed", inter);
+    write_file(outd + "/gene.cnt", format_counts(rg, ftGene, pg)); write_file(outd + "/exon.cnt", format_counts(re, ftExon, pe)); write_file(outd + "/junction.cnt", "");
+    char buf[512];
+    snprintf(buf, sizeof buf, "NUMBER_MAPPED_READS=%ld\nNUMBER_EXPRESSED_READS=%ld\nNUM_WEIGHT_OBJECTS=%ld\nORACLE_SECONDS=%.6f\nSUM_WEIGHTS_GENE=%.4f\nSUM_WEIGHTS_EXON=%.4f\nSUM_WEIGHTS_JUNCTION=0.0000\n",
+             cs.mappedFragments, rg.stats.included, rg.stats.numWeightObjects, secs, rg.stats.sumObjectWeight, re.stats.sumObjectWeight);
+    write_file(outd + "/stats.txt", buf);
+    if (!quiet) fputs(buf, stdout);
+    return 0;
+  } catch (const std::exception& e) { fprintf(stderr, "ERROR: %s\n", e.what()); return 1; }
+}
+
 int main(int argc, char** argv) {
+  if (argc >= 5 && !strcmp(argv[1], "genomic")) return run_genomic(argc, argv);
   if (argc < 6 || strcmp(argv[1], "run")) {
+    fprintf(stderr, "usage: eqp_oracle genomic <annodir> <sam> <outdir> [--stranded=forward|backward] [--unweighted] [--unambig] [--containment] [--nonsplice] [--quiet]\n");
     fprintf(stderr, "usage: eqp_oracle run <annodir> <chunkdir> <se|pe> <outdir> [--stranded=forward|backward] [--unweighted] [--unambig] [--containment] [--nonsplice] [--no-adjust-shortcut] [--quiet]\n");
     return 2;
   }

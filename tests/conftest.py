@@ -58,6 +58,19 @@ class World:
         return self.chunks[name]
 
 
+    def genomic_chunk(self, name, seed, first, n, layout, flags=()):
+        """One SAM of a spliced genome aligner (worldgen ... genomic) + the oracle's compute-genomic-counts.sh restatement."""
+        if name in self.chunks:
+            return self.chunks[name]
+        d = os.path.join(self.root, name)
+        o = os.path.join(d, "oracle")
+        os.makedirs(o, exist_ok=True)
+        run([self.tools["worldgen"], "reads", self.anno, d, str(seed), str(first), str(n), layout, "genomic"])
+        sam = os.path.join(d, "genomic-%s.sam" % ("pe" if layout == "pe" else "sr"))
+        run([self.tools["oracle"], "genomic", self.anno, sam, o, "--quiet"] + list(flags))
+        self.chunks[name] = {"dir": d, "oracle": o, "layout": layout, "n": n, "flags": tuple(flags), "sam": sam}
+        return self.chunks[name]
+
     def oracle_run(self, name, flags):
         """Oracle outputs of a chunk under extra switches (--unweighted, --unambig, --containment, --nonsplice)."""
         c = self.chunks[name]

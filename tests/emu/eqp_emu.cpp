@@ -79,7 +79,8 @@ int main(int argc, char** argv) {
     H.load((base + "_100_combined_exons.bed").c_str(), (base + "_transcript_exons.bed").c_str(), (base + "_exon_gene.map").c_str(),
            (base + "_exon_exon.map").c_str(), (base + "_exon_junction.map").c_str(), (base + "_exon_junction_transcript.map").c_str(),
            (base + "_100_junction_junction_coordinate.map").c_str(), (base + "_equivalent_junctions.map").c_str(), (anno + "/genome.fa.fai").c_str());
-    std::string T = slurp(chunk + "/transcript-" + sfx + ".sam"), J = slurp(chunk + "/junction-" + sfx + ".sam"), G = slurp(chunk + "/genome-" + sfx + ".sam");
+    bool genomicIn = false; for (int i = 5; i < argc; i++) genomicIn |= !strcmp(argv[i], "--genomic");
+    std::string T = slurp(chunk + (genomicIn ? "/genomic-" : "/transcript-") + sfx + ".sam"), J = genomicIn ? std::string() : slurp(chunk + "/junction-" + sfx + ".sam"), G = genomicIn ? std::string() : slurp(chunk + "/genome-" + sfx + ".sam");
     RunParams P{}; P.overlap[0] = 1; P.overlap[1] = 5; P.overlap[2] = 8;
     for (int m = 0; m < 3; m++) { P.spliceConforming[m] = 1; P.containment[m] = 0; P.unambiguous[m] = 0; }
     P.unweighted = 0;
@@ -88,10 +89,11 @@ int main(int argc, char** argv) {
       else if (!strcmp(argv[i], "--unambig")) P.unambiguous[0] = P.unambiguous[1] = 1;
       else if (!strcmp(argv[i], "--containment")) P.containment[0] = 1;
       else if (!strcmp(argv[i], "--nonsplice")) P.spliceConforming[0] = P.spliceConforming[1] = 0;
+      else if (!strcmp(argv[i], "--genomic")) P.genomic = 1;
       else if (!strcmp(argv[i], "--stranded=forward")) P.stranded = 1;
       else if (!strcmp(argv[i], "--stranded=backward")) P.stranded = 2;
     }
-    P.modes = 7; P.weightThreshold = 0.01; P.slack = 0.25;
+    P.modes = P.genomic ? 3 : 7; P.weightThreshold = 0.01; P.slack = 0.25;
     HostBackend be; Pipeline<HostBackend> pl(be, H.view(), P);
     const char* text[3] = {T.data(), J.data(), G.data()}; uint64_t len[3] = {T.size(), J.size(), G.size()};
     ChunkResult R{};

@@ -75,6 +75,29 @@ def test_strand_specific_mode(shape_worlds, layout, seed, direction, code):
         check_weights(cx, o)
 
 
+@pytest.mark.parametrize("layout,seed", [("se", 1201), ("pe", 1203)])
+def test_genomic_aligner_input(shape_worlds, layout, seed):
+    """the SAM of a spliced genome aligner (N CIGARs, HI:i hit indices) counted with eqp_params.genomic_input
+    against the oracle's restatement of compute-genomic-counts.sh (gene and exon runs)."""
+    w = shape_worlds("mixed")
+    c = w.genomic_chunk("genomic_" + layout, seed, 1, 6000, layout)
+    p = eqp.default_params()
+    p.genomic_input, p.modes = 1, 3
+    with eqp.CountContext(0).load_annotation(w.anno) as cx:
+        res = cx.count_chunk(open(c["sam"], "rb").read(), b"", b"", params=p)
+        st = read_stats(os.path.join(c["oracle"], "stats.txt"))
+        assert res.number_mapped_reads == int(st["NUMBER_MAPPED_READS"]) and res.number_expressed_reads == int(st["NUMBER_EXPRESSED_READS"])
+        assert res.num_weight_objects[0] == int(st["NUM_WEIGHT_OBJECTS"])
+        for m in ("gene", "exon"):
+            assert_rows_match(res.rows(m), read_rows(os.path.join(c["oracle"], m + ".cnt")), what="genomic " + m)
+        p.modes = 7
+        with pytest.raises(eqp.EqpError) as e:
+            cx.count_chunk(open(c["sam"], "rb").read(), b"", b"", params=p)
+        assert e.value.code == -5                                           # the junction run of that script is not built
+        with pytest.raises(eqp.EqpError):                                   # an HI tag outside the genomic mode is still refused
+            cx.count_chunk(open(c["sam"], "rb").read(), b"", b"")
+
+
 def test_weight_intermediates_match_oracle(world, ctx):
     """*-sam.wgt (a4), trans-junction weights (a6 -e) and final.wgt (a6/a20) against the oracle's files."""
     c = world.chunk("pe_small", 1003, 1, 3000, "pe")

@@ -68,6 +68,25 @@ def test_alternate_paths_on_the_mixed_world(shape_worlds, variant):
         assert emu["stats"][k] == st[k], k
 
 
+@pytest.mark.parametrize("layout,seed", [("se", 1201), ("pe", 1203)])
+def test_genomic_aligner_input(shape_worlds, layout, seed):
+    """SURVEY 8f rank 2 (compute-genomic-counts.sh:1040-1058,1126-1152): one SAM of a spliced genome aligner — N CIGARs of 2-4 segments,
+    indels, HI:i hit indices, secondary alignments — joined with the genome exon rows: BedRecord.computeGenomicInterval(ga) (:555-578) and
+    the first / inner / last splice-conforming rules (:696-733) with maxSeg > 0."""
+    w = shape_worlds("mixed")
+    c = w.genomic_chunk("genomic_" + layout, seed, 1, 6000, layout)
+    emu = w.emu_run("genomic_" + layout, ("--genomic",))
+    st = read_stats(os.path.join(c["oracle"], "stats.txt"))
+    for k in ("NUMBER_MAPPED_READS", "NUMBER_EXPRESSED_READS", "NUM_WEIGHT_OBJECTS"):
+        assert emu["stats"][k] == st[k], k
+    for m in ("gene", "exon"):
+        assert_rows_match(emu[m + "_rows"], read_rows(os.path.join(c["oracle"], m + ".cnt")), what="genomic %s %s" % (layout, m))
+    cigars = [l.split("\t")[5] for l in open(c["sam"]) if not l.startswith("@")]
+    assert sum(x.count("N") >= 2 for x in cigars) > 20 and any("I" in x for x in cigars) and any("D" in x for x in cigars)
+    inter = open(os.path.join(c["oracle"], "intersection.bed")).read()
+    assert "-F1-2/" in inter and "-F2-2/" in inter                        # inner and last segments of three-segment alignments reach the counting
+
+
 def test_default_world_has_the_survey_mix(world):
     """The default world (what bench.py counts, scaled down) carries every shape at the SURVEY 8d rates."""
     bed = open(os.path.join(world.anno, "ensembl_rna_hs_100_combined_exons.bed")).read()

@@ -16,6 +16,7 @@
 // Usage:
 //   worldgen anno  <outdir> <seed> <n_genes> [key=value ...]
 //   worldgen reads <annodir> <outdir> <seed> <first_frag> <n_frags> <se|pe> [spliced_frac]
+//   worldgen reads <annodir> <outdir> <seed> <first_frag> <n_frags> <se|pe> genomic      one genomic-<sr|pe>.sam of a spliced genome aligner
 // `reads` re-derives the world from <annodir>/world.seed so annotation and reads agree.
 // Annotation shape knobs (SURVEY.md 8d "Ensembl76-shaped"; defaults in Knobs):
 //   ld=F     fraction of transcripts with one exon whose transcript length differs from its genome length by +-1..3 bp
@@ -266,6 +267,16 @@ static void write_annotation(const World& w, const std::string& dir, uint64_t se
       if (i == 0 || rows[i].first != rows[i - 1].first) fputs(rows[i].second.c_str(), bed);
   }
   fclose(bed); fclose(tbed);
+  // <base>_genome_exons.bed: the B file of compute-genomic-counts.sh (:775): the genome rows only
+  { FILE* gb = xopen(base + "_genome_exons.bed", "w");
+    std::vector<std::pair<std::string, std::string>> rows;
+    for (auto& G : w.genes) for (size_t k = 0; k < G.ex.size(); k++) {
+      std::string key = exon_key(w, G, (int)k);
+      rows.push_back({key, fmt("%s\t%d\t%d\t%s/%s\t0\t%c\n", w.chrs[G.chr].c_str(), G.ex[k].s - 1, G.ex[k].e, G.id.c_str(), key.c_str(), G.strand)});
+    }
+    std::stable_sort(rows.begin(), rows.end(), [](auto& a, auto& b) { return a.first < b.first; });
+    for (size_t i = 0; i < rows.size(); i++) if (i == 0 || rows[i].first != rows[i - 1].first) fputs(rows[i].second.c_str(), gb);
+    fclose(gb); }
   FILE* eg = xopen(base + "_exon_gene.map", "w"); FILE* ee = xopen(base + "_exon_exon.map", "w");
   fprintf(eg, "Exon Id\tGene Id\n"); fprintf(ee, "Exon Id\tExon Id\n");
   int exonNo = 0;
@@ -562,6 +573,84 @@ static void gen_reads(const World& w, const std::string& dir, uint64_t seed, int
   T.flush(); J.flush(); Gn.flush(); fclose(T.f); fclose(J.f); fclose(Gn.f);
 }
 
+// ---------------------------------------------------------------- genomic-aligner output (compute-genomic-counts.sh)
+// One name-sorted SAM as a spliced genome aligner (tophat2 / STAR / hisat) writes it: reads aligned to the chromosomes, introns as
+// N operations, every alignment of a fragment numbered by an HI:i tag that both mates of a pair share (SamRecord.java:233-240,658-660),
+// NH:i present (and ignored by the reference).  ids stay Fnnnnnnnnn (the reference renumbers foreign ids itself, SamReader.java:157-186).
+static std::string spliced_cigar(const Place& P, int span, int shape) {
+  std::string c; int used = 0;
+  for (size_t i = 0; i < P.b.size(); i++) {
+    int len = P.b[i].ge - P.b[i].gs + 1; used += len;
+    if (i) c += fmt("%dN", P.b[i].gs - P.b[i - 1].ge - 1);
+    if (i == 0 && shape == 1 && len > 12) c += fmt("%dM1I%dM", 6, len - 7);          // an insertion in the first block (read length = span)
+    else if (i + 1 == P.b.size() && shape == 2 && len > 12) c += fmt("%dM1D%dM", len - 6, 5);   // a deletion in the last block: 1 reference base is skipped
+    else c += fmt("%dM", len);
+  }
+  (void)span; (void)used;
+  return c;
+}
+static void gen_genomic(const World& w, const std::string& dir, uint64_t seed, int first, int n, bool pe) {
+  Rng init(seed ^ 0xABCDEFULL);
+  for (size_t i = 0; i < sizeof g_seq; i++) { g_seq[i] = "ACGT"[init.below(4)]; g_qual[i] = (char)(35 + init.below(38)); }
+  Out S{"", xopen(dir + "/genomic-" + (pe ? "pe" : "sr") + ".sam", "w")};
+  if (first == 1) { S.buf += "@HD\tVN:1.0\tSO:queryname\n"; for (size_t c = 0; c < w.chrs.size(); c++) S.buf += fmt("@SQ\tSN:%s\tLN:%d\n", w.chrs[c].c_str(), w.chrLen[c]); }
+  auto put = [&](int frag, int flag, const char* rname, int pos, const std::string& cigar, int seqLen, const char* rnext, int pnext, int tlen, int nm, int nh, int hi, int seqOff) {
+    char line[900]; int k;
+    if (flag & 4) k = snprintf(line, sizeof line, "F%09d\t%d\t*\t0\t0\t*\t*\t0\t0\t%.*s\t%.*s\tYT:Z:UU\n", frag, flag, seqLen, g_seq + seqOff, seqLen, g_qual + seqOff);
+    else k = snprintf(line, sizeof line, "F%09d\t%d\t%s\t%d\t%d\t%s\t%s\t%d\t%d\t%.*s\t%.*s\tAS:i:%d\tNM:i:%d\tNH:i:%d\tHI:i:%d\n", frag, flag, rname, pos, nh == 1 ? 50 : 3,
+                      cigar.c_str(), rnext, pnext, tlen, seqLen, g_seq + seqOff, seqLen, g_qual + seqOff, -6 * nm, nm, nh, hi);
+    S.buf.append(line, k); if (S.buf.size() > (1u << 22)) S.flush();
+  };
+  for (int f = 0; f < n; f++) {
+    int frag = first + f; Rng r(seed * 1000003ULL + (uint64_t)frag);
+    int seqOff[2] = {r.below(60000), r.below(60000)};
+    double cat = r.uni();
+    struct GA { int chr; int pos[2]; std::string cig[2]; int len[2]; int rev; int nm[2]; bool two; };
+    std::vector<GA> alns;
+    if (cat >= 0.03) {
+      int nLoci = 1; double u = r.uni(); if (u < 0.10) nLoci = 2 + r.below(4); else if (u < 0.115) nLoci = 6 + r.below(10);
+      for (int l = 0; l < nLoci; l++) {
+        GA a; a.two = false; a.rev = r.below(2);
+        if (cat < 0.10) {                                                  // intronic / intergenic, unspliced
+          const Gene& G = w.genes[pick_gene(w, r)]; a.chr = G.chr;
+          int lo = std::max(1, G.ex.front().s - 300), hi = G.ex.back().e + 300;
+          a.pos[0] = lo + r.below(hi - lo + 1); a.cig[0] = "101M"; a.len[0] = READ_LEN; a.nm[0] = draw_nm(r);
+          if (pe && r.uni() < 0.8) { a.two = true; a.pos[1] = a.pos[0] + 100 + r.below(250); a.cig[1] = "101M"; a.len[1] = READ_LEN; a.nm[1] = draw_nm(r); }
+        } else {                                                           // from a transcript: the footprint's blocks become M runs, the introns N runs
+          Place P[2]; int sh[2] = {0, 0}; for (int m = 0; m < 2; m++) { double v = r.uni(); sh[m] = v < 0.95 ? 0 : v < 0.975 ? 1 : 2; }
+          bool ok = false;
+          for (int attempt = 0; attempt < 8 && !ok; attempt++) ok = random_place(w, r, READ_LEN, P[0]) && P[0].clean;
+          if (!ok) continue;
+          a.chr = w.genes[P[0].gene].chr; a.pos[0] = P[0].b[0].gs; a.cig[0] = spliced_cigar(P[0], 0, sh[0]); a.nm[0] = draw_nm(r) + (sh[0] ? 1 : 0);
+          a.len[0] = a.cig[0].find('D') != std::string::npos ? READ_LEN - 1 : READ_LEN;   // "xM1D5M" reads one base less than the footprint's reference span
+          if (pe && r.uni() > 0.06) {
+            const Transcript& Tr = w.trs[P[0].tr]; int ins = std::max(READ_LEN, std::min(500, (int)(300 + 50 * r.normal())));
+            int go2 = std::max(0, std::min(Tr.len - READ_LEN, P[0].go + ins - READ_LEN));
+            if (place(w, P[0].tr, go2, READ_LEN, P[1]) && P[1].clean) { a.two = true; a.pos[1] = P[1].b[0].gs; a.cig[1] = spliced_cigar(P[1], 0, 0); a.len[1] = READ_LEN; a.nm[1] = draw_nm(r); }
+          }
+        }
+        alns.push_back(a);
+      }
+    }
+    if (alns.empty()) {
+      if (!pe) put(frag, 4, "*", 0, "*", READ_LEN, "*", 0, 0, 0, 0, 0, seqOff[0]);
+      else { put(frag, 77, "*", 0, "*", READ_LEN, "*", 0, 0, 0, 0, 0, seqOff[0]); put(frag, 141, "*", 0, "*", READ_LEN, "*", 0, 0, 0, 0, 0, seqOff[1]); }
+      continue;
+    }
+    int nh = (int)alns.size();
+    for (int k = 0; k < nh; k++) {
+      const GA& a = alns[k]; const char* chr = w.chrs[a.chr].c_str(); int sec = k ? 256 : 0;
+      if (!pe) put(frag, (a.rev ? 16 : 0) | sec, chr, a.pos[0], a.cig[0], a.len[0], "*", 0, 0, a.nm[0], nh, k + 1, seqOff[0]);
+      else if (a.two) {
+        int tl = a.pos[1] - a.pos[0] + READ_LEN;
+        put(frag, 1 + 2 + 64 + (a.rev ? 16 : 32) + sec, chr, a.pos[0], a.cig[0], a.len[0], "=", a.pos[1], tl, a.nm[0], nh, k + 1, seqOff[0]);
+        put(frag, 1 + 2 + 128 + (a.rev ? 32 : 16) + sec, chr, a.pos[1], a.cig[1], a.len[1], "=", a.pos[0], -tl, a.nm[1], nh, k + 1, seqOff[1]);
+      } else put(frag, 1 + 8 + 64 + (a.rev ? 16 : 0) + sec, chr, a.pos[0], a.cig[0], a.len[0], "*", 0, 0, a.nm[0], nh, k + 1, seqOff[0]);
+    }
+  }
+  S.flush(); fclose(S.f);
+}
+
 int main(int argc, char** argv) {
   if (argc >= 5 && !strcmp(argv[1], "anno")) {
     World w; uint64_t seed = strtoull(argv[3], 0, 10); int ng = atoi(argv[4]);
@@ -584,9 +673,10 @@ int main(int argc, char** argv) {
     if (fscanf(fs, "%llu %d %lf %lf %lf %lf %lf %lf %d %d", &seed, &ng, &w.k.ld, &w.k.tr, &w.k.trlong, &w.k.inv, &w.k.ver, &w.k.ver2, &w.k.scaf, &w.k.map3) != 10) return 1;
     fclose(fs);
     build_world(w, seed, ng);
-    gen_reads(w, argv[3], strtoull(argv[4], 0, 10), atoi(argv[5]), atoi(argv[6]), !strcmp(argv[7], "pe"), argc > 8 ? atof(argv[8]) : 0.0);
+    if (argc > 8 && !strcmp(argv[8], "genomic")) gen_genomic(w, argv[3], strtoull(argv[4], 0, 10), atoi(argv[5]), atoi(argv[6]), !strcmp(argv[7], "pe"));
+    else gen_reads(w, argv[3], strtoull(argv[4], 0, 10), atoi(argv[5]), atoi(argv[6]), !strcmp(argv[7], "pe"), argc > 8 ? atof(argv[8]) : 0.0);
     return 0;
   }
-  fprintf(stderr, "usage: worldgen anno <outdir> <seed> <n_genes> [ld=F tr=F trlong=F inv=F ver=F ver2=F scaf=N map3=0|1] | reads <annodir> <outdir> <seed> <first_frag> <n_frags> <se|pe> [spliced_frac]\n");
+  fprintf(stderr, "usage: worldgen anno <outdir> <seed> <n_genes> [ld=F tr=F trlong=F inv=F ver=F ver2=F scaf=N map3=0|1] | reads <annodir> <outdir> <seed> <first_frag> <n_frags> <se|pe> [spliced_frac | genomic]\n");
   return 2;
 }
