@@ -48,7 +48,10 @@ def main():
     torch.cuda.synchronize()
     dargs = [(d.data_ptr(), d.numel()) for d in dev]
     libs = [("product", b.LIB_PATH)] + [(os.path.basename(p)[12:-3], p) for p in sorted(glob.glob(os.path.join(VDIR, "libeqpcount_*.so")))]
-    for name, path in libs:
+    runs = [(n, p, f) for n, p in libs for f in ("0", "1")]
+    for name, path, fused in runs:
+        os.environ["EQP_FUSED"] = fused
+        name = name + ("+fused" if fused == "1" else "")
         r, w = os.pipe()
         saved = os.dup(2)
         ctx = eqp.CountContext(0, path).load_annotation(anno)
