@@ -321,8 +321,8 @@ EQP_HD int exon_filter(const AnnoView& A, ExonSet& e, int32_t gs, int32_t ge) {
   int ne = e.n; int32_t* exon = e.exon; uint8_t* exGen = e.gen;
   if (ne > 1) {
     int maxOv = 0;
-    for (int q = 0; q < ne; q++) if (!exGen[q]) { int en = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = en - gs + 1; if (ov < 0) ov = 0; if (ov > maxOv) maxOv = ov; }
-    if (maxOv > 0) { int w = 0; for (int q = 0; q < ne; q++) { int en = A.exEnd[exon[q]] < ge ? A.exEnd[exon[q]] : ge; int ov = en - gs + 1; if (ov < 0) ov = 0; if (exGen[q] || ov >= maxOv) { exon[w] = exon[q]; exGen[w] = exGen[q]; w++; } } ne = w; }
+    for (int q = 0; q < ne; q++) if (!exGen[q]) { int en = A.ex[exon[q]].end < ge ? A.ex[exon[q]].end : ge; int ov = en - gs + 1; if (ov < 0) ov = 0; if (ov > maxOv) maxOv = ov; }
+    if (maxOv > 0) { int w = 0; for (int q = 0; q < ne; q++) { int en = A.ex[exon[q]].end < ge ? A.ex[exon[q]].end : ge; int ov = en - gs + 1; if (ov < 0) ov = 0; if (exGen[q] || ov >= maxOv) { exon[w] = exon[q]; exGen[w] = exGen[q]; w++; } } ne = w; }
   }
   e.n = ne; return ne;
 }

@@ -34,10 +34,11 @@ struct RecKey { int readIdx, readStart, eStart, eEnd, eStrand, row; };
 EQP_HD RecKey rec_key(const AnnoView& A, const ChunkView& C, const Hit& h) {
   const Block& b = C.blocks[h.block]; RecKey k;
   k.readIdx = b.readIdx; k.readStart = b.start + 1; k.row = h.row;
-  int es = A.rowStart[h.row] + 1, ee = A.rowEnd[h.row]; int ex = A.rowExon[h.row];
-  int refDiff = ee - es + 1, genDiff = A.exEnd[ex] - A.exStart[ex] + 1;
-  if (es == 1 && refDiff < genDiff && !(A.rowFlags[h.row] & 1)) es -= genDiff - refDiff;     // BedRecord.java:136-141
-  k.eStart = es; k.eEnd = ee; k.eStrand = (A.rowFlags[h.row] >> 1) & 3;
+  const RowA r = A.row[h.row]; const ExonA e = A.ex[r.exon()];
+  int es = r.start + 1, ee = r.end;
+  int refDiff = ee - es + 1, genDiff = e.end - e.start + 1;
+  if (es == 1 && refDiff < genDiff && !(r.flags() & 1)) es -= genDiff - refDiff;             // BedRecord.java:136-141
+  k.eStart = es; k.eEnd = ee; k.eStrand = (int)((r.flags() >> 1) & 3);
   return k;
 }
 EQP_HD int rec_cmp(const RecKey& a, const RecKey& b) {                 // BedRecord.compareTo for records of one alignment
@@ -51,9 +52,10 @@ EQP_HD int rec_cmp(const RecKey& a, const RecKey& b) {                 // BedRec
 
 // lengthDifference of a record: transcript exon length (after the 5' fix) minus genome exon length; genomic records have none
 EQP_HD int record_ld(const AnnoView& A, const ChunkView& C, const Hit& h) {
-  if (A.rowFlags[h.row] & 1) return 0;
-  RecKey rk = rec_key(A, C, h); int ex = A.rowExon[h.row];
-  return (rk.eEnd - rk.eStart + 1) - (A.exEnd[ex] - A.exStart[ex] + 1);
+  const RowA r = A.row[h.row];
+  if (r.flags() & 1) return 0;
+  RecKey rk = rec_key(A, C, h); const ExonA e = A.ex[r.exon()];
+  return (rk.eEnd - rk.eStart + 1) - (e.end - e.start + 1);
 }
 
 EQP_HD uint64_t mix64(uint64_t h, uint64_t v) { h ^= v + 0x9E3779B97F4A7C15ULL + (h << 6) + (h >> 2); h *= 0xBF58476D1CE4E5B9ULL; return h ^ (h >> 29); }
@@ -71,15 +73,15 @@ EQP_HD void build_half(const AnnoView& A, const ChunkView& C, const CountView& V
     if (!dup) n++;
   }
   const Block& b0 = C.blocks[C.hits[h0].block];
-  bool genomic = A.rowFlags[C.hits[h0].row] & 1; bool junction = A.bktFlags[b0.bucket] & 1, inv = A.bktFlags[b0.bucket] & 2;
+  bool genomic = A.row[C.hits[h0].row].flags() & 1; bool junction = A.bktFlags[b0.bucket] & 1, inv = A.bktFlags[b0.bucket] & 2;
   int i = -1, iJ = -1; int prevExon = -1; const Block* prevBlk = nullptr; bool anyTr = false, anyLd = false; int trSign = 1;
   for (uint32_t k = h0; k < h1; k++) {
     HitX& x = V.hx[k]; if (!(x.flags & 1)) continue;
-    const Hit& h = C.hits[k]; const Block& b = C.blocks[h.block]; int ex = A.rowExon[h.row];
-    if (((A.rowFlags[h.row] & 1) != 0) != genomic) raise(C.err, DERR_INCONSISTENT, frag);           // "Change of BED record type"
+    const Hit& h = C.hits[k]; const Block& b = C.blocks[h.block]; const RowA row = A.row[h.row]; const int ex = row.exon(); const ExonA exn = A.ex[ex];
+    if (((row.flags() & 1) != 0) != genomic) raise(C.err, DERR_INCONSISTENT, frag);                 // "Change of BED record type"
     if (prevBlk && b.strand != prevBlk->strand) raise(C.err, DERR_INCONSISTENT, frag);               // differing strand
-    const bool tr = A.exChr[ex] <= -2;                                   // tr- transcript exon (Exon.java:230-301): coordinates on the transcript
-    int exS = A.exStart[ex], exE = A.exEnd[ex]; char ostrand = (char)A.exStrand[ex];
+    const bool tr = exn.chr <= -2;                                       // tr- transcript exon (Exon.java:230-301): coordinates on the transcript
+    int exS = exn.start, exE = exn.end; char ostrand = (char)exn.strand;
     int readStart = b.start + 1, readEnd = b.end;
     RecKey rk = rec_key(A, C, h);
     int gs, ge, ld = 0, fieldIdx, fieldJ; char ivStrand; bool first, last;
@@ -133,7 +135,7 @@ EQP_HD void build_half(const AnnoView& A, const ChunkView& C, const CountView& V
       int thr = P.overlap[m] < (exE - exS + 1) ? P.overlap[m] : (exE - exS + 1);
       if (c && h.overlap >= thr) conf |= (uint8_t)(4 << m);              // GenomicInterval.java:144
     }
-    x.gs = gs; x.ge = ge; x.chr = A.exChr[ex]; x.ivField = (int8_t)fieldIdx; x.ivFieldJ = (int8_t)fieldJ; x.exon = ex;
+    x.gs = gs; x.ge = ge; x.chr = exn.chr; x.ivField = (int8_t)fieldIdx; x.ivFieldJ = (int8_t)fieldJ; x.exon = ex;
     x.flags = (uint8_t)(1 | (genomic ? 2 : 0) | conf | (ivStrand == '-' ? 32 : 0));
     prevBlk = &b; prevExon = ex;
   }

@@ -57,6 +57,7 @@ struct AnnoHost {
   std::vector<uint32_t> bktRowOff; std::vector<uint8_t> bktFlags; std::vector<int32_t> bktRefId;
   std::vector<int32_t> rowStart, rowEnd, rowMaxEnd, rowExon; std::vector<uint8_t> rowFlags;
   std::vector<int32_t> exChr, exStart, exEnd; std::vector<uint8_t> exStrand;
+  std::vector<RowA> rowA; std::vector<ExonA> exA;                        // the device form of the row / exon tables
   std::vector<uint32_t> featOff[3], feat[3]; std::vector<std::string> featIds[3];
   std::vector<uint32_t> featAct; std::vector<std::string> actIds; int mapColumns[3] = {2, 2, 2};
   // rows of the count file in print order (ComputeCounts.java:875-950): 2-column maps print every id of the map in TreeSet order,
@@ -159,6 +160,10 @@ struct AnnoHost {
       }
       bktRowOff.push_back((uint32_t)rowStart.size());
     }
+    rowA.resize(rowStart.size()); exA.resize(exChr.size());
+    for (size_t i = 0; i < rowA.size(); i++) rowA[i] = RowA{rowStart[i], rowEnd[i], rowMaxEnd[i], ((uint32_t)rowExon[i] << 3) | (uint32_t)(rowFlags[i] & 7)};
+    for (size_t i = 0; i < exA.size(); i++) exA[i] = ExonA{exChr[i], exStart[i], exEnd[i], (uint32_t)exStrand[i]};
+    if (exA.size() >= (1u << 29)) throw AnnoError(-3, "too many distinct exons");
     // ---- reference-name dictionary: bucket names, base ids of transcript_exons.bed, genome.fa.fai names
     std::unordered_map<std::string, int32_t> refIdx;
     std::map<std::string, std::vector<std::string>> versions;           // base id -> versioned ids, first-seen order
@@ -287,8 +292,7 @@ struct AnnoHost {
     v.refVerOff = refVerOff.data(); v.refVerBucket = refVerBucket.data(); v.refActOff = refActOff.data(); v.refAct = refAct.data();
     v.nRef = (int32_t)refStrOff.size();
     v.bktRowOff = bktRowOff.data(); v.bktFlags = bktFlags.data(); v.bktRefId = bktRefId.data(); v.nBucket = (int32_t)bktFlags.size();
-    v.rowStart = rowStart.data(); v.rowEnd = rowEnd.data(); v.rowMaxEnd = rowMaxEnd.data(); v.rowExon = rowExon.data(); v.rowFlags = rowFlags.data();
-    v.exChr = exChr.data(); v.exStart = exStart.data(); v.exEnd = exEnd.data(); v.exStrand = exStrand.data(); v.nExon = (int32_t)exChr.size(); v.nTrChr = (int32_t)trChrNames.size();
+    v.row = rowA.data(); v.ex = exA.data(); v.nExon = (int32_t)exChr.size(); v.nTrChr = (int32_t)trChrNames.size();
     v.featAct = featAct.empty() ? nullptr : featAct.data(); v.nAct = (int32_t)actIds.size();
     for (int m = 0; m < 3; m++) { v.featOff[m] = featOff[m].data(); v.feat[m] = feat[m].data(); v.nFeat[m] = (int32_t)featIds[m].size(); }
     return v;

@@ -152,13 +152,14 @@ EQP_HD uint32_t join_block(const AnnoView& A, const Block& b, Hit* out, uint32_t
   const uint32_t wantStrand = b.strand == '+' ? 0u : 1u;
   int32_t lo = (int32_t)A.bktRowOff[b.bucket], hi = (int32_t)A.bktRowOff[b.bucket + 1];
   int32_t l = lo, h = hi;                                                // first row with start >= b.end
-  while (l < h) { int32_t m = (l + h) >> 1; if (A.rowStart[m] < b.end) l = m + 1; else h = m; }
+  while (l < h) { int32_t m = (l + h) >> 1; if (A.row[m].start < b.end) l = m + 1; else h = m; }
   uint32_t n = 0;
   for (int32_t k = l - 1; k >= lo; k--) {
-    if (A.rowMaxEnd[k] <= b.start) break;
-    int32_t re = A.rowEnd[k];
-    if (re > b.start && (!sameStrand || ((A.rowFlags[k] >> 1) & 3u) == wantStrand)) {
-      int32_t ov = (re < b.end ? re : b.end) - (A.rowStart[k] > b.start ? A.rowStart[k] : b.start);
+    const RowA r = A.row[k];
+    if (r.maxEnd <= b.start) break;
+    int32_t re = r.end;
+    if (re > b.start && (!sameStrand || ((r.flags() >> 1) & 3u) == wantStrand)) {
+      int32_t ov = (re < b.end ? re : b.end) - (r.start > b.start ? r.start : b.start);
 #ifdef EQP_VAR_DESC_HITS
       if (ov >= 1) { if (out) { Hit& o = out[n]; o.block = blockIdx; o.row = k; o.overlap = ov; } n++; }
 #else

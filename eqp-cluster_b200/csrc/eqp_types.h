@@ -47,6 +47,11 @@ enum {
 // reference-name dictionary slot: key = (name_hash(name) & ~0xFFFF) | length, 0 = empty.  One 16-byte load yields everything lookup_ref needs.
 struct alignas(16) DictEntry { uint64_t key; int32_t val; uint32_t off; };
 
+// one row of the B file / one distinct exon, 16 bytes each: a hit needs all fields of its row and of its exon, one load apiece
+struct alignas(16) RowA { int32_t start, end, maxEnd; uint32_t exonFlags;      // exonFlags = exon << 3 | flags: bit0 genomic row (bucket name == exon chromosome), bits1-2 row strand (0 '+', 1 '-', 2 other)
+  EQP_HD int32_t exon() const { return (int32_t)(exonFlags >> 3); } EQP_HD uint32_t flags() const { return exonFlags & 7u; } };
+struct alignas(16) ExonA { int32_t chr, start, end; uint32_t strand; };         // chr <= -2: tr- exon of transcript -2 - chr; strand: the character
+
 struct AnnoView {
   // reference-name dictionary (open addressing, power-of-two capacity)
   const DictEntry* dict; uint32_t dictMask;
@@ -59,10 +64,9 @@ struct AnnoView {
   const uint32_t* bktRowOff; const uint8_t* bktFlags;       // bit0 junction, bit1 .inv-strand
   const int32_t* bktRefId;          // identity of the bucket's reference id after BedRecord.java:154-176 (.inv-strand and version stripped)
   int32_t nBucket;
-  const int32_t* rowStart; const int32_t* rowEnd; const int32_t* rowMaxEnd; const int32_t* rowExon;
-  const uint8_t* rowFlags;          // bit0 genomic row (bucket name == exon chromosome), bits1-2 row strand (0 '+', 1 '-', 2 other)
+  const RowA* row;                  // rows of a bucket sorted by start; maxEnd = running maximum of end (the join's search key)
   // distinct exons
-  const int32_t* exChr; const int32_t* exStart; const int32_t* exEnd; const uint8_t* exStrand;   // exChr <= -2: tr- exon of transcript -2 - exChr
+  const ExonA* ex;
   int32_t nExon; int32_t nTrChr;    // nTrChr: number of distinct tr- chromosomes (0: the annotation has no tr- exons)
   // exon -> feature lists per mode; junction entries carry bit31 = "row also in exon_junction_transcript.map"
   const uint32_t* featOff[3]; const uint32_t* feat[3]; int32_t nFeat[3];

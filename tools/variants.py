@@ -34,6 +34,8 @@ def main():
     ap.add_argument("--reads", type=int, default=25_000_000)
     ap.add_argument("--layout", default="se")
     ap.add_argument("--genes", type=int, default=60000)
+    ap.add_argument("--knobs", default="", help="comma-separated worldgen annotation knobs, e.g. ld=0,tr=0,inv=0,ver=0,ver2=0,scaf=0 (the round-1 world)")
+    ap.add_argument("--only", default="", help="comma-separated variant names to run (default: all)")
     args = ap.parse_args()
     import torch
     sys.path.insert(0, ROOT)
@@ -41,6 +43,11 @@ def main():
     work = os.path.join(tempfile.gettempdir(), "eqp_variants")
     os.makedirs(work, exist_ok=True)
     b.build_tools()
+    if args.knobs:
+        work = os.path.join(work, "knobs_" + args.knobs.replace(",", "_").replace("=", ""))
+        os.makedirs(os.path.join(work, "anno"), exist_ok=True)
+        if not os.path.exists(os.path.join(work, "anno", "world.seed")):
+            subprocess.run([b.WORLDGEN_BIN, "anno", os.path.join(work, "anno"), "76", str(args.genes)] + args.knobs.split(","), check=True, stdout=subprocess.DEVNULL)
     anno = bench.make_annotation(b, work, args.genes)
     dirs = bench.generate_blocks(b, anno, os.path.join(work, "chunk"), 1001, 1, args.reads, args.layout, os.cpu_count() or 1)
     host = bench.load_blocks_pinned(torch, dirs, args.layout)
@@ -48,7 +55,7 @@ def main():
     torch.cuda.synchronize()
     dargs = [(d.data_ptr(), d.numel()) for d in dev]
     libs = [("product", b.LIB_PATH)] + [(os.path.basename(p)[12:-3], p) for p in sorted(glob.glob(os.path.join(VDIR, "libeqpcount_*.so")))]
-    runs = [(n, p, f) for n, p in libs for f in ("0", "1")]
+    runs = [(n, p, f) for n, p in libs for f in ("0", "1") if not args.only or (n + ("+fused" if f == "1" else "")) in args.only.split(",")]
     for name, path, fused in runs:
         os.environ["EQP_FUSED"] = fused
         name = name + ("+fused" if fused == "1" else "")
