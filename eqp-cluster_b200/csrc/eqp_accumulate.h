@@ -112,17 +112,17 @@ EQP_HD_CALL bool keys_equal(const HitX* hx, const Aln& a, uint64_t ka, const Aln
 EQP_HD void alignment_build(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, uint32_t a) {
   uint32_t b0 = C.alnBlk[a], b1 = C.alnBlk[a + 1];
   uint32_t k = C.hitCnt[b0], e = C.hitCnt[b1];                           // hits are grouped by block, blocks by alignment
-  Aln& al = V.alns[a]; al.hit0 = al.hit1 = al.split = 0; al.flags = 0; al.repr = a; al.key = 0; al.next = 0xFFFFFFFFu;
-  if (k == e) return;
+  Aln al{}; al.repr = a; al.next = 0xFFFFFFFFu;                          // assembled in registers, stored once (48 bytes = three 16-byte stores)
+  if (k == e) { V.alns[a] = al; return; }
   uint32_t frag = C.base + C.blocks[b0].slot;
-  for (uint32_t i = k + 1; i < e; i++) {                                 // insertion sort by (readIdx, readStart, eRefStart, eRefEnd, strand, row)
+  for (uint32_t i = k + 1; i < e; i++) {                                 // insertion sort by (readIdx, readStart, eRefStart, eRefEnd, strand, row); join_block emits every block's hits in that order
     Hit cur = C.hits[i]; RecKey ck = rec_key(A, C, cur); uint32_t j = i;
     while (j > k) { RecKey pk = rec_key(A, C, C.hits[j - 1]); int c = rec_cmp(pk, ck); if (c < 0 || (c == 0 && pk.row <= ck.row)) break; C.hits[j] = C.hits[j - 1]; j--; }
-    C.hits[j] = cur;
+    if (j != i) C.hits[j] = cur;
   }
   uint32_t split = k; while (split < e && C.blocks[C.hits[split].block].readIdx == 1) split++;
   al.hit0 = k; al.split = split; al.hit1 = e;
-  const Block& fb = C.blocks[C.hits[k].block];
+  const Block fb = C.blocks[C.hits[k].block];
   uint8_t fl = fb.paired ? 1 : 0;
   for (uint32_t i = k; i < e; i++) if ((C.blocks[C.hits[i].block].paired ? 1 : 0) != (fl & 1)) raise(C.err, DERR_INCONSISTENT, frag);
   al.start1 = al.start2 = 0x7fffffff; al.nIv1 = al.nIv2 = 0; al.maxField1 = al.maxField2 = -1;
@@ -131,8 +131,9 @@ EQP_HD void alignment_build(const AnnoView& A, const ChunkView& C, const CountVi
   if (e > split) { build_half(A, C, V, P, split, e, 2, al.start2, al.nIv2, al.maxField2, tr2, frag); fl |= 4; }
   if (!(fl & 1)) fl |= (uint8_t)(((fl & 2) ? 1 : 2) << 3);
   if (!(fl & 1) && (fl & 2) && (fl & 4)) raise(C.err, DERR_INCONSISTENT, frag);     // single-read alignment with both read indices
-  al.flags = fl; al.tr = (uint8_t)(tr1 | (tr2 << 3)); al.pad[0] = al.pad[1] = 0;
+  al.flags = fl; al.tr = (uint8_t)(tr1 | (tr2 << 3));
   al.key = alignment_key_inl(V.hx, al, false);
+  V.alns[a] = al;
 }
 
 EQP_HD uint64_t hit_group_key(const HitX& x) { return ((uint64_t)((x.flags & 1) ? 0 : 1) << 40) | ((uint64_t)x.grp << 24) | ((uint64_t)x.half << 16) | x.ivRank; }

@@ -32,7 +32,7 @@ struct CountView {
 
 struct RecKey { int readIdx, readStart, eStart, eEnd, eStrand, row; };
 EQP_HD RecKey rec_key(const AnnoView& A, const ChunkView& C, const Hit& h) {
-  const Block& b = C.blocks[h.block]; RecKey k;
+  const Block b = C.blocks[h.block]; RecKey k;
   k.readIdx = b.readIdx; k.readStart = b.start + 1; k.row = h.row;
   const RowA r = A.row[h.row]; const ExonA e = A.ex[r.exon()];
   int es = r.start + 1, ee = r.end;
@@ -74,10 +74,10 @@ EQP_HD void build_half(const AnnoView& A, const ChunkView& C, const CountView& V
   }
   const Block& b0 = C.blocks[C.hits[h0].block];
   bool genomic = A.row[C.hits[h0].row].flags() & 1; bool junction = A.bktFlags[b0.bucket] & 1, inv = A.bktFlags[b0.bucket] & 2;
-  int i = -1, iJ = -1; int prevExon = -1; const Block* prevBlk = nullptr; bool anyTr = false, anyLd = false; int trSign = 1;
+  int i = -1, iJ = -1; int prevExon = -1; Block prevCopy{}; const Block* prevBlk = nullptr; bool anyTr = false, anyLd = false; int trSign = 1;
   for (uint32_t k = h0; k < h1; k++) {
     HitX& x = V.hx[k]; if (!(x.flags & 1)) continue;
-    const Hit& h = C.hits[k]; const Block& b = C.blocks[h.block]; const RowA row = A.row[h.row]; const int ex = row.exon(); const ExonA exn = A.ex[ex];
+    const Hit h = C.hits[k]; const Block b = C.blocks[h.block]; const RowA row = A.row[h.row]; const int ex = row.exon(); const ExonA exn = A.ex[ex];
     if (((row.flags() & 1) != 0) != genomic) raise(C.err, DERR_INCONSISTENT, frag);                 // "Change of BED record type"
     if (prevBlk && b.strand != prevBlk->strand) raise(C.err, DERR_INCONSISTENT, frag);               // differing strand
     const bool tr = exn.chr <= -2;                                       // tr- transcript exon (Exon.java:230-301): coordinates on the transcript
@@ -135,9 +135,10 @@ EQP_HD void build_half(const AnnoView& A, const ChunkView& C, const CountView& V
       int thr = P.overlap[m] < (exE - exS + 1) ? P.overlap[m] : (exE - exS + 1);
       if (c && h.overlap >= thr) conf |= (uint8_t)(4 << m);              // GenomicInterval.java:144
     }
-    x.gs = gs; x.ge = ge; x.chr = exn.chr; x.ivField = (int8_t)fieldIdx; x.ivFieldJ = (int8_t)fieldJ; x.exon = ex;
-    x.flags = (uint8_t)(1 | (genomic ? 2 : 0) | conf | (ivStrand == '-' ? 32 : 0));
-    prevBlk = &b; prevExon = ex;
+    { HitX y; y.gs = gs; y.ge = ge; y.chr = exn.chr; y.ivField = (int8_t)fieldIdx; y.ivFieldJ = (int8_t)fieldJ; y.ivRank = 0; y.exon = ex;
+      y.flags = (uint8_t)(1 | (genomic ? 2 : 0) | conf | (ivStrand == '-' ? 32 : 0)); y.half = (uint8_t)half; y.grp = 0;
+      x = y; }                                                           // one 24-byte store
+    prevCopy = b; prevBlk = &prevCopy; prevExon = ex;
   }
   // With a tr- record the junction run numbers the later records differently, and the adapted coordinates of a record with a length
   // difference depend on its number (:417-452): the two runs would then need different coordinates.  Not handled.

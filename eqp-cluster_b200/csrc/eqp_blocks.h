@@ -115,14 +115,15 @@ EQP_HD void fragment_blocks(const AnnoView& A, const ChunkView& C, uint32_t slot
         int sumRead; bool bad; uint32_t firstOfRec = nb;
         int nSeg = record_segments(R, li, [&](int seg, int off, int refLen, int readLen, int insSoft, int del) {
           if (readLen <= 0) return;
-          if (fill) {
-            Block& b = C.blocks[bo + nb];
+          if (fill) {                                                    // assembled in registers, stored as one 32-byte struct
+            Block b;
             b.bucket = bucket; b.start = bedStart + off; b.end = bedStart + off + refLen; b.L = (uint16_t)readLen; b.I = (uint16_t)insSoft; b.D = (uint16_t)del;
             b.seg = (uint8_t)seg; b.maxSeg = 0; b.aln = na; b.readIdx = ridx; b.paired = paired; b.strand = strand; b.pad = 0; b.slot = slot;
+            C.blocks[bo + nb] = b;
           }
           nb++;
         }, sumRead, bad);
-        if (fill) for (uint32_t k = firstOfRec; k < nb; k++) C.blocks[bo + k].maxSeg = (uint8_t)(nSeg - 1);
+        if (fill && nSeg > 1) for (uint32_t k = firstOfRec; k < nb; k++) C.blocks[bo + k].maxSeg = (uint8_t)(nSeg - 1);
         if (bad) raise(C.err, DERR_CIGAR_OP, C.base + slot);
         if (sumRead != R.seqLen[li]) raise(C.err, DERR_CIGAR_LEN, C.base + slot);
       }
@@ -161,9 +162,9 @@ EQP_HD uint32_t join_block(const AnnoView& A, const Block& b, Hit* out, uint32_t
     if (re > b.start && (!sameStrand || ((r.flags() >> 1) & 3u) == wantStrand)) {
       int32_t ov = (re < b.end ? re : b.end) - (r.start > b.start ? r.start : b.start);
 #ifdef EQP_VAR_DESC_HITS
-      if (ov >= 1) { if (out) { Hit& o = out[n]; o.block = blockIdx; o.row = k; o.overlap = ov; } n++; }
+      if (ov >= 1) { if (out) out[n] = Hit{blockIdx, k, ov, 0}; n++; }
 #else
-      if (ov >= 1) { if (out) { Hit& o = out[nOut - 1 - n]; o.block = blockIdx; o.row = k; o.overlap = ov; } n++; }
+      if (ov >= 1) { if (out) out[nOut - 1 - n] = Hit{blockIdx, k, ov, 0}; n++; }
 #endif
     }
   }

@@ -136,7 +136,7 @@ struct CudaBackend {
   explicit CudaBackend(cudaStream_t s, int sms) : stream(s), nSm(sms > 0 ? sms : EQP_NUM_SMS_DEFAULT), mainStream(s) {}
   ~CudaBackend() { finish_timing(); release(); }
   // EQP_STAGE_TIMING=1: CUDA-event time between consecutive stage() marks on the main stream, printed to stderr per chunk
-  bool fused() const { const char* e = getenv("EQP_FUSED"); return e && e[0] == '1'; }   // development switch (tools/variants.py)
+  static bool env_flag(const char* name) { const char* e = getenv(name); return e && e[0] == '1'; }
   bool timing = getenv("EQP_STAGE_TIMING") != nullptr; std::vector<std::pair<const char*, cudaEvent_t>> marks;
   void stage(const char* name) {
     if (!timing) return;

@@ -71,7 +71,7 @@ EQP_HD void counter_add64(unsigned long long* p, uint64_t v) {          // v < 2
 // stage tags: they only name the kernels (profiler listings)
 namespace st { struct misc; struct frag_table; struct frag_stats; struct select_tj_weights; struct select_stage1; struct select_stage2; struct seen_refs; struct junction_active;
                struct blocks_count; struct blocks_fill; struct join_count; struct join_fill; struct work_class; struct alignment_build; struct work_lists; struct fragment_adjust;
-               struct fragment_weight; struct fragment_weight_gene; struct fragment_count; struct fragment_count_large; struct fragment_fused; }
+               struct fragment_weight; struct fragment_weight_gene; struct fragment_count; struct fragment_count_large; struct fragment_weight_count; }
 
 struct ChunkResult {
   std::vector<double> counts[3]; std::vector<unsigned long long> fixed[3]; std::vector<uint8_t> junctionActive;
@@ -258,7 +258,10 @@ struct Pipeline {
     // neighbouring memory.  Keys sort descending: the expensive fragments start first.
     { const ChunkView C = this->C; be.template launch<st::work_class>(N, [=] EQP_LAMBDA(uint64_t s) {
         uint32_t h = C.hitCnt[C.blkOff[s + 1]] - C.hitCnt[C.blkOff[s]], na = C.alnOff[s + 1] - C.alnOff[s], key = 0;
-#ifdef EQP_VAR_COARSE_KEYS
+#ifdef EQP_VAR_ONE_CLASS
+        if (h) key = 1;
+        if (0)
+#elif defined(EQP_VAR_COARSE_KEYS)
         if (h) { uint32_t c = 0, x = h; while (x) { c++; x >>= 1; } key = c; }
         if (0)
 #else
@@ -269,17 +272,15 @@ struct Pipeline {
     uint32_t nWork = be.order_by_work(work, N, perm);
     { const ChunkView C = this->C; const CountView V = this->V;
       be.stage("order");
-      const bool fused = be.fused();
-      if (!fused) {
       be.template launch<st::alignment_build>(nAln, [=] EQP_LAMBDA(uint64_t a) { alignment_build(A, C, V, P, (uint32_t)a); });
       be.stage("alignment-build");
       // the rare shapes (transcript exon longer than its genome exon; tr- exons) go through work lists built on the device
       be.template launch<st::work_lists>(nWork, [=] EQP_LAMBDA(uint64_t i) { uint32_t s = perm[i]; if (C.slotLd[s]) list_push(listCnt, listLd, s); if (C.slotTr[s]) list_push(listCnt + 1, listTr, s); });
       be.template launch_counted<st::fragment_adjust>(listCnt, N, [=] EQP_LAMBDA(uint64_t i) { fragment_adjust(A, C, V, listLd[i]); });                         // a17 before the dedupe
-      be.template launch_occ<st::fragment_weight, 4>(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
-      if (V.alnG) be.template launch_counted<st::fragment_weight_gene>(listCnt + 1, N, [=] EQP_LAMBDA(uint64_t i) { fragment_weight_gene(C, V, listTr[i]); });      // gene-run keys of tr- fragments
+      const bool fuseWC = be.env_flag("EQP_FUSE_WC");                     // development switch (tools/variants.py): weight + count in one thread per fragment
+      if (!fuseWC) be.template launch_occ<st::fragment_weight, 4>(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
+      if (V.alnG && !fuseWC) be.template launch_counted<st::fragment_weight_gene>(listCnt + 1, N, [=] EQP_LAMBDA(uint64_t i) { fragment_weight_gene(C, V, listTr[i]); });      // gene-run keys of tr- fragments
       be.stage("fragment-weight");
-      }
       // the three counting runs of one fragment back to back in one thread: runs two and three find the fragment's alignments and
       // hits in cache instead of paying the DRAM latency chain again (the runs were latency-bound as three concurrent kernels).
       // First launch: small per-thread tables; (fragment, run) pairs that overflow them are queued for a second launch with the large tables.
@@ -289,26 +290,20 @@ struct Pipeline {
         counter_add(&V.stats[m * 3 + 0], r ? 1u : 0u); counter_add(&V.stats[m * 3 + 1], r == 1 ? 1u : 0u); counter_add(&V.stats[m * 3 + 2], r == 2 ? 1u : 0u);
         counter_add64(&V.stats[10 + m], ws);
       };
-      if (!fused) be.template launch<st::fragment_count>(nWork, [=] EQP_LAMBDA(uint64_t i) {
+      // (A variant that fused alignment_build + weight + count into one thread per fragment ran 10x slower, 217-266 ms against 67 ms for the three
+      // kernels at 25M reads, profiles/r03d_variants_fused_25Mreads.jsonl: the per-alignment kernel has 2.7x the parallelism and coalesced access.)
+      if (fuseWC) be.template launch_occ<st::fragment_weight_count, 3>(nWork, [=] EQP_LAMBDA(uint64_t i) {
         uint32_t s = perm[i];
+        fragment_weight(A, C, V, P, s);
+        if (V.alnG && C.slotTr[s]) fragment_weight_gene(C, V, s);
         for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) {
           uint64_t ws; int r = fragment_count<EQP_FS_SMALL, EQP_FT_SMALL>(A, C, V, P, m, s, ws);
           if (r < 0) { uint32_t k = atomic_inc_u32(bigCnt); if (k < N) bigList[k] = s * 4u + (uint32_t)m; else raise(C.err, DERR_CAPACITY, C.base + s); r = 0; ws = 0; }
           tally(m, r, ws);
         }
       });
-      // Fused variant: one thread takes a fragment from its hits to its counts — alignment_build for each of its alignments, a17 and the gene-run
-      // dedupe when the fragment needs them, the dedupe / weight stage, the three counting runs — so that HitX / Aln are re-read from the thread's
-      // own cache lines instead of from HBM by three later kernels.  The work keys put fragments with the same (alignments, hits) in a warp.
-#ifndef EQP_FUSED_OCC
-#define EQP_FUSED_OCC 3
-#endif
-      else be.template launch_occ<st::fragment_fused, EQP_FUSED_OCC>(nWork, [=] EQP_LAMBDA(uint64_t i) {
+      else be.template launch<st::fragment_count>(nWork, [=] EQP_LAMBDA(uint64_t i) {
         uint32_t s = perm[i];
-        for (uint32_t a = C.alnOff[s]; a < C.alnOff[s + 1]; a++) alignment_build(A, C, V, P, a);
-        if (C.slotLd[s]) fragment_adjust(A, C, V, s);
-        fragment_weight(A, C, V, P, s);
-        if (V.alnG && C.slotTr[s]) fragment_weight_gene(C, V, s);
         for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) {
           uint64_t ws; int r = fragment_count<EQP_FS_SMALL, EQP_FT_SMALL>(A, C, V, P, m, s, ws);
           if (r < 0) { uint32_t k = atomic_inc_u32(bigCnt); if (k < N) bigList[k] = s * 4u + (uint32_t)m; else raise(C.err, DERR_CAPACITY, C.base + s); r = 0; ws = 0; }

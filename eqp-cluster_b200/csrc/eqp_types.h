@@ -101,7 +101,7 @@ struct FragFile {                  // record range + presence bits of one fragme
   uint8_t bits;                    // bit0 present, bit1 mapped idx1, bit2 mapped idx2, bit3 has idx1 rec, bit4 has idx2 rec, bit5 mapped idx0
 };
 
-struct Block {                     // one aligned block of the combined BED (a10), 32 bytes
+struct alignas(16) Block {         // one aligned block of the combined BED (a10), 32 bytes: two 16-byte loads / stores
   int32_t bucket; int32_t start, end;              // 0-based half-open, in the bucket's coordinates
   uint16_t L, I, D; uint8_t seg, maxSeg;           // -L -I -D -F<seg>-<maxSeg>
   uint32_t aln;                                    // alignment number within the fragment (A-counter - 1)
@@ -109,9 +109,9 @@ struct Block {                     // one aligned block of the combined BED (a10
   uint32_t slot;                                   // fragment slot the block belongs to
 };
 
-struct Hit { uint32_t block; int32_t row; int32_t overlap; };   // a11 output (12 bytes)
+struct alignas(16) Hit { uint32_t block; int32_t row; int32_t overlap; uint32_t pad; };   // a11 output, padded to one 16-byte load / store
 
-struct HitX {                      // per hit, after the per-alignment sort/dedupe (a12-a16), 24 bytes
+struct alignas(8) HitX {            // per hit, after the per-alignment sort/dedupe (a12-a16), 24 bytes = three 8-byte words
   int32_t gs, ge;                  // genomic interval, 1-based closed
   int32_t chr;                     // chromosome index of the exon
   int8_t ivField, ivFieldJ;        // field index of the (kept) interval this record belongs to; ivFieldJ: the same in the junction run, where
@@ -124,7 +124,7 @@ struct HitX {                      // per hit, after the per-alignment sort/dedu
                                    // among the non-tr intervals of its half (0xFFFF for a tr- interval), see eqp_accumulate.h
 };
 
-struct Aln {                       // one WeightObjectAlignment (a15-a19), 48 bytes
+struct alignas(16) Aln {            // one WeightObjectAlignment (a15-a19), 48 bytes
   uint32_t hit0, split, hit1;      // hits [hit0,split) read 1, [split,hit1) read 2
   uint32_t repr;                   // global index of the first alignment of the fragment with the same key
   uint64_t key;

@@ -31,7 +31,7 @@ struct HostBackend {
     }
   }
   void stage(const char*) {}
-  bool fused() const { const char* e = getenv("EQP_FUSED"); return e && e[0] == '1'; }
+  static bool env_flag(const char* name) { const char* e = getenv(name); return e && e[0] == '1'; }
   static const bool kFusedDecode = false;
   void decode_fused(const AnnoView&, SamView&, uint8_t*&, const char*, uint64_t, uint32_t*, uint32_t*) {}
   void fork() {}

@@ -316,7 +316,7 @@ def test_streamed_chunk_gives_the_same_counts(world, ctx):
 
 BLOCK = np.dtype([("bucket", "<i4"), ("start", "<i4"), ("end", "<i4"), ("L", "<u2"), ("I", "<u2"), ("D", "<u2"), ("seg", "u1"), ("maxSeg", "u1"),
                   ("aln", "<u4"), ("readIdx", "u1"), ("paired", "u1"), ("strand", "u1"), ("pad", "u1"), ("slot", "<u4")])
-HIT = np.dtype([("block", "<u4"), ("row", "<i4"), ("overlap", "<i4")])
+HIT = np.dtype([("block", "<u4"), ("row", "<i4"), ("overlap", "<i4"), ("pad", "<u4")])
 
 
 def test_selection_blocks_and_join_taps(world, ctx):

@@ -55,10 +55,12 @@ def main():
     torch.cuda.synchronize()
     dargs = [(d.data_ptr(), d.numel()) for d in dev]
     libs = [("product", b.LIB_PATH)] + [(os.path.basename(p)[12:-3], p) for p in sorted(glob.glob(os.path.join(VDIR, "libeqpcount_*.so")))]
-    runs = [(n, p, f) for n, p in libs for f in ("0", "1") if not args.only or (n + ("+fused" if f == "1" else "")) in args.only.split(",")]
-    for name, path, fused in runs:
-        os.environ["EQP_FUSED"] = fused
-        name = name + ("+fused" if fused == "1" else "")
+    runs = [(n + e, p, e) for n, p in libs for e in ("", "+EQP_FUSE_WC") if not args.only or (n + e) in args.only.split(",")]
+    for name, path, env in runs:
+        for k in ("EQP_FUSE_WC",):
+            os.environ.pop(k, None)
+        if env:
+            os.environ[env[1:]] = "1"
         r, w = os.pipe()
         saved = os.dup(2)
         ctx = eqp.CountContext(0, path).load_annotation(anno)
