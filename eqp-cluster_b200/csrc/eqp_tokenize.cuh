@@ -50,6 +50,12 @@ __device__ __forceinline__ uint32_t tk_smem_addr(const void* p) { return (uint32
 // borrow across bytes.  The multiply moves the marker of byte k (bit 3 for tab, bit 7 for newline) to bit 24+k / 28+k: all 32
 // partial-product positions are distinct, so nothing carries.
 __device__ __forceinline__ uint32_t tk_marks4(uint32_t w) {
+#ifdef EQP_VAR_OLD_MARKS
+  uint32_t xn = w ^ 0x0a0a0a0au, xt = w ^ 0x09090909u;
+  uint32_t zn0 = ~(((xn & 0x7f7f7f7fu) + 0x7f7f7f7fu) | xn | 0x7f7f7f7fu);
+  uint32_t zt0 = ~(((xt & 0x7f7f7f7fu) + 0x7f7f7f7fu) | xt | 0x7f7f7f7fu);
+  return (zn0 | (zt0 >> 4)) * 0x00204081u;
+#endif
   uint32_t x = w ^ 0x08080808u;
   uint32_t t = (x | 0x80808080u) - 0x04040404u;                        // top bit of a byte clear <=> its low 7 bits are below 4
   uint32_t m = ~(t | x) & 0x80808080u;
@@ -227,7 +233,9 @@ k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamVi
   uint32_t fmin = 0xFFFFFFFFu, fmax = 0;                             // fragment id range of this thread's records
   // One copy of the parser in the instruction stream: ncu showed the loop peeled into two ~4500-instruction bodies (144 KB of hot
   // code, "no instruction" stalls of 1.3-1.7 warps per issue slot); a tile holds ~90 lines for 128 threads, so the loop rarely turns twice.
+#ifndef EQP_VAR_PEEL
 #pragma unroll 1
+#endif
   for (uint32_t j = tid; j < nOwned; j += TK_THREADS) {
     int s = (int)sh.nlPos[j] + 1;                                    // staged position of the line's first byte
     uint64_t g = (uint64_t)(v0 + s - a0);

@@ -51,6 +51,8 @@ def main():
     anno = bench.make_annotation(b, work, args.genes)
     dirs = bench.generate_blocks(b, anno, os.path.join(work, "chunk"), 1001, 1, args.reads, args.layout, os.cpu_count() or 1)
     host = bench.load_blocks_pinned(torch, dirs, args.layout)
+    import shutil
+    shutil.rmtree(os.path.join(work, "chunk"), ignore_errors=True)       # 45 GB of text per chunk: two worlds on one disk do not fit
     dev = [h.cuda() for h in host]
     torch.cuda.synchronize()
     dargs = [(d.data_ptr(), d.numel()) for d in dev]
@@ -64,7 +66,13 @@ def main():
         r, w = os.pipe()
         saved = os.dup(2)
         ctx = eqp.CountContext(0, path).load_annotation(anno)
-        ctx.count_chunk(*dargs, on_device=True, fetch=False)
+        try:
+            ctx.count_chunk(*dargs, on_device=True, fetch=False)
+        except eqp.EqpError as e:
+            print(json.dumps({"variant": name, "error": str(e)}), flush=True)
+            os.close(r); os.close(w); os.close(saved)
+            ctx.close()
+            continue
         os.environ["EQP_STAGE_TIMING"] = "1"
         ms = []
         os.dup2(w, 2)
