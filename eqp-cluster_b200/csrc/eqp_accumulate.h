@@ -182,17 +182,17 @@ EQP_HD uint32_t dedupe_fragment(const CountView& V, uint32_t a0, uint32_t a1) {
 }
 
 EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountView& V, const RunParams& P, uint32_t slot) {
-  uint32_t b0 = C.blkOff[slot], b1 = C.blkOff[slot + 1];
-  V.a20[slot] = 0; V.nFinal[slot] = 0;
-  if (b0 == b1 || C.hitCnt[b0] == C.hitCnt[b1]) return;
-  uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1]; const uint32_t nA = a1 - a0;
+  (void)A; (void)P;
+  const SlotPack sp = V.pack[slot];
+  if (sp.hit0 == sp.hit1) return;                                         // a20 / nFinal stay 0
+  uint32_t a0 = sp.aln0, a1 = sp.aln1; const uint32_t nA = a1 - a0;
   const uint32_t a20 = dedupe_fragment<false>(V, a0, a1);
   // tag every hit with its representative (index within the fragment) and with the representative's half it merges into
   // (combineExons pairs mate-swapped duplicates crosswise, WeightObjectAlignment.java:312-337): a22-a25 then read the
   // fragment's hits as one flat range instead of walking duplicate chains.  Fragments with tr- exon hits are left untagged: their
   // gene run has its own dedupe (fragment_weight_gene) and HitX::grp keeps the non-tr ordinal of the interval.
   if (nA > 0xFFFFu) { raise(C.err, DERR_CAPACITY, C.base + slot); return; }
-  const bool trFrag = C.slotTr[slot] != 0;
+  const bool trFrag = (sp.g & SP_TR) != 0;
   if (!trFrag) for (uint32_t a = a0; a < a1; a++) {
     const Aln& al = V.alns[a]; if (al.hit0 == al.hit1) continue;
     bool sw = al.repr != a && (al.flags & 32); uint16_t g = (uint16_t)(al.repr - a0);
@@ -201,7 +201,7 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
   // small fragments: regroup the hits by (representative, half, interval), stable, dropped duplicates last: the counting runs
   // then stream each fragment's hits once.  (hx is only indexed through Aln.hit0.. before this point; large fragments keep
   // their order and walk the duplicate chains.)
-  if (!trFrag) { uint32_t h0 = C.hitCnt[b0], h1 = C.hitCnt[b1];
+  if (!trFrag) { uint32_t h0 = sp.hit0, h1 = sp.hit1;
     bool sorted = true; uint64_t prev = 0;
     if (h1 - h0 <= EQP_FLAT_SCAN) for (uint32_t i = h0; i < h1; i++) { uint64_t k = hit_group_key(V.hx[i]); sorted &= k >= prev; prev = k; }   // independent loads
     if (h1 - h0 <= EQP_FLAT_SCAN && !sorted)
@@ -210,24 +210,28 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
         while (j > h0 && hit_group_key(V.hx[j - 1]) > ck) { V.hx[j] = V.hx[j - 1]; j--; }
         if (j != i) V.hx[j] = cur;
       } }
-  V.a20[slot] = a20;
-  // final.wgt entry: BED weight (single-read, read index 1, n = a20) vs genome SAM weight, T+J entry as class arbiter
-  FragStat bed{}; bed.nSr1 = (uint16_t)(a20 > 65535 ? 65535 : a20); bed.flags = FS_EXISTS | (1 << 2);
-  const FragStat& g = C.st[FILE_G][slot];
-  uint32_t n = a20;
-  if (P.genomic) n = (uint32_t)fe_n(C.st[FILE_T][slot]);                  // ComputeCounts -w <ComputeReadWeightsSam output> (compute-genomic-counts.sh:1000-1010)
-  else if (g.flags & FS_EXISTS) {
-    uint32_t ax = C.auxSlot[slot]; int cm = 0;
-    if (ax != 0xFFFFFFFFu) cm = fe_cmp_mult(C.stTJ[ax], g);               // aux.compareMultiplicity(entry2), CombineReadWeightFiles.java:192-195
-    if (cm == 1) n = a20; else if (cm == -1) n = (uint32_t)fe_n(g); else n = (int)a20 >= fe_n(g) ? a20 : (uint32_t)fe_n(g);
-  }
-  V.nFinal[slot] = n;
+  // final.wgt entry: BED weight (single-read, read index 1, n = a20) against the genome SAM weight with the T+J entry as class arbiter
+  // (CombineReadWeightFiles.java:192-214); how the two combine does not depend on a20 and was worked out in slot order (slot_weight_mode)
+  const uint32_t gN = sp.g & 0xFFFFFFu, how = (sp.g >> 24) & 3u;
+  const uint32_t n = how == SP_A20 ? a20 : how == SP_GENOME ? gN : (a20 >= gN ? a20 : gN);
+  V.pack[slot].a20 = a20; V.pack[slot].nFinal = n;
+}
+// the part of the final weight that does not depend on a20: numAlignments of the genome entry and how it combines (SlotPack::g)
+EQP_HD uint32_t slot_weight_mode(const ChunkView& C, const RunParams& P, uint32_t slot) {
+  if (P.genomic) { uint32_t n = (uint32_t)fe_n(C.st[FILE_T][slot]); return (n > 0xFFFFFFu ? 0xFFFFFFu : n) | ((uint32_t)SP_GENOME << 24); }   // ComputeCounts -w <ComputeReadWeightsSam output> (compute-genomic-counts.sh:1000-1010)
+  const FragStat g = C.st[FILE_G][slot];
+  if (!(g.flags & FS_EXISTS)) return (uint32_t)SP_A20 << 24;
+  uint32_t ax = C.auxSlot[slot]; int cm = 0;
+  if (ax != 0xFFFFFFFFu) cm = fe_cmp_mult(C.stTJ[ax], g);                   // aux.compareMultiplicity(entry2), CombineReadWeightFiles.java:192-195
+  uint32_t n = (uint32_t)fe_n(g); if (n > 0xFFFFFFu) n = 0xFFFFFFu;
+  return n | ((uint32_t)(cm == 1 ? SP_A20 : cm == -1 ? SP_GENOME : SP_MAX) << 24);
 }
 
 // second dedupe of a fragment with tr- exon hits, under the gene run's keys (a20 can differ between the runs)
 EQP_HD void fragment_weight_gene(const ChunkView& C, const CountView& V, uint32_t slot) {
-  if (V.a20[slot] == 0) { V.a20G[slot] = 0; return; }
-  V.a20G[slot] = dedupe_fragment<true>(V, C.alnOff[slot], C.alnOff[slot + 1]);
+  (void)C;
+  const SlotPack sp = V.pack[slot];
+  V.pack[slot].a20G = sp.a20 == 0 ? 0u : dedupe_fragment<true>(V, sp.aln0, sp.aln1);
 }
 
 // ---- a17 for a fragment with a positive lengthDifference: WeightObject.adjustGenomicAlignments (:180-204) ->
@@ -439,12 +443,13 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
   typedef FeatSetT<FS_CAP> FeatSet;
   const bool retry = FS_CAP < EQP_FS_CAP;                                  // an overflow is not final
   wsum = 0;
-  const bool trFrag = C.slotTr[slot] != 0;
-  uint32_t a20 = trFrag && mode == MODE_GENE ? V.a20G[slot] : V.a20[slot];
-  if (V.a20[slot] == 0) return 0;
-  uint32_t frag = C.base + slot; uint32_t a0 = C.alnOff[slot], a1 = C.alnOff[slot + 1];
-  const uint32_t hEnd = C.hitCnt[C.blkOff[slot + 1]];                    // end of the fragment's hit range
-  double w = 1.0 / (double)V.nFinal[slot];
+  const SlotPack sp = V.pack[slot];
+  const bool trFrag = (sp.g & SP_TR) != 0;
+  uint32_t a20 = trFrag && mode == MODE_GENE ? sp.a20G : sp.a20;
+  if (sp.a20 == 0) return 0;
+  uint32_t frag = C.base + slot; uint32_t a0 = sp.aln0, a1 = sp.aln1;
+  const uint32_t hEnd = sp.hit1;                                          // end of the fragment's hit range
+  double w = 1.0 / (double)sp.nFinal;
   if (w > 1.0 / (double)a20) w = 1.0 / (double)a20;                      // ComputeCounts.java:762-764
   if (!(w >= P.weightThreshold)) return 2;
   double addW = P.unweighted ? 1.0 : w;
@@ -466,7 +471,7 @@ EQP_HD int fragment_count(const AnnoView& A, const ChunkView& C, const CountView
       }
     }
   };
-  const uint32_t hBeg = C.hitCnt[C.blkOff[slot]];
+  const uint32_t hBeg = sp.hit0;
   if (hEnd - hBeg <= EQP_FLAT_SCAN && !trFrag) {
     // hits regrouped by fragment_weight: (representative, half, interval) runs, representatives in file order
     FeatSet fs; uint32_t i = hBeg;

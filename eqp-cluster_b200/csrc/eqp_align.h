@@ -20,11 +20,10 @@ struct IvAdj { int32_t ld, orig; };  // a17 scratch of an interval (kept at its 
 
 struct CountView {
   HitX* hx; Aln* alns;             // hx parallel to hits; alns indexed by alnOff[slot] + alignment number
-  AlnG* alnG; uint32_t* a20G;      // gene-run dedupe of fragments with tr- exon hits (null when the annotation has no tr- exons)
+  AlnG* alnG;                      // gene-run dedupe of fragments with tr- exon hits (null when the annotation has no tr- exons)
+  SlotPack* pack;                  // per slot: ranges, weight-stage inputs and outputs
   IvAdj* ivAdj;                    // parallel to hits; only touched for fragments with a positive length difference
   uint32_t* dedupTab; uint32_t* alnTail;   // a19 scratch: per-fragment representative table (2 per alignment, zeroed), chain tails
-  uint32_t* a20;                   // per slot: number of genomic alignments (0 = fragment not in the intersection)
-  uint32_t* nFinal;                // per slot: numAlignments of the final.wgt entry
   unsigned long long* acc[3];      // fixed-point accumulators per mode (nFeat entries)
   const uint8_t* junctionActive;   // per junction feature
   unsigned long long* stats;       // [mode*3 + {objects, included, excluded}], [9] = mapped fragments

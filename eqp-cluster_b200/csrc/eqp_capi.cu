@@ -462,8 +462,13 @@ int eqp_debug_fetch(eqp_ctx* ctx, const char* what, void* dst, size_t dstBytes, 
   else if (w == "weights:J") { src = pl.C.st[1]; bytes = N * sizeof(FragStat); }
   else if (w == "weights:G") { src = pl.C.st[2]; bytes = N * sizeof(FragStat); }
   else if (w == "weights:TJ") { src = pl.C.stTJ; bytes = N * sizeof(FragStat); }
-  else if (w == "weights:final") { src = pl.V.nFinal; bytes = N * 4; }
-  else if (w == "a20") { src = pl.V.a20; bytes = N * 4; }
+  else if (w == "weights:final" || w == "a20") {                            // one field of the per-slot SlotPack
+    bytes = N * 4; *nWritten = bytes; if (!dst) return EQP_OK;
+    if (dstBytes < bytes) return fail(ctx, EQP_ERR_ARG, "eqp_debug_fetch: buffer too small");
+    try { EQP_CUDA(cudaSetDevice(ctx->device)); std::vector<SlotPack> sp(N); if (N) ctx->be->to_host(sp.data(), pl.V.pack, N * sizeof(SlotPack));
+      uint32_t* o = (uint32_t*)dst; for (size_t i = 0; i < N; i++) o[i] = w == "a20" ? sp[i].a20 : sp[i].nFinal; return EQP_OK; }
+    catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+  }
   else if (w == "selection") { src = pl.C.setC; bytes = N * sizeof(SetDesc); }
   else if (w == "blocks") { src = pl.C.blocks; bytes = (size_t)pl.nBlocks * sizeof(Block); }
   else if (w == "hits") { src = pl.C.hits; bytes = (size_t)pl.nHits * sizeof(Hit); }

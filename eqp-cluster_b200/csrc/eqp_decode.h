@@ -285,8 +285,12 @@ EQP_HD void decode_record_t(const AnnoView& A, const SamView& S, uint32_t li, co
   store_record(S, li, parse_record_t(A, p, n, src), err);
 }
 
-// a real call on the device: the generic parser is the tokenizer kernel's cold path (lines longer than the overhang, crowded tiles)
-EQP_HD_CALL void decode_record(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, uint32_t* err) {
+#ifdef EQP_VAR_ONE_BODY
+EQP_HD_CALL
+#else
+EQP_HD
+#endif
+void decode_record(const AnnoView& A, const SamView& S, uint32_t li, const char* p, int n, uint32_t* err) {
   ScanSrc src; decode_record_t(A, S, li, p, n, src, err);
 }
 

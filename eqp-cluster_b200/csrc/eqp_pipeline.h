@@ -241,14 +241,13 @@ struct Pipeline {
     // ---- a12-a25
     V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
     V.dedupTab = be.template alloc<uint32_t>(2 * (uint64_t)nAln + 2); be.memset(V.dedupTab, 0, (2 * (uint64_t)nAln + 2) * 4); V.alnTail = be.template alloc<uint32_t>((uint64_t)nAln + 1);
-    V.a20 = be.template alloc<uint32_t>((uint64_t)N + 1); V.nFinal = be.template alloc<uint32_t>((uint64_t)N + 1);
+    V.pack = be.template alloc<SlotPack>((uint64_t)N + 1);
     V.ivAdj = be.template alloc<IvAdj>((uint64_t)nHits + 1);                // a17 scratch, touched for fragments with a positive length difference only
-    V.alnG = nullptr; V.a20G = nullptr;
-    if (A.nTrChr > 0) { V.alnG = be.template alloc<AlnG>((uint64_t)nAln + 1); V.a20G = be.template alloc<uint32_t>((uint64_t)N + 1); }
+    V.alnG = nullptr;
+    if (A.nTrChr > 0) V.alnG = be.template alloc<AlnG>((uint64_t)nAln + 1);
     uint32_t* listLd = be.template alloc<uint32_t>((uint64_t)N + 1); uint32_t* listTr = be.template alloc<uint32_t>((uint64_t)N + 1);
     uint32_t* listCnt = scal + 96; be.memset(listCnt, 0, 8);                // [0] fragments with a positive length difference, [1] with tr- exon hits
     for (int m = 0; m < 3; m++) { V.acc[m] = accOut[m] ? accOut[m] : be.template alloc<unsigned long long>((uint64_t)A.nFeat[m] + 1); be.memset(V.acc[m], 0, ((uint64_t)A.nFeat[m] + 1) * 8); }
-    be.memset(V.a20, 0, ((uint64_t)N + 1) * 4); be.memset(V.nFinal, 0, ((uint64_t)N + 1) * 4);
     be.stage("alloc-a12");
     // fragments with hits, ordered by descending hit-count class (stable within a class): warps of the thread-per-fragment stages get
     // fragments of similar cost while neighbouring lanes still touch neighbouring memory
@@ -256,8 +255,12 @@ struct Pipeline {
     // work key: small fragments (at most 15 alignments and 15 hits) are binned by their exact (alignments, hits) pair, so that the lanes of a warp
     // run the same trip counts in the per-fragment loops; larger ones by 1 + floor(log2(hits)).  Bins keep slot order: neighbouring lanes still touch
     // neighbouring memory.  Keys sort descending: the expensive fragments start first.
-    { const ChunkView C = this->C; be.template launch<st::work_class>(N, [=] EQP_LAMBDA(uint64_t s) {
-        uint32_t h = C.hitCnt[C.blkOff[s + 1]] - C.hitCnt[C.blkOff[s]], na = C.alnOff[s + 1] - C.alnOff[s], key = 0;
+    { const ChunkView C = this->C; SlotPack* pack = V.pack;
+      be.template launch<st::work_class>(N, [=] EQP_LAMBDA(uint64_t s) {       // slot order: the SlotPack of every fragment + its work key
+        SlotPack sp; sp.hit0 = C.hitCnt[C.blkOff[s]]; sp.hit1 = C.hitCnt[C.blkOff[s + 1]]; sp.aln0 = C.alnOff[s]; sp.aln1 = C.alnOff[s + 1];
+        sp.a20 = sp.nFinal = sp.a20G = 0; sp.g = sp.hit0 != sp.hit1 ? slot_weight_mode(C, P, (uint32_t)s) : 0u;
+        pack[s] = sp;
+        uint32_t h = sp.hit1 - sp.hit0, na = sp.aln1 - sp.aln0, key = 0;
 #ifdef EQP_VAR_ONE_CLASS
         if (h) key = 1;
         if (0)
@@ -275,7 +278,9 @@ struct Pipeline {
       be.template launch<st::alignment_build>(nAln, [=] EQP_LAMBDA(uint64_t a) { alignment_build(A, C, V, P, (uint32_t)a); });
       be.stage("alignment-build");
       // the rare shapes (transcript exon longer than its genome exon; tr- exons) go through work lists built on the device
-      be.template launch<st::work_lists>(nWork, [=] EQP_LAMBDA(uint64_t i) { uint32_t s = perm[i]; if (C.slotLd[s]) list_push(listCnt, listLd, s); if (C.slotTr[s]) list_push(listCnt + 1, listTr, s); });
+      be.template launch<st::work_lists>(N, [=] EQP_LAMBDA(uint64_t s) {      // slot order (coalesced): flags from alignment_build into the packs and the lists
+        if (C.slotLd[s]) { list_push(listCnt, listLd, (uint32_t)s); V.pack[s].g |= SP_LD; }
+        if (C.slotTr[s]) { list_push(listCnt + 1, listTr, (uint32_t)s); V.pack[s].g |= SP_TR; } });
       be.template launch_counted<st::fragment_adjust>(listCnt, N, [=] EQP_LAMBDA(uint64_t i) { fragment_adjust(A, C, V, listLd[i]); });                         // a17 before the dedupe
       const bool fuseWC = be.env_flag("EQP_FUSE_WC");                     // development switch (tools/variants.py): weight + count in one thread per fragment
       if (!fuseWC) be.template launch_occ<st::fragment_weight, 4>(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
@@ -295,7 +300,7 @@ struct Pipeline {
       if (fuseWC) be.template launch_occ<st::fragment_weight_count, 3>(nWork, [=] EQP_LAMBDA(uint64_t i) {
         uint32_t s = perm[i];
         fragment_weight(A, C, V, P, s);
-        if (V.alnG && C.slotTr[s]) fragment_weight_gene(C, V, s);
+        if (V.alnG && (V.pack[s].g & SP_TR)) fragment_weight_gene(C, V, s);
         for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) {
           uint64_t ws; int r = fragment_count<EQP_FS_SMALL, EQP_FT_SMALL>(A, C, V, P, m, s, ws);
           if (r < 0) { uint32_t k = atomic_inc_u32(bigCnt); if (k < N) bigList[k] = s * 4u + (uint32_t)m; else raise(C.err, DERR_CAPACITY, C.base + s); r = 0; ws = 0; }

@@ -231,9 +231,10 @@ k_tokenize_sam(const __grid_constant__ AnnoView A, const __grid_constant__ SamVi
   // ---- phase 2: one thread per owned line
   const bool reachesEof = v0 + TK_STAGE >= vEnd;
   uint32_t fmin = 0xFFFFFFFFu, fmax = 0;                             // fragment id range of this thread's records
-  // One copy of the parser in the instruction stream: ncu showed the loop peeled into two ~4500-instruction bodies (144 KB of hot
-  // code, "no instruction" stalls of 1.3-1.7 warps per issue slot); a tile holds ~90 lines for 128 threads, so the loop rarely turns twice.
-#ifndef EQP_VAR_PEEL
+  // (ncu shows this loop peeled into two ~4500-instruction bodies and "no instruction" stalls of 1.3-1.7 warps per issue slot; forcing one
+  // copy with `#pragma unroll 1` and real calls for the cold parser shrank the kernel from 23k to 8k instructions but raised it from 80 to
+  // 96 registers and was SLOWER, 38.1 vs 36.2 ms per chunk, profiles/r03f: EQP_VAR_ONE_BODY keeps that variant for A/B runs.)
+#ifdef EQP_VAR_ONE_BODY
 #pragma unroll 1
 #endif
   for (uint32_t j = tid; j < nOwned; j += TK_THREADS) {

@@ -136,6 +136,18 @@ struct alignas(16) Aln {            // one WeightObjectAlignment (a15-a19), 48 b
   uint32_t next;                   // next alignment of the fragment with the same key (duplicate chain, file order), UINT32_MAX = end
 };
 
+// Everything the per-fragment stages (weight, count) need to know about a fragment slot, and their per-fragment outputs, in ONE 32-byte
+// sector: those kernels walk the fragments in work order, so every separate per-slot array they touch costs its own DRAM sector per fragment
+// (ncu: fragment_weight moved 1.8 KB per fragment, profiles/r03d).  Built in slot order after the join (coalesced).
+struct alignas(32) SlotPack {
+  uint32_t hit0, hit1;             // the fragment's hit range
+  uint32_t aln0, aln1;             // its alignment range
+  uint32_t a20, nFinal;            // fragment_weight: number of genomic alignments (0 = not in the intersection), numAlignments of the final.wgt entry
+  uint32_t a20G;                   // fragment_weight_gene: a20 under the gene run's keys (fragments with tr- exon hits)
+  uint32_t g;                      // bits 0-23 numAlignments of the genome SAM weight entry, bits 24-25 how it combines with a20 (SP_*), bit 27 tr- hit, bit 28 positive length difference
+};
+enum { SP_A20 = 0, SP_GENOME = 1, SP_MAX = 2, SP_TR = 1u << 27, SP_LD = 1u << 28 };
+
 // second dedupe of the alignments of a fragment with tr- exon hits: keys of the gene run, where tr- intervals are printed (GenomicInterval.java:711-713)
 struct AlnG { uint64_t key; uint32_t repr, next; uint8_t flags; uint8_t pad[7]; };   // flags bit5: halves swapped relative to repr
 

@@ -120,7 +120,7 @@ int main(int argc, char** argv) {
       fclose(f);
     }
     { FILE* f = fopen((outd + "/weights.tsv").c_str(), "w");
-      for (uint32_t s = 0; s < pl.C.nSlots; s++) if (pl.V.a20[s]) fprintf(f, "F%09u\t%u\t%u\n", pl.C.base + s, pl.V.a20[s], pl.V.nFinal[s]);
+      for (uint32_t s = 0; s < pl.C.nSlots; s++) if (pl.V.pack[s].a20) fprintf(f, "F%09u\t%u\t%u\n", pl.C.base + s, pl.V.pack[s].a20, pl.V.pack[s].nFinal);
       fclose(f); }
     { FILE* f = fopen((outd + "/samweights.tsv").c_str(), "w");
       const char* fn[4] = {"T", "J", "G", "TJ"};
