@@ -131,7 +131,7 @@ EQP_HD void alignment_build(const AnnoView& A, const ChunkView& C, const CountVi
   if (e > split) { build_half(A, C, V, P, split, e, 2, al.start2, al.nIv2, al.maxField2, tr2, frag); fl |= 4; }
   if (!(fl & 1)) fl |= (uint8_t)(((fl & 2) ? 1 : 2) << 3);
   if (!(fl & 1) && (fl & 2) && (fl & 4)) raise(C.err, DERR_INCONSISTENT, frag);     // single-read alignment with both read indices
-  al.flags = fl; al.tr = (uint8_t)(tr1 | (tr2 << 3));
+  al.flags = fl; al.tr = (uint8_t)(tr1 | (tr2 << 3)); al.tail = 0;
   al.key = alignment_key_inl(V.hx, al, false);
   V.alns[a] = al;
 }
@@ -145,6 +145,7 @@ EQP_HD uint64_t hit_group_key(const HitX& x) { return ((uint64_t)((x.flags & 1) 
 template <bool GENE>
 EQP_HD uint32_t dedupe_fragment(const CountView& V, uint32_t a0, uint32_t a1) {
   int left = 0, right = 0; bool hasTr = false; uint32_t nA = a1 - a0, cap = 2 * nA; uint32_t* tab = V.dedupTab + 2 * (uint64_t)a0;
+  if (nA > 0xFFFFu) return 0;                                              // chain tails are 16-bit; the caller reports the capacity error
   if (GENE) { for (uint32_t a = a0; a < a1; a++) { AlnG& g = V.alnG[a]; g.repr = a; g.next = 0xFFFFFFFFu; g.flags = 0; g.key = V.alns[a].hit0 == V.alns[a].hit1 ? 0 : alignment_key(V.hx, V.alns[a], true); }
     if (nA > 4) for (uint32_t s = 0; s < cap; s++) tab[s] = 0; }            // the table was used by the first dedupe
   for (uint32_t a = a0; a < a1; a++) {
@@ -168,11 +169,12 @@ EQP_HD uint32_t dedupe_fragment(const CountView& V, uint32_t a0, uint32_t a1) {
       }
     }
     if (found != 0xFFFFFFFFu) {                                            // duplicate: append to the representative's chain (file order)
-      if (GENE) { V.alnG[a].repr = found; if (sw) V.alnG[a].flags |= 32; V.alnG[V.alnTail[found]].next = a; }
-      else { al.repr = found; if (sw) al.flags |= 32; V.alns[V.alnTail[found]].next = a; }
-      V.alnTail[found] = a;
+      Aln& R = V.alns[found]; const uint32_t last = a0 + R.tail;
+      if (GENE) { V.alnG[a].repr = found; if (sw) V.alnG[a].flags |= 32; V.alnG[last].next = a; }
+      else { al.repr = found; if (sw) al.flags |= 32; V.alns[last].next = a; }
+      R.tail = (uint16_t)(a - a0);
     } else {
-      V.alnTail[a] = a;
+      al.tail = (uint16_t)(a - a0);
       // getNumGenomicAlignments (WeightObject.java:819-880): alignments of tr- intervals only are not counted but add one in total
       const bool trAln = (!(al.flags & 2) || (al.tr & 2)) && (!(al.flags & 4) || (al.tr & 16));
       if (trAln) hasTr = true; else if (key_form(al, GENE) == 2) right++; else left++;   // ":r-" forms (:859-865)
@@ -186,12 +188,12 @@ EQP_HD void fragment_weight(const AnnoView& A, const ChunkView& C, const CountVi
   const SlotPack sp = V.pack[slot];
   if (sp.hit0 == sp.hit1) return;                                         // a20 / nFinal stay 0
   uint32_t a0 = sp.aln0, a1 = sp.aln1; const uint32_t nA = a1 - a0;
+  if (nA > 0xFFFFu) { raise(C.err, DERR_CAPACITY, C.base + slot); return; }
   const uint32_t a20 = dedupe_fragment<false>(V, a0, a1);
   // tag every hit with its representative (index within the fragment) and with the representative's half it merges into
   // (combineExons pairs mate-swapped duplicates crosswise, WeightObjectAlignment.java:312-337): a22-a25 then read the
   // fragment's hits as one flat range instead of walking duplicate chains.  Fragments with tr- exon hits are left untagged: their
   // gene run has its own dedupe (fragment_weight_gene) and HitX::grp keeps the non-tr ordinal of the interval.
-  if (nA > 0xFFFFu) { raise(C.err, DERR_CAPACITY, C.base + slot); return; }
   const bool trFrag = (sp.g & SP_TR) != 0;
   if (!trFrag) for (uint32_t a = a0; a < a1; a++) {
     const Aln& al = V.alns[a]; if (al.hit0 == al.hit1) continue;
@@ -331,6 +333,12 @@ EQP_HD int exon_filter(const AnnoView& A, ExonSet& e, int32_t gs, int32_t ge) {
   }
   e.n = ne; return ne;
 }
+// features of exon `ex` in run `mode`: cnt entries; inl: the single entry is `first` itself, else they are feat[mode][first .. first + cnt)
+EQP_HD void exon_features(const AnnoView& A, int mode, int ex, uint32_t& first, uint32_t& cnt, bool& inl) {
+  const ExonFeat f = A.exf[ex];
+  if (mode == MODE_JUNCTION) { first = f.jOff; cnt = f.n >> 16; inl = false; }
+  else { cnt = mode == MODE_GENE ? (f.n & 0xFFu) : ((f.n >> 8) & 0xFFu); first = mode == MODE_GENE ? f.g : f.e; inl = cnt == 1; }
+}
 // Junction run, a half with exactly two intervals of one exon each (the ordinary spliced read): a junction conforms iff it is a
 // candidate of both exons and the two fields are consecutive (:679-701), i.e. the intersection of the two exons' feature lists.
 // The lists are sorted by id when the annotation is loaded, so this is one merge instead of a set with field masks.
@@ -341,8 +349,9 @@ EQP_HD bool junction_pair(const AnnoView& A, const CountView& V, ExonSet& ea, in
   if (exon_filter(A, ea, gsa, gea) != 1 || exon_filter(A, eb, gsb, geb) != 1) return false;   // the filter is idempotent: the general path may run it again
   out.n = 0;
   if (fa - fb != 1 && fb - fa != 1) return true;
-  const uint32_t* F = A.feat[MODE_JUNCTION]; const uint32_t* O = A.featOff[MODE_JUNCTION];
-  uint32_t i = O[ea.exon[0]], i1 = O[ea.exon[0] + 1], j = O[eb.exon[0]], j1 = O[eb.exon[0] + 1];
+  const uint32_t* F = A.feat[MODE_JUNCTION];
+  uint32_t i, i1, j, j1; bool inl;
+  exon_features(A, MODE_JUNCTION, ea.exon[0], i, i1, inl); i1 += i; exon_features(A, MODE_JUNCTION, eb.exon[0], j, j1, inl); j1 += j;
   while (i < i1 && j < j1) {
     uint32_t va = F[i], vb = F[j], ia = va & 0x7fffffffu, ib = vb & 0x7fffffffu;
     if (ia < ib) i++; else if (ib < ia) j++;
@@ -365,9 +374,10 @@ EQP_HD bool interval_features(const AnnoView& A, const ChunkView& C, const Count
   if (mode == MODE_EXON && P.unambiguous[mode] && ne >= 2) ne = 0;      // -U with genomicIntervalMode (:603-608)
   const uint32_t bit = field >= 0 ? 1u << field : 0u;                   // a tr- record of the junction run has no field (:638-656)
   for (int q = 0; q < ne; q++) {
-    int ex = exon[q]; uint32_t f0 = A.featOff[mode][ex], f1 = A.featOff[mode][ex + 1]; bool any = false;
-    for (uint32_t f = f0; f < f1; f++) {
-      uint32_t v = A.feat[mode][f]; uint32_t id = v & 0x7fffffffu;
+    int ex = exon[q]; uint32_t f0, cnt; bool inl, any = false;
+    exon_features(A, mode, ex, f0, cnt, inl);
+    for (uint32_t f = f0; f < f0 + cnt; f++) {
+      uint32_t v = inl ? f0 : A.feat[mode][f]; uint32_t id = v & 0x7fffffffu;
       if (mode == MODE_JUNCTION && !(v & 0x80000000u) && !V.junctionActive[A.featAct ? A.featAct[f] : id]) continue;   // row removed by the per-chunk map filter (a27)
       any = true;
       if (!fs_add(fs, id, bit)) return false;

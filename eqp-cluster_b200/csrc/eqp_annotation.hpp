@@ -56,7 +56,7 @@ struct AnnoHost {
   std::vector<uint32_t> bktRowOff; std::vector<uint8_t> bktFlags; std::vector<int32_t> bktRefId;
   std::vector<int32_t> rowStart, rowEnd, rowMaxEnd, rowExon; std::vector<uint8_t> rowFlags;
   std::vector<int32_t> exChr, exStart, exEnd; std::vector<uint8_t> exStrand;
-  std::vector<RowA> rowA; std::vector<ExonA> exA;                        // the device form of the row / exon tables
+  std::vector<RowA> rowA; std::vector<ExonA> exA; std::vector<ExonFeat> exF;                        // the device form of the row / exon tables
   std::vector<uint32_t> featOff[3], feat[3]; std::vector<std::string> featIds[3];
   std::vector<uint32_t> featAct; std::vector<std::string> actIds; int mapColumns[3] = {2, 2, 2};
   // rows of the count file in print order (ComputeCounts.java:875-950): 2-column maps print every id of the map in TreeSet order,
@@ -252,6 +252,14 @@ struct AnnoHost {
         for (auto* r : v) outRows[m].push_back({r->printed, (int32_t)fidx[r->feat], (int32_t)jActIdx[r->printed], (uint8_t)(r->always ? 1 : 0)});
       }
     }
+    exF.resize(exons.size());
+    for (size_t x = 0; x < exons.size(); x++) {
+      uint32_t n[3]; for (int m = 0; m < 3; m++) n[m] = featOff[m][x + 1] - featOff[m][x];
+      if (n[0] > 255 || n[1] > 255 || n[2] > 65535) throw AnnoError(-3, "an exon maps to more than 255 genes / exons or 65535 junctions");
+      exF[x].g = n[0] == 1 ? (feat[0][featOff[0][x]] & 0x7fffffffu) : featOff[0][x];
+      exF[x].e = n[1] == 1 ? (feat[1][featOff[1][x]] & 0x7fffffffu) : featOff[1][x];
+      exF[x].jOff = featOff[2][x]; exF[x].n = n[0] | (n[1] << 8) | (n[2] << 16);
+    }
     // ---- a27: which junction features does a reference id seen in the chunk keep alive?
     std::unordered_map<std::string, std::vector<std::string>> jjExt;    // internal junction id -> external ids
     { std::string t = slurp(jjCoordinateMap);
@@ -291,9 +299,9 @@ struct AnnoHost {
     v.refVerOff = refVerOff.data(); v.refVerBucket = refVerBucket.data(); v.refActOff = refActOff.data(); v.refAct = refAct.data();
     v.nRef = (int32_t)refStrOff.size();
     v.bktRowOff = bktRowOff.data(); v.bktFlags = bktFlags.data(); v.bktRefId = bktRefId.data(); v.nBucket = (int32_t)bktFlags.size();
-    v.row = rowA.data(); v.ex = exA.data(); v.nExon = (int32_t)exChr.size(); v.nTrChr = (int32_t)trChrNames.size();
+    v.row = rowA.data(); v.ex = exA.data(); v.exf = exF.data(); v.nExon = (int32_t)exChr.size(); v.nTrChr = (int32_t)trChrNames.size();
     v.featAct = featAct.empty() ? nullptr : featAct.data(); v.nAct = (int32_t)actIds.size();
-    for (int m = 0; m < 3; m++) { v.featOff[m] = featOff[m].data(); v.feat[m] = feat[m].data(); v.nFeat[m] = (int32_t)featIds[m].size(); }
+    for (int m = 0; m < 3; m++) { v.feat[m] = feat[m].data(); v.nFeat[m] = (int32_t)featIds[m].size(); }
     return v;
   }
 };

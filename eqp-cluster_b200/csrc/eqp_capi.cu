@@ -29,22 +29,22 @@ struct AnnoDevice {
   DevArray<DictEntry> dict; DevArray<char> strPool; DevArray<uint32_t> refStrOff; DevArray<uint16_t> refStrLen;
   DevArray<uint8_t> refFlags; DevArray<uint32_t> refVerOff; DevArray<int32_t> refVerBucket; DevArray<uint32_t> refActOff; DevArray<int32_t> refAct;
   DevArray<uint32_t> bktRowOff; DevArray<uint8_t> bktFlags; DevArray<int32_t> bktRefId; DevArray<uint32_t> featAct; DevArray<RowA> row;
-  DevArray<ExonA> ex; DevArray<uint32_t> featOff[3], feat[3];
+  DevArray<ExonA> ex; DevArray<ExonFeat> exf; DevArray<uint32_t> feat[3];
   size_t bytes = 0;
   AnnoView upload(const AnnoHost& H) {
     AnnoView v = H.view();
     dict.upload(H.dict); strPool.upload(H.strPool.data(), H.strPool.size()); refStrOff.upload(H.refStrOff);
     refStrLen.upload(H.refStrLen); refFlags.upload(H.refFlags); refVerOff.upload(H.refVerOff); refVerBucket.upload(H.refVerBucket);
     refActOff.upload(H.refActOff); refAct.upload(H.refAct); bktRowOff.upload(H.bktRowOff); bktFlags.upload(H.bktFlags); bktRefId.upload(H.bktRefId); featAct.upload(H.featAct);
-    row.upload(H.rowA); ex.upload(H.exA);
+    row.upload(H.rowA); ex.upload(H.exA); exf.upload(H.exF);
     v.dict = dict.p; v.strPool = strPool.p; v.refStrOff = refStrOff.p; v.refStrLen = refStrLen.p; v.refFlags = refFlags.p;
     v.refVerOff = refVerOff.p; v.refVerBucket = refVerBucket.p; v.refActOff = refActOff.p; v.refAct = refAct.p;
     v.bktRowOff = bktRowOff.p; v.bktFlags = bktFlags.p; v.bktRefId = bktRefId.p; v.featAct = H.featAct.empty() ? nullptr : featAct.p; v.row = row.p;
-    v.ex = ex.p;
-    for (int m = 0; m < 3; m++) { featOff[m].upload(H.featOff[m]); feat[m].upload(H.feat[m]); v.featOff[m] = featOff[m].p; v.feat[m] = feat[m].p; }
+    v.ex = ex.p; v.exf = exf.p;
+    for (int m = 0; m < 3; m++) { feat[m].upload(H.feat[m]); v.feat[m] = feat[m].p; }
     bytes = H.dict.size() * 16 + H.strPool.size() + H.refStrOff.size() * 7 + H.refVerOff.size() * 4 + H.refVerBucket.size() * 4 + H.refActOff.size() * 4 + H.refAct.size() * 4 +
             H.bktRowOff.size() * 9 + H.rowA.size() * 16 + H.exA.size() * 16 + H.featAct.size() * 4;
-    for (int m = 0; m < 3; m++) bytes += (H.featOff[m].size() + H.feat[m].size()) * 4;
+    bytes += H.exF.size() * 16; for (int m = 0; m < 3; m++) bytes += H.feat[m].size() * 4;
     return v;
   }
 };

@@ -240,7 +240,7 @@ struct Pipeline {
     be.stage("join");
     // ---- a12-a25
     V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
-    V.dedupTab = be.template alloc<uint32_t>(2 * (uint64_t)nAln + 2); be.memset(V.dedupTab, 0, (2 * (uint64_t)nAln + 2) * 4); V.alnTail = be.template alloc<uint32_t>((uint64_t)nAln + 1);
+    V.dedupTab = be.template alloc<uint32_t>(2 * (uint64_t)nAln + 2); be.memset(V.dedupTab, 0, (2 * (uint64_t)nAln + 2) * 4);
     V.pack = be.template alloc<SlotPack>((uint64_t)N + 1);
     V.ivAdj = be.template alloc<IvAdj>((uint64_t)nHits + 1);                // a17 scratch, touched for fragments with a positive length difference only
     V.alnG = nullptr;

@@ -52,6 +52,13 @@ struct alignas(16) RowA { int32_t start, end, maxEnd; uint32_t exonFlags;      /
   EQP_HD int32_t exon() const { return (int32_t)(exonFlags >> 3); } EQP_HD uint32_t flags() const { return exonFlags & 7u; } };
 struct alignas(16) ExonA { int32_t chr, start, end; uint32_t strand; };         // chr <= -2: tr- exon of transcript -2 - chr; strand: the character
 
+// Where the features of a distinct exon are, for all three runs in one 16-byte load (the counting runs look up every hit's exon in each run)
+struct alignas(16) ExonFeat {
+  uint32_t g, e;                   // gene / exon run: the feature id itself when the exon has exactly one (the usual case), else the offset of its list in feat[run]
+  uint32_t jOff;                   // junction run: offset of its id-sorted list in feat[MODE_JUNCTION]
+  uint32_t n;                      // list lengths: bits 0-7 gene run, 8-15 exon run, 16-31 junction run
+};
+
 struct AnnoView {
   // reference-name dictionary (open addressing, power-of-two capacity)
   const DictEntry* dict; uint32_t dictMask;
@@ -69,7 +76,7 @@ struct AnnoView {
   const ExonA* ex;
   int32_t nExon; int32_t nTrChr;    // nTrChr: number of distinct tr- chromosomes (0: the annotation has no tr- exons)
   // exon -> feature lists per mode; junction entries carry bit31 = "row also in exon_junction_transcript.map"
-  const uint32_t* featOff[3]; const uint32_t* feat[3]; int32_t nFeat[3];
+  const ExonFeat* exf; const uint32_t* feat[3]; int32_t nFeat[3];
   // 3-column junction map (Exon.java:107-125): a row is switched on by its column-2 id, counted under its column-3 id.
   // featAct is parallel to feat[MODE_JUNCTION] (null: the activation index is the feature id); nAct = number of activation ids
   const uint32_t* featAct; int32_t nAct;
@@ -132,7 +139,7 @@ struct alignas(16) Aln {            // one WeightObjectAlignment (a15-a19), 48 b
   uint16_t nIv1, nIv2; int16_t maxField1, maxField2;
   uint8_t flags;                   // bit0 paired, bit1 has half 1, bit2 has half 2, bits3-4 SR read index, bit5 halves swapped relative to repr
   uint8_t tr;                      // per half h (shift 3*(h-1)): bit0 has a tr- interval, bit1 all intervals are tr-, i.e. its string is the literal "" outside the gene run
-  uint8_t pad[2];
+  uint16_t tail;                   // representative only: last alignment of its duplicate chain, relative to the fragment's first alignment (a19 scratch)
   uint32_t next;                   // next alignment of the fragment with the same key (duplicate chain, file order), UINT32_MAX = end
 };
 
