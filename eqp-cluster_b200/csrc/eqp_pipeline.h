@@ -70,7 +70,7 @@ EQP_HD void counter_add64(unsigned long long* p, uint64_t v) {          // v < 2
 
 // stage tags: they only name the kernels (profiler listings)
 namespace st { struct misc; struct frag_table; struct frag_stats; struct select_tj_weights; struct select_stage1; struct select_stage2; struct seen_refs; struct junction_active;
-               struct blocks_count; struct blocks_fill; struct join_count; struct join_fill; struct work_class; struct alignment_build; struct work_lists; struct fragment_adjust;
+               struct blocks_order; struct blocks_count; struct blocks_fill; struct join_count; struct join_fill; struct work_class; struct alignment_build; struct work_lists; struct fragment_adjust;
                struct fragment_weight; struct fragment_weight_gene; struct fragment_count; struct fragment_count_large; struct fragment_weight_count; }
 
 struct ChunkResult {
@@ -222,15 +222,31 @@ struct Pipeline {
     // ---- a8-a10: blocks (count, scan, fill)
     V.stats = be.template alloc<unsigned long long>(16); be.memset(V.stats, 0, 16 * sizeof(unsigned long long));
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
+    // The two passes walk a fragment's record set in one thread; record counts have a long tail (multi-mappers), and in slot order a warp ran at
+    // 4.7 active lanes of 32 (ncu, profiles/r03d).  So the fragments are visited in descending order of their record count (bins keep slot order),
+    // while the outputs stay in slot order: the offsets come from scans over the per-slot counts.
+    uint32_t* bkey = be.template alloc<uint32_t>((uint64_t)N + 1); uint32_t* bperm = be.template alloc<uint32_t>((uint64_t)N + 1);
+    be.memset(C.blkOff, 0, ((uint64_t)N + 1) * 4); be.memset(C.alnOff, 0, ((uint64_t)N + 1) * 4);
+    { const ChunkView C = this->C;
+      be.template launch<st::blocks_order>(N, [=] EQP_LAMBDA(uint64_t s) {
+        SetDesc sd = C.setC[s]; uint32_t n = 0;
+        for (int k = 0; k < sd_n(sd); k++) { const FragFile ff = C.ff[sd_file(sd, k)][s]; n += ff.end - ff.first; }
+#ifdef EQP_VAR_BLOCKS_UNSORTED
+        bkey[s] = n ? 1u : 0u;
+#else
+        bkey[s] = n < 255u ? n : 255u;
+#endif
+      }); }
+    const uint32_t nB = be.order_by_work(bkey, N, bperm);
     { const ChunkView C = this->C; unsigned long long* stats = V.stats;
-      be.template launch<st::blocks_count>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, false, P.stranded, nb, na); C.blkOff[s] = nb; C.alnOff[s] = na;
-        SetCursor c{0, 0xFFFFFFFFu}; int f; counter_add(&stats[9], set_next(C, C.setC[s], (uint32_t)s, c, f) ? 1u : 0u); }); }
+      be.template launch<st::blocks_count>(nB, [=] EQP_LAMBDA(uint64_t i) { const uint32_t s = bperm[i]; uint32_t nb, na; fragment_blocks(A, C, s, false, P.stranded, nb, na); C.blkOff[s] = nb; C.alnOff[s] = na;
+        SetCursor c{0, 0xFFFFFFFFu}; int f; counter_add(&stats[9], set_next(C, C.setC[s], s, c, f) ? 1u : 0u); }); }
     be.scan(C.blkOff, N); be.scan(C.alnOff, N);
     be.to_host(&nBlocks, C.blkOff + N, 4); be.to_host(&nAln, C.alnOff + N, 4);
     C.blocks = be.template alloc<Block>((uint64_t)nBlocks + 1); C.hitCnt = be.template alloc<uint32_t>((uint64_t)nBlocks + 1);
     C.alnBlk = be.template alloc<uint32_t>((uint64_t)nAln + 1); be.to_device(C.alnBlk + nAln, &nBlocks, 4);
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
-    { const ChunkView C = this->C; be.template launch_occ<st::blocks_fill, 6>(N, [=] EQP_LAMBDA(uint64_t s) { uint32_t nb, na; fragment_blocks(A, C, (uint32_t)s, true, P.stranded, nb, na); }); }
+    { const ChunkView C = this->C; be.template launch_occ<st::blocks_fill, 6>(nB, [=] EQP_LAMBDA(uint64_t i) { uint32_t nb, na; fragment_blocks(A, C, bperm[i], true, P.stranded, nb, na); }); }
     be.stage("blocks");
     // ---- a11: interval join (count, scan, fill)
     { const ChunkView C = this->C; be.template launch<st::join_count>(nBlocks, [=] EQP_LAMBDA(uint64_t b) { C.hitCnt[b] = join_block(A, C.blocks[b], nullptr, 0, (uint32_t)b, P.stranded != 0); }); }
