@@ -71,7 +71,7 @@ EQP_HD void counter_add64(unsigned long long* p, uint64_t v) {          // v < 2
 // stage tags: they only name the kernels (profiler listings)
 namespace st { struct misc; struct frag_table; struct frag_stats; struct select_tj_weights; struct select_stage1; struct select_stage2; struct seen_refs; struct junction_active;
                struct blocks_order; struct blocks_count; struct blocks_fill; struct join_count; struct join_fill; struct work_class; struct alignment_build; struct work_lists; struct fragment_adjust;
-               struct fragment_weight; struct fragment_weight_gene; struct fragment_count; struct fragment_count_large; struct fragment_weight_count; }
+               struct fragment_weight; struct fragment_weight_gene; struct fragment_count; struct fragment_count_large; }
 
 struct ChunkResult {
   std::vector<double> counts[3]; std::vector<unsigned long long> fixed[3]; std::vector<uint8_t> junctionActive;
@@ -298,9 +298,8 @@ struct Pipeline {
         if (C.slotLd[s]) { list_push(listCnt, listLd, (uint32_t)s); V.pack[s].g |= SP_LD; }
         if (C.slotTr[s]) { list_push(listCnt + 1, listTr, (uint32_t)s); V.pack[s].g |= SP_TR; } });
       be.template launch_counted<st::fragment_adjust>(listCnt, N, [=] EQP_LAMBDA(uint64_t i) { fragment_adjust(A, C, V, listLd[i]); });                         // a17 before the dedupe
-      const bool fuseWC = be.env_flag("EQP_FUSE_WC");                     // development switch (tools/variants.py): weight + count in one thread per fragment
-      if (!fuseWC) be.template launch_occ<st::fragment_weight, 4>(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
-      if (V.alnG && !fuseWC) be.template launch_counted<st::fragment_weight_gene>(listCnt + 1, N, [=] EQP_LAMBDA(uint64_t i) { fragment_weight_gene(C, V, listTr[i]); });      // gene-run keys of tr- fragments
+      be.template launch_occ<st::fragment_weight, 4>(nWork, [=] EQP_LAMBDA(uint64_t i) { fragment_weight(A, C, V, P, perm[i]); });
+      if (V.alnG) be.template launch_counted<st::fragment_weight_gene>(listCnt + 1, N, [=] EQP_LAMBDA(uint64_t i) { fragment_weight_gene(C, V, listTr[i]); });      // gene-run keys of tr- fragments
       be.stage("fragment-weight");
       // the three counting runs of one fragment back to back in one thread: runs two and three find the fragment's alignments and
       // hits in cache instead of paying the DRAM latency chain again (the runs were latency-bound as three concurrent kernels).
@@ -311,19 +310,9 @@ struct Pipeline {
         counter_add(&V.stats[m * 3 + 0], r ? 1u : 0u); counter_add(&V.stats[m * 3 + 1], r == 1 ? 1u : 0u); counter_add(&V.stats[m * 3 + 2], r == 2 ? 1u : 0u);
         counter_add64(&V.stats[10 + m], ws);
       };
-      // (A variant that fused alignment_build + weight + count into one thread per fragment ran 10x slower, 217-266 ms against 67 ms for the three
-      // kernels at 25M reads, profiles/r03d_variants_fused_25Mreads.jsonl: the per-alignment kernel has 2.7x the parallelism and coalesced access.)
-      if (fuseWC) be.template launch_occ<st::fragment_weight_count, 3>(nWork, [=] EQP_LAMBDA(uint64_t i) {
-        uint32_t s = perm[i];
-        fragment_weight(A, C, V, P, s);
-        if (V.alnG && (V.pack[s].g & SP_TR)) fragment_weight_gene(C, V, s);
-        for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) {
-          uint64_t ws; int r = fragment_count<EQP_FS_SMALL, EQP_FT_SMALL>(A, C, V, P, m, s, ws);
-          if (r < 0) { uint32_t k = atomic_inc_u32(bigCnt); if (k < N) bigList[k] = s * 4u + (uint32_t)m; else raise(C.err, DERR_CAPACITY, C.base + s); r = 0; ws = 0; }
-          tally(m, r, ws);
-        }
-      });
-      else be.template launch<st::fragment_count>(nWork, [=] EQP_LAMBDA(uint64_t i) {
+      // (Fusing did not pay: alignment_build + weight + count in one thread per fragment ran 217-266 ms against 67 ms for the three kernels at 25M
+      // reads, weight + count alone 66-82 ms against 54 ms: profiles/r03d_variants_fused_25Mreads.jsonl, profiles/r03e_variants_25Mreads.jsonl.)
+      be.template launch<st::fragment_count>(nWork, [=] EQP_LAMBDA(uint64_t i) {
         uint32_t s = perm[i];
         for (int m = 0; m < 3; m++) if (P.modes & (1 << m)) {
           uint64_t ws; int r = fragment_count<EQP_FS_SMALL, EQP_FT_SMALL>(A, C, V, P, m, s, ws);

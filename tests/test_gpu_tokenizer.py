@@ -142,3 +142,26 @@ def test_bad_lines_raise_the_same_code(ctx, tools, tmp_path):
 
 def emu_line_index(before):
     return len(before)
+
+
+def test_short_lines_take_the_second_pass(ctx):
+    """The record tables are sized for len/160 lines before the pass; texts whose lines average less take the pass twice
+    (eqp_cuda_backend.cuh::decode_fused).  20,000 unaligned records of 45 bytes: every line decoded, nothing mapped; and the
+    golden chunk with 60,000 such records behind its genome input counts to the same bits as without them."""
+    import numpy as np
+    from conftest import read_sams
+
+    def unaligned(first, n):
+        return b"".join(b"F%09d\t4\t*\t0\t0\t*\t*\t0\t0\tACGT\tIIII\n" % (first + i) for i in range(n))
+    short = unaligned(1, 20000)
+    assert len(short) / 160 + 1024 < 20000
+    res = ctx.count_chunk(short, b"", b"")
+    assert res.n_records[0] == 20000 and res.number_mapped_reads == 0
+    rows, code, _ = ctx.debug_decode(short)
+    assert code == 0 and len(rows) == 20000 and rows[19999].split("\t")[1:4] == ["REC", "20000", "4"]
+    t, j, g = read_sams(os.path.join(GOLDEN, "appB", "chunk"), "se")
+    ref = ctx.count_chunk(t, j, g)
+    mixed = ctx.count_chunk(t, j, g + unaligned(1000, 60000))
+    assert ref.number_mapped_reads == mixed.number_mapped_reads == 3
+    for m in eqp.MODES:
+        assert np.array_equal(ref.fixed[m], mixed.fixed[m]), m

@@ -57,12 +57,8 @@ def main():
     torch.cuda.synchronize()
     dargs = [(d.data_ptr(), d.numel()) for d in dev]
     libs = [("product", b.LIB_PATH)] + [(os.path.basename(p)[12:-3], p) for p in sorted(glob.glob(os.path.join(VDIR, "libeqpcount_*.so")))]
-    runs = [(n + e, p, e) for n, p in libs for e in ("", "+EQP_FUSE_WC") if not args.only or (n + e) in args.only.split(",")]
-    for name, path, env in runs:
-        for k in ("EQP_FUSE_WC",):
-            os.environ.pop(k, None)
-        if env:
-            os.environ[env[1:]] = "1"
+    runs = [(n, p) for n, p in libs if not args.only or n in args.only.split(",")]
+    for name, path in runs:
         r, w = os.pipe()
         saved = os.dup(2)
         ctx = eqp.CountContext(0, path).load_annotation(anno)
