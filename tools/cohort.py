@@ -65,12 +65,17 @@ def generate(b, anno, d, seed, first, n, layout, spliced, procs):
     return out
 
 
-def oracle_chunk(b, anno, d, seed, first, n, layout, spliced):
-    """Generates the chunk as plain files and runs the oracle on it; returns the oracle's output dir."""
+def oracle_chunk(b, anno, d, seed, first, n, layout, spliced, wait=True):
+    """Generates the chunk as plain files and runs the oracle on it; returns the oracle's output dir (wait=False: (dir, process))."""
     o = os.path.join(d, "oracle")
     os.makedirs(o, exist_ok=True)
-    sh([b.WORLDGEN_BIN, "reads", anno, d, str(seed), str(first), str(n), layout] + ([str(spliced)] if spliced else []))
-    sh([b.ORACLE_BIN, "run", anno, d, layout, o, "--quiet"])
+    gen = " ".join([b.WORLDGEN_BIN, "reads", anno, d, str(seed), str(first), str(n), layout] + ([str(spliced)] if spliced else []))
+    run = " ".join([b.ORACLE_BIN, "run", anno, d, layout, o, "--quiet"])
+    p = subprocess.Popen(["bash", "-c", gen + " && " + run], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    if not wait:
+        return o, p
+    if p.wait():
+        raise RuntimeError("oracle run failed")
     return o
 
 
@@ -213,8 +218,11 @@ def main():
             continue
         si = names.index(s)
         files = {m: [] for m in eqp.MODES}
-        for c in range(args.chunks):
-            o = oracle_chunk(b, anno, os.path.join(workdir, "verify_%s_c%d" % (s, c)), 2000 + (si + 1) * 10 + c, 1 + c * args.verify_reads, args.verify_reads, args.layout, 0)
+        jobs = [oracle_chunk(b, anno, os.path.join(workdir, "verify_%s_c%d" % (s, c)), 2000 + (si + 1) * 10 + c, 1 + c * args.verify_reads, args.verify_reads, args.layout, 0, wait=False)
+                for c in range(args.chunks)]                               # the chunks' oracle runs side by side
+        for o, p in jobs:
+            if p.wait():
+                raise RuntimeError("oracle run failed")
             for m in eqp.MODES:
                 files[m].append(os.path.join(o, m + ".cnt"))
         for m in eqp.MODES:
