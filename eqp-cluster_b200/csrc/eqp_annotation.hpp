@@ -23,9 +23,10 @@ namespace eqpb {
 // can feed it one aligned shared-memory word pair per step instead of one byte.  Two 32-bit lanes give the 64-bit key.
 struct NameHash {
   uint32_t a = 0x811C9DC5u, b = 0x9E3779B9u;
-  EQP_HD void add(uint32_t w) {                       // two multiply-xorshift lanes; finish() does the avalanche
-    a = (a ^ w) * 0x9E3779B1u; a ^= a >> 15;
-    b = (b + w) * 0x85EBCA6Bu; b = (b << 13) | (b >> 19);
+  EQP_HD void add(uint32_t w) {
+    uint32_t k = w * 0xCC9E2D51u; k = (k << 15) | (k >> 17); k *= 0x1B873593u;
+    a ^= k; a = (a << 13) | (a >> 19); a = a * 5u + 0xE6546B64u;
+    b = (b ^ w) * 0x85EBCA6Bu; b ^= b >> 15;
   }
   EQP_HD uint64_t finish(int n) {
     uint32_t x = a ^ (uint32_t)n; x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;

@@ -125,8 +125,20 @@ EQP_HD int find_tab(const char* p, int from, int n) {
   return res;
 }
 
-// 0x80 in every byte of w that equals ':' (exact SWAR compare)
+// number of ':' in p[a, b): aligned 4-byte words, exact SWAR byte compare.  Only words holding at least one byte of [a, b) are read.
 EQP_HD uint32_t colon_marker(uint32_t w) { uint32_t x = w ^ 0x3a3a3a3au; return ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu); }
+EQP_HD int colon_count(const char* p, int a, int b) {
+  int cnt = 0;
+  if (a < b) {
+    uintptr_t s = (uintptr_t)(p + a), e = (uintptr_t)(p + b), wa = s & ~(uintptr_t)3, we = (e - 1) & ~(uintptr_t)3;
+    uint32_t m0 = 0xFFFFFFFFu << (8 * (int)(s - wa)), m1 = 0xFFFFFFFFu >> (8 * (int)(we + 4 - e));
+    uint32_t z = colon_marker(*reinterpret_cast<const uint32_t*>(wa)) & m0;
+    for (; wa < we; wa += 4) { cnt += eqp_popc32(z); z = colon_marker(*reinterpret_cast<const uint32_t*>(wa + 4)); }
+    cnt += eqp_popc32(z & m1);
+  }
+  return cnt;
+}
+
 // General tag-block scan (any token shape): field count with the reference's rule, first [nN]M:i:<digits>, HI:i: at a token start
 // (hiAt = offset of its value, the last such token wins as in the reference's loop).  Only reached for lines whose tags are not all of the
 // form XX:T:value.
@@ -189,27 +201,22 @@ EQP_HD DecodedRec parse_record_t(const AnnoView& A, const char* p, int n, Src& s
       // (no field increment), the NM regex can only match at the token start and HI:i: is a plain prefix test.  "Every token has
       // ':' at offsets 2 and 4 and the block holds exactly two ':' per token" is that shape for all tokens at once.
       const uint32_t NMI = 'n' | ('M' << 8) | (':' << 16) | ((uint32_t)'i' << 24), HII = 'H' | ('I' << 8) | (':' << 16) | ((uint32_t)'i' << 24);
-      fields = 11; bool odd = false; int t = from;
+      fields = 11; bool odd = false; int t = from, nTok = 0;
       while (t < n && !odd) {
         int te = src.next(p, t, n), len = te - t;
         uint32_t w = Src::load4(p + t, len);
         if (len >= 5 && ((w >> 16) & 0xFFu) == ':' && p[t + 4] == ':') {
-          // no further ':' in the value (4-byte groups; a zero-padded tail cannot match): with exactly the two colons of "XX:T:" the token
-          // is a tag and the NM / HI patterns can only match at its start
-          uint32_t z = 0;
-          for (int q = t + 5; q < te; q += 4) z |= colon_marker(Src::load4(p + q, te - q));
-          if (z) odd = true;
-          else {
-            if (nm < 0 && (w | 0x20u) == NMI) {
-              int d = t + 5, v = 0; bool dig = false;
-              while (d < te && p[d] >= '0' && p[d] <= '9' && v <= 30000) { v = v * 10 + (p[d] - '0'); d++; dig = true; }
-              if (dig) nm = v;
-            }
-            if (w == HII) hiAt = t + 5;
-            t = te + 1;
+          nTok++;
+          if (nm < 0 && (w | 0x20u) == NMI) {
+            int d = t + 5, v = 0; bool dig = false;
+            while (d < te && p[d] >= '0' && p[d] <= '9' && v <= 30000) { v = v * 10 + (p[d] - '0'); d++; dig = true; }
+            if (dig) nm = v;
           }
+          if (w == HII) hiAt = t + 5;
+          t = te + 1;
         } else odd = true;
       }
+      if (!odd && colon_count(p, from, n) != 2 * nTok) odd = true;
       if (odd) { hiAt = -1; tags_general(p, from, n, fields, nm, hiAt); }
       if (hiAt >= 0) {                                                    // new Integer(token.substring(5)): the rest of the token must be an integer
         int e = hiAt; while (e < n && p[e] != '\t') e++;
