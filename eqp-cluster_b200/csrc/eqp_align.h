@@ -23,7 +23,7 @@ struct CountView {
   AlnG* alnG;                      // gene-run dedupe of fragments with tr- exon hits (null when the annotation has no tr- exons)
   SlotPack* pack;                  // per slot: ranges, weight-stage inputs and outputs
   IvAdj* ivAdj;                    // parallel to hits; only touched for fragments with a positive length difference
-  uint32_t* dedupTab;              // a19 scratch: per-fragment representative table (2 per alignment, zeroed)
+  uint32_t* dedupTab; uint32_t* alnTail;   // a19 scratch: per-fragment representative table (2 per alignment, zeroed), chain tails
   unsigned long long* acc[3];      // fixed-point accumulators per mode (nFeat entries)
   const uint8_t* junctionActive;   // per junction feature
   unsigned long long* stats;       // [mode*3 + {objects, included, excluded}], [9] = mapped fragments

@@ -222,19 +222,20 @@ struct Pipeline {
     // ---- a8-a10: blocks (count, scan, fill)
     V.stats = be.template alloc<unsigned long long>(16); be.memset(V.stats, 0, 16 * sizeof(unsigned long long));
     for (int f = 0; f < 3; f++) be.memset(C.proc[f], 0, C.sam[f].nLines);
-    // The two passes walk a fragment's record set in one thread; record counts have a long tail (multi-mappers), and in slot order a warp ran at
-    // 4.7 active lanes of 32 (ncu, profiles/r03d).  So the fragments are visited in descending order of their record count (bins keep slot order),
-    // while the outputs stay in slot order: the offsets come from scans over the per-slot counts.
+    // The two passes walk a fragment's record set in one thread; record counts have a long tail (multi-mappers), and in slot order a warp runs at
+    // 4.7 active lanes of 32 (ncu, profiles/r03d).  Visiting the fragments in descending order of their record count (EQP_VAR_BLOCKS_SORTED) fixes the
+    // lanes but scatters the reads of the record arrays: measured 25.5 ms against 21.0 ms in slot order (profiles/r03h), so slot order stays; the
+    // list below only drops the fragments without records.
     uint32_t* bkey = be.template alloc<uint32_t>((uint64_t)N + 1); uint32_t* bperm = be.template alloc<uint32_t>((uint64_t)N + 1);
     be.memset(C.blkOff, 0, ((uint64_t)N + 1) * 4); be.memset(C.alnOff, 0, ((uint64_t)N + 1) * 4);
     { const ChunkView C = this->C;
       be.template launch<st::blocks_order>(N, [=] EQP_LAMBDA(uint64_t s) {
         SetDesc sd = C.setC[s]; uint32_t n = 0;
         for (int k = 0; k < sd_n(sd); k++) { const FragFile ff = C.ff[sd_file(sd, k)][s]; n += ff.end - ff.first; }
-#ifdef EQP_VAR_BLOCKS_UNSORTED
-        bkey[s] = n ? 1u : 0u;
-#else
+#ifdef EQP_VAR_BLOCKS_SORTED
         bkey[s] = n < 255u ? n : 255u;
+#else
+        bkey[s] = n ? 1u : 0u;
 #endif
       }); }
     const uint32_t nB = be.order_by_work(bkey, N, bperm);
@@ -256,7 +257,7 @@ struct Pipeline {
     be.stage("join");
     // ---- a12-a25
     V.hx = be.template alloc<HitX>((uint64_t)nHits + 1); V.alns = be.template alloc<Aln>((uint64_t)nAln + 1);
-    V.dedupTab = be.template alloc<uint32_t>(2 * (uint64_t)nAln + 2); be.memset(V.dedupTab, 0, (2 * (uint64_t)nAln + 2) * 4);
+    V.dedupTab = be.template alloc<uint32_t>(2 * (uint64_t)nAln + 2); be.memset(V.dedupTab, 0, (2 * (uint64_t)nAln + 2) * 4); V.alnTail = be.template alloc<uint32_t>((uint64_t)nAln + 1);
     V.pack = be.template alloc<SlotPack>((uint64_t)N + 1);
     V.ivAdj = be.template alloc<IvAdj>((uint64_t)nHits + 1);                // a17 scratch, touched for fragments with a positive length difference only
     V.alnG = nullptr;

@@ -139,7 +139,7 @@ struct alignas(16) Aln {            // one WeightObjectAlignment (a15-a19), 48 b
   uint16_t nIv1, nIv2; int16_t maxField1, maxField2;
   uint8_t flags;                   // bit0 paired, bit1 has half 1, bit2 has half 2, bits3-4 SR read index, bit5 halves swapped relative to repr
   uint8_t tr;                      // per half h (shift 3*(h-1)): bit0 has a tr- interval, bit1 all intervals are tr-, i.e. its string is the literal "" outside the gene run
-  uint16_t tail;                   // representative only: last alignment of its duplicate chain, relative to the fragment's first alignment (a19 scratch)
+  uint8_t pad[2];
   uint32_t next;                   // next alignment of the fragment with the same key (duplicate chain, file order), UINT32_MAX = end
 };
 

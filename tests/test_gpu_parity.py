@@ -138,8 +138,9 @@ def test_switches(world, ctx, flags, field):
     check_chunk(ctx, c, o, params=p, exact=("--unweighted" in flags))      # integer counts: bit-exact
 
 
-def test_golden_appendix_b():
-    g = os.path.join(GOLDEN, "appB")
+@pytest.mark.parametrize("case", ["appB", "appC"])
+def test_golden_hand_traced(case):
+    g = os.path.join(GOLDEN, case)
     with eqp.CountContext(0).load_annotation(os.path.join(g, "anno")) as c:
         res = c.count_chunk(*read_sams(os.path.join(g, "chunk"), "se"))
         for m in eqp.MODES:

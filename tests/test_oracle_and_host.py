@@ -22,6 +22,15 @@ def test_oracle_appendix_b_golden(tools, tmp_path):
     assert st["NUMBER_MAPPED_READS"] == "3" and st["NUMBER_EXPRESSED_READS"] == "3"
 
 
+def test_oracle_junction_filter_golden(tools, tmp_path):
+    """tests/golden/appC: the per-chunk junction-map filter (a27) and a junction-reference read, traced by hand (expected/README.md)."""
+    g = os.path.join(GOLDEN, "appC")
+    run([tools["oracle"], "run", os.path.join(g, "anno"), os.path.join(g, "chunk"), "se", str(tmp_path), "--quiet"])
+    for name in ("gene.cnt", "exon.cnt", "junction.cnt"):
+        assert open(os.path.join(str(tmp_path), name)).read() == open(os.path.join(g, "expected", name)).read(), name
+    assert "JCT_24" not in open(os.path.join(str(tmp_path), "exon_junction_filtered.map")).read()
+
+
 def test_oracle_self_checks(world):
     """Invariants the reference asserts at run time hold on the oracle's intermediates."""
     c = world.chunk("se_small", 1001, 1, 3000, "se")
@@ -74,8 +83,9 @@ def test_device_functions_switches(world, flags):
         assert_counts_match(got, want, exact=("--unweighted" in flags), what="%s %s" % (flags, m))
 
 
-def test_device_functions_golden(tools, tmp_path):
-    g = os.path.join(GOLDEN, "appB")
+@pytest.mark.parametrize("case", ["appB", "appC"])
+def test_device_functions_golden(tools, tmp_path, case):
+    g = os.path.join(GOLDEN, case)
     run([tools["emu"], os.path.join(g, "anno"), os.path.join(g, "chunk"), "se", str(tmp_path)])
     for m in ("gene", "exon", "junction"):
         got = {l.split("\t")[0]: float(l.split("\t")[2]) for l in open(os.path.join(str(tmp_path), m + ".tsv"))}
