@@ -85,6 +85,11 @@ def load_library(path=None):
     lib.eqp_feature_id.argtypes = [vp, C.c_int, C.c_int64]; lib.eqp_feature_id.restype = C.c_char_p
     lib.eqp_device_vector.argtypes = [vp, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
     lib.eqp_accumulate.argtypes = [vp, vp]
+    if not hasattr(lib, "eqp_map_columns"):                              # an ABI-1 build (tools/variants.py times old builds): the common entry points only
+        lib.eqp_last_error.argtypes = [vp]; lib.eqp_last_error.restype = C.c_char_p
+        lib.eqp_destroy.argtypes = [vp]; lib.eqp_destroy.restype = None
+        lib.eqp_debug_fetch.argtypes = [vp, C.c_char_p, vp, C.c_size_t, C.POINTER(C.c_size_t)]
+        return lib
     lib.eqp_map_columns.argtypes = [vp, C.c_int]
     lib.eqp_output_row_count.argtypes = [vp, C.c_int]; lib.eqp_output_row_count.restype = C.c_int64
     lib.eqp_get_output_row.argtypes = [vp, C.c_int, C.c_int64, C.POINTER(OutputRow)]
@@ -198,6 +203,8 @@ class CountContext:
         for i, m in enumerate(MODES):
             n = self.lib.eqp_feature_count(self.h, i)
             self.feature_ids[m] = [self.lib.eqp_feature_id(self.h, i, k).decode() for k in range(n)]
+            if not hasattr(self.lib, "eqp_map_columns"):
+                continue
             self.map_columns[m] = self.lib.eqp_map_columns(self.h, i)
             rows = []
             for k in range(self.lib.eqp_output_row_count(self.h, i)):
