@@ -155,7 +155,9 @@ EQP_HD uint32_t dedupe_fragment(const CountView& V, uint32_t a0, uint32_t a1) {
     if (nA <= 4) {                                                         // tiny fragment: compare with the earlier representatives directly
       for (uint32_t p = a0; p < a; p++) {
         const Aln& q = V.alns[p]; if (q.hit0 == q.hit1 || (GENE ? V.alnG[p].repr : q.repr) != p) continue;
-        if (keys_equal(V.hx, q, GENE ? V.alnG[p].key : q.key, al, key, GENE, sw)) { found = p; break; }
+        const uint64_t qk = GENE ? V.alnG[p].key : q.key;
+        if (qk != key) continue;                                             // the hash decides almost every comparison without the call
+        if (keys_equal(V.hx, q, qk, al, key, GENE, sw)) { found = p; break; }
       }
     } else {                                                               // per-fragment open-addressing table of representatives (2 slots per alignment, zeroed)
       uint32_t s = (uint32_t)(((key * 0x9E3779B97F4A7C15ULL) >> 32) % cap);
@@ -163,7 +165,8 @@ EQP_HD uint32_t dedupe_fragment(const CountView& V, uint32_t a0, uint32_t a1) {
         uint32_t e = tab[s];
         if (!e) { tab[s] = a - a0 + 1; break; }
         const uint32_t p = a0 + e - 1;
-        if (keys_equal(V.hx, V.alns[p], GENE ? V.alnG[p].key : V.alns[p].key, al, key, GENE, sw)) { found = p; break; }   // insertion order along the probe path = file order: first equal key wins
+        const uint64_t pk = GENE ? V.alnG[p].key : V.alns[p].key;
+        if (pk == key && keys_equal(V.hx, V.alns[p], pk, al, key, GENE, sw)) { found = p; break; }   // insertion order along the probe path = file order: first equal key wins
         s = s + 1 == cap ? 0 : s + 1;
       }
     }
