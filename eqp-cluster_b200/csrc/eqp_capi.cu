@@ -133,11 +133,20 @@ struct eqp_ctx {
   void feed_drop() { for (int f = 0; f < 3; f++) { if (feed.dev[f]) cudaFreeAsync(feed.dev[f], copyStream ? copyStream : stream); } feed = Feed(); }
   // NCCL communicator of this context (one rank per context)
   nccl_comm_t comm = nullptr; int commRanks = 0, commRank = -1;
+  // device address of g_noalloc_scratch on this context's device (eqp_tokenize_noalloc), resolved in eqp_create
+  unsigned long long* noallocScratch = nullptr; cudaError_t noallocRc = cudaErrorNotReady;
   void pin(void* p, size_t bytes) { if (bytes && cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) pinned.push_back(p); else cudaGetLastError(); }
   void unpin() { for (void* p : pinned) cudaHostUnregister(p); pinned.clear(); }
 };
 
 static thread_local std::string g_err;                              // errors raised before a ctx exists
+
+// Scratch of eqp_tokenize_noalloc: the tokenizer's tile states [nTiles], newline total, tile ticket, and (last two words) the error
+// slot + fragment id range.  One copy per GPU that loads the library.  In host code this NAME is only a stand-in for the symbol:
+// the device address comes from cudaGetSymbolAddress (eqp_create, with the context's device current) and is what the kernel gets.
+static const size_t kNoallocWords = EQP_NOALLOC_SCRATCH_BYTES / 8;
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[EQP_NOALLOC_SCRATCH_BYTES / 8];
+static_assert((EQP_NOALLOC_MAX_TEXT_BYTES + 15) / TK_OWNED + 1 + 2 + 2 <= EQP_NOALLOC_SCRATCH_BYTES / 8, "scratch array holds the largest accepted text's tile states");
 
 static int fail(eqp_ctx* ctx, int code, const std::string& msg) { if (ctx) ctx->err = msg; else g_err = msg; return code; }
 
@@ -168,6 +177,8 @@ int eqp_create(int device, eqp_ctx** out) {
     cudaMemPool_t pool; EQP_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
     uint64_t keep = ~0ULL; EQP_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));   // keep chunk buffers cached between chunks
     EQP_CUDA(cudaEventCreate(&c->ev0)); EQP_CUDA(cudaEventCreate(&c->ev1));
+    c->noallocRc = cudaGetSymbolAddress((void**)&c->noallocScratch, g_noalloc_scratch);   // this device's copy; a failure is reported by eqp_tokenize_noalloc
+    if (c->noallocRc != cudaSuccess) { c->noallocScratch = nullptr; cudaGetLastError(); }
     *out = c.release(); return EQP_OK;
   } catch (const std::exception& ex) { return fail(nullptr, EQP_ERR_CUDA, ex.what()); }
 }
@@ -519,6 +530,52 @@ int eqp_debug_decode(eqp_ctx* ctx, const uint8_t* sam, size_t len, int misalign,
       snprintf(buf, sizeof buf, "\t%u\t%u\n", sl[i], rf[i]); out += buf;
     }
     *text = out.c_str(); *textLen = out.size(); return EQP_OK;
+  } catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+
+// No counterpart in the reference (include/eqp_count.h): the tokenizer kernel with its scratch in g_noalloc_scratch and its output in the
+// caller's buffer.  Nothing here allocates: cudaMemsetAsync, the launch, two small copies to host stack variables, a stream synchronise.
+int eqp_tokenize_noalloc(eqp_ctx* ctx, const uint8_t* devSam, size_t len, uint64_t maxLines, void* devOut, size_t devOutBytes, eqp_record_columns* cols) {
+  if (!ctx || !cols || (len && !devSam)) return fail(ctx, EQP_ERR_ARG, "eqp_tokenize_noalloc: null argument");
+  memset(cols, 0, sizeof *cols);
+  if (!ctx->annoLoaded) return fail(ctx, EQP_ERR_ARG, "eqp_tokenize_noalloc: call eqp_load_annotation first");
+  if (len > EQP_NOALLOC_MAX_TEXT_BYTES) return fail(ctx, EQP_ERR_ARG, "eqp_tokenize_noalloc: text of " + std::to_string(len) + " bytes exceeds EQP_NOALLOC_MAX_TEXT_BYTES (" + std::to_string(EQP_NOALLOC_MAX_TEXT_BYTES) + "): use eqp_count_chunk");
+  if (maxLines == 0 || maxLines > 0xFFFFFFF0ull) return fail(ctx, EQP_ERR_ARG, "eqp_tokenize_noalloc: max_lines out of range");
+  if (!devOut || devOutBytes < EQP_NOALLOC_OUT_BYTES(maxLines)) return fail(ctx, EQP_ERR_ARG, "eqp_tokenize_noalloc: dev_out is smaller than EQP_NOALLOC_OUT_BYTES(max_lines)");
+  if (ctx->noallocRc != cudaSuccess || !ctx->noallocScratch) return fail(ctx, EQP_ERR_CUDA, std::string("eqp_tokenize_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(ctx->noallocRc));
+  try {
+    EQP_CUDA(cudaSetDevice(ctx->device));
+    // columns inside the caller's buffer, each on a 256-byte boundary
+    uintptr_t base = (uintptr_t)devOut, cur = base;
+    auto col = [&](uint64_t& off, size_t bytes) { cur = (cur + 255) & ~(uintptr_t)255; off = cur - base; void* p = (void*)cur; cur += bytes; return p; };
+    const size_t cap = (size_t)maxLines;
+    SamView S{}; S.text = (const char*)devSam; S.len = len; S.hi = nullptr;
+    S.lineOff = (uint64_t*)col(cols->line_off, (cap + 1) * 8);
+    S.frag = (uint32_t*)col(cols->frag, cap * 4); S.ref = (int32_t*)col(cols->ref, cap * 4); S.pos = (int32_t*)col(cols->pos, cap * 4);
+    S.rnext = (int32_t*)col(cols->rnext, cap * 4); S.pnext = (int32_t*)col(cols->pnext, cap * 4);
+    S.flag = (uint16_t*)col(cols->flag, cap * 2); S.nm = (int16_t*)col(cols->nm, cap * 2); S.cigOff = (uint16_t*)col(cols->cig_off, cap * 2);
+    S.cigLen = (uint16_t*)col(cols->cig_len, cap * 2); S.seqLen = (uint16_t*)col(cols->seq_len, cap * 2); S.cigM = (uint16_t*)col(cols->cig_m, cap * 2);
+    S.rf = (uint8_t*)col(cols->rf, cap);
+    if (cur - base > devOutBytes) return fail(ctx, EQP_ERR_ARG, "eqp_tokenize_noalloc: dev_out is too small for its alignment (give it EQP_NOALLOC_OUT_BYTES(max_lines), 256-byte aligned)");
+    if (!len) return EQP_OK;
+    const uint64_t vEnd = len + ((uintptr_t)devSam & 15), nTiles = vEnd / TK_OWNED + 1;
+    if (nTiles + 4 > kNoallocWords) return fail(ctx, EQP_ERR_ARG, "eqp_tokenize_noalloc: text needs more tile states than the scratch array holds");
+    unsigned long long* status = ctx->noallocScratch;                    // the device address, never &g_noalloc_scratch
+    uint32_t* err = (uint32_t*)(status + kNoallocWords - 2);              // err[0..1] code/detail, err[2..3] fragment id min/max
+    EQP_CUDA(cudaMemsetAsync(status, 0, kNoallocWords * 8, ctx->stream)); // the array keeps the previous call's states: everything starts at zero
+    EQP_CUDA(cudaMemsetAsync(err + 2, 0xFF, 4, ctx->stream));
+    EQP_CUDA(cudaFuncSetAttribute(k_tokenize_sam, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TokShared)));
+    k_tokenize_sam<<<(unsigned)nTiles, TK_THREADS, sizeof(TokShared), ctx->stream>>>(ctx->A, S, (uint32_t)cap, (uint32_t)nTiles, status, (uint32_t*)(status + nTiles + 1), status + nTiles, err, err + 2);
+    EQP_CUDA(cudaGetLastError());
+    unsigned long long tot = 0; uint32_t h[2] = {0, 0}; char last = 0;
+    EQP_CUDA(cudaMemcpyAsync(&tot, status + nTiles, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    EQP_CUDA(cudaMemcpyAsync(h, err, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    EQP_CUDA(cudaMemcpyAsync(&last, devSam + len - 1, 1, cudaMemcpyDeviceToHost, ctx->stream));
+    EQP_CUDA(cudaStreamSynchronize(ctx->stream));
+    const uint64_t nl = tot - 1, lines = last == '\n' ? nl : nl + 1;      // tot counts the virtual newline in front of text[0]
+    cols->n_lines = lines; cols->err_code = h[0]; cols->err_detail = h[1];
+    if (lines > cap) return fail(ctx, EQP_ERR_ARG, "eqp_tokenize_noalloc: the text has " + std::to_string(lines) + " lines, max_lines is " + std::to_string(cap));
+    return EQP_OK;
   } catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
 }
 

@@ -54,10 +54,22 @@ class OutputRow(C.Structure):
     _fields_ = [("id", C.c_char_p), ("feature", C.c_int64), ("act", C.c_int64), ("always", C.c_int32), ("reserved", C.c_int32)]
 
 
+class RecordColumns(C.Structure):
+    """eqp_record_columns: byte offsets of the decoded-record columns inside the caller's device buffer."""
+    _fields_ = [(k, C.c_uint64) for k in ("line_off", "frag", "ref", "pos", "rnext", "pnext", "flag", "nm", "cig_off", "cig_len", "seq_len", "cig_m", "rf", "n_lines")] + \
+               [("err_code", C.c_uint32), ("err_detail", C.c_uint32)]
+
+
 EXPORTS = ("eqp_version", "eqp_default_params", "eqp_create", "eqp_load_annotation", "eqp_annotation_bytes", "eqp_count_chunk", "eqp_prefetch_chunk",
            "eqp_feature_count", "eqp_feature_id", "eqp_map_columns", "eqp_output_row_count", "eqp_get_output_row", "eqp_device_vector", "eqp_accumulate",
            "eqp_wide_to_double", "eqp_comm_id", "eqp_comm_init", "eqp_reduce_sample", "eqp_reduce_sample_local", "eqp_chunk_begin", "eqp_chunk_feed",
-           "eqp_chunk_end", "eqp_debug_fetch", "eqp_debug_decode", "eqp_last_error", "eqp_destroy")
+           "eqp_chunk_end", "eqp_debug_fetch", "eqp_debug_decode", "eqp_tokenize_noalloc", "eqp_last_error", "eqp_destroy")
+NOALLOC_MAX_TEXT_BYTES = 128 << 20
+
+
+def noalloc_out_bytes(max_lines):
+    """EQP_NOALLOC_OUT_BYTES(max_lines) of include/eqp_count.h."""
+    return max_lines * 41 + 8 + 13 * 256
 COMM_ID_BYTES = 128
 
 _lib = None
@@ -103,6 +115,8 @@ def load_library(path=None):
     lib.eqp_chunk_end.argtypes = [vp, C.POINTER(Params), C.POINTER(Counts)]
     lib.eqp_debug_fetch.argtypes = [vp, C.c_char_p, vp, C.c_size_t, C.POINTER(C.c_size_t)]
     lib.eqp_debug_decode.argtypes = [vp, vp, C.c_size_t, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    if hasattr(lib, "eqp_tokenize_noalloc"):
+        lib.eqp_tokenize_noalloc.argtypes = [vp, vp, C.c_size_t, C.c_uint64, vp, C.c_size_t, C.POINTER(RecordColumns)]
     lib.eqp_last_error.argtypes = [vp]; lib.eqp_last_error.restype = C.c_char_p
     lib.eqp_destroy.argtypes = [vp]; lib.eqp_destroy.restype = None
     lib.eqp_annotation_bytes.argtypes = [vp]; lib.eqp_annotation_bytes.restype = C.c_int64
@@ -285,6 +299,13 @@ class CountContext:
         self._check(self.lib.eqp_debug_decode(self.h, addr, n, misalign, C.byref(text), C.byref(tlen), C.byref(ec), C.byref(ed)))
         rows = C.string_at(text, tlen.value).decode().splitlines() if tlen.value else []
         return rows, ec.value, ed.value
+
+    def tokenize_noalloc(self, dev_sam_ptr, length, max_lines, dev_out_ptr, dev_out_bytes):
+        """eqp_tokenize_noalloc: device text in, decoded-record columns in the caller's device buffer out; performs no allocation on the
+        device.  Returns the RecordColumns (offsets, n_lines, err_code, err_detail)."""
+        cols = RecordColumns()
+        self._check(self.lib.eqp_tokenize_noalloc(self.h, C.c_void_p(dev_sam_ptr), length, max_lines, C.c_void_p(dev_out_ptr), dev_out_bytes, C.byref(cols)))
+        return cols
 
     def __del__(self):
         try:

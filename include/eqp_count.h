@@ -180,6 +180,34 @@ int  eqp_debug_fetch(eqp_ctx* ctx, const char* what, void* dst, size_t dst_bytes
 int  eqp_debug_decode(eqp_ctx* ctx, const uint8_t* sam, size_t len, int misalign, const char** text, size_t* text_len,
                       uint32_t* err_code, uint32_t* err_detail);
 
+/* ---- allocation-free tokenizer call.  This entry point has NO counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  It runs the a1/a2 tokenizer kernel (the one eqp_count_chunk / eqp_debug_decode launch) on ONE SAM text
+ * that is already in device memory and writes the decoded records into a device buffer the CALLER owns.  The kernel's scratch
+ * (tile look-back states, tile ticket, newline total, error slot) lives in a file-scope device array of the library
+ * (EQP_NOALLOC_SCRATCH_BYTES per GPU that loads the library, held until the process exits), so the call performs no cudaMalloc /
+ * cudaFree / pool allocation.  Limits: len <= EQP_NOALLOC_MAX_TEXT_BYTES (larger texts are refused with EQP_ERR_ARG);
+ * dev_out_bytes >= EQP_NOALLOC_OUT_BYTES(max_lines); a text with more than max_lines lines is refused with EQP_ERR_ARG
+ * (cols->n_lines then tells how many it has).  HI:i: tags are rejected as in the default flow (err_code 2).
+ * All calls on one GPU share the scratch array: the call clears it, runs on the context's stream and returns when the kernel
+ * has finished, so calls in sequence are safe; calls that OVERLAP on one GPU (two contexts / two host threads) race.
+ * cols receives the byte offset of every column inside dev_out (element types as named; a column has max_lines entries,
+ * line_off max_lines + 1), the line count and the device error slot (0 = none; records are undefined after an error).
+ * Columns other than frag / rf are only written for record lines (rf bit 0). */
+#define EQP_NOALLOC_MAX_TEXT_BYTES ((size_t)128 << 20)
+#define EQP_NOALLOC_SCRATCH_BYTES  36864
+#define EQP_NOALLOC_OUT_BYTES(max_lines) ((size_t)(max_lines) * 41 + 8 + 13 * 256)
+typedef struct eqp_record_columns {
+  uint64_t line_off;                                    /* uint64: text offset of each line; entry i + 1 minus 1 = end of line i */
+  uint64_t frag, ref, pos, rnext, pnext;                /* uint32 fragment id; int32 reference index (-1 "*"), POS, RNEXT index, PNEXT */
+  uint64_t flag, nm, cig_off, cig_len, seq_len, cig_m;  /* uint16 FLAG; int16 NM (-1 none); uint16 CIGAR offset in line / length; SEQ length; n of "<n>M" or 0xFFFF */
+  uint64_t rf;                                          /* uint8: bit0 record, bit1 mapped, bit2 has mate, bits3-4 read index */
+  uint64_t n_lines;
+  uint32_t err_code, err_detail;
+} eqp_record_columns;
+int  eqp_tokenize_noalloc(eqp_ctx* ctx, const uint8_t* dev_sam, size_t len, uint64_t max_lines,
+                          void* dev_out, size_t dev_out_bytes, eqp_record_columns* cols);
+
 const char* eqp_last_error(eqp_ctx* ctx);
 void eqp_destroy(eqp_ctx* ctx);
 
