@@ -142,6 +142,9 @@ EQP_HD uint64_t hit_group_key(const HitX& x) { return ((uint64_t)((x.flags & 1) 
 // a19 + a20 for one fragment: dedupe its alignments by key (first in file order is the representative, later ones are chained to it)
 // and count the representatives.  GENE = false: keys of the weight pass and of the exon / junction runs, state in Aln; GENE = true: keys
 // of the gene run, state in AlnG (only fragments with tr- exon hits need it: without a tr- interval the two keys are the same string).
+// Cost (bisect r03l, 25M reads on the round-1 world, kernel fragment_weight): 22.98 ms as built; 6.71 ms with this loop skipped; 21.03 ms with
+// round-1 style rank equality instead of the token lists; the hash pre-check in front of keys_equal: 24.1 vs 24.2 ms on the shaped world.  The
+// loop is bound by the scattered 48-byte Aln reads of the fragment's alignments, not by the comparisons.
 template <bool GENE>
 EQP_HD uint32_t dedupe_fragment(const CountView& V, uint32_t a0, uint32_t a1) {
   int left = 0, right = 0; bool hasTr = false; uint32_t nA = a1 - a0, cap = 2 * nA; uint32_t* tab = V.dedupTab + 2 * (uint64_t)a0;
