@@ -16,6 +16,8 @@ CLI_PATH = os.path.join(LIB_DIR, "eqp_compute_counts")
 ORACLE_BIN = os.path.join(ROOT, "oracle", "_build", "eqp_oracle")
 WORLDGEN_BIN = os.path.join(ROOT, "tools", "_build", "worldgen")
 EMU_BIN = os.path.join(ROOT, "tools", "_build", "eqp_emu")
+INFLATE_EMU_BIN = os.path.join(ROOT, "tools", "_build", "inflate_emu")
+PGZIP_BIN = os.path.join(ROOT, "tools", "_build", "pgzip")
 
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "--extended-lambda",
               "-Xcompiler", "-fPIC", "-shared", "-diag-suppress", "550"]
@@ -83,6 +85,11 @@ def build_tools(force=False):
         _run(["g++", "-std=c++17", "-O2", "-o", EMU_BIN, emu_src, "-lz"])
         _run(["g++", "-std=c++17", "-O2", "-DEQP_FLAT_SCAN=0", "-o", EMU_BIN + "_chain", emu_src, "-lz"])   # duplicate-chain walk for every fragment
         _run(["g++", "-std=c++17", "-O2", "-DEQP_FS_SMALL=2", "-DEQP_FT_SMALL=3", "-o", EMU_BIN + "_retry", emu_src, "-lz"])   # tiny small tables: most fragments take the large-table retry
+    zf_src = os.path.join(ROOT, "tests", "emu", "inflate_emu.cpp")
+    if force or _newer([zf_src, os.path.join(CSRC, "eqp_inflate.h"), os.path.join(CSRC, "eqp_types.h")], INFLATE_EMU_BIN):
+        _run(["g++", "-std=c++17", "-O2", "-o", INFLATE_EMU_BIN, zf_src])
+    if force or _newer([os.path.join(d, "pgzip.cpp")], PGZIP_BIN):
+        _run(["g++", "-std=c++17", "-O2", "-o", PGZIP_BIN, os.path.join(d, "pgzip.cpp"), "-lz", "-lpthread"])
     return WORLDGEN_BIN, EMU_BIN
 
 

@@ -8,6 +8,7 @@
 #include "../../include/eqp_count.h"
 #include "eqp_cuda_backend.cuh"
 #include "eqp_nccl.h"
+#include "eqp_inflate.cuh"
 
 using namespace eqpb;
 
@@ -131,6 +132,8 @@ struct eqp_ctx {
     feed.dev[f] = (char*)d; feed.cap[f] = cap;
   }
   void feed_drop() { for (int f = 0; f < 3; f++) { if (feed.dev[f]) cudaFreeAsync(feed.dev[f], copyStream ? copyStream : stream); } feed = Feed(); }
+  // device inflate (eqp_chunk_feed_gz / eqp_count_chunk_gz): compressed bytes travel on their own stream, the inflate runs on the copy stream
+  cudaStream_t gzStream = nullptr; eqp_inflate_info lastInflate[3] = {};
   // NCCL communicator of this context (one rank per context)
   nccl_comm_t comm = nullptr; int commRanks = 0, commRank = -1;
   // device address of g_noalloc_scratch on this context's device (eqp_tokenize_noalloc), resolved in eqp_create
@@ -349,6 +352,90 @@ int eqp_chunk_end(eqp_ctx* ctx, const eqp_params* p, eqp_counts* out) {
     return run_chunk(ctx, p, text, len, ready, out);
   } catch (const CudaError& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
   catch (const std::exception& ex) { return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+
+// ---- .sam.gz input inflated on the device (eqp_inflate.cuh).  The compressed bytes of one gzip member go to the device on gzStream; the
+// inflate runs on the copy stream, on which the feed buffers live, and appends its text to the input's feed buffer.
+static size_t inflate_scratch_budget() {
+  size_t budget = (size_t)24 << 30;
+  if (const char* e = getenv("EQP_INFLATE_SCRATCH_GB")) { double g = atof(e); if (g >= 0.001) budget = (size_t)(g * (double)((size_t)1 << 30)); }
+  size_t freeB = 0, totalB = 0;
+  if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess && freeB > ((size_t)4 << 30)) budget = std::min(budget, (freeB - ((size_t)2 << 30)) / 2);
+  return budget;
+}
+static uint64_t env_u64(const char* name, uint64_t dflt) { const char* e = getenv(name); return e && *e ? strtoull(e, nullptr, 10) : dflt; }
+static char* gz_upload(eqp_ctx* ctx, const uint8_t* gz, size_t len, cudaEvent_t* ready) {
+  if (!ctx->gzStream) EQP_CUDA(cudaStreamCreateWithFlags(&ctx->gzStream, cudaStreamNonBlocking));
+  void* d = nullptr; EQP_CUDA(cudaMallocAsync(&d, len + 16, ctx->gzStream));
+  EQP_CUDA(cudaMemsetAsync((char*)d + (len & ~(size_t)3), 0, len + 16 - (len & ~(size_t)3), ctx->gzStream));       // the words past the last byte read as zero
+  EQP_CUDA(cudaMemcpyAsync(d, gz, len, cudaMemcpyHostToDevice, ctx->gzStream));
+  EQP_CUDA(cudaEventCreateWithFlags(ready, cudaEventDisableTiming)); EQP_CUDA(cudaEventRecord(*ready, ctx->gzStream));
+  return (char*)d;
+}
+static int gz_inflate_into_feed(eqp_ctx* ctx, int f, const uint8_t* gz, const char* zDev, size_t len, cudaEvent_t ready) {
+  eqp_ctx::Feed& F = ctx->feed; const size_t base = F.len[f];
+  EQP_CUDA(cudaStreamWaitEvent(ctx->copyStream, ready, 0));
+  try {
+    ctx->feed_reserve(f, base + std::max<size_t>(3 * len, 1));
+    zf::InflateInfo info = zf::device_inflate(gz, (const uint8_t*)zDev, len, ctx->copyStream,
+        [&](uint64_t n) { ctx->feed_reserve(f, base + (size_t)n); return (uint8_t*)F.dev[f] + base; },
+        env_u64("EQP_INFLATE_SEG", 65536), 0, inflate_scratch_budget());
+    F.len[f] = base + (size_t)info.outBytes;
+    eqp_inflate_info& o = ctx->lastInflate[f];
+    o.gz_bytes = len; o.text_bytes = info.outBytes; o.segments = info.nSeg; o.chain = info.nChain; o.bogus_starts = info.nBogus; o.waves = info.nWaves;
+    o.search_ms = info.msSearch; o.decode_ms = info.msDecode; o.resolve_ms = info.msResolve; o.emit_ms = info.msEmit;
+    return EQP_OK;
+  } catch (const zf::InflateError& e) { return fail(ctx, e.unsupported ? EQP_ERR_UNSUPPORTED : EQP_ERR_FORMAT, "gzip input " + std::to_string(f) + ": " + e.msg); }
+}
+
+int eqp_chunk_feed_gz(eqp_ctx* ctx, int input, const uint8_t* gz, size_t len) {
+  if (!ctx || input < 0 || input > 2 || !gz || len < 18) return fail(ctx, EQP_ERR_ARG, "eqp_chunk_feed_gz: bad argument");
+  if (!ctx->feed.active) return fail(ctx, EQP_ERR_ARG, "eqp_chunk_feed_gz: call eqp_chunk_begin first");
+  cudaEvent_t ready = nullptr; char* d = nullptr;
+  try {
+    EQP_CUDA(cudaSetDevice(ctx->device));
+    d = gz_upload(ctx, gz, len, &ready);
+    int rc = gz_inflate_into_feed(ctx, input, gz, d, len, ready);
+    cudaFreeAsync(d, ctx->copyStream); cudaEventDestroy(ready);
+    return rc;
+  } catch (const std::exception& ex) { if (d) cudaFreeAsync(d, ctx->copyStream); if (ready) cudaEventDestroy(ready); return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+}
+
+int eqp_count_chunk_gz(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_gz, size_t t_len, const uint8_t* j_gz, size_t j_len, const uint8_t* g_gz, size_t g_len, eqp_counts* out) {
+  if (!ctx || !p || !out) return fail(ctx, EQP_ERR_ARG, "eqp_count_chunk_gz: null argument");
+  const uint8_t* gz[3] = {t_gz, j_gz, g_gz}; const size_t len[3] = {t_len, j_len, g_len};
+  for (int f = 0; f < 3; f++) if (len[f] && (!gz[f] || len[f] < 18)) return fail(ctx, EQP_ERR_ARG, "eqp_count_chunk_gz: bad gzip buffer");
+  if (int rc = eqp_chunk_begin(ctx, 0, 0, 0)) return rc;
+  cudaEvent_t ready[3] = {nullptr, nullptr, nullptr}; char* d[3] = {nullptr, nullptr, nullptr}; int rc = EQP_OK;
+  try {
+    for (int f = 0; f < 3; f++) if (len[f]) d[f] = gz_upload(ctx, gz[f], len[f], &ready[f]);       // all three copies are queued before the first inflate
+    for (int f = 0; f < 3 && rc == EQP_OK; f++) if (len[f]) rc = gz_inflate_into_feed(ctx, f, gz[f], d[f], len[f], ready[f]);
+  } catch (const std::exception& ex) { rc = fail(ctx, EQP_ERR_CUDA, ex.what()); }
+  if (ctx->gzStream && rc != EQP_OK) cudaStreamSynchronize(ctx->gzStream);
+  for (int f = 0; f < 3; f++) { if (d[f]) cudaFreeAsync(d[f], ctx->copyStream); if (ready[f]) cudaEventDestroy(ready[f]); }
+  if (rc != EQP_OK) { ctx->feed_drop(); return rc; }
+  return eqp_chunk_end(ctx, p, out);
+}
+
+// test tap: inflate one member on the device and copy the text back (dst may be null to ask for the size)
+int eqp_debug_inflate(eqp_ctx* ctx, const uint8_t* gz, size_t len, uint8_t* dst, size_t dst_bytes, size_t* n_text) {
+  if (!ctx || !gz || !n_text) return fail(ctx, EQP_ERR_ARG, "eqp_debug_inflate: null argument");
+  if (int rc = eqp_chunk_begin(ctx, 0, 0, 0)) return rc;
+  int rc = eqp_chunk_feed_gz(ctx, 0, gz, len);
+  if (rc == EQP_OK) {
+    *n_text = ctx->feed.len[0];
+    if (dst && dst_bytes >= ctx->feed.len[0] && ctx->feed.len[0]) {
+      if (cudaMemcpyAsync(dst, ctx->feed.dev[0], ctx->feed.len[0], cudaMemcpyDeviceToHost, ctx->copyStream) != cudaSuccess || cudaStreamSynchronize(ctx->copyStream) != cudaSuccess)
+        rc = fail(ctx, EQP_ERR_CUDA, "eqp_debug_inflate: copy to host failed");
+    } else if (dst && dst_bytes < ctx->feed.len[0]) rc = fail(ctx, EQP_ERR_ARG, "eqp_debug_inflate: dst too small");
+  }
+  cudaStreamSynchronize(ctx->copyStream); ctx->feed_drop();
+  return rc;
+}
+
+int eqp_last_inflate(eqp_ctx* ctx, int input, eqp_inflate_info* out) {
+  if (!ctx || !out || input < 0 || input > 2) return fail(ctx, EQP_ERR_ARG, "eqp_last_inflate: bad argument");
+  *out = ctx->lastInflate[input]; return EQP_OK;
 }
 
 int eqp_prefetch_chunk(eqp_ctx* ctx, const uint8_t* t_sam, size_t t_len, const uint8_t* j_sam, size_t j_len, const uint8_t* g_sam, size_t g_len) {
@@ -595,6 +682,7 @@ void eqp_destroy(eqp_ctx* ctx) {
   if (ctx->vec) cudaFree(ctx->vec);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->gzStream) { cudaStreamSynchronize(ctx->gzStream); cudaStreamDestroy(ctx->gzStream); }
   if (ctx->copyStream) cudaStreamDestroy(ctx->copyStream);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;

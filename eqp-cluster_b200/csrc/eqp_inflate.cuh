@@ -1,0 +1,220 @@
+// Kernels and host driver of the device inflate (eqp_inflate.h has the algorithm and the per-thread functions).
+//   k_zf_search   thread per segment: first plausible dynamic-block start inside the segment
+//   k_zf_decode   thread per listed segment: blocks -> 16-bit symbols in the segment's scratch region (Huffman tables in shared memory,
+//                 interleaved over the CTA's threads)
+//   k_zf_resolve  ONE CTA per stream walks the verified chain: markers in every segment's last 32 K symbols -> bytes, 32 KB window in shared memory
+//   k_zf_emit     CTA per (segment, slice): pass 0 writes the tails' bytes, pass 1 everything else (markers read the text in front of the segment)
+#pragma once
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <string>
+#include <vector>
+#include "eqp_inflate.h"
+
+namespace eqpb {
+namespace zf {
+
+static const int ZF_THREADS = 128;                                   // per CTA of search / decode: 768 bytes of tables per thread
+static const int ZF_TABLE_U16 = 16 + 16 + 16 + 16 + 288 + 32;        // limit/base of both codes + symbols
+static const size_t ZF_SMEM = (size_t)ZF_TABLE_U16 * ZF_THREADS * 2;
+
+__device__ __forceinline__ void zf_tables(uint16_t* sm, Huff& hl, Huff& hd) {
+  const int t = threadIdx.x, S = ZF_THREADS;
+  hl.limit = sm + t; hl.base = (int16_t*)(sm + 16 * S + t); hd.limit = sm + 32 * S + t; hd.base = (int16_t*)(sm + 48 * S + t);
+  hl.sym = sm + 64 * S + t; hd.sym = sm + (64 + 288) * S + t; hl.stride = hd.stride = S;
+}
+
+__global__ void __launch_bounds__(ZF_THREADS) k_zf_search(const uint32_t* w, uint64_t nWords, uint64_t totalBits, uint64_t dataBit, uint64_t segBits, uint32_t nSeg, uint64_t* segStart) {
+  extern __shared__ __align__(16) uint16_t zf_sm[];
+  Huff hl, hd; zf_tables(zf_sm, hl, hd);
+  uint32_t i = blockIdx.x * ZF_THREADS + threadIdx.x;
+  if (i >= nSeg) return;
+  if (i == 0) { segStart[0] = dataBit; return; }
+  uint64_t from = dataBit + (uint64_t)i * segBits, to = from + segBits; if (to > totalBits) to = totalBits;
+  segStart[i] = from < to ? find_block_start(w, nWords, from, to, totalBits, hl, hd) : ZF_NONE;
+}
+
+// one thread per listed segment.  WRITE = false: the counting pass (block boundaries and output lengths, no memory traffic besides the
+// compressed words); WRITE = true: 16-bit symbols into the segment's exact-size scratch region.
+struct DecodeItem { uint64_t sym, cap; uint32_t seg, pad; };
+template <bool WRITE>
+__global__ void __launch_bounds__(ZF_THREADS) k_zf_decode(const uint32_t* w, uint64_t nWords, uint64_t totalBits, const uint64_t* segStart, const uint8_t* bogus, uint32_t nSeg,
+                                                          const DecodeItem* list, uint32_t nList, uint16_t* scratch, SegOut* res) {
+  extern __shared__ __align__(16) uint16_t zf_sm[];
+  Huff hl, hd; zf_tables(zf_sm, hl, hd);
+  uint32_t k = blockIdx.x * ZF_THREADS + threadIdx.x;
+  if (k >= nList) return;
+  const DecodeItem it = list[k];
+  Sink s; s.out = WRITE ? scratch + it.sym : nullptr; s.o = 0; s.cap = it.cap; s.window = it.seg != 0; s.status = 0;
+  res[k] = inflate_segment<WRITE>(w, nWords, totalBits, segStart, nSeg, it.seg, bogus, hl, hd, s);
+}
+
+struct ChainSeg { uint64_t sym; uint64_t abs; uint64_t len; };       // scratch offset (symbols), position in the stream's output, symbols
+
+// one CTA: the chain in order.  win[x & 32767] holds output byte x for the 32 K bytes in front of the current segment.
+static const int ZF_RES_THREADS = 1024;
+__global__ void __launch_bounds__(ZF_RES_THREADS) k_zf_resolve(uint16_t* scratch, const ChainSeg* chain, uint32_t nChain, uint8_t* winCarry, uint32_t* err) {
+  __shared__ uint8_t win[ZF_WINDOW];
+  const uint32_t t = threadIdx.x;
+  for (uint32_t k = t; k < ZF_WINDOW; k += ZF_RES_THREADS) win[k] = winCarry[k];
+  __syncthreads();
+  for (uint32_t c = 0; c < nChain; c++) {
+    const ChainSeg cs = chain[c];
+    const uint32_t T = cs.len < ZF_WINDOW ? (uint32_t)cs.len : ZF_WINDOW;
+    uint16_t* tail = scratch + cs.sym + (cs.len - T);
+    const uint64_t absTail = cs.abs + (cs.len - T);
+    uint8_t r[ZF_WINDOW / ZF_RES_THREADS];
+#pragma unroll
+    for (int q = 0; q < (int)(ZF_WINDOW / ZF_RES_THREADS); q++) {
+      const uint32_t k = t + q * ZF_RES_THREADS;
+      if (k < T) {
+        uint16_t v = tail[k];
+        if (v & 0x8000u) {                                             // byte w of the window in front of the segment
+          const uint64_t a = cs.abs - ZF_WINDOW + (v & 0x7FFFu);
+          if (cs.abs < ZF_WINDOW && (v & 0x7FFFu) < ZF_WINDOW - cs.abs) atomicExch(err, 1u);   // reaches in front of the stream
+          v = win[a & (ZF_WINDOW - 1)]; tail[k] = v;
+        }
+        r[q] = (uint8_t)v;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < (int)(ZF_WINDOW / ZF_RES_THREADS); q++) { const uint32_t k = t + q * ZF_RES_THREADS; if (k < T) win[(absTail + k) & (ZF_WINDOW - 1)] = r[q]; }
+    __syncthreads();
+  }
+  for (uint32_t k = t; k < ZF_WINDOW; k += ZF_RES_THREADS) winCarry[k] = win[k];
+}
+
+// pass 0: the last min(len, 32 K) symbols of every chain segment (marker-free after k_zf_resolve); pass 1: the symbols in front of them
+static const uint32_t ZF_EMIT_SLICE = 1u << 16;
+__global__ void __launch_bounds__(256) k_zf_emit(const uint16_t* scratch, const ChainSeg* chain, const uint32_t* sliceSeg, const uint32_t* sliceIdx, int pass, uint8_t* text) {
+  const ChainSeg cs = chain[sliceSeg[blockIdx.x]];
+  const uint64_t T = cs.len < ZF_WINDOW ? cs.len : ZF_WINDOW, head = cs.len - T;
+  uint64_t k0 = (uint64_t)sliceIdx[blockIdx.x] * ZF_EMIT_SLICE, k1 = k0 + ZF_EMIT_SLICE;
+  if (pass == 0) { k0 += head; k1 += head; if (k1 > cs.len) k1 = cs.len; } else if (k1 > head) k1 = head;
+  const uint16_t* src = scratch + cs.sym; uint8_t* dst = text + cs.abs;
+  for (uint64_t k = k0 + threadIdx.x; k < k1; k += 256) {
+    uint16_t v = src[k];
+    if (v & 0x8000u) v = text[cs.abs - ZF_WINDOW + (v & 0x7FFFu)];
+    dst[k] = (uint8_t)v;
+  }
+}
+
+struct InflateInfo { uint64_t outBytes = 0; uint32_t nSeg = 0, nChain = 0, nBogus = 0, nWaves = 0, reruns = 0; float msSearch = 0, msDecode = 0, msResolve = 0, msEmit = 0; };
+struct InflateError { std::string msg; bool unsupported; };          // unsupported: a valid gzip file this decoder does not take (several members)
+
+#define ZF_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) throw InflateError{std::string("device inflate: ") + cudaGetErrorString(e_), false}; } while (0)
+
+// Inflates ONE gzip member.  zHost: the whole file in host memory (header and trailer are read there); zDev: the same bytes in device
+// memory, 4-byte aligned, followed by at least 8 zero bytes; copyDone: event after which zDev is complete (may be null).
+// reserve(n) returns a device buffer of at least n bytes that keeps what was written so far (it may move).  Work runs on `st`; returns
+// after the last kernel has finished.  segBytes / scratchBytes: segment size, scratch budget (ratio is unused: the counting pass sizes every segment exactly).
+template <class Reserve>
+InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t zLen, cudaStream_t st, Reserve reserve,
+                           uint64_t segBytes = 65536, uint64_t ratio = 0, uint64_t scratchBytes = 24ull << 30) {
+  InflateInfo info;
+  if (zLen < 18 || zHost[0] != 0x1f || zHost[1] != 0x8b || zHost[2] != 8) throw InflateError{"not a gzip file (magic / method)", false};
+  const uint8_t flg = zHost[3]; uint64_t off = 10;
+  if (flg & 4) { if (off + 2 > zLen) throw InflateError{"truncated gzip header", false}; off += 2 + (zHost[off] | (zHost[off + 1] << 8)); }
+  if (flg & 8) { while (off < zLen && zHost[off]) off++; off++; }
+  if (flg & 16) { while (off < zLen && zHost[off]) off++; off++; }
+  if (flg & 2) off += 2;
+  if (off + 8 >= zLen) throw InflateError{"truncated gzip file", false};
+  const uint64_t dataBit = off * 8, totalBits = (zLen - 8) * 8, nWords = (zLen + 3) / 4 + 1;
+  const uint32_t isize = zHost[zLen - 4] | (zHost[zLen - 3] << 8) | (zHost[zLen - 2] << 16) | ((uint32_t)zHost[zLen - 1] << 24);
+  const uint64_t nSeg64 = (zLen - 8 - off + segBytes - 1) / segBytes;
+  if (nSeg64 > 0x7FFFFFF0ull) throw InflateError{"gzip file too large for the segment counter", false};
+  const uint32_t nSeg = (uint32_t)nSeg64; info.nSeg = nSeg;
+  const uint32_t* w = (const uint32_t*)zDev;
+  (void)ratio;
+
+  std::vector<void*> owned;
+  auto dalloc = [&](size_t bytes) { void* p = nullptr; ZF_CUDA(cudaMallocAsync(&p, bytes ? bytes : 16, st)); owned.push_back(p); return p; };
+  auto release = [&]() { for (void* p : owned) cudaFreeAsync(p, st); owned.clear(); };
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  try {
+    ZF_CUDA(cudaEventCreate(&ev[0])); ZF_CUDA(cudaEventCreate(&ev[1]));
+    auto timed = [&](float& acc, auto&& launch) { ZF_CUDA(cudaEventRecord(ev[0], st)); launch(); ZF_CUDA(cudaGetLastError()); ZF_CUDA(cudaEventRecord(ev[1], st)); ZF_CUDA(cudaEventSynchronize(ev[1])); float ms = 0; cudaEventElapsedTime(&ms, ev[0], ev[1]); acc += ms; };
+    ZF_CUDA(cudaFuncSetAttribute(k_zf_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ZF_SMEM));
+    ZF_CUDA(cudaFuncSetAttribute(k_zf_decode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ZF_SMEM));
+    ZF_CUDA(cudaFuncSetAttribute(k_zf_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ZF_SMEM));
+    uint64_t* dStart = (uint64_t*)dalloc((size_t)nSeg * 8); uint8_t* dBogus = (uint8_t*)dalloc(nSeg); SegOut* dRes = (SegOut*)dalloc((size_t)nSeg * sizeof(SegOut));
+    DecodeItem* dList = (DecodeItem*)dalloc((size_t)nSeg * sizeof(DecodeItem));
+    uint8_t* dWin = (uint8_t*)dalloc(ZF_WINDOW); uint32_t* dErr = (uint32_t*)dalloc(16);
+    ZF_CUDA(cudaMemsetAsync(dBogus, 0, nSeg, st)); ZF_CUDA(cudaMemsetAsync(dWin, 0, ZF_WINDOW, st)); ZF_CUDA(cudaMemsetAsync(dErr, 0, 16, st));
+    timed(info.msSearch, [&] { k_zf_search<<<(nSeg + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dataBit, segBytes * 8, nSeg, dStart); });
+    std::vector<uint64_t> start(nSeg); ZF_CUDA(cudaMemcpyAsync(start.data(), dStart, (size_t)nSeg * 8, cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
+    std::vector<uint8_t> bogus(nSeg, 0);
+    // ---- counting pass over every segment with a start, then the chain walk (a chain member that passed a claimed start proves it bogus)
+    std::vector<DecodeItem> items; std::vector<uint32_t> itemOf(nSeg, 0xFFFFFFFFu);
+    for (uint32_t i = 0; i < nSeg; i++) if (start[i] != ZF_NONE) { itemOf[i] = (uint32_t)items.size(); items.push_back(DecodeItem{0, 0, i, 0}); }
+    std::vector<SegOut> res(items.size());
+    ZF_CUDA(cudaMemcpyAsync(dList, items.data(), items.size() * sizeof(DecodeItem), cudaMemcpyHostToDevice, st));
+    timed(info.msDecode, [&] { k_zf_decode<false><<<((uint32_t)items.size() + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dStart, dBogus, nSeg, dList, (uint32_t)items.size(), nullptr, dRes); });
+    ZF_CUDA(cudaMemcpyAsync(res.data(), dRes, items.size() * sizeof(SegOut), cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
+    std::vector<ChainSeg> chain; std::vector<uint32_t> chainSeg; uint64_t abs = 0, endBit = 0; bool done = false;
+    for (uint32_t cur = 0; !done;) {
+      if (cur >= nSeg || itemOf[cur] == 0xFFFFFFFFu) throw InflateError{"deflate stream ends without a final block", false};
+      const SegOut r = res[itemOf[cur]];
+      if (r.status == ZF_RETRY) {
+        if (r.endSeg >= nSeg || bogus[r.endSeg]) throw InflateError{"inconsistent block chain", false};
+        bogus[r.endSeg] = 1; info.nBogus++; info.reruns++;
+        ZF_CUDA(cudaMemcpyAsync(dBogus + r.endSeg, &bogus[r.endSeg], 1, cudaMemcpyHostToDevice, st));
+        k_zf_decode<false><<<1, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dStart, dBogus, nSeg, dList + itemOf[cur], 1u, nullptr, dRes + itemOf[cur]);
+        ZF_CUDA(cudaGetLastError());
+        ZF_CUDA(cudaMemcpyAsync(&res[itemOf[cur]], dRes + itemOf[cur], sizeof(SegOut), cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
+        continue;
+      }
+      if (r.status != ZF_OK && r.status != ZF_FINAL) throw InflateError{"invalid deflate data (segment " + std::to_string(cur) + ", code " + std::to_string(r.status) + ")", false};
+      chain.push_back(ChainSeg{0, abs, r.outLen}); chainSeg.push_back(cur); abs += r.outLen;
+      if (r.status == ZF_FINAL) { done = true; endBit = r.endBit; } else cur = r.endSeg;
+    }
+    info.nChain = (uint32_t)chain.size();
+    if ((endBit + 7) / 8 + 8 != zLen) throw InflateError{"bytes after the first gzip member (several members / BGZF are not inflated on the device)", true};
+    if ((uint32_t)abs != isize) throw InflateError{"gzip length check failed (ISIZE)", false};
+    uint8_t* text = reserve(abs);
+    // ---- writing pass in waves: as many chain segments as the scratch holds, tightly packed
+    uint64_t scratchSyms = std::max<uint64_t>(std::min<uint64_t>(scratchBytes / 2, abs), 1);
+    for (const ChainSeg& c : chain) scratchSyms = std::max(scratchSyms, c.len);          // (a single segment larger than the budget still has to fit)
+    uint16_t* scratch = (uint16_t*)dalloc(scratchSyms * 2);
+    ChainSeg* dChain = (ChainSeg*)dalloc(chain.size() * sizeof(ChainSeg) + 16); uint32_t* dSlice = nullptr; size_t sliceCap = 0;
+    const uint32_t nChain = (uint32_t)chain.size();
+    for (uint32_t c0 = 0; c0 < nChain;) {
+      uint32_t c1 = c0; uint64_t used = 0;
+      while (c1 < nChain && (c1 == c0 || used + chain[c1].len <= scratchSyms)) { chain[c1].sym = used; used += chain[c1].len; c1++; }
+      info.nWaves++;
+      const uint32_t n = c1 - c0;
+      std::vector<DecodeItem> wl(n); for (uint32_t c = c0; c < c1; c++) wl[c - c0] = DecodeItem{chain[c].sym, chain[c].len, chainSeg[c], 0};
+      ZF_CUDA(cudaMemcpyAsync(dList, wl.data(), (size_t)n * sizeof(DecodeItem), cudaMemcpyHostToDevice, st));
+      ZF_CUDA(cudaMemcpyAsync(dChain, chain.data() + c0, (size_t)n * sizeof(ChainSeg), cudaMemcpyHostToDevice, st));
+      timed(info.msDecode, [&] { k_zf_decode<true><<<(n + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dStart, dBogus, nSeg, dList, n, scratch, dRes); });
+      std::vector<SegOut> wr(n); ZF_CUDA(cudaMemcpyAsync(wr.data(), dRes, (size_t)n * sizeof(SegOut), cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
+      for (uint32_t k = 0; k < n; k++) {
+        if (wr[k].status == ZF_BAD || wr[k].status == ZF_NOWINDOW) throw InflateError{"invalid deflate data (distance too far back, segment " + std::to_string(wl[k].seg) + ")", false};
+        if (wr[k].outLen != wl[k].cap || (wr[k].status != ZF_OK && wr[k].status != ZF_FINAL)) throw InflateError{"the two decoding passes disagree (segment " + std::to_string(wl[k].seg) + ")", false};
+      }
+      std::vector<uint32_t> sl[2][2];                                      // per pass: slice -> (chain index within the wave, slice index)
+      for (uint32_t c = 0; c < n; c++) {
+        const uint64_t len = chain[c0 + c].len, T = len < ZF_WINDOW ? len : ZF_WINDOW, hd = len - T;
+        for (uint64_t k = 0; k * ZF_EMIT_SLICE < T; k++) { sl[0][0].push_back(c); sl[0][1].push_back((uint32_t)k); }
+        for (uint64_t k = 0; k * ZF_EMIT_SLICE < hd; k++) { sl[1][0].push_back(c); sl[1][1].push_back((uint32_t)k); }
+      }
+      const size_t nSl = 2 * (sl[0][0].size() + sl[1][0].size());
+      if (nSl > sliceCap) { sliceCap = 2 * nSl + 16; dSlice = (uint32_t*)dalloc(sliceCap * 4); }
+      uint32_t* dS[2][2]; size_t at = 0;
+      for (int p = 0; p < 2; p++) for (int q = 0; q < 2; q++) { dS[p][q] = dSlice + at; if (!sl[p][q].empty()) ZF_CUDA(cudaMemcpyAsync(dS[p][q], sl[p][q].data(), sl[p][q].size() * 4, cudaMemcpyHostToDevice, st)); at += sl[p][q].size(); }
+      timed(info.msResolve, [&] { k_zf_resolve<<<1, ZF_RES_THREADS, 0, st>>>(scratch, dChain, n, dWin, dErr); });
+      for (int p = 0; p < 2; p++) if (!sl[p][0].empty()) timed(info.msEmit, [&] { k_zf_emit<<<(uint32_t)sl[p][0].size(), 256, 0, st>>>(scratch, dChain, dS[p][0], dS[p][1], p, text); });
+      ZF_CUDA(cudaStreamSynchronize(st));                                  // the host vectors above are reused by the next wave
+      c0 = c1;
+    }
+    uint32_t herr = 0; ZF_CUDA(cudaMemcpyAsync(&herr, dErr, 4, cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
+    if (herr) throw InflateError{"invalid deflate data (distance in front of the stream)", false};
+    info.outBytes = abs;
+    release(); cudaEventDestroy(ev[0]); cudaEventDestroy(ev[1]);
+    return info;
+  } catch (...) { release(); if (ev[0]) cudaEventDestroy(ev[0]); if (ev[1]) cudaEventDestroy(ev[1]); throw; }
+}
+
+}  // namespace zf
+}  // namespace eqpb

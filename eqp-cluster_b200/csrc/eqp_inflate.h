@@ -1,0 +1,263 @@
+// DEFLATE (RFC 1951) decoding on the device: the `zcat X.sam.gz | java ...` step of compute-intersection-bed-file.sh:644-662 (SURVEY.md §8f
+// rank 1) without the host inflate.  A gzip member is ONE bit stream whose blocks can only be found by decoding, so the work is made
+// parallel speculatively (the approach of pugz, Kerbiriou & Chikhi 2019, restated for a GPU):
+//   search   the compressed bytes are cut into segments; a thread scans its segment bit by bit for a plausible dynamic-block header
+//            (complete code-length code, complete literal/length code, end-of-block code present, first symbols are SAM text bytes)
+//   decode   a thread decodes from its start up to the start of the next segment, one 16-bit symbol per output byte: 0..255 = the byte,
+//            0x8000|w = "byte w of the 32 KB window in front of this segment" (a match that reaches back past the segment start).
+//            A decoder that passes the next segment's claimed start without landing on it proves that start bogus; it is dropped and
+//            the decoder re-run through it, so the accepted starts form one verified chain from the stream's first bit to its last block.
+//   resolve  one CTA walks the chain in order and replaces the markers in the last 32 K symbols of every segment (window in shared memory)
+//   emit     all segments in parallel: bytes of the tails first, then everything else, markers read from the text already written.
+// These are the per-thread functions (also compiled on the host, tests/emu inflate); the kernels are in eqp_inflate.cuh.
+#pragma once
+#include "eqp_types.h"
+
+namespace eqpb {
+namespace zf {
+
+enum { ZF_OK = 0, ZF_FINAL = 1, ZF_BAD = 2, ZF_OVERFLOW = 3, ZF_RETRY = 4, ZF_NOWINDOW = 5 };
+static const uint64_t ZF_NONE = ~0ull;
+static const uint32_t ZF_WINDOW = 32768;
+
+// ---- bit reader: LSB-first, 32-bit words, at least 33 valid bits after bits_fill
+struct Bits { const uint32_t* w; uint64_t nWords, wi; uint64_t buf; int cnt; };
+EQP_HD void bits_seek(Bits& b, uint64_t bitpos) {
+  b.wi = bitpos >> 5; uint32_t sh = (uint32_t)(bitpos & 31); uint32_t x = b.wi < b.nWords ? b.w[b.wi] : 0u;
+  b.buf = (uint64_t)(x >> sh); b.cnt = 32 - (int)sh; b.wi++;
+}
+EQP_HD void bits_fill(Bits& b) { if (b.cnt <= 32) { uint32_t x = b.wi < b.nWords ? b.w[b.wi] : 0u; b.buf |= (uint64_t)x << b.cnt; b.cnt += 32; b.wi++; } }
+EQP_HD uint32_t bits_peek(const Bits& b, int n) { return (uint32_t)b.buf & ((1u << n) - 1u); }
+EQP_HD void bits_drop(Bits& b, int n) { b.buf >>= n; b.cnt -= n; }
+EQP_HD uint32_t bits_take(Bits& b, int n) { uint32_t v = bits_peek(b, n); bits_drop(b, n); return v; }
+EQP_HD uint64_t bits_pos(const Bits& b) { return b.wi * 32 - (uint64_t)b.cnt; }
+EQP_HD uint32_t rev15(uint32_t v) {                                    // the next 15 stream bits as a left-justified Huffman code
+#if defined(__CUDA_ARCH__)
+  return __brev(v) >> 17;
+#else
+  v = ((v >> 1) & 0x55555555u) | ((v & 0x55555555u) << 1); v = ((v >> 2) & 0x33333333u) | ((v & 0x33333333u) << 2);
+  v = ((v >> 4) & 0x0F0F0F0Fu) | ((v & 0x0F0F0F0Fu) << 4); v = ((v >> 8) & 0x00FF00FFu) | ((v & 0x00FF00FFu) << 8);
+  v = (v >> 16) | (v << 16); return v >> 17;
+#endif
+}
+
+// ---- canonical Huffman code: limit[L] = left-justified (15-bit) end of the codes of length L, base[L] = index of the first symbol of
+// length L minus its first code; limit[0] = shortest length in use.  Element k of an array sits at [k * stride] (shared memory is
+// interleaved over the CTA's threads).
+struct Huff { uint16_t* limit; int16_t* base; uint16_t* sym; int stride; };
+// returns false when over-subscribed; `complete`: Kraft sum is exactly one; `maxLen`: longest code
+EQP_HD bool huff_build(const uint8_t* lens, int n, const Huff& h, bool& complete, int& maxLen) {
+  uint16_t count[16]; for (int i = 0; i < 16; i++) count[i] = 0;
+  for (int i = 0; i < n; i++) count[lens[i]]++;
+  uint16_t offs[16]; uint32_t code = 0, idx = 0; int minLen = 0; maxLen = 0; uint32_t kraft = 0;
+  for (int L = 1; L <= 15; L++) {
+    if (code + count[L] > (1u << L)) return false;
+    h.limit[L * h.stride] = (uint16_t)((code + count[L]) << (15 - L));
+    h.base[L * h.stride] = (int16_t)((int)idx - (int)code);
+    offs[L] = (uint16_t)idx; idx += count[L]; kraft += (uint32_t)count[L] << (15 - L);
+    if (count[L]) { if (!minLen) minLen = L; maxLen = L; }
+    code = (code + count[L]) << 1;
+  }
+  h.limit[0] = (uint16_t)(minLen ? minLen : 1);
+  for (int i = 0; i < n; i++) if (lens[i]) h.sym[(offs[lens[i]]++) * h.stride] = (uint16_t)i;
+  complete = kraft == 32768u;
+  return true;
+}
+EQP_HD int huff_decode(Bits& b, const Huff& h) {
+  const uint32_t c = rev15((uint32_t)b.buf & 0x7FFFu);
+  for (int L = h.limit[0]; L <= 15; L++)
+    if (c < h.limit[L * h.stride]) { bits_drop(b, L); return h.sym[((int)h.base[L * h.stride] + (int)(c >> (15 - L))) * h.stride]; }
+  return -1;
+}
+
+// ---- block headers
+// dynamic block (after the 3 header bits): code lengths -> the two codes.  zlib's rules (inftrees.c): an over-subscribed code is an error, an
+// incomplete one too unless it has a single code of length 1; the end-of-block symbol must have a code.  strict (the search): every code complete.
+EQP_HD bool read_dynamic(Bits& b, const Huff& hl, const Huff& hd, bool strict) {
+  bits_fill(b);
+  const int hlit = (int)bits_take(b, 5) + 257, hdist = (int)bits_take(b, 5) + 1, hclen = (int)bits_take(b, 4) + 4;
+  if (hlit > 286 || hdist > 30) return false;
+  uint8_t cl[19]; for (int i = 0; i < 19; i++) cl[i] = 0;
+  const uint8_t order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+  uint32_t kraft = 0;
+  for (int i = 0; i < hclen; i++) { bits_fill(b); uint8_t v = (uint8_t)bits_take(b, 3); cl[order[i]] = v; if (v) kraft += 128u >> v; }
+  if (kraft != 128u) return false;                                     // inflate_table(CODES): incomplete or over-subscribed set
+  uint16_t cLimit[16]; int16_t cBase[16]; uint16_t cSym[19]; Huff hc{cLimit, cBase, cSym, 1};
+  bool complete; int maxLen;
+  if (!huff_build(cl, 19, hc, complete, maxLen)) return false;
+  uint8_t lens[320]; int i = 0; const int total = hlit + hdist;
+  while (i < total) {
+    bits_fill(b);
+    int s = huff_decode(b, hc); if (s < 0) return false;
+    if (s < 16) { lens[i++] = (uint8_t)s; continue; }
+    int rep; uint8_t val = 0;
+    if (s == 16) { if (!i) return false; val = lens[i - 1]; rep = 3 + (int)bits_take(b, 2); }
+    else if (s == 17) rep = 3 + (int)bits_take(b, 3);
+    else rep = 11 + (int)bits_take(b, 7);
+    if (i + rep > total) return false;
+    while (rep--) lens[i++] = val;
+  }
+  if (!lens[256]) return false;                                        // "invalid code -- missing end-of-block"
+  if (!huff_build(lens, hlit, hl, complete, maxLen) || (!complete && (strict || maxLen != 1))) return false;
+  if (!huff_build(lens + hlit, hdist, hd, complete, maxLen) || (!complete && (strict || maxLen > 1))) return false;
+  return true;
+}
+EQP_HD void read_fixed(const Huff& hl, const Huff& hd) {
+  uint8_t lens[288]; bool c; int m;
+  for (int i = 0; i < 288; i++) lens[i] = (uint8_t)(i < 144 ? 8 : i < 256 ? 9 : i < 280 ? 7 : 8);
+  huff_build(lens, 288, hl, c, m);
+  for (int i = 0; i < 32; i++) lens[i] = 5;
+  huff_build(lens, 32, hd, c, m);
+}
+
+// ---- symbol sink of one segment: 16-bit symbols in global memory, markers for matches that reach in front of the segment
+struct Sink {
+  uint16_t* out; uint64_t o, cap; bool window;                        // window: a window exists in front of the segment (false: first segment of the stream)
+  int status;
+};
+// WRITE = false: the counting pass (lengths and block boundaries only; nothing is loaded or stored)
+template <bool WRITE> EQP_HD void sink_lit(Sink& s, uint32_t v) {
+  if (WRITE) { if (s.o < s.cap) s.out[s.o] = (uint16_t)v; else s.status = ZF_OVERFLOW; }
+  s.o++;
+}
+template <bool WRITE> EQP_HD void sink_copy(Sink& s, uint32_t dist, uint32_t len) {
+  if (!WRITE) { s.o += len; return; }
+  if (s.o + len > s.cap) { s.status = ZF_OVERFLOW; s.o += len; return; }
+  if (dist > s.o) {                                                    // starts in the window in front of the segment
+    if (dist - s.o > ZF_WINDOW || !s.window) { s.status = s.window ? ZF_BAD : ZF_NOWINDOW; s.o += len; return; }
+  }
+  uint64_t o = s.o; const uint64_t e = o + len;
+  while (o < e && o < dist) { s.out[o] = (uint16_t)(0x8000u | (uint32_t)(ZF_WINDOW + o - dist)); o++; }
+  // the segment's own symbols: up to 8 independent loads, then their stores (a symbol-by-symbol copy waits one L2 round trip per symbol)
+  while (o < e) {
+    uint64_t n = e - o; if (n > dist) n = dist; if (n > 8) n = 8;
+    const uint16_t* src = s.out + (o - dist); uint16_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) if ((uint64_t)k < n) v[k] = src[k];
+#pragma unroll
+    for (int k = 0; k < 8; k++) if ((uint64_t)k < n) s.out[o + k] = v[k];
+    o += n;
+  }
+  s.o = e;
+}
+// the search's sink: nothing is stored, literals must be bytes of SAM text
+EQP_HD bool sam_text_byte(uint32_t v) { return v == '\t' || v == '\n' || v == '\r' || (v >= 0x20 && v < 0x7F); }
+
+EQP_HD uint32_t len_base(int sym, int& extra) {                        // length symbol 257..285
+  if (sym < 265) { extra = 0; return (uint32_t)(sym - 254); }
+  if (sym == 285) { extra = 0; return 258; }
+  extra = (sym - 261) >> 2; return 3u + ((4u + (uint32_t)((sym - 265) & 3)) << extra);
+}
+EQP_HD uint32_t dist_base(int sym, int& extra) {                       // distance symbol 0..29
+  if (sym < 4) { extra = 0; return (uint32_t)(sym + 1); }
+  extra = (sym >> 1) - 1; return 1u + ((2u + (uint32_t)(sym & 1)) << extra);
+}
+
+// one compressed block's symbols (the two codes are built): ZF_OK at end-of-block
+template <bool WRITE> EQP_HD int inflate_symbols(Bits& b, const Huff& hl, const Huff& hd, Sink& s) {
+  while (true) {
+    bits_fill(b);
+    int sym = huff_decode(b, hl);
+    if (sym < 0) return ZF_BAD;
+    if (sym < 256) { sink_lit<WRITE>(s, (uint32_t)sym); if (WRITE && s.status) return s.status; continue; }
+    if (sym == 256) return ZF_OK;
+    if (sym > 285) return ZF_BAD;
+    int ex; uint32_t len = len_base(sym, ex); len += bits_take(b, ex);
+    bits_fill(b);
+    int ds = huff_decode(b, hd);
+    if (ds < 0 || ds > 29) return ZF_BAD;
+    uint32_t dist = dist_base(ds, ex); dist += bits_take(b, ex);
+    sink_copy<WRITE>(s, dist, len);
+    if (WRITE && s.status) return s.status;
+  }
+}
+// the first symbols of a candidate block: valid codes, literals are text, distances stay inside what could exist
+EQP_HD bool probe_symbols(Bits& b, const Huff& hl, const Huff& hd, uint32_t maxSyms) {
+  uint64_t o = 0;
+  for (uint32_t k = 0; k < maxSyms; k++) {
+    bits_fill(b);
+    int sym = huff_decode(b, hl);
+    if (sym < 0 || sym > 285) return false;
+    if (sym < 256) { if (!sam_text_byte((uint32_t)sym)) return false; o++; continue; }
+    if (sym == 256) return k > 0;                                      // an empty block is legal but not worth starting on
+    int ex; uint32_t len = len_base(sym, ex); len += bits_take(b, ex);
+    bits_fill(b);
+    int ds = huff_decode(b, hd);
+    if (ds < 0 || ds > 29) return false;
+    uint32_t dist = dist_base(ds, ex); dist += bits_take(b, ex);
+    if (dist > o + ZF_WINDOW) return false;
+    o += len;
+  }
+  return true;
+}
+
+// ---- search: first bit position in [from, to) at which a non-final dynamic block plausibly starts (ZF_NONE: none)
+EQP_HD uint64_t find_block_start(const uint32_t* w, uint64_t nWords, uint64_t from, uint64_t to, uint64_t totalBits, const Huff& hl, const Huff& hd) {
+  Bits b; b.w = w; b.nWords = nWords; bits_seek(b, from);
+  uint64_t p = from;
+  while (p < to) {
+    // (1) advance to the next position whose 13 header bits fit: BFINAL = 0, BTYPE = 2, HLIT <= 29, HDIST <= 29 (one position in nine).
+    //     Written as its own loop so that a warp's lanes meet again before the longer checks.
+    bool hit = false;
+    while (p < to) {
+      bits_fill(b);
+      const uint32_t v = (uint32_t)b.buf;
+      if ((v & 7u) == 4u && ((v >> 3) & 31u) <= 29u && ((v >> 8) & 31u) <= 29u) { hit = true; break; }
+      bits_drop(b, 1); p++;
+    }
+    if (!hit) break;
+    // (2) the code-length code must be complete: Kraft sum of its (HCLEN + 4) three-bit lengths
+    Bits c = b; bits_drop(c, 13);
+    const int hclen = (int)bits_take(c, 4) + 4; uint32_t kraft = 0;
+    for (int i = 0; i < hclen; i++) { bits_fill(c); const uint32_t v = bits_take(c, 3); kraft += (128u >> v) & 127u; }
+    // (3) rare: the whole header and the first symbols
+    if (kraft == 128u) {
+      c = b; bits_drop(c, 3);
+      if (read_dynamic(c, hl, hd, true) && probe_symbols(c, hl, hd, 96) && bits_pos(c) <= totalBits) return p;
+    }
+    bits_drop(b, 1); p++;
+  }
+  return ZF_NONE;
+}
+
+// ---- decode of one segment: blocks from `start` until a block boundary coincides with the start of a later segment (ZF_OK, endSeg = that
+// segment), the final block ends (ZF_FINAL), or something is wrong.  segStart[j] == ZF_NONE: segment j has no start (nothing found);
+// bogus[j]: its claimed start was proven wrong.  A boundary that passes a claimed start stops the decode with ZF_RETRY and endSeg = that
+// segment: the host, walking the chain from the stream's first (genuine) segment, marks it bogus and re-runs this segment.  Only chain
+// members may accuse: a bogus segment decodes garbage and would pass genuine starts.
+struct SegOut { uint64_t endBit, outLen; uint32_t endSeg; int status; };
+template <bool WRITE> EQP_HD SegOut inflate_segment(const uint32_t* w, uint64_t nWords, uint64_t totalBits, const uint64_t* segStart, uint32_t nSeg, uint32_t self,
+                              const uint8_t* bogus, const Huff& hl, const Huff& hd, Sink& s) {
+  Bits b; b.w = w; b.nWords = nWords; bits_seek(b, segStart[self]);
+  SegOut r; r.endSeg = nSeg; r.status = ZF_BAD;
+  uint32_t j = self + 1;
+  while (true) {
+    const uint64_t pos = bits_pos(b);
+    if (pos != segStart[self]) {                                       // at a block boundary after at least one block
+      while (j < nSeg && (segStart[j] == ZF_NONE || bogus[j])) j++;
+      if (j < nSeg && segStart[j] == pos) { r.status = ZF_OK; r.endSeg = j; break; }
+      if (j < nSeg && segStart[j] < pos) { r.status = ZF_RETRY; r.endSeg = j; break; }
+    }
+    if (pos + 3 > totalBits) { r.status = ZF_BAD; break; }
+    bits_fill(b);
+    const uint32_t hdr = bits_take(b, 3); const uint32_t type = hdr >> 1;
+    int st;
+    if (type == 0) {                                                   // stored: skip to the byte boundary, LEN, NLEN, bytes
+      uint64_t p = (bits_pos(b) + 7) & ~7ull; bits_seek(b, p); bits_fill(b);
+      uint32_t len = bits_take(b, 16); bits_fill(b); uint32_t nlen = bits_take(b, 16);
+      if ((len ^ nlen) != 0xFFFFu || p + 32 + 8ull * len > totalBits) { r.status = ZF_BAD; break; }
+      for (uint32_t k = 0; k < len; k++) { bits_fill(b); sink_lit<WRITE>(s, bits_take(b, 8)); }
+      st = s.status;
+    } else if (type == 1) { read_fixed(hl, hd); st = inflate_symbols<WRITE>(b, hl, hd, s); }
+    else if (type == 2) { st = read_dynamic(b, hl, hd, false) ? inflate_symbols<WRITE>(b, hl, hd, s) : ZF_BAD; }
+    else st = ZF_BAD;
+    if (st != ZF_OK) { r.status = st; break; }
+    if (bits_pos(b) > totalBits) { r.status = ZF_BAD; break; }
+    if (hdr & 1u) { r.status = ZF_FINAL; break; }
+  }
+  r.endBit = bits_pos(b); r.outLen = s.o;
+  return r;
+}
+
+}  // namespace zf
+}  // namespace eqpb

@@ -54,6 +54,15 @@ class OutputRow(C.Structure):
     _fields_ = [("id", C.c_char_p), ("feature", C.c_int64), ("act", C.c_int64), ("always", C.c_int32), ("reserved", C.c_int32)]
 
 
+class InflateInfo(C.Structure):
+    """eqp_inflate_info: what the device inflate of one gzip member did."""
+    _fields_ = [("gz_bytes", C.c_uint64), ("text_bytes", C.c_uint64), ("segments", C.c_uint32), ("chain", C.c_uint32), ("bogus_starts", C.c_uint32), ("waves", C.c_uint32),
+                ("search_ms", C.c_float), ("decode_ms", C.c_float), ("resolve_ms", C.c_float), ("emit_ms", C.c_float)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
 class RecordColumns(C.Structure):
     """eqp_record_columns: byte offsets of the decoded-record columns inside the caller's device buffer."""
     _fields_ = [(k, C.c_uint64) for k in ("line_off", "frag", "ref", "pos", "rnext", "pnext", "flag", "nm", "cig_off", "cig_len", "seq_len", "cig_m", "rf", "n_lines")] + \
@@ -63,7 +72,8 @@ class RecordColumns(C.Structure):
 EXPORTS = ("eqp_version", "eqp_default_params", "eqp_create", "eqp_load_annotation", "eqp_annotation_bytes", "eqp_count_chunk", "eqp_prefetch_chunk",
            "eqp_feature_count", "eqp_feature_id", "eqp_map_columns", "eqp_output_row_count", "eqp_get_output_row", "eqp_device_vector", "eqp_accumulate",
            "eqp_wide_to_double", "eqp_comm_id", "eqp_comm_init", "eqp_reduce_sample", "eqp_reduce_sample_local", "eqp_chunk_begin", "eqp_chunk_feed",
-           "eqp_chunk_end", "eqp_debug_fetch", "eqp_debug_decode", "eqp_tokenize_noalloc", "eqp_last_error", "eqp_destroy")
+           "eqp_chunk_end", "eqp_debug_fetch", "eqp_debug_decode", "eqp_tokenize_noalloc", "eqp_chunk_feed_gz", "eqp_count_chunk_gz",
+           "eqp_last_inflate", "eqp_debug_inflate", "eqp_last_error", "eqp_destroy")
 NOALLOC_MAX_TEXT_BYTES = 128 << 20
 
 
@@ -115,6 +125,11 @@ def load_library(path=None):
     lib.eqp_chunk_end.argtypes = [vp, C.POINTER(Params), C.POINTER(Counts)]
     lib.eqp_debug_fetch.argtypes = [vp, C.c_char_p, vp, C.c_size_t, C.POINTER(C.c_size_t)]
     lib.eqp_debug_decode.argtypes = [vp, vp, C.c_size_t, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    if hasattr(lib, "eqp_count_chunk_gz"):
+        lib.eqp_chunk_feed_gz.argtypes = [vp, C.c_int, vp, C.c_size_t]
+        lib.eqp_count_chunk_gz.argtypes = [vp, C.POINTER(Params), vp, C.c_size_t, vp, C.c_size_t, vp, C.c_size_t, C.POINTER(Counts)]
+        lib.eqp_last_inflate.argtypes = [vp, C.c_int, C.POINTER(InflateInfo)]
+        lib.eqp_debug_inflate.argtypes = [vp, vp, C.c_size_t, vp, C.c_size_t, C.POINTER(C.c_size_t)]
     if hasattr(lib, "eqp_tokenize_noalloc"):
         lib.eqp_tokenize_noalloc.argtypes = [vp, vp, C.c_size_t, C.c_uint64, vp, C.c_size_t, C.POINTER(RecordColumns)]
     lib.eqp_last_error.argtypes = [vp]; lib.eqp_last_error.restype = C.c_char_p
@@ -255,6 +270,29 @@ class CountContext:
         c = Counts()
         self._check(self.lib.eqp_chunk_end(self.h, C.byref(p), C.byref(c)))
         return ChunkCounts(c, self.feature_ids, self.output_rows, self.map_columns)
+
+    def count_chunk_gz(self, t_gz, j_gz, g_gz, params=None, fetch=True):
+        """eqp_count_chunk_gz: three gzip members (host memory) are copied compressed and inflated on the device."""
+        p = params or default_params()
+        bufs = [_buf(x) for x in (t_gz, j_gz, g_gz)]
+        c = Counts()
+        self._check(self.lib.eqp_count_chunk_gz(self.h, C.byref(p), bufs[0][0], bufs[0][1], bufs[1][0], bufs[1][1], bufs[2][0], bufs[2][1], C.byref(c)))
+        return ChunkCounts(c, self.feature_ids, self.output_rows, self.map_columns) if fetch else c
+
+    def last_inflate(self, which):
+        info = InflateInfo()
+        self._check(self.lib.eqp_last_inflate(self.h, int(which), C.byref(info)))
+        return info.as_dict()
+
+    def debug_inflate(self, gz):
+        """Test tap: the text the device inflate makes of one gzip member (bytes)."""
+        addr, n, keep = _buf(gz)
+        size = C.c_size_t()
+        self._check(self.lib.eqp_debug_inflate(self.h, addr, n, None, 0, C.byref(size)))
+        out = np.empty(size.value, dtype=np.uint8)
+        if size.value:
+            self._check(self.lib.eqp_debug_inflate(self.h, addr, n, out.ctypes.data, out.size, C.byref(size)))
+        return out.tobytes()
 
     def prefetch_chunk(self, t_sam, j_sam, g_sam):
         """Start the H2D copy of a later chunk's host buffers; the count_chunk call with the same buffers picks it up."""

@@ -168,6 +168,28 @@ int  eqp_chunk_begin(eqp_ctx* ctx, size_t t_hint, size_t j_hint, size_t g_hint);
 int  eqp_chunk_feed(eqp_ctx* ctx, int input /* 0 transcript, 1 junction, 2 genome */, const uint8_t* buf, size_t len);
 int  eqp_chunk_end(eqp_ctx* ctx, const eqp_params* params, eqp_counts* out);
 
+/* ---- `.sam.gz` input inflated on the device (replaces the `zcat` of compute-intersection-bed-file.sh:644-662 and the
+ * GZIPInputStream of the Java mains).  `gz` is ONE complete gzip member in host memory (what `gzip` / `bowtie2 | gzip` write): the compressed
+ * bytes cross PCIe, a speculative block-parallel DEFLATE decoder (eqp_inflate.h) rebuilds the text in HBM and appends it to the input's feed
+ * buffer.  eqp_chunk_feed_gz belongs to the begin / feed / end family (one member per call, may be mixed with eqp_chunk_feed);
+ * eqp_count_chunk_gz = begin + three members (their copies overlap the inflate of the one before) + end.  Checked: header, block chain
+ * (every accepted block start is landed on exactly by the decoder in front of it), ISIZE; the CRC-32 of the trailer is NOT verified.
+ * EQP_ERR_UNSUPPORTED: a valid file this decoder does not take — several members / BGZF — inflate such a file on the host and use
+ * eqp_chunk_feed.  EQP_ERR_FORMAT: not gzip / corrupt.
+ * Tunables (environment): EQP_INFLATE_SEG (bytes of compressed data per decoder thread, default 65536), EQP_INFLATE_SCRATCH_GB
+ * (16-bit symbol scratch, default 24, at most half of the free device memory; a larger text is written in several waves). */
+typedef struct eqp_inflate_info {
+  uint64_t gz_bytes, text_bytes;
+  uint32_t segments, chain, bogus_starts, waves;   /* segments cut, segments on the verified chain, block starts proven wrong, scratch refills */
+  float    search_ms, decode_ms, resolve_ms, emit_ms;
+} eqp_inflate_info;
+int  eqp_chunk_feed_gz(eqp_ctx* ctx, int input, const uint8_t* gz, size_t len);
+int  eqp_count_chunk_gz(eqp_ctx* ctx, const eqp_params* params, const uint8_t* t_gz, size_t t_len, const uint8_t* j_gz, size_t j_len,
+                        const uint8_t* g_gz, size_t g_len, eqp_counts* out);
+int  eqp_last_inflate(eqp_ctx* ctx, int input, eqp_inflate_info* out);   /* what the last inflate of that input did */
+/* Test tap: inflate one member on the device and copy the text to dst (dst == NULL: only *n_text is set). */
+int  eqp_debug_inflate(eqp_ctx* ctx, const uint8_t* gz, size_t len, uint8_t* dst, size_t dst_bytes, size_t* n_text);
+
 /* Debug/parity taps: copy a device intermediate of the last chunk to the host.
  * what: "weights:<T|J|G|TJ|final>", "selection", "blocks", "hits", "a20", "meta"; "anno:buckets" (newline-separated reference names in
  * bucket order) and "anno:rows" (int32 start,end per B row) decode the bucket / row indices.  Layouts are documented in DESIGN.md. */
