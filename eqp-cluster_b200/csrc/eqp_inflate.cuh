@@ -2,7 +2,7 @@
 //   k_zf_search   thread per segment: first plausible dynamic-block start inside the segment
 //   k_zf_decode   thread per listed segment: blocks -> 16-bit symbols in the segment's scratch region (Huffman tables in shared memory,
 //                 interleaved over the CTA's threads)
-//   k_zf_resolve  ONE CTA per stream walks the verified chain: markers in every segment's last 32 K symbols -> bytes, 32 KB window in shared memory
+//   k_zf_resolve_groups / k_zf_chain_windows  markers in every chain segment's last 32 K symbols, by groups of segments (see there)
 //   k_zf_emit     CTA per (segment, slice): pass 0 writes the tails' bytes, pass 1 everything else (markers read the text in front of the segment)
 #pragma once
 #include <cuda_runtime.h>
@@ -24,14 +24,25 @@ __device__ __forceinline__ void zf_tables(uint16_t* sm, Huff& hl, Huff& hd) {
   hl.sym = sm + 64 * S + t; hd.sym = sm + (64 + 288) * S + t; hl.stride = hd.stride = S;
 }
 
+// Every lane runs one bounded step of its state machine between two warp barriers, until all lanes of the warp are done: without the barrier
+// the lanes drift apart at the first early exit and never meet again (measured: the plain per-thread loops ran at one active lane per warp).
 __global__ void __launch_bounds__(ZF_THREADS) k_zf_search(const uint32_t* w, uint64_t nWords, uint64_t totalBits, uint64_t dataBit, uint64_t segBits, uint32_t nSeg, uint64_t* segStart) {
   extern __shared__ __align__(16) uint16_t zf_sm[];
   Huff hl, hd; zf_tables(zf_sm, hl, hd);
-  uint32_t i = blockIdx.x * ZF_THREADS + threadIdx.x;
-  if (i >= nSeg) return;
-  if (i == 0) { segStart[0] = dataBit; return; }
-  uint64_t from = dataBit + (uint64_t)i * segBits, to = from + segBits; if (to > totalBits) to = totalBits;
-  segStart[i] = from < to ? find_block_start(w, nWords, from, to, totalBits, hl, hd) : ZF_NONE;
+  __shared__ uint8_t lut[512];
+  for (uint32_t k = threadIdx.x; k < 512; k += ZF_THREADS) lut[k] = kraft3(k);
+  __syncthreads();
+  const uint32_t i = blockIdx.x * ZF_THREADS + threadIdx.x;
+  Search s; search_init(s, 0, 0);
+  if (i > 0 && i < nSeg) { uint64_t from = dataBit + (uint64_t)i * segBits, to = from + segBits; if (to > totalBits) to = totalBits; search_init(s, from, to); }
+  while (true) {
+    __syncwarp();
+    const uint32_t scanning = __ballot_sync(0xffffffffu, !s.done && !s.pending), pending = __ballot_sync(0xffffffffu, !s.done && s.pending);
+    if (!(scanning | pending)) break;
+    if (__popc(pending) >= 8 || !scanning) { if (!s.done && s.pending) search_check(s, w, nWords, totalBits, hl, hd); }   // the long check, for several lanes at once
+    else if (!s.done && !s.pending) search_scan(s, w, nWords, lut);
+  }
+  if (i < nSeg) segStart[i] = i == 0 ? dataBit : s.found;
 }
 
 // one thread per listed segment.  WRITE = false: the counting pass (block boundaries and output lengths, no memory traffic besides the
@@ -42,60 +53,140 @@ __global__ void __launch_bounds__(ZF_THREADS) k_zf_decode(const uint32_t* w, uin
                                                           const DecodeItem* list, uint32_t nList, uint16_t* scratch, SegOut* res) {
   extern __shared__ __align__(16) uint16_t zf_sm[];
   Huff hl, hd; zf_tables(zf_sm, hl, hd);
-  uint32_t k = blockIdx.x * ZF_THREADS + threadIdx.x;
-  if (k >= nList) return;
-  const DecodeItem it = list[k];
-  Sink s; s.out = WRITE ? scratch + it.sym : nullptr; s.o = 0; s.cap = it.cap; s.window = it.seg != 0; s.status = 0;
-  res[k] = inflate_segment<WRITE>(w, nWords, totalBits, segStart, nSeg, it.seg, bogus, hl, hd, s);
+  const uint32_t k = blockIdx.x * ZF_THREADS + threadIdx.x;
+  Dec d; d.state = ST_DONE;
+  if (k < nList) {
+    const DecodeItem it = list[k];
+    Sink s; s.out = WRITE ? scratch + it.sym : nullptr; s.o = 0; s.cap = it.cap; s.window = it.seg != 0; s.status = 0;
+    dec_init(d, w, nWords, segStart[it.seg], it.seg, nSeg, s);
+  }
+  while (true) {
+    __syncwarp();
+    if (!__any_sync(0xffffffffu, d.state != ST_DONE)) break;
+    if (d.state != ST_DONE) dec_step<WRITE>(d, totalBits, segStart, nSeg, bogus, hl, hd);
+  }
+  if (k < nList) res[k] = d.r;
 }
 
 struct ChainSeg { uint64_t sym; uint64_t abs; uint64_t len; };       // scratch offset (symbols), position in the stream's output, symbols
 
-// one CTA: the chain in order.  win[x & 32767] holds output byte x for the 32 K bytes in front of the current segment.
-static const int ZF_RES_THREADS = 1024;
-__global__ void __launch_bounds__(ZF_RES_THREADS) k_zf_resolve(uint16_t* scratch, const ChainSeg* chain, uint32_t nChain, uint8_t* winCarry, uint32_t* err) {
-  __shared__ uint8_t win[ZF_WINDOW];
-  const uint32_t t = threadIdx.x;
-  for (uint32_t k = t; k < ZF_WINDOW; k += ZF_RES_THREADS) win[k] = winCarry[k];
-  __syncthreads();
-  for (uint32_t c = 0; c < nChain; c++) {
-    const ChainSeg cs = chain[c];
-    const uint32_t T = cs.len < ZF_WINDOW ? (uint32_t)cs.len : ZF_WINDOW;
-    uint16_t* tail = scratch + cs.sym + (cs.len - T);
-    const uint64_t absTail = cs.abs + (cs.len - T);
-    uint8_t r[ZF_WINDOW / ZF_RES_THREADS];
+// ---- resolve: the markers in the last 32 K symbols of every chain segment.  A tail's markers point into the tail(s) in front of it, so the
+// chain is sequential — but "window in front of segment s" is a FUNCTION of the window in front of an earlier segment, and functions compose:
+//   k_zf_resolve_groups  the chain is cut into groups of consecutive segments, one CTA per group walks its segments in order with a
+//                        window of 16-bit ENTRIES in shared memory (a byte, or 0x8000|k = "byte k of the window in front of the GROUP");
+//                        afterwards every tail of the group and the group's final window F_g are expressed in the group's initial window
+//   k_zf_chain_windows   one CTA, one cheap step per group: initial window of group g (bytes) -> through F_g -> initial window of g + 1
+//   k_zf_emit pass 0     reads a tail's remaining markers from its group's initial window
+// (The first version walked the whole chain in one CTA: 8-10 us per segment, 0.4-0.9 s per 1.5 GB of gzip, whatever the instruction count.)
+static const int ZF_RES_THREADS = 512;
+static const int ZF_RES_GROUPS = 9;                                    // 9 * 512 groups of 8 symbols >= 32768 / 8 + 1
+struct TailRef { uint64_t a, lo, hi, absA; };                          // scratch index of group 0 (multiple of 8), valid scratch range [lo, hi), output position of a
+__device__ __forceinline__ TailRef zf_tail_ref(const ChainSeg& cs) {
+  const uint64_t T = cs.len < ZF_WINDOW ? cs.len : ZF_WINDOW; TailRef r; r.lo = cs.sym + (cs.len - T); r.hi = cs.sym + cs.len; r.a = r.lo & ~7ull;
+  r.absA = cs.abs + (r.a - cs.sym);                                     // (may wrap below zero for the stream's first bytes: only used with valid elements)
+  return r;
+}
+__device__ __forceinline__ void zf_tail_load(const uint16_t* scratch, const TailRef& r, uint32_t t, uint4 (&v)[ZF_RES_GROUPS]) {
 #pragma unroll
-    for (int q = 0; q < (int)(ZF_WINDOW / ZF_RES_THREADS); q++) {
-      const uint32_t k = t + q * ZF_RES_THREADS;
-      if (k < T) {
-        uint16_t v = tail[k];
-        if (v & 0x8000u) {                                             // byte w of the window in front of the segment
-          const uint64_t a = cs.abs - ZF_WINDOW + (v & 0x7FFFu);
-          if (cs.abs < ZF_WINDOW && (v & 0x7FFFu) < ZF_WINDOW - cs.abs) atomicExch(err, 1u);   // reaches in front of the stream
-          v = win[a & (ZF_WINDOW - 1)]; tail[k] = v;
+  for (int i = 0; i < ZF_RES_GROUPS; i++) {
+    const uint64_t g = r.a + 8ull * (t + (uint32_t)i * ZF_RES_THREADS);
+    v[i] = g < r.hi ? *reinterpret_cast<const uint4*>(scratch + g) : make_uint4(0, 0, 0, 0);
+  }
+}
+__global__ void __launch_bounds__(ZF_RES_THREADS) k_zf_resolve_groups(uint16_t* scratch, const ChainSeg* chain, uint32_t nChain, uint32_t perGroup, uint16_t* groupFinal) {
+  extern __shared__ __align__(16) uint16_t win[];                      // win[x & 32767]: entry of output position x, for the 32 K positions in front of the current segment
+  const uint32_t t = threadIdx.x, c0 = blockIdx.x * perGroup, c1 = min(nChain, c0 + perGroup);
+  if (c0 >= c1) return;
+  const ChainSeg none{0, 0, 0};
+  ChainSeg cs = chain[c0], nx = c0 + 1 < c1 ? chain[c0 + 1] : none;
+  const uint64_t absG = cs.abs;
+  for (uint32_t k = t; k < ZF_WINDOW; k += ZF_RES_THREADS) win[(absG - ZF_WINDOW + k) & (ZF_WINDOW - 1)] = (uint16_t)(0x8000u | k);
+  uint4 v[ZF_RES_GROUPS], vn[ZF_RES_GROUPS];
+  zf_tail_load(scratch, zf_tail_ref(cs), t, v);
+  __syncthreads();
+  uint64_t absEnd = absG;
+  for (uint32_t c = c0; c < c1; c++) {
+    const ChainSeg nn = c + 2 < c1 ? chain[c + 2] : none;
+    zf_tail_load(scratch, zf_tail_ref(nx), t, vn);                     // in flight during this step
+    const TailRef r = zf_tail_ref(cs);
+#pragma unroll
+    for (int i = 0; i < ZF_RES_GROUPS; i++) {
+      const uint64_t g = r.a + 8ull * (t + (uint32_t)i * ZF_RES_THREADS);
+      uint32_t q[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+      if (g < r.hi && ((q[0] | q[1] | q[2] | q[3]) & 0x80008000u)) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+          const uint32_t x = (q[e >> 1] >> (16 * (e & 1))) & 0xFFFFu;
+          if ((x & 0x8000u) && g + e >= r.lo && g + e < r.hi) {         // entry w of the window in front of the segment
+            const uint32_t b = win[(cs.abs - ZF_WINDOW + (x & 0x7FFFu)) & (ZF_WINDOW - 1)]; scratch[g + e] = (uint16_t)b;
+            q[e >> 1] = (q[e >> 1] & ~(0xFFFFu << (16 * (e & 1)))) | (b << (16 * (e & 1)));
+          }
         }
-        r[q] = (uint8_t)v;
+        v[i] = make_uint4(q[0], q[1], q[2], q[3]);
       }
     }
     __syncthreads();
 #pragma unroll
-    for (int q = 0; q < (int)(ZF_WINDOW / ZF_RES_THREADS); q++) { const uint32_t k = t + q * ZF_RES_THREADS; if (k < T) win[(absTail + k) & (ZF_WINDOW - 1)] = r[q]; }
+    for (int i = 0; i < ZF_RES_GROUPS; i++) {
+      const uint64_t g = r.a + 8ull * (t + (uint32_t)i * ZF_RES_THREADS);
+      if (g < r.hi) {
+        const uint32_t q[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+        const uint32_t at = (uint32_t)(r.absA + (g - r.a));
+#pragma unroll
+        for (int e = 0; e < 8; e++) if (g + e >= r.lo && g + e < r.hi) win[(at + e) & (ZF_WINDOW - 1)] = (uint16_t)(q[e >> 1] >> (16 * (e & 1)));
+      }
+    }
     __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ZF_RES_GROUPS; i++) v[i] = vn[i];
+    absEnd = cs.abs + cs.len; cs = nx; nx = nn;
   }
-  for (uint32_t k = t; k < ZF_WINDOW; k += ZF_RES_THREADS) winCarry[k] = win[k];
+  uint16_t* F = groupFinal + (size_t)blockIdx.x * ZF_WINDOW;           // entry k = output position absEnd - 32768 + k
+  for (uint32_t k = t; k < ZF_WINDOW; k += ZF_RES_THREADS) F[k] = win[(absEnd - ZF_WINDOW + k) & (ZF_WINDOW - 1)];
+}
+// winCarry: the 32 K bytes in front of the wave (byte k = output position start - 32768 + k).  groupInit[g] = window in front of group g.
+__global__ void __launch_bounds__(1024) k_zf_chain_windows(const ChainSeg* chain, uint32_t nChain, uint32_t perGroup, uint32_t nGroups, const uint16_t* groupFinal, uint8_t* groupInit, uint8_t* winCarry, uint32_t* err) {
+  extern __shared__ __align__(16) uint8_t zf_L[];                       // two windows
+  uint8_t (*L)[ZF_WINDOW] = reinterpret_cast<uint8_t (*)[ZF_WINDOW]>(zf_L);
+  const uint32_t t = threadIdx.x;
+  for (uint32_t k = t; k < ZF_WINDOW; k += 1024) L[0][k] = winCarry[k];
+  __syncthreads();
+  int cur = 0;
+  for (uint32_t g = 0; g < nGroups; g++) {
+    const uint64_t absG = chain[g * perGroup].abs; const uint16_t* F = groupFinal + (size_t)g * ZF_WINDOW; uint8_t* init = groupInit + (size_t)g * ZF_WINDOW;
+    for (uint32_t k = t; k < ZF_WINDOW; k += 1024) {
+      init[k] = L[cur][k];
+      const uint32_t e = F[k]; uint32_t b = e;
+      if (e & 0x8000u) { const uint32_t w = e & 0x7FFFu; b = L[cur][w]; }
+      L[cur ^ 1][k] = (uint8_t)b;
+    }
+    (void)absG;
+    __syncthreads();
+    cur ^= 1;
+  }
+  for (uint32_t k = t; k < ZF_WINDOW; k += 1024) winCarry[k] = L[cur][k];
+  (void)err; (void)nChain;
 }
 
-// pass 0: the last min(len, 32 K) symbols of every chain segment (marker-free after k_zf_resolve); pass 1: the symbols in front of them
+// pass 0: the last min(len, 32 K) symbols of every chain segment (their markers now point into the group's initial window);
+// pass 1: the symbols in front of them (markers read the text in front of the segment, which pass 0 has written)
 static const uint32_t ZF_EMIT_SLICE = 1u << 16;
-__global__ void __launch_bounds__(256) k_zf_emit(const uint16_t* scratch, const ChainSeg* chain, const uint32_t* sliceSeg, const uint32_t* sliceIdx, int pass, uint8_t* text) {
-  const ChainSeg cs = chain[sliceSeg[blockIdx.x]];
+__global__ void __launch_bounds__(256) k_zf_emit(const uint16_t* scratch, const ChainSeg* chain, const uint32_t* sliceSeg, const uint32_t* sliceIdx, int pass, uint8_t* text,
+                                                 uint32_t perGroup, const uint8_t* groupInit, uint32_t* err) {
+  const uint32_t c = sliceSeg[blockIdx.x];
+  const ChainSeg cs = chain[c];
   const uint64_t T = cs.len < ZF_WINDOW ? cs.len : ZF_WINDOW, head = cs.len - T;
   uint64_t k0 = (uint64_t)sliceIdx[blockIdx.x] * ZF_EMIT_SLICE, k1 = k0 + ZF_EMIT_SLICE;
   if (pass == 0) { k0 += head; k1 += head; if (k1 > cs.len) k1 = cs.len; } else if (k1 > head) k1 = head;
   const uint16_t* src = scratch + cs.sym; uint8_t* dst = text + cs.abs;
+  const uint8_t* init = groupInit + (size_t)(c / perGroup) * ZF_WINDOW; const uint64_t absG = chain[(c / perGroup) * perGroup].abs;
   for (uint64_t k = k0 + threadIdx.x; k < k1; k += 256) {
-    uint16_t v = src[k];
-    if (v & 0x8000u) v = text[cs.abs - ZF_WINDOW + (v & 0x7FFFu)];
+    uint32_t v = src[k];
+    if (v & 0x8000u) {
+      const uint32_t w = v & 0x7FFFu;
+      if (pass == 0) { if (absG < ZF_WINDOW && w < ZF_WINDOW - absG) atomicExch(err, 1u); v = init[w]; }          // (reaches in front of the stream: corrupt data)
+      else { if (cs.abs < ZF_WINDOW && w < ZF_WINDOW - cs.abs) { atomicExch(err, 1u); v = 0; } else v = text[cs.abs - ZF_WINDOW + w]; }
+    }
     dst[k] = (uint8_t)v;
   }
 }
@@ -176,8 +267,11 @@ InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t z
     // ---- writing pass in waves: as many chain segments as the scratch holds, tightly packed
     uint64_t scratchSyms = std::max<uint64_t>(std::min<uint64_t>(scratchBytes / 2, abs), 1);
     for (const ChainSeg& c : chain) scratchSyms = std::max(scratchSyms, c.len);          // (a single segment larger than the budget still has to fit)
-    uint16_t* scratch = (uint16_t*)dalloc(scratchSyms * 2);
+    uint16_t* scratch = (uint16_t*)dalloc(scratchSyms * 2 + 64);     // (the resolve kernel reads whole 16-byte groups)
     ChainSeg* dChain = (ChainSeg*)dalloc(chain.size() * sizeof(ChainSeg) + 16); uint32_t* dSlice = nullptr; size_t sliceCap = 0;
+    uint16_t* dGroupFinal = nullptr; uint8_t* dGroupInit = nullptr; uint32_t groupCap = 0;
+    ZF_CUDA(cudaFuncSetAttribute(k_zf_resolve_groups, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ZF_WINDOW * 2)));
+    ZF_CUDA(cudaFuncSetAttribute(k_zf_chain_windows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ZF_WINDOW * 2)));
     const uint32_t nChain = (uint32_t)chain.size();
     for (uint32_t c0 = 0; c0 < nChain;) {
       uint32_t c1 = c0; uint64_t used = 0;
@@ -203,8 +297,13 @@ InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t z
       if (nSl > sliceCap) { sliceCap = 2 * nSl + 16; dSlice = (uint32_t*)dalloc(sliceCap * 4); }
       uint32_t* dS[2][2]; size_t at = 0;
       for (int p = 0; p < 2; p++) for (int q = 0; q < 2; q++) { dS[p][q] = dSlice + at; if (!sl[p][q].empty()) ZF_CUDA(cudaMemcpyAsync(dS[p][q], sl[p][q].data(), sl[p][q].size() * 4, cudaMemcpyHostToDevice, st)); at += sl[p][q].size(); }
-      timed(info.msResolve, [&] { k_zf_resolve<<<1, ZF_RES_THREADS, 0, st>>>(scratch, dChain, n, dWin, dErr); });
-      for (int p = 0; p < 2; p++) if (!sl[p][0].empty()) timed(info.msEmit, [&] { k_zf_emit<<<(uint32_t)sl[p][0].size(), 256, 0, st>>>(scratch, dChain, dS[p][0], dS[p][1], p, text); });
+      const uint32_t nGroups = std::min<uint32_t>(n, 296), perGroup = (n + nGroups - 1) / nGroups, usedGroups = (n + perGroup - 1) / perGroup;
+      if (usedGroups > groupCap) { groupCap = usedGroups; dGroupFinal = (uint16_t*)dalloc((size_t)groupCap * ZF_WINDOW * 2); dGroupInit = (uint8_t*)dalloc((size_t)groupCap * ZF_WINDOW); }
+      timed(info.msResolve, [&] {
+        k_zf_resolve_groups<<<usedGroups, ZF_RES_THREADS, ZF_WINDOW * 2, st>>>(scratch, dChain, n, perGroup, dGroupFinal);
+        k_zf_chain_windows<<<1, 1024, ZF_WINDOW * 2, st>>>(dChain, n, perGroup, usedGroups, dGroupFinal, dGroupInit, dWin, dErr);
+      });
+      for (int p = 0; p < 2; p++) if (!sl[p][0].empty()) timed(info.msEmit, [&] { k_zf_emit<<<(uint32_t)sl[p][0].size(), 256, 0, st>>>(scratch, dChain, dS[p][0], dS[p][1], p, text, perGroup, dGroupInit, dErr); });
       ZF_CUDA(cudaStreamSynchronize(st));                                  // the host vectors above are reused by the next wave
       c0 = c1;
     }

@@ -63,11 +63,18 @@ EQP_HD bool huff_build(const uint8_t* lens, int n, const Huff& h, bool& complete
   complete = kraft == 32768u;
   return true;
 }
+// Fixed cost for every lane of a warp: the limits are non-decreasing in L, so the code's length is one more than the number of limits
+// that are <= c — four probes of a binary search instead of a walk over the lengths (which costs the warp its slowest lane's walk).
 EQP_HD int huff_decode(Bits& b, const Huff& h) {
   const uint32_t c = rev15((uint32_t)b.buf & 0x7FFFu);
-  for (int L = h.limit[0]; L <= 15; L++)
-    if (c < h.limit[L * h.stride]) { bits_drop(b, L); return h.sym[((int)h.base[L * h.stride] + (int)(c >> (15 - L))) * h.stride]; }
-  return -1;
+  int L = c >= h.limit[8 * h.stride] ? 8 : 0;
+  if (c >= h.limit[(L + 4) * h.stride]) L += 4;
+  if (c >= h.limit[(L + 2) * h.stride]) L += 2;
+  if (c >= h.limit[(L + 1) * h.stride]) L += 1;
+  L += 1;
+  if (L > 15) return -1;
+  bits_drop(b, L);
+  return h.sym[((int)h.base[L * h.stride] + (int)(c >> (15 - L))) * h.stride];
 }
 
 // ---- block headers
@@ -86,15 +93,18 @@ EQP_HD bool read_dynamic(Bits& b, const Huff& hl, const Huff& hd, bool strict) {
   bool complete; int maxLen;
   if (!huff_build(cl, 19, hc, complete, maxLen)) return false;
   uint8_t lens[320]; int i = 0; const int total = hlit + hdist;
+  uint32_t kl = 0;                                                      // running Kraft sum of the literal/length code: a wrong start over-subscribes it within a few lengths
   while (i < total) {
     bits_fill(b);
     int s = huff_decode(b, hc); if (s < 0) return false;
-    if (s < 16) { lens[i++] = (uint8_t)s; continue; }
+    if (s < 16) { if (s && i < hlit) { kl += 32768u >> s; if (kl > 32768u) return false; } lens[i++] = (uint8_t)s; continue; }
     int rep; uint8_t val = 0;
     if (s == 16) { if (!i) return false; val = lens[i - 1]; rep = 3 + (int)bits_take(b, 2); }
     else if (s == 17) rep = 3 + (int)bits_take(b, 3);
     else rep = 11 + (int)bits_take(b, 7);
     if (i + rep > total) return false;
+    if (val) for (int r = 0; r < rep; r++) if (i + r < hlit) kl += 32768u >> val;
+    if (kl > 32768u) return false;
     while (rep--) lens[i++] = val;
   }
   if (!lens[256]) return false;                                        // "invalid code -- missing end-of-block"
@@ -120,27 +130,7 @@ template <bool WRITE> EQP_HD void sink_lit(Sink& s, uint32_t v) {
   if (WRITE) { if (s.o < s.cap) s.out[s.o] = (uint16_t)v; else s.status = ZF_OVERFLOW; }
   s.o++;
 }
-template <bool WRITE> EQP_HD void sink_copy(Sink& s, uint32_t dist, uint32_t len) {
-  if (!WRITE) { s.o += len; return; }
-  if (s.o + len > s.cap) { s.status = ZF_OVERFLOW; s.o += len; return; }
-  if (dist > s.o) {                                                    // starts in the window in front of the segment
-    if (dist - s.o > ZF_WINDOW || !s.window) { s.status = s.window ? ZF_BAD : ZF_NOWINDOW; s.o += len; return; }
-  }
-  uint64_t o = s.o; const uint64_t e = o + len;
-  while (o < e && o < dist) { s.out[o] = (uint16_t)(0x8000u | (uint32_t)(ZF_WINDOW + o - dist)); o++; }
-  // the segment's own symbols: up to 8 independent loads, then their stores (a symbol-by-symbol copy waits one L2 round trip per symbol)
-  while (o < e) {
-    uint64_t n = e - o; if (n > dist) n = dist; if (n > 8) n = 8;
-    const uint16_t* src = s.out + (o - dist); uint16_t v[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) if ((uint64_t)k < n) v[k] = src[k];
-#pragma unroll
-    for (int k = 0; k < 8; k++) if ((uint64_t)k < n) s.out[o + k] = v[k];
-    o += n;
-  }
-  s.o = e;
-}
-// the search's sink: nothing is stored, literals must be bytes of SAM text
+// the search's probe stores nothing; its literals must be bytes of SAM text
 EQP_HD bool sam_text_byte(uint32_t v) { return v == '\t' || v == '\n' || v == '\r' || (v >= 0x20 && v < 0x7F); }
 
 EQP_HD uint32_t len_base(int sym, int& extra) {                        // length symbol 257..285
@@ -153,24 +143,6 @@ EQP_HD uint32_t dist_base(int sym, int& extra) {                       // distan
   extra = (sym >> 1) - 1; return 1u + ((2u + (uint32_t)(sym & 1)) << extra);
 }
 
-// one compressed block's symbols (the two codes are built): ZF_OK at end-of-block
-template <bool WRITE> EQP_HD int inflate_symbols(Bits& b, const Huff& hl, const Huff& hd, Sink& s) {
-  while (true) {
-    bits_fill(b);
-    int sym = huff_decode(b, hl);
-    if (sym < 0) return ZF_BAD;
-    if (sym < 256) { sink_lit<WRITE>(s, (uint32_t)sym); if (WRITE && s.status) return s.status; continue; }
-    if (sym == 256) return ZF_OK;
-    if (sym > 285) return ZF_BAD;
-    int ex; uint32_t len = len_base(sym, ex); len += bits_take(b, ex);
-    bits_fill(b);
-    int ds = huff_decode(b, hd);
-    if (ds < 0 || ds > 29) return ZF_BAD;
-    uint32_t dist = dist_base(ds, ex); dist += bits_take(b, ex);
-    sink_copy<WRITE>(s, dist, len);
-    if (WRITE && s.status) return s.status;
-  }
-}
 // the first symbols of a candidate block: valid codes, literals are text, distances stay inside what could exist
 EQP_HD bool probe_symbols(Bits& b, const Huff& hl, const Huff& hd, uint32_t maxSyms) {
   uint64_t o = 0;
@@ -191,33 +163,56 @@ EQP_HD bool probe_symbols(Bits& b, const Huff& hl, const Huff& hd, uint32_t maxS
   return true;
 }
 
-// ---- search: first bit position in [from, to) at which a non-final dynamic block plausibly starts (ZF_NONE: none)
-EQP_HD uint64_t find_block_start(const uint32_t* w, uint64_t nWords, uint64_t from, uint64_t to, uint64_t totalBits, const Huff& hl, const Huff& hd) {
-  Bits b; b.w = w; b.nWords = nWords; bits_seek(b, from);
-  uint64_t p = from;
-  while (p < to) {
-    // (1) advance to the next position whose 13 header bits fit: BFINAL = 0, BTYPE = 2, HLIT <= 29, HDIST <= 29 (one position in nine).
-    //     Written as its own loop so that a warp's lanes meet again before the longer checks.
-    bool hit = false;
-    while (p < to) {
-      bits_fill(b);
-      const uint32_t v = (uint32_t)b.buf;
-      if ((v & 7u) == 4u && ((v >> 3) & 31u) <= 29u && ((v >> 8) & 31u) <= 29u) { hit = true; break; }
-      bits_drop(b, 1); p++;
+// ---- search: first bit position in [from, to) at which a non-final dynamic block plausibly starts (ZF_NONE: none).
+// Three sieves: (1) the 13 header bits — BFINAL = 0, BTYPE = 2, HLIT <= 29, HDIST <= 29 — tested for 48 positions at once with
+// bitwise operations on a 64-bit window (4 % of the positions of real gzip data pass); (2) the code-length code must be complete:
+// Kraft sum of its (HCLEN + 4) three-bit lengths from a 512-entry table, three lengths per lookup (0.4 % of those pass);
+// (3) the whole header, strict, and the first 96 symbols.  (1)+(2) are search_scan, (3) is search_check: the kernel lets lanes
+// with a candidate wait until several have one, so that the long check runs for many lanes at once.
+EQP_HD uint64_t bits64(const uint32_t* w, uint64_t nWords, uint64_t p) {
+  const uint64_t i = p >> 5; const uint32_t sh = (uint32_t)(p & 31);
+  const uint32_t a = i < nWords ? w[i] : 0u, b = i + 1 < nWords ? w[i + 1] : 0u, c = i + 2 < nWords ? w[i + 2] : 0u;
+  const uint64_t lo = ((uint64_t)b << 32) | a;
+  return sh ? (lo >> sh) | ((uint64_t)c << (64 - sh)) : lo;
+}
+EQP_HD uint8_t kraft3(uint32_t x) {                                   // table entry: three 3-bit code lengths -> sum of 2^(7 - len) over the non-zero ones
+  uint32_t k = 0; for (int i = 0; i < 3; i++) { const uint32_t v = (x >> (3 * i)) & 7u; k += (128u >> v) & 127u; } return (uint8_t)k;
+}
+struct Search { uint64_t p, to, cand, found; bool pending, done; };
+EQP_HD void search_init(Search& s, uint64_t from, uint64_t to) { s.p = from; s.to = to; s.cand = 0; s.found = ZF_NONE; s.pending = false; s.done = from >= to; }
+EQP_HD void search_scan(Search& s, const uint32_t* w, uint64_t nWords, const uint8_t* lut) {
+  for (int win = 0; win < 4 && s.p < s.to; win++) {
+    const uint64_t x = bits64(w, nWords, s.p);
+    uint64_t m = ~x & ~(x >> 1) & (x >> 2) & ~((x >> 4) & (x >> 5) & (x >> 6) & (x >> 7)) & ~((x >> 9) & (x >> 10) & (x >> 11) & (x >> 12));
+    const uint64_t span = s.to - s.p < 48 ? s.to - s.p : 48;
+    m &= (1ull << span) - 1ull;
+    while (m) {
+#if defined(__CUDA_ARCH__)
+      const int k = __ffsll((long long)m) - 1;
+#else
+      const int k = __builtin_ctzll(m);
+#endif
+      m &= m - 1;
+      const int hclen = (int)((x >> (k + 13)) & 15u) + 4;
+      const uint64_t y = bits64(w, nWords, s.p + k + 17) & ((1ull << (3 * hclen)) - 1ull);
+      const uint32_t sum = (uint32_t)lut[y & 511u] + lut[(y >> 9) & 511u] + lut[(y >> 18) & 511u] + lut[(y >> 27) & 511u] + lut[(y >> 36) & 511u] + lut[(y >> 45) & 511u] + lut[(y >> 54) & 511u];
+      if (sum == 128u) { s.pending = true; s.cand = s.p + k; return; }
     }
-    if (!hit) break;
-    // (2) the code-length code must be complete: Kraft sum of its (HCLEN + 4) three-bit lengths
-    Bits c = b; bits_drop(c, 13);
-    const int hclen = (int)bits_take(c, 4) + 4; uint32_t kraft = 0;
-    for (int i = 0; i < hclen; i++) { bits_fill(c); const uint32_t v = bits_take(c, 3); kraft += (128u >> v) & 127u; }
-    // (3) rare: the whole header and the first symbols
-    if (kraft == 128u) {
-      c = b; bits_drop(c, 3);
-      if (read_dynamic(c, hl, hd, true) && probe_symbols(c, hl, hd, 96) && bits_pos(c) <= totalBits) return p;
-    }
-    bits_drop(b, 1); p++;
+    s.p += span;
   }
-  return ZF_NONE;
+  if (s.p >= s.to) s.done = true;
+}
+EQP_HD void search_check(Search& s, const uint32_t* w, uint64_t nWords, uint64_t totalBits, const Huff& hl, const Huff& hd) {
+  Bits c; c.w = w; c.nWords = nWords; bits_seek(c, s.cand + 3);
+  if (read_dynamic(c, hl, hd, true) && probe_symbols(c, hl, hd, 96) && bits_pos(c) <= totalBits) { s.found = s.cand; s.done = true; return; }
+  s.pending = false; s.p = s.cand + 1;
+  if (s.p >= s.to) s.done = true;
+}
+EQP_HD uint64_t find_block_start(const uint32_t* w, uint64_t nWords, uint64_t from, uint64_t to, uint64_t totalBits, const Huff& hl, const Huff& hd) {
+  uint8_t lut[512]; for (uint32_t i = 0; i < 512; i++) lut[i] = kraft3(i);
+  Search s; search_init(s, from, to);
+  while (!s.done) { if (s.pending) search_check(s, w, nWords, totalBits, hl, hd); else search_scan(s, w, nWords, lut); }
+  return s.found;
 }
 
 // ---- decode of one segment: blocks from `start` until a block boundary coincides with the start of a later segment (ZF_OK, endSeg = that
@@ -225,38 +220,100 @@ EQP_HD uint64_t find_block_start(const uint32_t* w, uint64_t nWords, uint64_t fr
 // bogus[j]: its claimed start was proven wrong.  A boundary that passes a claimed start stops the decode with ZF_RETRY and endSeg = that
 // segment: the host, walking the chain from the stream's first (genuine) segment, marks it bogus and re-runs this segment.  Only chain
 // members may accuse: a bogus segment decodes garbage and would pass genuine starts.
+// A state machine, one bounded step at a time (see Search): block boundary / header, up to two symbols, up to eight copied symbols,
+// up to eight stored bytes.
 struct SegOut { uint64_t endBit, outLen; uint32_t endSeg; int status; };
-template <bool WRITE> EQP_HD SegOut inflate_segment(const uint32_t* w, uint64_t nWords, uint64_t totalBits, const uint64_t* segStart, uint32_t nSeg, uint32_t self,
-                              const uint8_t* bogus, const Huff& hl, const Huff& hd, Sink& s) {
-  Bits b; b.w = w; b.nWords = nWords; bits_seek(b, segStart[self]);
-  SegOut r; r.endSeg = nSeg; r.status = ZF_BAD;
-  uint32_t j = self + 1;
-  while (true) {
-    const uint64_t pos = bits_pos(b);
-    if (pos != segStart[self]) {                                       // at a block boundary after at least one block
-      while (j < nSeg && (segStart[j] == ZF_NONE || bogus[j])) j++;
-      if (j < nSeg && segStart[j] == pos) { r.status = ZF_OK; r.endSeg = j; break; }
-      if (j < nSeg && segStart[j] < pos) { r.status = ZF_RETRY; r.endSeg = j; break; }
-    }
-    if (pos + 3 > totalBits) { r.status = ZF_BAD; break; }
-    bits_fill(b);
-    const uint32_t hdr = bits_take(b, 3); const uint32_t type = hdr >> 1;
-    int st;
-    if (type == 0) {                                                   // stored: skip to the byte boundary, LEN, NLEN, bytes
-      uint64_t p = (bits_pos(b) + 7) & ~7ull; bits_seek(b, p); bits_fill(b);
-      uint32_t len = bits_take(b, 16); bits_fill(b); uint32_t nlen = bits_take(b, 16);
-      if ((len ^ nlen) != 0xFFFFu || p + 32 + 8ull * len > totalBits) { r.status = ZF_BAD; break; }
-      for (uint32_t k = 0; k < len; k++) { bits_fill(b); sink_lit<WRITE>(s, bits_take(b, 8)); }
-      st = s.status;
-    } else if (type == 1) { read_fixed(hl, hd); st = inflate_symbols<WRITE>(b, hl, hd, s); }
-    else if (type == 2) { st = read_dynamic(b, hl, hd, false) ? inflate_symbols<WRITE>(b, hl, hd, s) : ZF_BAD; }
-    else st = ZF_BAD;
-    if (st != ZF_OK) { r.status = st; break; }
-    if (bits_pos(b) > totalBits) { r.status = ZF_BAD; break; }
-    if (hdr & 1u) { r.status = ZF_FINAL; break; }
+enum { ST_BOUNDARY = 0, ST_SYMBOL = 1, ST_COPY = 2, ST_STORED = 3, ST_DONE = 4 };
+struct Dec { Bits b; Sink s; int state; uint32_t len, dist, self, j; bool final, first; SegOut r; };
+EQP_HD void dec_init(Dec& d, const uint32_t* w, uint64_t nWords, uint64_t start, uint32_t self, uint32_t nSeg, const Sink& s) {
+  d.b.w = w; d.b.nWords = nWords; bits_seek(d.b, start); d.s = s; d.state = ST_BOUNDARY; d.len = d.dist = 0; d.self = self; d.j = self + 1;
+  d.final = false; d.first = true; d.r.status = ZF_BAD; d.r.endSeg = nSeg; d.r.endBit = start; d.r.outLen = 0;
+}
+EQP_HD void dec_finish(Dec& d, int status) { d.r.status = status; d.r.endBit = bits_pos(d.b); d.r.outLen = d.s.o; d.state = ST_DONE; }
+EQP_HD void dec_block_end(Dec& d, uint64_t totalBits) {
+  if (bits_pos(d.b) > totalBits) dec_finish(d, ZF_BAD);
+  else if (d.final) dec_finish(d, ZF_FINAL);
+  else d.state = ST_BOUNDARY;
+}
+// up to eight symbols of the pending match: markers for the part in front of the segment, else independent loads first, then their stores
+// (a symbol-by-symbol copy would wait one L2 round trip per symbol)
+EQP_HD void dec_copy_batch(Dec& d) {
+  Sink& s = d.s; const uint64_t o = s.o; uint32_t n = d.len < 8u ? d.len : 8u;
+  if (o < d.dist) {
+    const uint64_t m64 = d.dist - o; if (m64 < n) n = (uint32_t)m64;
+    for (uint32_t k = 0; k < n; k++) s.out[o + k] = (uint16_t)(0x8000u | (uint32_t)(ZF_WINDOW + o + k - d.dist));
+  } else {
+    if (d.dist < n) n = d.dist;
+    const uint16_t* src = s.out + (o - d.dist); uint16_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) if ((uint32_t)k < n) v[k] = src[k];
+#pragma unroll
+    for (int k = 0; k < 8; k++) if ((uint32_t)k < n) s.out[o + k] = v[k];
   }
-  r.endBit = bits_pos(b); r.outLen = s.o;
-  return r;
+  s.o += n; d.len -= n;
+}
+// Straight-line: (A) one literal/length symbol for the lanes in ST_SYMBOL, (B) one batch of a pending match for the lanes in ST_COPY
+// (including those that just decoded it), then the rare states.  No early returns in (A) and (B): the lanes of a warp walk through them together.
+template <bool WRITE>
+EQP_HD void dec_step(Dec& d, uint64_t totalBits, const uint64_t* segStart, uint32_t nSeg, const uint8_t* bogus, const Huff& hl, const Huff& hd) {
+  Bits& b = d.b; Sink& s = d.s;
+  if (d.state == ST_SYMBOL) {
+    bits_fill(b);
+    const int sym = huff_decode(b, hl);
+    if (sym < 256) {
+      if (sym < 0) dec_finish(d, ZF_BAD);
+      else { sink_lit<WRITE>(s, (uint32_t)sym); if (WRITE && s.status) dec_finish(d, s.status); }
+    } else if (sym == 256) dec_block_end(d, totalBits);
+    else if (sym > 285) dec_finish(d, ZF_BAD);
+    else {
+      int ex; uint32_t len = len_base(sym, ex); len += bits_take(b, ex);
+      bits_fill(b);
+      const int ds = huff_decode(b, hd);
+      if (ds < 0 || ds > 29) dec_finish(d, ZF_BAD);
+      else {
+        uint32_t dist = dist_base(ds, ex); dist += bits_take(b, ex);
+        if (!WRITE) s.o += len;
+        else if (s.o + len > s.cap) dec_finish(d, ZF_OVERFLOW);
+        else if (dist > s.o && (dist - s.o > ZF_WINDOW || !s.window)) dec_finish(d, s.window ? ZF_BAD : ZF_NOWINDOW);
+        else { d.len = len; d.dist = dist; d.state = ST_COPY; }
+      }
+    }
+  }
+  if (WRITE && d.state == ST_COPY) { dec_copy_batch(d); if (!d.len) d.state = ST_SYMBOL; }
+  if (d.state == ST_SYMBOL || d.state == ST_COPY || d.state == ST_DONE) return;
+  if (d.state == ST_STORED) {
+    for (int k = 0; k < 8 && d.len; k++, d.len--) { bits_fill(b); sink_lit<WRITE>(s, bits_take(b, 8)); }
+    if (WRITE && s.status) { dec_finish(d, s.status); return; }
+    if (!d.len) dec_block_end(d, totalBits);
+    return;
+  }
+  if (d.state != ST_BOUNDARY) return;
+  const uint64_t pos = bits_pos(b);
+  if (!d.first) {                                                       // a block boundary after at least one block
+    while (d.j < nSeg && (segStart[d.j] == ZF_NONE || bogus[d.j])) d.j++;
+    if (d.j < nSeg && segStart[d.j] == pos) { d.r.endSeg = d.j; dec_finish(d, ZF_OK); return; }
+    if (d.j < nSeg && segStart[d.j] < pos) { d.r.endSeg = d.j; dec_finish(d, ZF_RETRY); return; }
+  }
+  d.first = false;
+  if (pos + 3 > totalBits) { dec_finish(d, ZF_BAD); return; }
+  bits_fill(b);
+  const uint32_t hdr = bits_take(b, 3); const uint32_t type = hdr >> 1; d.final = hdr & 1u;
+  if (type == 0) {                                                      // stored: skip to the byte boundary, LEN, NLEN, bytes
+    const uint64_t p = (bits_pos(b) + 7) & ~7ull; bits_seek(b, p); bits_fill(b);
+    const uint32_t len = bits_take(b, 16); bits_fill(b); const uint32_t nlen = bits_take(b, 16);
+    if ((len ^ nlen) != 0xFFFFu || p + 32 + 8ull * len > totalBits) { dec_finish(d, ZF_BAD); return; }
+    d.len = len;
+    if (len) d.state = ST_STORED; else dec_block_end(d, totalBits);
+  } else if (type == 1) { read_fixed(hl, hd); d.state = ST_SYMBOL; }
+  else if (type == 2) { if (read_dynamic(b, hl, hd, false)) d.state = ST_SYMBOL; else dec_finish(d, ZF_BAD); }
+  else dec_finish(d, ZF_BAD);
+}
+template <bool WRITE> EQP_HD SegOut inflate_segment(const uint32_t* w, uint64_t nWords, uint64_t totalBits, const uint64_t* segStart, uint32_t nSeg, uint32_t self,
+                                                    const uint8_t* bogus, const Huff& hl, const Huff& hd, Sink& s) {
+  Dec d; dec_init(d, w, nWords, segStart[self], self, nSeg, s);
+  while (d.state != ST_DONE) dec_step<WRITE>(d, totalBits, segStart, nSeg, bogus, hl, hd);
+  s = d.s;
+  return d.r;
 }
 
 }  // namespace zf
