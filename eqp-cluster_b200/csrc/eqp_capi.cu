@@ -379,7 +379,7 @@ static int gz_inflate_into_feed(eqp_ctx* ctx, int f, const uint8_t* gz, const ch
     ctx->feed_reserve(f, base + std::max<size_t>(3 * len, 1));
     zf::InflateInfo info = zf::device_inflate(gz, (const uint8_t*)zDev, len, ctx->copyStream,
         [&](uint64_t n) { ctx->feed_reserve(f, base + (size_t)n); return (uint8_t*)F.dev[f] + base; },
-        env_u64("EQP_INFLATE_SEG", 65536), 0, inflate_scratch_budget());
+        env_u64("EQP_INFLATE_SEG", 16384), 0, inflate_scratch_budget());
     F.len[f] = base + (size_t)info.outBytes;
     eqp_inflate_info& o = ctx->lastInflate[f];
     o.gz_bytes = len; o.text_bytes = info.outBytes; o.segments = info.nSeg; o.chain = info.nChain; o.bogus_starts = info.nBogus; o.waves = info.nWaves;

@@ -14,21 +14,37 @@
 namespace eqpb {
 namespace zf {
 
-static const int ZF_THREADS = 128;                                   // per CTA of search / decode: 768 bytes of tables per thread
-static const int ZF_TABLE_U16 = 16 + 16 + 16 + 16 + 288 + 32;        // limit/base of both codes + symbols
+// Occupancy is what these kernels live on (every lane follows its own bit stream: a step is a chain of dependent shared-memory and L2
+// latencies): the code limits / bases stay in shared memory (128 bytes per thread), the symbol tables (640 bytes per thread) live in global
+// memory, one contiguous table per thread — 1024 threads per SM instead of 256 with everything in shared memory.
+#ifdef EQP_VAR_ZF_SMEM_SYMS                                          // A/B: everything in shared memory, 768 bytes per thread, 256 threads per SM
+static const int ZF_THREADS = 128;
+static const int ZF_CTAS = 2;
+static const int ZF_TABLE_U16 = 16 + 16 + 16 + 16 + 288 + 32;
+#else
+static const int ZF_THREADS = 256;
+static const int ZF_CTAS = 4;
+static const int ZF_TABLE_U16 = 16 + 16 + 16 + 16;                   // limit / base of both codes, interleaved over the CTA's threads
+#endif
 static const size_t ZF_SMEM = (size_t)ZF_TABLE_U16 * ZF_THREADS * 2;
+static const int ZF_SYMS = 320;                                      // 288 literal/length + 32 distance symbols per thread
 
-__device__ __forceinline__ void zf_tables(uint16_t* sm, Huff& hl, Huff& hd) {
+__device__ __forceinline__ void zf_tables(uint16_t* sm, uint16_t* symTables, Huff& hl, Huff& hd) {
   const int t = threadIdx.x, S = ZF_THREADS;
   hl.limit = sm + t; hl.base = (int16_t*)(sm + 16 * S + t); hd.limit = sm + 32 * S + t; hd.base = (int16_t*)(sm + 48 * S + t);
-  hl.sym = sm + 64 * S + t; hd.sym = sm + (64 + 288) * S + t; hl.stride = hd.stride = S;
+  hl.stride = hd.stride = S;
+#ifdef EQP_VAR_ZF_SMEM_SYMS
+  (void)symTables; hl.sym = sm + 64 * S + t; hd.sym = sm + (64 + 288) * S + t; hl.symStride = hd.symStride = S;
+#else
+  hl.sym = symTables + ((size_t)blockIdx.x * ZF_THREADS + t) * ZF_SYMS; hd.sym = hl.sym + 288; hl.symStride = hd.symStride = 1;
+#endif
 }
 
 // Every lane runs one bounded step of its state machine between two warp barriers, until all lanes of the warp are done: without the barrier
 // the lanes drift apart at the first early exit and never meet again (measured: the plain per-thread loops ran at one active lane per warp).
-__global__ void __launch_bounds__(ZF_THREADS) k_zf_search(const uint32_t* w, uint64_t nWords, uint64_t totalBits, uint64_t dataBit, uint64_t segBits, uint32_t nSeg, uint64_t* segStart) {
+__global__ void __launch_bounds__(ZF_THREADS, ZF_CTAS) k_zf_search(const uint32_t* w, uint64_t nWords, uint64_t totalBits, uint64_t dataBit, uint64_t segBits, uint32_t nSeg, uint64_t* segStart, uint16_t* symTables) {
   extern __shared__ __align__(16) uint16_t zf_sm[];
-  Huff hl, hd; zf_tables(zf_sm, hl, hd);
+  Huff hl, hd; zf_tables(zf_sm, symTables, hl, hd);
   __shared__ uint8_t lut[512];
   for (uint32_t k = threadIdx.x; k < 512; k += ZF_THREADS) lut[k] = kraft3(k);
   __syncthreads();
@@ -49,10 +65,10 @@ __global__ void __launch_bounds__(ZF_THREADS) k_zf_search(const uint32_t* w, uin
 // compressed words); WRITE = true: 16-bit symbols into the segment's exact-size scratch region.
 struct DecodeItem { uint64_t sym, cap; uint32_t seg, pad; };
 template <bool WRITE>
-__global__ void __launch_bounds__(ZF_THREADS) k_zf_decode(const uint32_t* w, uint64_t nWords, uint64_t totalBits, const uint64_t* segStart, const uint8_t* bogus, uint32_t nSeg,
-                                                          const DecodeItem* list, uint32_t nList, uint16_t* scratch, SegOut* res) {
+__global__ void __launch_bounds__(ZF_THREADS, ZF_CTAS) k_zf_decode(const uint32_t* w, uint64_t nWords, uint64_t totalBits, const uint64_t* segStart, const uint8_t* bogus, uint32_t nSeg,
+                                                                   const DecodeItem* list, uint32_t nList, uint16_t* scratch, SegOut* res, uint16_t* symTables) {
   extern __shared__ __align__(16) uint16_t zf_sm[];
-  Huff hl, hd; zf_tables(zf_sm, hl, hd);
+  Huff hl, hd; zf_tables(zf_sm, symTables, hl, hd);
   const uint32_t k = blockIdx.x * ZF_THREADS + threadIdx.x;
   Dec d; d.state = ST_DONE;
   if (k < nList) {
@@ -232,8 +248,9 @@ InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t z
     uint64_t* dStart = (uint64_t*)dalloc((size_t)nSeg * 8); uint8_t* dBogus = (uint8_t*)dalloc(nSeg); SegOut* dRes = (SegOut*)dalloc((size_t)nSeg * sizeof(SegOut));
     DecodeItem* dList = (DecodeItem*)dalloc((size_t)nSeg * sizeof(DecodeItem));
     uint8_t* dWin = (uint8_t*)dalloc(ZF_WINDOW); uint32_t* dErr = (uint32_t*)dalloc(16);
+    uint16_t* dSym = (uint16_t*)dalloc(((size_t)nSeg + ZF_THREADS) * ZF_SYMS * 2);      // one symbol table per launched thread
     ZF_CUDA(cudaMemsetAsync(dBogus, 0, nSeg, st)); ZF_CUDA(cudaMemsetAsync(dWin, 0, ZF_WINDOW, st)); ZF_CUDA(cudaMemsetAsync(dErr, 0, 16, st));
-    timed(info.msSearch, [&] { k_zf_search<<<(nSeg + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dataBit, segBytes * 8, nSeg, dStart); });
+    timed(info.msSearch, [&] { k_zf_search<<<(nSeg + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dataBit, segBytes * 8, nSeg, dStart, dSym); });
     std::vector<uint64_t> start(nSeg); ZF_CUDA(cudaMemcpyAsync(start.data(), dStart, (size_t)nSeg * 8, cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
     std::vector<uint8_t> bogus(nSeg, 0);
     // ---- counting pass over every segment with a start, then the chain walk (a chain member that passed a claimed start proves it bogus)
@@ -241,7 +258,7 @@ InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t z
     for (uint32_t i = 0; i < nSeg; i++) if (start[i] != ZF_NONE) { itemOf[i] = (uint32_t)items.size(); items.push_back(DecodeItem{0, 0, i, 0}); }
     std::vector<SegOut> res(items.size());
     ZF_CUDA(cudaMemcpyAsync(dList, items.data(), items.size() * sizeof(DecodeItem), cudaMemcpyHostToDevice, st));
-    timed(info.msDecode, [&] { k_zf_decode<false><<<((uint32_t)items.size() + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dStart, dBogus, nSeg, dList, (uint32_t)items.size(), nullptr, dRes); });
+    timed(info.msDecode, [&] { k_zf_decode<false><<<((uint32_t)items.size() + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dStart, dBogus, nSeg, dList, (uint32_t)items.size(), nullptr, dRes, dSym); });
     ZF_CUDA(cudaMemcpyAsync(res.data(), dRes, items.size() * sizeof(SegOut), cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
     std::vector<ChainSeg> chain; std::vector<uint32_t> chainSeg; uint64_t abs = 0, endBit = 0; bool done = false;
     for (uint32_t cur = 0; !done;) {
@@ -251,7 +268,7 @@ InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t z
         if (r.endSeg >= nSeg || bogus[r.endSeg]) throw InflateError{"inconsistent block chain", false};
         bogus[r.endSeg] = 1; info.nBogus++; info.reruns++;
         ZF_CUDA(cudaMemcpyAsync(dBogus + r.endSeg, &bogus[r.endSeg], 1, cudaMemcpyHostToDevice, st));
-        k_zf_decode<false><<<1, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dStart, dBogus, nSeg, dList + itemOf[cur], 1u, nullptr, dRes + itemOf[cur]);
+        k_zf_decode<false><<<1, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dStart, dBogus, nSeg, dList + itemOf[cur], 1u, nullptr, dRes + itemOf[cur], dSym);
         ZF_CUDA(cudaGetLastError());
         ZF_CUDA(cudaMemcpyAsync(&res[itemOf[cur]], dRes + itemOf[cur], sizeof(SegOut), cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
         continue;
@@ -281,7 +298,7 @@ InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t z
       std::vector<DecodeItem> wl(n); for (uint32_t c = c0; c < c1; c++) wl[c - c0] = DecodeItem{chain[c].sym, chain[c].len, chainSeg[c], 0};
       ZF_CUDA(cudaMemcpyAsync(dList, wl.data(), (size_t)n * sizeof(DecodeItem), cudaMemcpyHostToDevice, st));
       ZF_CUDA(cudaMemcpyAsync(dChain, chain.data() + c0, (size_t)n * sizeof(ChainSeg), cudaMemcpyHostToDevice, st));
-      timed(info.msDecode, [&] { k_zf_decode<true><<<(n + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dStart, dBogus, nSeg, dList, n, scratch, dRes); });
+      timed(info.msDecode, [&] { k_zf_decode<true><<<(n + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dStart, dBogus, nSeg, dList, n, scratch, dRes, dSym); });
       std::vector<SegOut> wr(n); ZF_CUDA(cudaMemcpyAsync(wr.data(), dRes, (size_t)n * sizeof(SegOut), cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
       for (uint32_t k = 0; k < n; k++) {
         if (wr[k].status == ZF_BAD || wr[k].status == ZF_NOWINDOW) throw InflateError{"invalid deflate data (distance too far back, segment " + std::to_string(wl[k].seg) + ")", false};

@@ -21,12 +21,14 @@ static const uint64_t ZF_NONE = ~0ull;
 static const uint32_t ZF_WINDOW = 32768;
 
 // ---- bit reader: LSB-first, 32-bit words, at least 33 valid bits after bits_fill
-struct Bits { const uint32_t* w; uint64_t nWords, wi; uint64_t buf; int cnt; };
+// The word after the buffered ones is already loaded (nxt): a refill never waits for memory, the load it issues is used a few symbols later.
+struct Bits { const uint32_t* w; uint64_t nWords, wi; uint64_t buf; uint32_t nxt; int cnt; };
+EQP_HD uint32_t bits_word(const Bits& b, uint64_t i) { return i < b.nWords ? b.w[i] : 0u; }
 EQP_HD void bits_seek(Bits& b, uint64_t bitpos) {
-  b.wi = bitpos >> 5; uint32_t sh = (uint32_t)(bitpos & 31); uint32_t x = b.wi < b.nWords ? b.w[b.wi] : 0u;
-  b.buf = (uint64_t)(x >> sh); b.cnt = 32 - (int)sh; b.wi++;
+  b.wi = bitpos >> 5; const uint32_t sh = (uint32_t)(bitpos & 31); const uint32_t x = bits_word(b, b.wi);
+  b.buf = (uint64_t)(x >> sh); b.cnt = 32 - (int)sh; b.wi++; b.nxt = bits_word(b, b.wi);
 }
-EQP_HD void bits_fill(Bits& b) { if (b.cnt <= 32) { uint32_t x = b.wi < b.nWords ? b.w[b.wi] : 0u; b.buf |= (uint64_t)x << b.cnt; b.cnt += 32; b.wi++; } }
+EQP_HD void bits_fill(Bits& b) { if (b.cnt <= 32) { b.buf |= (uint64_t)b.nxt << b.cnt; b.cnt += 32; b.wi++; b.nxt = bits_word(b, b.wi); } }
 EQP_HD uint32_t bits_peek(const Bits& b, int n) { return (uint32_t)b.buf & ((1u << n) - 1u); }
 EQP_HD void bits_drop(Bits& b, int n) { b.buf >>= n; b.cnt -= n; }
 EQP_HD uint32_t bits_take(Bits& b, int n) { uint32_t v = bits_peek(b, n); bits_drop(b, n); return v; }
@@ -44,7 +46,7 @@ EQP_HD uint32_t rev15(uint32_t v) {                                    // the ne
 // ---- canonical Huffman code: limit[L] = left-justified (15-bit) end of the codes of length L, base[L] = index of the first symbol of
 // length L minus its first code; limit[0] = shortest length in use.  Element k of an array sits at [k * stride] (shared memory is
 // interleaved over the CTA's threads).
-struct Huff { uint16_t* limit; int16_t* base; uint16_t* sym; int stride; };
+struct Huff { uint16_t* limit; int16_t* base; uint16_t* sym; int stride, symStride; };   // symStride: the symbol table may live elsewhere (global memory, one contiguous table per thread)
 // returns false when over-subscribed; `complete`: Kraft sum is exactly one; `maxLen`: longest code
 EQP_HD bool huff_build(const uint8_t* lens, int n, const Huff& h, bool& complete, int& maxLen) {
   uint16_t count[16]; for (int i = 0; i < 16; i++) count[i] = 0;
@@ -59,7 +61,7 @@ EQP_HD bool huff_build(const uint8_t* lens, int n, const Huff& h, bool& complete
     code = (code + count[L]) << 1;
   }
   h.limit[0] = (uint16_t)(minLen ? minLen : 1);
-  for (int i = 0; i < n; i++) if (lens[i]) h.sym[(offs[lens[i]]++) * h.stride] = (uint16_t)i;
+  for (int i = 0; i < n; i++) if (lens[i]) h.sym[(offs[lens[i]]++) * h.symStride] = (uint16_t)i;
   complete = kraft == 32768u;
   return true;
 }
@@ -74,7 +76,7 @@ EQP_HD int huff_decode(Bits& b, const Huff& h) {
   L += 1;
   if (L > 15) return -1;
   bits_drop(b, L);
-  return h.sym[((int)h.base[L * h.stride] + (int)(c >> (15 - L))) * h.stride];
+  return h.sym[((int)h.base[L * h.stride] + (int)(c >> (15 - L))) * h.symStride];
 }
 
 // ---- block headers
@@ -89,7 +91,7 @@ EQP_HD bool read_dynamic(Bits& b, const Huff& hl, const Huff& hd, bool strict) {
   uint32_t kraft = 0;
   for (int i = 0; i < hclen; i++) { bits_fill(b); uint8_t v = (uint8_t)bits_take(b, 3); cl[order[i]] = v; if (v) kraft += 128u >> v; }
   if (kraft != 128u) return false;                                     // inflate_table(CODES): incomplete or over-subscribed set
-  uint16_t cLimit[16]; int16_t cBase[16]; uint16_t cSym[19]; Huff hc{cLimit, cBase, cSym, 1};
+  uint16_t cLimit[16]; int16_t cBase[16]; uint16_t cSym[19]; Huff hc{cLimit, cBase, cSym, 1, 1};
   bool complete; int maxLen;
   if (!huff_build(cl, 19, hc, complete, maxLen)) return false;
   uint8_t lens[320]; int i = 0; const int total = hlit + hdist;

@@ -91,8 +91,21 @@ int main(int argc, char** argv) {
     // text comes out of zlib, so inflating, the host-to-device copies and (for the later inputs) each other overlap.  The context is not
     // thread-safe: feed calls are serialised by a mutex (they only copy into a page-locked staging buffer and queue an async copy).
     if (p_eqp_chunk_begin(ctx, 0, 0, 0)) { fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(ctx)); return 1; }
+    // A `.gz` input goes to the device COMPRESSED and is inflated there (eqp_chunk_feed_gz); a file that decoder does not take (several gzip
+    // members, BGZF) or EQP_HOST_INFLATE=1 leaves it to the zlib thread below.
+    bool onDevice[3] = {false, false, false};
+    { const std::string* paths[3] = {&tPath, &jPath, &gPath}; auto p_feed_gz = (decltype(&::eqp_chunk_feed_gz))dlsym(lib, "eqp_chunk_feed_gz");
+      for (int f = 0; f < 3 && p_feed_gz && !getenv("EQP_HOST_INFLATE"); f++) {
+        const std::string& path = *paths[f];
+        if (path.size() < 3 || path.compare(path.size() - 3, 3, ".gz")) continue;
+        FILE* fp = fopen(path.c_str(), "rb"); if (!fp) { fprintf(stderr, "ERROR: cannot open %s\n", path.c_str()); return 1; }
+        std::vector<uint8_t> z; { uint8_t buf[1 << 16]; size_t n; while ((n = fread(buf, 1, sizeof buf, fp)) > 0) z.insert(z.end(), buf, buf + n); } fclose(fp);
+        const int rc = z.size() >= 18 ? p_feed_gz(ctx, f, z.data(), z.size()) : EQP_ERR_UNSUPPORTED;
+        if (rc == EQP_OK) onDevice[f] = true;
+        else if (rc != EQP_ERR_UNSUPPORTED) { fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(ctx)); return 1; }
+      } }
     { std::mutex mu; std::string failed; const std::string* paths[3] = {&tPath, &jPath, &gPath}; std::vector<std::thread> th;
-      for (int f = 0; f < 3; f++) th.emplace_back([&, f] {
+      for (int f = 0; f < 3; f++) if (!onDevice[f]) th.emplace_back([&, f] {
         try {
           stream_maybe_gz(*paths[f], [&](const char* buf, size_t n) {
             std::lock_guard<std::mutex> lk(mu);

@@ -176,7 +176,7 @@ int  eqp_chunk_end(eqp_ctx* ctx, const eqp_params* params, eqp_counts* out);
  * (every accepted block start is landed on exactly by the decoder in front of it), ISIZE; the CRC-32 of the trailer is NOT verified.
  * EQP_ERR_UNSUPPORTED: a valid file this decoder does not take — several members / BGZF — inflate such a file on the host and use
  * eqp_chunk_feed.  EQP_ERR_FORMAT: not gzip / corrupt.
- * Tunables (environment): EQP_INFLATE_SEG (bytes of compressed data per decoder thread, default 65536), EQP_INFLATE_SCRATCH_GB
+ * Tunables (environment): EQP_INFLATE_SEG (bytes of compressed data per decoder thread, default 16384), EQP_INFLATE_SCRATCH_GB
  * (16-bit symbol scratch, default 24, at most half of the free device memory; a larger text is written in several waves). */
 typedef struct eqp_inflate_info {
   uint64_t gz_bytes, text_bytes;

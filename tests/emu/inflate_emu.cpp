@@ -12,7 +12,7 @@
 using namespace eqpb::zf;
 
 struct Tables { uint16_t lim[2][16]; int16_t base[2][16]; uint16_t sym[320]; Huff hl, hd;
-  Tables() { hl = Huff{lim[0], base[0], sym, 1}; hd = Huff{lim[1], base[1], sym + 288, 1}; } };
+  Tables() { hl = Huff{lim[0], base[0], sym, 1, 1}; hd = Huff{lim[1], base[1], sym + 288, 1, 1}; } };
 struct Chain { uint64_t sym, abs, len; };
 
 static int fail(const char* m) { fprintf(stderr, "ERROR: %s\n", m); return 1; }

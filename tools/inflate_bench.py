@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--layout", default="se")
     ap.add_argument("--genes", type=int, default=60000)
     ap.add_argument("--repeat", type=int, default=2)
+    ap.add_argument("--libs", default="", help="comma-separated variant names under eqp-cluster_b200/lib/variants (tools/variants.py build); default: the product library")
     args = ap.parse_args()
     import numpy as np
     import torch
@@ -50,6 +51,7 @@ def main():
     t_gz = time.time() - t0
     host = bench.load_blocks_pinned(torch, dirs, args.layout)
     shutil.rmtree(os.path.join(work, "chunk"), ignore_errors=True)
+    libs = [("product", None)] + [(n, os.path.join(ROOT, "eqp-cluster_b200", "lib", "variants", "libeqpcount_%s.so" % n)) for n in args.libs.split(",") if n]
     ctx = eqp.CountContext(0).load_annotation(anno)
     targs = [(h.data_ptr(), h.numel()) for h in host]
     gargs = [(g.data_ptr(), g.numel()) for g in gz]
@@ -61,7 +63,11 @@ def main():
         ms.append((time.perf_counter() - t0) * 1e3)
     print(json.dumps({"leg": "text in pinned host memory (eqp_count_chunk, no prefetch)", "reads": args.reads, "text_bytes": sum(h.numel() for h in host),
                       "gz_bytes": sum(g.numel() for g in gz), "gzip_level": args.level, "pgzip_seconds": round(t_gz, 1), "wall_ms": [round(x, 1) for x in ms], "device_ms": ref.device_ms}), flush=True)
-    for seg in [s for s in args.segs.split(",") if s]:
+    for lib_name, lib_path in libs:
+      if lib_path:
+        ctx.close()
+        ctx = eqp.CountContext(0, lib_path).load_annotation(anno)
+      for seg in [s for s in args.segs.split(",") if s]:
         os.environ["EQP_INFLATE_SEG"] = seg
         ms, infos, same = [], None, None
         for _ in range(args.repeat + 1):
@@ -69,14 +75,14 @@ def main():
             try:
                 c = ctx.count_chunk_gz(*gargs)
             except eqp.EqpError as e:
-                print(json.dumps({"leg": "gz", "seg": int(seg), "error": str(e)}), flush=True)
+                print(json.dumps({"leg": "gz", "lib": lib_name, "seg": int(seg), "error": str(e)}), flush=True)
                 break
             ms.append((time.perf_counter() - t0) * 1e3)
             infos = [ctx.last_inflate(f) for f in range(3)]
             same = all(np.array_equal(c.fixed[m], ref.fixed[m]) for m in eqp.MODES)
         else:
             tot = {k: round(sum(i[k] for i in infos), 1) for k in ("search_ms", "decode_ms", "resolve_ms", "emit_ms")}
-            print(json.dumps({"leg": "three .sam.gz members in pinned host memory (eqp_count_chunk_gz)", "seg": int(seg), "wall_ms": [round(x, 1) for x in ms], "count_device_ms": c.device_ms,
+            print(json.dumps({"leg": "three .sam.gz members in pinned host memory (eqp_count_chunk_gz)", "lib": lib_name, "seg": int(seg), "wall_ms": [round(x, 1) for x in ms], "count_device_ms": c.device_ms,
                               "same_vectors_as_text": same, "inflate_ms": tot, "segments": [i["segments"] for i in infos], "chain": [i["chain"] for i in infos],
                               "bogus_starts": sum(i["bogus_starts"] for i in infos), "waves": [i["waves"] for i in infos]}), flush=True)
     ctx.close()
