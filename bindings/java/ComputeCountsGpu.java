@@ -49,10 +49,22 @@ public class ComputeCountsGpu {
       // one inflate thread per input; the context is not thread-safe, so feed calls are serialised
       EqpCountNative.chunkBegin(ctx, 0, 0, 0);
       final Object lock = new Object(); final IOException[] failed = {null};
+      // a .gz input smaller than 2 GiB (one direct buffer) goes to the device compressed and is inflated there; the others take the threads below
+      final boolean[] onDevice = new boolean[3];
+      for (int f = 0; f < 3; f++) {
+        if (!sam[f].endsWith(".gz") || System.getenv("EQP_HOST_INFLATE") != null) continue;
+        try (java.nio.channels.FileChannel ch = java.nio.channels.FileChannel.open(java.nio.file.Paths.get(sam[f]))) {
+          if (ch.size() >= Integer.MAX_VALUE) continue;
+          java.nio.ByteBuffer gz = java.nio.ByteBuffer.allocateDirect((int) ch.size());
+          while (gz.hasRemaining() && ch.read(gz) > 0) { }
+          onDevice[f] = EqpCountNative.chunkFeedGz(ctx, f, gz, ch.size());
+        }
+      }
       Thread[] th = new Thread[3];
       for (int f = 0; f < 3; f++) {
         final int input = f;
         th[f] = new Thread(() -> {
+          if (onDevice[input]) return;
           byte[] buf = new byte[8 << 20];
           try (InputStream in = open(sam[input])) {
             for (int k; (k = in.read(buf)) > 0; ) synchronized (lock) { if (failed[0] != null) return; EqpCountNative.chunkFeed(ctx, input, buf, k); }

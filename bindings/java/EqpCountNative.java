@@ -23,6 +23,8 @@ public final class EqpCountNative {
   public static native void prefetchChunk(long ctx, ByteBuffer t, long tLen, ByteBuffer j, long jLen, ByteBuffer g, long gLen) throws IOException;
   public static native void chunkBegin(long ctx, long tHint, long jHint, long gHint) throws IOException;
   public static native void chunkFeed(long ctx, int input, byte[] buf, int len) throws IOException;
+  /** One complete .sam.gz member in a direct buffer, inflated on the device; false: inflate it on the host (GZIPInputStream) and use chunkFeed. */
+  public static native boolean chunkFeedGz(long ctx, int input, ByteBuffer gz, long len) throws IOException;
   public static native void chunkEnd(long ctx, int[] intParams, double[] doubleParams, double[] gene, double[] exon, double[] junction, byte[] junctionActive,
                                      long[] scalars, double[] sumWeights) throws IOException;
   public static native String[] rowIds(long ctx, int mode);

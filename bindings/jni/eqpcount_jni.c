@@ -94,6 +94,17 @@ JNIEXPORT void JNICALL Java_EqpCountNative_chunkFeed(JNIEnv* e, jclass k, jlong 
   (*e)->ReleasePrimitiveArrayCritical(e, buf, p, JNI_ABORT);
   if (rc) throw_io(e, ctx);
 }
+/* one complete .sam.gz member (a direct ByteBuffer holding the file's bytes): compressed over PCIe, inflated on the device.
+ * JNI_FALSE: a valid file the device decoder does not take (several members / BGZF): inflate it with GZIPInputStream and chunkFeed. */
+JNIEXPORT jboolean JNICALL Java_EqpCountNative_chunkFeedGz(JNIEnv* e, jclass k, jlong h, jint input, jobject gz, jlong len) {
+  eqp_ctx* ctx = (eqp_ctx*)(intptr_t)h; const uint8_t* p = (const uint8_t*)(*e)->GetDirectBufferAddress(e, gz); int rc;
+  (void)k;
+  if (!p) { jclass io = (*e)->FindClass(e, "java/io/IOException"); if (io) (*e)->ThrowNew(e, io, "chunkFeedGz: not a direct ByteBuffer"); return JNI_FALSE; }
+  rc = eqp_chunk_feed_gz(ctx, input, p, (size_t)len);
+  if (rc == EQP_ERR_UNSUPPORTED) return JNI_FALSE;
+  if (rc) throw_io(e, ctx);
+  return JNI_TRUE;
+}
 JNIEXPORT void JNICALL Java_EqpCountNative_chunkEnd(JNIEnv* e, jclass k, jlong h, jintArray ip, jdoubleArray dp,
     jdoubleArray gene, jdoubleArray exon, jdoubleArray junc, jbyteArray act, jlongArray sc, jdoubleArray sums) {
   eqp_ctx* ctx = (eqp_ctx*)(intptr_t)h; eqp_params p; eqp_counts c;
