@@ -9,6 +9,8 @@ typedef jarray jlongArray; typedef jarray jdoubleArray; typedef jarray jbyteArra
 #define JNIEXPORT
 #define JNICALL
 #define JNI_ABORT 2
+#define JNI_FALSE 0
+#define JNI_TRUE 1
 struct JNINativeInterface_; typedef const struct JNINativeInterface_* JNIEnv;
 struct JNINativeInterface_ {
   jclass (*FindClass)(JNIEnv*, const char*);
