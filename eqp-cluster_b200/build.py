@@ -52,7 +52,7 @@ def build_library(force=False):
     srcs = _glob(CSRC, (".cu", ".cuh", ".h", ".hpp")) + [os.path.join(ROOT, "include", "eqp_count.h")]
     if force or _newer(srcs, LIB_PATH):
         os.makedirs(LIB_DIR, exist_ok=True)
-        _run([nvcc_path()] + NVCC_FLAGS + ["-o", LIB_PATH, os.path.join(CSRC, "eqp_capi.cu"), "-lz"])
+        _run([nvcc_path()] + NVCC_FLAGS + ["-o", LIB_PATH, os.path.join(CSRC, "eqp_capi.cu"), "-lz", "-lpthread"])
     return LIB_PATH
 
 

@@ -5,6 +5,7 @@
 #include <chrono>
 #include <deque>
 #include <memory>
+#include <thread>
 #include "../../include/eqp_count.h"
 #include "eqp_cuda_backend.cuh"
 #include "eqp_nccl.h"
@@ -123,17 +124,18 @@ struct eqp_ctx {
   static const int kStages = 4; static const size_t kStageBytes = 16u << 20;
   struct Feed { bool active = false; char* dev[3] = {nullptr, nullptr, nullptr}; size_t len[3] = {0, 0, 0}, cap[3] = {0, 0, 0}; } feed;
   uint8_t* stage[kStages] = {nullptr, nullptr, nullptr, nullptr}; cudaEvent_t stageFree[kStages] = {nullptr, nullptr, nullptr, nullptr}; int nextStage = 0;
-  void feed_reserve(int f, size_t want) {                           // grow on the copy stream: earlier pieces are copied over in stream order
+  void feed_reserve(int f, size_t want) { feed_reserve_on(f, want, feed.len[f], copyStream); }   // grow on the copy stream: earlier pieces are copied over in stream order
+  void feed_reserve_on(int f, size_t want, size_t keep, cudaStream_t st) {                       // keep: bytes of the old buffer that hold text
     if (want <= feed.cap[f]) return;
     size_t cap = feed.cap[f] ? feed.cap[f] * 2 : (size_t)64 << 20; if (cap < want) cap = want;
-    void* d = nullptr; EQP_CUDA(cudaMallocAsync(&d, cap + 16, copyStream));
-    if (feed.len[f]) EQP_CUDA(cudaMemcpyAsync(d, feed.dev[f], feed.len[f], cudaMemcpyDeviceToDevice, copyStream));
-    if (feed.dev[f]) EQP_CUDA(cudaFreeAsync(feed.dev[f], copyStream));
+    void* d = nullptr; EQP_CUDA(cudaMallocAsync(&d, cap + 16, st));
+    if (keep) EQP_CUDA(cudaMemcpyAsync(d, feed.dev[f], keep, cudaMemcpyDeviceToDevice, st));
+    if (feed.dev[f]) EQP_CUDA(cudaFreeAsync(feed.dev[f], st));
     feed.dev[f] = (char*)d; feed.cap[f] = cap;
   }
   void feed_drop() { for (int f = 0; f < 3; f++) { if (feed.dev[f]) cudaFreeAsync(feed.dev[f], copyStream ? copyStream : stream); } feed = Feed(); }
   // device inflate (eqp_chunk_feed_gz / eqp_count_chunk_gz): compressed bytes travel on their own stream, the inflate runs on the copy stream
-  cudaStream_t gzStream = nullptr; eqp_inflate_info lastInflate[3] = {};
+  cudaStream_t gzStream = nullptr, inflateStream[3] = {nullptr, nullptr, nullptr}; eqp_inflate_info lastInflate[3] = {};
   // NCCL communicator of this context (one rank per context)
   nccl_comm_t comm = nullptr; int commRanks = 0, commRank = -1;
   // device address of g_noalloc_scratch on this context's device (eqp_tokenize_noalloc), resolved in eqp_create
@@ -401,19 +403,48 @@ int eqp_chunk_feed_gz(eqp_ctx* ctx, int input, const uint8_t* gz, size_t len) {
   } catch (const std::exception& ex) { if (d) cudaFreeAsync(d, ctx->copyStream); if (ready) cudaEventDestroy(ready); return fail(ctx, EQP_ERR_CUDA, ex.what()); }
 }
 
+// The three members are inflated side by side: one host thread and one CUDA stream per input (copy of the compressed bytes, then the
+// inflate's kernels in order on that stream), so the copies overlap the inflates and the kernels of one input fill the SMs another one's
+// launch leaves idle (a stream of a few million reads has fewer deflate blocks than the device has thread slots).
 int eqp_count_chunk_gz(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_gz, size_t t_len, const uint8_t* j_gz, size_t j_len, const uint8_t* g_gz, size_t g_len, eqp_counts* out) {
   if (!ctx || !p || !out) return fail(ctx, EQP_ERR_ARG, "eqp_count_chunk_gz: null argument");
   const uint8_t* gz[3] = {t_gz, j_gz, g_gz}; const size_t len[3] = {t_len, j_len, g_len};
   for (int f = 0; f < 3; f++) if (len[f] && (!gz[f] || len[f] < 18)) return fail(ctx, EQP_ERR_ARG, "eqp_count_chunk_gz: bad gzip buffer");
   if (int rc = eqp_chunk_begin(ctx, 0, 0, 0)) return rc;
-  cudaEvent_t ready[3] = {nullptr, nullptr, nullptr}; char* d[3] = {nullptr, nullptr, nullptr}; int rc = EQP_OK;
+  int rcs[3] = {EQP_OK, EQP_OK, EQP_OK}; std::string errs[3];
   try {
-    for (int f = 0; f < 3; f++) if (len[f]) d[f] = gz_upload(ctx, gz[f], len[f], &ready[f]);       // all three copies are queued before the first inflate
-    for (int f = 0; f < 3 && rc == EQP_OK; f++) if (len[f]) rc = gz_inflate_into_feed(ctx, f, gz[f], d[f], len[f], ready[f]);
-  } catch (const std::exception& ex) { rc = fail(ctx, EQP_ERR_CUDA, ex.what()); }
-  if (ctx->gzStream && rc != EQP_OK) cudaStreamSynchronize(ctx->gzStream);
-  for (int f = 0; f < 3; f++) { if (d[f]) cudaFreeAsync(d[f], ctx->copyStream); if (ready[f]) cudaEventDestroy(ready[f]); }
-  if (rc != EQP_OK) { ctx->feed_drop(); return rc; }
+    cudaEvent_t begun; EQP_CUDA(cudaEventCreateWithFlags(&begun, cudaEventDisableTiming)); EQP_CUDA(cudaEventRecord(begun, ctx->copyStream));
+    for (int f = 0; f < 3; f++) {
+      if (!ctx->inflateStream[f]) EQP_CUDA(cudaStreamCreateWithFlags(&ctx->inflateStream[f], cudaStreamNonBlocking));
+      EQP_CUDA(cudaStreamWaitEvent(ctx->inflateStream[f], begun, 0));           // the feed buffers were reserved on the copy stream
+    }
+    cudaEventDestroy(begun);
+    const size_t budget = inflate_scratch_budget() / 3; const uint64_t seg = env_u64("EQP_INFLATE_SEG", 16384);
+    auto work = [&](int f) {
+      cudaStream_t st = ctx->inflateStream[f]; void* d = nullptr;
+      try {
+        EQP_CUDA(cudaSetDevice(ctx->device));
+        EQP_CUDA(cudaMallocAsync(&d, len[f] + 16, st));
+        EQP_CUDA(cudaMemsetAsync((char*)d + (len[f] & ~(size_t)3), 0, len[f] + 16 - (len[f] & ~(size_t)3), st));
+        EQP_CUDA(cudaMemcpyAsync(d, gz[f], len[f], cudaMemcpyHostToDevice, st));
+        eqp_ctx::Feed& F = ctx->feed; size_t written = 0;
+        ctx->feed_reserve_on(f, std::max<size_t>(3 * len[f], 1), 0, st);
+        zf::InflateInfo info = zf::device_inflate(gz[f], (const uint8_t*)d, len[f], st,
+            [&](uint64_t n) { ctx->feed_reserve_on(f, (size_t)n, written, st); written = (size_t)n; return (uint8_t*)F.dev[f]; }, seg, 0, budget);
+        F.len[f] = (size_t)info.outBytes;
+        eqp_inflate_info& o = ctx->lastInflate[f];
+        o.gz_bytes = len[f]; o.text_bytes = info.outBytes; o.segments = info.nSeg; o.chain = info.nChain; o.bogus_starts = info.nBogus; o.waves = info.nWaves;
+        o.search_ms = info.msSearch; o.decode_ms = info.msDecode; o.resolve_ms = info.msResolve; o.emit_ms = info.msEmit;
+      } catch (const zf::InflateError& e) { rcs[f] = e.unsupported ? EQP_ERR_UNSUPPORTED : EQP_ERR_FORMAT; errs[f] = "gzip input " + std::to_string(f) + ": " + e.msg; }
+      catch (const std::exception& ex) { rcs[f] = EQP_ERR_CUDA; errs[f] = ex.what(); }
+      if (d) cudaFreeAsync(d, st);
+      cudaStreamSynchronize(st);
+    };
+    std::vector<std::thread> th;
+    for (int f = 0; f < 3; f++) if (len[f]) th.emplace_back(work, f);
+    for (auto& t : th) t.join();
+  } catch (const std::exception& ex) { ctx->feed_drop(); return fail(ctx, EQP_ERR_CUDA, ex.what()); }
+  for (int f = 0; f < 3; f++) if (rcs[f] != EQP_OK) { ctx->feed_drop(); return fail(ctx, rcs[f], errs[f]); }
   return eqp_chunk_end(ctx, p, out);
 }
 
@@ -683,6 +714,7 @@ void eqp_destroy(eqp_ctx* ctx) {
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   if (ctx->gzStream) { cudaStreamSynchronize(ctx->gzStream); cudaStreamDestroy(ctx->gzStream); }
+  for (int f = 0; f < 3; f++) if (ctx->inflateStream[f]) { cudaStreamSynchronize(ctx->inflateStream[f]); cudaStreamDestroy(ctx->inflateStream[f]); }
   if (ctx->copyStream) cudaStreamDestroy(ctx->copyStream);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;

@@ -25,7 +25,7 @@ def main():
         for spec in sys.argv[2:]:
             name, _, flags = spec.partition("=")
             out = os.path.join(VDIR, "libeqpcount_%s.so" % name)
-            b._run([b.nvcc_path()] + b.NVCC_FLAGS + [f for f in flags.split(",") if f] + ["-o", out, os.path.join(b.CSRC, "eqp_capi.cu"), "-lz"])
+            b._run([b.nvcc_path()] + b.NVCC_FLAGS + [f for f in flags.split(",") if f] + ["-o", out, os.path.join(b.CSRC, "eqp_capi.cu"), "-lz", "-lpthread"])
             print("built", out)
         return
     import argparse
