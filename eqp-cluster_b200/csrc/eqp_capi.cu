@@ -358,11 +358,17 @@ int eqp_chunk_end(eqp_ctx* ctx, const eqp_params* p, eqp_counts* out) {
 
 // ---- .sam.gz input inflated on the device (eqp_inflate.cuh).  The compressed bytes of one gzip member go to the device on gzStream; the
 // inflate runs on the copy stream, on which the feed buffers live, and appends its text to the input's feed buffer.
-static size_t inflate_scratch_budget() {
+static size_t inflate_scratch_budget(int sharers = 1) {                // per concurrently inflated member
   size_t budget = (size_t)24 << 30;
   if (const char* e = getenv("EQP_INFLATE_SCRATCH_GB")) { double g = atof(e); if (g >= 0.001) budget = (size_t)(g * (double)((size_t)1 << 30)); }
   size_t freeB = 0, totalB = 0;
-  if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess && freeB > ((size_t)4 << 30)) budget = std::min(budget, (freeB - ((size_t)2 << 30)) / 2);
+  if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess) {
+    int dev = 0; cudaMemPool_t pool; uint64_t reserved = 0, used = 0;   // memory the stream-ordered pool holds but does not use is ours to take as well
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess &&
+        cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved) == cudaSuccess && cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used) == cudaSuccess && reserved > used)
+      freeB += (size_t)(reserved - used);
+    if (freeB > ((size_t)4 << 30)) budget = std::min(budget, (freeB - ((size_t)2 << 30)) / (2 * (size_t)sharers));
+  }
   return budget;
 }
 static uint64_t env_u64(const char* name, uint64_t dflt) { const char* e = getenv(name); return e && *e ? strtoull(e, nullptr, 10) : dflt; }
@@ -419,7 +425,7 @@ int eqp_count_chunk_gz(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_gz, s
       EQP_CUDA(cudaStreamWaitEvent(ctx->inflateStream[f], begun, 0));           // the feed buffers were reserved on the copy stream
     }
     cudaEventDestroy(begun);
-    const size_t budget = inflate_scratch_budget() / 3; const uint64_t seg = env_u64("EQP_INFLATE_SEG", 16384);
+    const size_t budget = inflate_scratch_budget(3); const uint64_t seg = env_u64("EQP_INFLATE_SEG", 16384);
     auto work = [&](int f) {
       cudaStream_t st = ctx->inflateStream[f]; void* d = nullptr;
       try {

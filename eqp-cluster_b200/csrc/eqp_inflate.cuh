@@ -79,10 +79,7 @@ __global__ void __launch_bounds__(ZF_THREADS, ZF_CTAS) k_zf_decode(const uint32_
   while (true) {
     __syncwarp();
     if (!__any_sync(0xffffffffu, d.state != ST_DONE)) break;
-    if (d.state != ST_DONE) dec_step<WRITE>(d, totalBits, segStart, nSeg, bogus, hl, hd);
-#ifdef EQP_VAR_ZF_STEPS2
-    if (d.state != ST_DONE) dec_step<WRITE>(d, totalBits, segStart, nSeg, bogus, hl, hd);   // A/B: two steps per warp barrier (no gain: 392-428 vs 372-490 ms per 6M-read chunk, profiles/r05i)
-#endif
+    dec_step<WRITE>(d, totalBits, segStart, nSeg, bogus, hl, hd);      // every lane, finished or not: the step has a warp barrier inside
   }
   if (k < nList) res[k] = d.r;
 }

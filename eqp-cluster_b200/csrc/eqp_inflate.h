@@ -225,7 +225,12 @@ EQP_HD uint64_t find_block_start(const uint32_t* w, uint64_t nWords, uint64_t fr
 // A state machine, one bounded step at a time (see Search): block boundary / header, up to two symbols, up to eight copied symbols,
 // up to eight stored bytes.
 struct SegOut { uint64_t endBit, outLen; uint32_t endSeg; int status; };
-enum { ST_BOUNDARY = 0, ST_SYMBOL = 1, ST_COPY = 2, ST_STORED = 3, ST_DONE = 4 };
+enum { ST_BOUNDARY = 0, ST_SYMBOL = 1, ST_COPY = 2, ST_STORED = 3, ST_DONE = 4, ST_DIST = 5 };
+#if defined(__CUDA_ARCH__)
+#define EQP_WARP_MEET() __syncwarp()
+#else
+#define EQP_WARP_MEET()
+#endif
 struct Dec { Bits b; Sink s; int state; uint32_t len, dist, self, j; bool final, first; SegOut r; };
 EQP_HD void dec_init(Dec& d, const uint32_t* w, uint64_t nWords, uint64_t start, uint32_t self, uint32_t nSeg, const Sink& s) {
   d.b.w = w; d.b.nWords = nWords; bits_seek(d.b, start); d.s = s; d.state = ST_BOUNDARY; d.len = d.dist = 0; d.self = self; d.j = self + 1;
@@ -254,35 +259,41 @@ EQP_HD void dec_copy_batch(Dec& d) {
   }
   s.o += n; d.len -= n;
 }
-// Straight-line: (A) one literal/length symbol for the lanes in ST_SYMBOL, (B) one batch of a pending match for the lanes in ST_COPY
-// (including those that just decoded it), then the rare states.  No early returns in (A) and (B): the lanes of a warp walk through them together.
+// Straight-line: (A) ONE Huffman symbol — a literal/length symbol for the lanes in ST_SYMBOL, the distance symbol of a pending match for the
+// lanes in ST_DIST, through the same instructions (only the table differs) — then, after the lanes have met again, (B) one batch of a pending
+// copy for the lanes in ST_COPY, then the rare states.  (ncu on the first straight-line version, profiles/r05k: the distance path ran in
+// almost every step with 3 active lanes, and the copy path twice per step because the lanes that skipped (A) reached it early.)
 template <bool WRITE>
 EQP_HD void dec_step(Dec& d, uint64_t totalBits, const uint64_t* segStart, uint32_t nSeg, const uint8_t* bogus, const Huff& hl, const Huff& hd) {
   Bits& b = d.b; Sink& s = d.s;
-  if (d.state == ST_SYMBOL) {
+  if (d.state == ST_SYMBOL || d.state == ST_DIST) {
+    const bool isDist = d.state == ST_DIST;
+    Huff h; h.limit = isDist ? hd.limit : hl.limit; h.base = isDist ? hd.base : hl.base; h.sym = isDist ? hd.sym : hl.sym; h.stride = hl.stride; h.symStride = hl.symStride;
     bits_fill(b);
-    const int sym = huff_decode(b, hl);
-    if (sym < 256) {
-      if (sym < 0) dec_finish(d, ZF_BAD);
-      else { sink_lit<WRITE>(s, (uint32_t)sym); if (WRITE && s.status) dec_finish(d, s.status); }
-    } else if (sym == 256) dec_block_end(d, totalBits);
-    else if (sym > 285) dec_finish(d, ZF_BAD);
-    else {
-      int ex; uint32_t len = len_base(sym, ex); len += bits_take(b, ex);
-      bits_fill(b);
-      const int ds = huff_decode(b, hd);
-      if (ds < 0 || ds > 29) dec_finish(d, ZF_BAD);
+    const int sym = huff_decode(b, h);
+    if (!isDist) {
+      if (sym < 256) {
+        if (sym < 0) dec_finish(d, ZF_BAD);
+        else { sink_lit<WRITE>(s, (uint32_t)sym); if (WRITE && s.status) dec_finish(d, s.status); }
+      } else if (sym == 256) dec_block_end(d, totalBits);
+      else if (sym > 285) dec_finish(d, ZF_BAD);
+      else { int ex; uint32_t len = len_base(sym, ex); d.len = len + bits_take(b, ex); d.state = ST_DIST; }
+    } else {
+      if (sym < 0 || sym > 29) dec_finish(d, ZF_BAD);
       else {
-        uint32_t dist = dist_base(ds, ex); dist += bits_take(b, ex);
-        if (!WRITE) s.o += len;
-        else if (s.o + len > s.cap) dec_finish(d, ZF_OVERFLOW);
+        int ex; uint32_t dist = dist_base(sym, ex); dist += bits_take(b, ex);
+        if (!WRITE) { s.o += d.len; d.state = ST_SYMBOL; }
+        else if (s.o + d.len > s.cap) dec_finish(d, ZF_OVERFLOW);
         else if (dist > s.o && (dist - s.o > ZF_WINDOW || !s.window)) dec_finish(d, s.window ? ZF_BAD : ZF_NOWINDOW);
-        else { d.len = len; d.dist = dist; d.state = ST_COPY; }
+        else { d.dist = dist; d.state = ST_COPY; }
       }
     }
   }
-  if (WRITE && d.state == ST_COPY) { dec_copy_batch(d); if (!d.len) d.state = ST_SYMBOL; }
-  if (d.state == ST_SYMBOL || d.state == ST_COPY || d.state == ST_DONE) return;
+  if (WRITE) {
+    EQP_WARP_MEET();
+    if (d.state == ST_COPY) { dec_copy_batch(d); if (!d.len) d.state = ST_SYMBOL; }
+  }
+  if (d.state == ST_SYMBOL || d.state == ST_DIST || d.state == ST_COPY || d.state == ST_DONE) return;
   if (d.state == ST_STORED) {
     for (int k = 0; k < 8 && d.len; k++, d.len--) { bits_fill(b); sink_lit<WRITE>(s, bits_take(b, 8)); }
     if (WRITE && s.status) { dec_finish(d, s.status); return; }
