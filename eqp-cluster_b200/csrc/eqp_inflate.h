@@ -180,35 +180,39 @@ EQP_HD uint64_t bits64(const uint32_t* w, uint64_t nWords, uint64_t p) {
 EQP_HD uint8_t kraft3(uint32_t x) {                                   // table entry: three 3-bit code lengths -> sum of 2^(7 - len) over the non-zero ones
   uint32_t k = 0; for (int i = 0; i < 3; i++) { const uint32_t v = (x >> (3 * i)) & 7u; k += (128u >> v) & 127u; } return (uint8_t)k;
 }
-struct Search { uint64_t p, to, cand, found; bool pending, done; };
-EQP_HD void search_init(Search& s, uint64_t from, uint64_t to) { s.p = from; s.to = to; s.cand = 0; s.found = ZF_NONE; s.pending = false; s.done = from >= to; }
+// One bounded sub-step per call (the kernel puts a warp barrier between calls): either load the next 48-position window and sieve it (1), or
+// take ONE candidate of the current window through the Kraft test (2).  (ncu on the version that looped over a window's candidates inside
+// the call, profiles/r05k: the lanes drifted apart inside the loop, its body ran 11.6 times per window with 7 of 32 lanes — 53 % of the kernel.)
+struct Search { uint64_t p, to, cand, found, x, m; uint32_t span; bool pending, done; };
+EQP_HD void search_init(Search& s, uint64_t from, uint64_t to) { s.p = from; s.to = to; s.cand = 0; s.found = ZF_NONE; s.x = s.m = 0; s.span = 0; s.pending = false; s.done = from >= to; }
+EQP_HD void search_advance(Search& s) { s.p += s.span; s.span = 0; if (s.p >= s.to) s.done = true; }   // the current window is exhausted
 EQP_HD void search_scan(Search& s, const uint32_t* w, uint64_t nWords, const uint8_t* lut) {
-  for (int win = 0; win < 4 && s.p < s.to; win++) {
+  if (!s.m) {
     const uint64_t x = bits64(w, nWords, s.p);
     uint64_t m = ~x & ~(x >> 1) & (x >> 2) & ~((x >> 4) & (x >> 5) & (x >> 6) & (x >> 7)) & ~((x >> 9) & (x >> 10) & (x >> 11) & (x >> 12));
     const uint64_t span = s.to - s.p < 48 ? s.to - s.p : 48;
     m &= (1ull << span) - 1ull;
-    while (m) {
-#if defined(__CUDA_ARCH__)
-      const int k = __ffsll((long long)m) - 1;
-#else
-      const int k = __builtin_ctzll(m);
-#endif
-      m &= m - 1;
-      const int hclen = (int)((x >> (k + 13)) & 15u) + 4;
-      const uint64_t y = bits64(w, nWords, s.p + k + 17) & ((1ull << (3 * hclen)) - 1ull);
-      const uint32_t sum = (uint32_t)lut[y & 511u] + lut[(y >> 9) & 511u] + lut[(y >> 18) & 511u] + lut[(y >> 27) & 511u] + lut[(y >> 36) & 511u] + lut[(y >> 45) & 511u] + lut[(y >> 54) & 511u];
-      if (sum == 128u) { s.pending = true; s.cand = s.p + k; return; }
-    }
-    s.p += span;
+    s.x = x; s.m = m; s.span = (uint32_t)span;
+    if (!m) search_advance(s);
+    return;
   }
-  if (s.p >= s.to) s.done = true;
+#if defined(__CUDA_ARCH__)
+  const int k = __ffsll((long long)s.m) - 1;
+#else
+  const int k = __builtin_ctzll(s.m);
+#endif
+  s.m &= s.m - 1;
+  const int hclen = (int)((s.x >> (k + 13)) & 15u) + 4;
+  const uint64_t y = bits64(w, nWords, s.p + k + 17) & ((1ull << (3 * hclen)) - 1ull);
+  const uint32_t sum = (uint32_t)lut[y & 511u] + lut[(y >> 9) & 511u] + lut[(y >> 18) & 511u] + lut[(y >> 27) & 511u] + lut[(y >> 36) & 511u] + lut[(y >> 45) & 511u] + lut[(y >> 54) & 511u];
+  if (sum == 128u) { s.pending = true; s.cand = s.p + k; return; }
+  if (!s.m) search_advance(s);
 }
 EQP_HD void search_check(Search& s, const uint32_t* w, uint64_t nWords, uint64_t totalBits, const Huff& hl, const Huff& hd) {
   Bits c; c.w = w; c.nWords = nWords; bits_seek(c, s.cand + 3);
   if (read_dynamic(c, hl, hd, true) && probe_symbols(c, hl, hd, 96) && bits_pos(c) <= totalBits) { s.found = s.cand; s.done = true; return; }
-  s.pending = false; s.p = s.cand + 1;
-  if (s.p >= s.to) s.done = true;
+  s.pending = false;
+  if (!s.m) search_advance(s);
 }
 EQP_HD uint64_t find_block_start(const uint32_t* w, uint64_t nWords, uint64_t from, uint64_t to, uint64_t totalBits, const Huff& hl, const Huff& hd) {
   uint8_t lut[512]; for (uint32_t i = 0; i < 512; i++) lut[i] = kraft3(i);
