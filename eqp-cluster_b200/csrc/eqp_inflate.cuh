@@ -215,10 +215,11 @@ struct InflateError { std::string msg; bool unsupported; };          // unsuppor
 // Inflates ONE gzip member.  zHost: the whole file in host memory (header and trailer are read there); zDev: the same bytes in device
 // memory, 4-byte aligned, followed by at least 8 zero bytes; copyDone: event after which zDev is complete (may be null).
 // reserve(n) returns a device buffer of at least n bytes that keeps what was written so far (it may move).  Work runs on `st`; returns
-// after the last kernel has finished.  segBytes / scratchBytes: segment size, scratch budget (ratio is unused: the counting pass sizes every segment exactly).
+// after the last kernel has finished.  segBytes / scratchBytes: segment size, scratch budget (ratio is unused: the counting pass sizes every segment exactly); maxGroups: CTAs of the
+// resolve; testBogusEvery: test hook.
 template <class Reserve>
 InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t zLen, cudaStream_t st, Reserve reserve,
-                           uint64_t segBytes = 65536, uint64_t ratio = 0, uint64_t scratchBytes = 24ull << 30) {
+                           uint64_t segBytes = 65536, uint64_t ratio = 0, uint64_t scratchBytes = 24ull << 30, uint32_t maxGroups = 296, uint32_t testBogusEvery = 0) {
   InflateInfo info;
   if (zLen < 18 || zHost[0] != 0x1f || zHost[1] != 0x8b || zHost[2] != 8) throw InflateError{"not a gzip file (magic / method)", false};
   const uint8_t flg = zHost[3]; uint64_t off = 10;
@@ -253,6 +254,10 @@ InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t z
     timed(info.msSearch, [&] { k_zf_search<<<(nSeg + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dataBit, segBytes * 8, nSeg, dStart, dSym); });
     std::vector<uint64_t> start(nSeg); ZF_CUDA(cudaMemcpyAsync(start.data(), dStart, (size_t)nSeg * 8, cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
     std::vector<uint8_t> bogus(nSeg, 0);
+    if (testBogusEvery) {                                                 // test hook: every k-th found start is moved one bit on, i.e. made wrong
+      for (uint32_t i = 1, k = 0; i < nSeg; i++) if (start[i] != ZF_NONE && ++k % testBogusEvery == 0) start[i] += 1;
+      ZF_CUDA(cudaMemcpyAsync(dStart, start.data(), (size_t)nSeg * 8, cudaMemcpyHostToDevice, st));
+    }
     // ---- counting pass over every segment with a start, then the chain walk (a chain member that passed a claimed start proves it bogus)
     std::vector<DecodeItem> items; std::vector<uint32_t> itemOf(nSeg, 0xFFFFFFFFu);
     for (uint32_t i = 0; i < nSeg; i++) if (start[i] != ZF_NONE) { itemOf[i] = (uint32_t)items.size(); items.push_back(DecodeItem{0, 0, i, 0}); }
@@ -314,7 +319,7 @@ InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t z
       if (nSl > sliceCap) { sliceCap = 2 * nSl + 16; dSlice = (uint32_t*)dalloc(sliceCap * 4); }
       uint32_t* dS[2][2]; size_t at = 0;
       for (int p = 0; p < 2; p++) for (int q = 0; q < 2; q++) { dS[p][q] = dSlice + at; if (!sl[p][q].empty()) ZF_CUDA(cudaMemcpyAsync(dS[p][q], sl[p][q].data(), sl[p][q].size() * 4, cudaMemcpyHostToDevice, st)); at += sl[p][q].size(); }
-      const uint32_t nGroups = std::min<uint32_t>(n, 296), perGroup = (n + nGroups - 1) / nGroups, usedGroups = (n + perGroup - 1) / perGroup;
+      const uint32_t nGroups = std::min<uint32_t>(n, std::max<uint32_t>(maxGroups, 1)), perGroup = (n + nGroups - 1) / nGroups, usedGroups = (n + perGroup - 1) / perGroup;
       if (usedGroups > groupCap) { groupCap = usedGroups; dGroupFinal = (uint16_t*)dalloc((size_t)groupCap * ZF_WINDOW * 2); dGroupInit = (uint8_t*)dalloc((size_t)groupCap * ZF_WINDOW); }
       timed(info.msResolve, [&] {
         k_zf_resolve_groups<<<usedGroups, ZF_RES_THREADS, ZF_WINDOW * 2, st>>>(scratch, dChain, n, perGroup, dGroupFinal);

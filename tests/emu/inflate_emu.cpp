@@ -1,7 +1,7 @@
 // Host emulation of the device inflate (eqp-cluster_b200/csrc/eqp_inflate.h): the same per-thread functions, the kernels' loops run one
 // "thread" after the other, the host driver's chain walk and waves restated.  Test infrastructure (tests/test_inflate.py compares the
 // output with zlib's); never linked into the library.
-//   inflate_emu <in.gz> <out> [segBytes ratio segsPerWave]
+//   inflate_emu <in.gz> <out> [segBytes ratio segsPerWave bogusEvery]      bogusEvery = k: every k-th found start is moved one bit on (made wrong)
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -20,7 +20,7 @@ static int fail(const char* m) { fprintf(stderr, "ERROR: %s\n", m); return 1; }
 int main(int argc, char** argv) {
   if (argc < 3) return fail("usage: inflate_emu <in.gz> <out> [segBytes ratio segsPerWave]");
   const uint64_t segBytes = argc > 3 ? strtoull(argv[3], 0, 10) : 32768, ratio = argc > 4 ? strtoull(argv[4], 0, 10) : 8;
-  const uint32_t perWave = argc > 5 ? (uint32_t)strtoul(argv[5], 0, 10) : 1u << 30;
+  const uint32_t perWave = argc > 5 ? (uint32_t)strtoul(argv[5], 0, 10) : 1u << 30, bogusEvery = argc > 6 ? (uint32_t)strtoul(argv[6], 0, 10) : 0;
   FILE* f = fopen(argv[1], "rb"); if (!f) return fail("cannot open input");
   std::vector<uint8_t> z; { uint8_t buf[1 << 16]; size_t n; while ((n = fread(buf, 1, sizeof buf, f)) > 0) z.insert(z.end(), buf, buf + n); } fclose(f);
   const uint64_t zLen = z.size();
@@ -45,6 +45,7 @@ int main(int argc, char** argv) {
     if (from < to) start[i] = find_block_start(w, nWords, from, to, totalBits, T.hl, T.hd);
     found += start[i] != ZF_NONE;
   }
+  if (bogusEvery) for (uint32_t i = 1, k = 0; i < nSeg; i++) if (start[i] != ZF_NONE && ++k % bogusEvery == 0) start[i] += 1;
   std::vector<uint8_t> bogus(nSeg, 0), text; std::vector<SegOut> res(nSeg);
   std::vector<uint8_t> win(ZF_WINDOW, 0);
   uint64_t abs = 0, endBit = 0; uint32_t nBogus = 0, nWaves = 0;

@@ -68,3 +68,20 @@ def test_chunk_from_gzip_equals_chunk_from_text(ctx):
     for m in eqp.MODES:
         assert np.array_equal(a.fixed[m], b.fixed[m]), m
     assert a.number_mapped_reads == b.number_mapped_reads
+
+
+def test_wrong_block_starts_and_multi_segment_groups(ctx, text, monkeypatch):
+    """The retry path (a chain member passes a claimed start: it is dropped, the member re-run through it — by ONE thread, hence the small
+    inputs) and resolve groups of several segments (the suite's small inputs otherwise give every segment its own group)."""
+    monkeypatch.setenv("EQP_INFLATE_SEG", "8192")
+    monkeypatch.setenv("EQP_INFLATE_GROUPS", "7")
+    assert ctx.debug_inflate(gzip.compress(text, 6)) == text
+    assert ctx.last_inflate(0)["bogus_starts"] == 0
+    part = text[:1_500_000]
+    monkeypatch.setenv("EQP_INFLATE_TEST_BOGUS", "2")
+    assert ctx.debug_inflate(gzip.compress(part, 6)) == part
+    assert ctx.last_inflate(0)["bogus_starts"] >= 3
+    part = text[:300_000]
+    monkeypatch.setenv("EQP_INFLATE_TEST_BOGUS", "1")
+    assert ctx.debug_inflate(gzip.compress(part, 6)) == part
+    assert ctx.last_inflate(0)["chain"] == 1

@@ -105,3 +105,13 @@ def test_refusals(emu, tmp_path, text):
     assert p.returncode != 0 or out != text
     p, _ = run_emu(emu, tmp_path, b"plain text, not gzip at all\n")
     assert p.returncode != 0
+
+
+@pytest.mark.parametrize("every", [1, 3])
+def test_wrong_block_starts_are_dropped_by_the_chain_walk(emu, tmp_path, text, every):
+    """Test hook: every k-th found start is moved one bit on.  The decoder in front of it passes it without landing on it, the host marks it
+    bogus and re-runs that decoder through it: the output must not change (every = 1: no found start survives, one thread decodes everything)."""
+    p, out = run_emu(emu, tmp_path, gzip.compress(text, 6), (8192, 8, 1 << 30, every))
+    assert p.returncode == 0, p.stderr
+    assert out == text
+    assert "bogus 0" not in p.stdout
