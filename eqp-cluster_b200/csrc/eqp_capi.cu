@@ -387,7 +387,7 @@ static int gz_inflate_into_feed(eqp_ctx* ctx, int f, const uint8_t* gz, const ch
     ctx->feed_reserve(f, base + std::max<size_t>(3 * len, 1));
     zf::InflateInfo info = zf::device_inflate(gz, (const uint8_t*)zDev, len, ctx->copyStream,
         [&](uint64_t n) { ctx->feed_reserve(f, base + (size_t)n); return (uint8_t*)F.dev[f] + base; },
-        env_u64("EQP_INFLATE_SEG", 16384), 0, inflate_scratch_budget(), (uint32_t)env_u64("EQP_INFLATE_GROUPS", 296), (uint32_t)env_u64("EQP_INFLATE_TEST_BOGUS", 0));
+        env_u64("EQP_INFLATE_SEG", 16384), 0, inflate_scratch_budget(), (uint32_t)env_u64("EQP_INFLATE_GROUPS", 296), (uint32_t)env_u64("EQP_INFLATE_TEST_BOGUS", 0), !getenv("EQP_INFLATE_NO_CRC"));
     F.len[f] = base + (size_t)info.outBytes;
     eqp_inflate_info& o = ctx->lastInflate[f];
     o.gz_bytes = len; o.text_bytes = info.outBytes; o.segments = info.nSeg; o.chain = info.nChain; o.bogus_starts = info.nBogus; o.waves = info.nWaves;
@@ -436,7 +436,7 @@ int eqp_count_chunk_gz(eqp_ctx* ctx, const eqp_params* p, const uint8_t* t_gz, s
         eqp_ctx::Feed& F = ctx->feed; size_t written = 0;
         ctx->feed_reserve_on(f, std::max<size_t>(3 * len[f], 1), 0, st);
         zf::InflateInfo info = zf::device_inflate(gz[f], (const uint8_t*)d, len[f], st,
-            [&](uint64_t n) { ctx->feed_reserve_on(f, (size_t)n, written, st); written = (size_t)n; return (uint8_t*)F.dev[f]; }, seg, 0, budget, (uint32_t)env_u64("EQP_INFLATE_GROUPS", 296), (uint32_t)env_u64("EQP_INFLATE_TEST_BOGUS", 0));
+            [&](uint64_t n) { ctx->feed_reserve_on(f, (size_t)n, written, st); written = (size_t)n; return (uint8_t*)F.dev[f]; }, seg, 0, budget, (uint32_t)env_u64("EQP_INFLATE_GROUPS", 296), (uint32_t)env_u64("EQP_INFLATE_TEST_BOGUS", 0), !getenv("EQP_INFLATE_NO_CRC"));
         F.len[f] = (size_t)info.outBytes;
         eqp_inflate_info& o = ctx->lastInflate[f];
         o.gz_bytes = len[f]; o.text_bytes = info.outBytes; o.segments = info.nSeg; o.chain = info.nChain; o.bogus_starts = info.nBogus; o.waves = info.nWaves;

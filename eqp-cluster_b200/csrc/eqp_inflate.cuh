@@ -3,6 +3,7 @@
 //   k_zf_decode   thread per listed segment: blocks -> 16-bit symbols in the segment's scratch region (Huffman tables in shared memory,
 //                 interleaved over the CTA's threads)
 //   k_zf_resolve_groups / k_zf_chain_windows  markers in every chain segment's last 32 K symbols, by groups of segments (see there)
+//   k_zf_crc      CRC-32 of the finished text by 1 MB pieces (combined on the host) against the gzip trailer
 //   k_zf_emit     CTA per (segment, slice): pass 0 writes the tails' bytes, pass 1 everything else (markers read the text in front of the segment)
 #pragma once
 #include <cuda_runtime.h>
@@ -207,6 +208,32 @@ __global__ void __launch_bounds__(256) k_zf_emit(const uint16_t* scratch, const 
   }
 }
 
+// CRC-32 of the text: CTA per 1 MB piece, thread per 4 KB sub-piece (16-byte loads, byte-wise table in shared memory), thread 0 combines
+__global__ void __launch_bounds__(ZF_CRC_SUBS) k_zf_crc(const uint8_t* text, uint64_t n, uint32_t opSub, uint32_t* pieceCrc) {
+  __shared__ uint32_t table[256]; __shared__ uint32_t sub[ZF_CRC_SUBS];
+  const uint32_t t = threadIdx.x;
+  table[t] = crc_table_entry(t);
+  __syncthreads();
+  const uint64_t base = (uint64_t)blockIdx.x * ZF_CRC_SUB * ZF_CRC_SUBS, plen = n - base < (uint64_t)ZF_CRC_SUB * ZF_CRC_SUBS ? n - base : (uint64_t)ZF_CRC_SUB * ZF_CRC_SUBS;
+  const uint64_t lo = (uint64_t)t * ZF_CRC_SUB; uint32_t crc = 0;
+  if (lo < plen) {
+    const uint64_t len = plen - lo < ZF_CRC_SUB ? plen - lo : ZF_CRC_SUB; const uint8_t* p = text + base + lo;
+    uint32_t c = 0xFFFFFFFFu; uint64_t i = 0;
+    if ((((uintptr_t)p) & 15) == 0) for (; i + 16 <= len; i += 16) {
+      const uint4 q = *reinterpret_cast<const uint4*>(p + i); const uint32_t wv[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int k = 0; k < 4; k++) { uint32_t x = wv[k];
+#pragma unroll
+        for (int b = 0; b < 4; b++) { c = table[(c ^ x) & 0xFFu] ^ (c >> 8); x >>= 8; } }
+    }
+    for (; i < len; i++) c = table[(c ^ p[i]) & 0xFFu] ^ (c >> 8);
+    crc = ~c;
+  }
+  sub[t] = crc;
+  __syncthreads();
+  if (t == 0) pieceCrc[blockIdx.x] = crc_piece(sub, plen, opSub);
+}
+
 struct InflateInfo { uint64_t outBytes = 0; uint32_t nSeg = 0, nChain = 0, nBogus = 0, nWaves = 0, reruns = 0; float msSearch = 0, msDecode = 0, msResolve = 0, msEmit = 0; };
 struct InflateError { std::string msg; bool unsupported; };          // unsupported: a valid gzip file this decoder does not take (several members)
 
@@ -219,7 +246,7 @@ struct InflateError { std::string msg; bool unsupported; };          // unsuppor
 // resolve; testBogusEvery: test hook.
 template <class Reserve>
 InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t zLen, cudaStream_t st, Reserve reserve,
-                           uint64_t segBytes = 65536, uint64_t ratio = 0, uint64_t scratchBytes = 24ull << 30, uint32_t maxGroups = 296, uint32_t testBogusEvery = 0) {
+                           uint64_t segBytes = 65536, uint64_t ratio = 0, uint64_t scratchBytes = 24ull << 30, uint32_t maxGroups = 296, uint32_t testBogusEvery = 0, bool checkCrc = true) {
   InflateInfo info;
   if (zLen < 18 || zHost[0] != 0x1f || zHost[1] != 0x8b || zHost[2] != 8) throw InflateError{"not a gzip file (magic / method)", false};
   const uint8_t flg = zHost[3]; uint64_t off = 10;
@@ -331,6 +358,16 @@ InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t z
     }
     uint32_t herr = 0; ZF_CUDA(cudaMemcpyAsync(&herr, dErr, 4, cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
     if (herr) throw InflateError{"invalid deflate data (distance in front of the stream)", false};
+    if (checkCrc && abs) {                                                 // the trailer's CRC-32 against the text as it now stands in device memory
+      const uint64_t PIECE = (uint64_t)ZF_CRC_SUB * ZF_CRC_SUBS; const uint32_t nPieces = (uint32_t)((abs + PIECE - 1) / PIECE);
+      uint32_t* dCrc = (uint32_t*)dalloc((size_t)nPieces * 4); std::vector<uint32_t> pc(nPieces);
+      timed(info.msEmit, [&] { k_zf_crc<<<nPieces, ZF_CRC_SUBS, 0, st>>>(text, abs, crc_shift_op(ZF_CRC_SUB), dCrc); });
+      ZF_CUDA(cudaMemcpyAsync(pc.data(), dCrc, (size_t)nPieces * 4, cudaMemcpyDeviceToHost, st)); ZF_CUDA(cudaStreamSynchronize(st));
+      const uint32_t opPiece = crc_shift_op(PIECE); uint32_t acc = 0;
+      for (uint32_t i = 0; i < nPieces; i++) { const uint64_t plen = abs - (uint64_t)i * PIECE < PIECE ? abs - (uint64_t)i * PIECE : PIECE; acc = crc_combine(acc, pc[i], plen == PIECE ? opPiece : crc_shift_op(plen)); }
+      const uint32_t want = zHost[zLen - 8] | (zHost[zLen - 7] << 8) | (zHost[zLen - 6] << 16) | ((uint32_t)zHost[zLen - 5] << 24);
+      if (acc != want) throw InflateError{"gzip CRC check failed", false};
+    }
     info.outBytes = abs;
     release(); cudaEventDestroy(ev[0]); cudaEventDestroy(ev[1]);
     return info;

@@ -333,5 +333,43 @@ template <bool WRITE> EQP_HD SegOut inflate_segment(const uint32_t* w, uint64_t 
   return d.r;
 }
 
+// ---- CRC-32 of the inflated text (the gzip trailer's check).  The text is cut into pieces whose CRCs are computed independently and
+// combined: crc(A ‖ B) = crc(A) · x^(8|B|) mod P  xor  crc(B), polynomials over GF(2) in the reflected representation — the arithmetic of
+// zlib's crc32_combine_gen / crc32_combine_op (zlib 1.2.12+, crc32.c: multmodp, x2nmodp), restated.
+static const uint32_t ZF_CRC_POLY = 0xEDB88320u;
+EQP_HD uint32_t crc_multmodp(uint32_t a, uint32_t b) {                  // a(x) * b(x) mod P(x)
+  uint32_t m = 1u << 31, p = 0;
+  for (;;) {
+    if (a & m) { p ^= b; if ((a & (m - 1)) == 0) break; }
+    m >>= 1;
+    b = (b & 1u) ? (b >> 1) ^ ZF_CRC_POLY : b >> 1;
+  }
+  return p;
+}
+EQP_HD uint32_t crc_shift_op(uint64_t len) {                            // x^(8 * len) mod P: the operator that moves a CRC over `len` following bytes
+  uint32_t sq = 1u << 30, p = 1u << 31;                                 // x^1, x^0
+  sq = crc_multmodp(sq, sq); sq = crc_multmodp(sq, sq); sq = crc_multmodp(sq, sq);   // x^8 = x^(8 * 2^0)
+  while (len) { if (len & 1) p = crc_multmodp(sq, p); len >>= 1; if (len) sq = crc_multmodp(sq, sq); }
+  return p;
+}
+EQP_HD uint32_t crc_combine(uint32_t crc1, uint32_t crc2, uint32_t op) { return crc_multmodp(op, crc1) ^ crc2; }
+EQP_HD uint32_t crc_table_entry(uint32_t i) { uint32_t c = i; for (int k = 0; k < 8; k++) c = (c & 1u) ? ZF_CRC_POLY ^ (c >> 1) : c >> 1; return c; }
+EQP_HD uint32_t crc_bytes(const uint32_t* table, const uint8_t* p, uint64_t n) {   // the standard CRC-32 (pre- and post-conditioned) of n bytes
+  uint32_t c = 0xFFFFFFFFu;
+  for (uint64_t i = 0; i < n; i++) c = table[(c ^ p[i]) & 0xFFu] ^ (c >> 8);
+  return ~c;
+}
+static const uint32_t ZF_CRC_SUB = 4096, ZF_CRC_SUBS = 256;            // a piece = 256 sub-pieces of 4 KB = 1 MB
+// CRC of one piece from its sub-pieces' CRCs (sub-piece i covers bytes [i * 4 KB, ...) of the piece; the last ones may be short or empty)
+EQP_HD uint32_t crc_piece(const uint32_t* sub, uint64_t pieceLen, uint32_t opSub) {
+  uint32_t acc = 0;
+  for (uint32_t i = 0; i < ZF_CRC_SUBS; i++) {
+    const uint64_t lo = (uint64_t)i * ZF_CRC_SUB; if (lo >= pieceLen) break;
+    const uint64_t len = pieceLen - lo < ZF_CRC_SUB ? pieceLen - lo : ZF_CRC_SUB;
+    acc = crc_combine(acc, sub[i], len == ZF_CRC_SUB ? opSub : crc_shift_op(len));
+  }
+  return acc;
+}
+
 }  // namespace zf
 }  // namespace eqpb

@@ -93,6 +93,19 @@ int main(int argc, char** argv) {
   }
   if ((endBit + 7) / 8 + 8 != zLen) return fail("bytes after the first gzip member");
   if ((uint32_t)abs != isize) return fail("gzip length check failed (ISIZE)");
+  { // k_zf_crc + the host's combine: sub-piece CRCs, piece CRCs, the text's CRC against the trailer
+    uint32_t table[256]; for (uint32_t i = 0; i < 256; i++) table[i] = crc_table_entry(i);
+    const uint64_t PIECE = (uint64_t)ZF_CRC_SUB * ZF_CRC_SUBS; const uint32_t opSub = crc_shift_op(ZF_CRC_SUB), opPiece = crc_shift_op(PIECE);
+    uint32_t acc = 0;
+    for (uint64_t base = 0; base < abs; base += PIECE) {
+      const uint64_t plen = abs - base < PIECE ? abs - base : PIECE; uint32_t sub[ZF_CRC_SUBS];
+      for (uint32_t t = 0; t < ZF_CRC_SUBS; t++) { const uint64_t lo = (uint64_t)t * ZF_CRC_SUB; sub[t] = lo < plen ? crc_bytes(table, text.data() + base + lo, plen - lo < ZF_CRC_SUB ? plen - lo : ZF_CRC_SUB) : 0; }
+      acc = crc_combine(acc, crc_piece(sub, plen, opSub), plen == PIECE ? opPiece : crc_shift_op(plen));
+    }
+    const uint32_t want = z[zLen - 8] | (z[zLen - 7] << 8) | (z[zLen - 6] << 16) | ((uint32_t)z[zLen - 5] << 24);
+    if (acc != want) { fprintf(stderr, "crc %08x, trailer %08x\n", acc, want); return fail("gzip CRC check failed"); }
+    printf("crc %08x ", acc);
+  }
   f = fopen(argv[2], "wb"); if (!f) return fail("cannot open output");
   if (!text.empty()) fwrite(text.data(), 1, text.size(), f);
   fclose(f);

@@ -53,6 +53,14 @@ def test_refusals(ctx, text):
     with pytest.raises(eqp.EqpError):
         ctx.debug_inflate(b"plain text, not gzip at all, but long enough\n")
     z = bytearray(gzip.compress(text, 6))
+    z[-6] ^= 0x01                                                          # the trailer's CRC-32: the text itself inflates fine, the check must catch it
+    with pytest.raises(eqp.EqpError, match="CRC"):
+        ctx.debug_inflate(bytes(z))
+    z = bytearray(gzip.compress(text[:2_000_000], 0))                      # stored blocks: a flipped payload byte changes nothing but the CRC
+    z[len(z) // 2] ^= 0x20
+    with pytest.raises(eqp.EqpError, match="CRC"):
+        ctx.debug_inflate(bytes(z))
+    z = bytearray(gzip.compress(text, 6))
     z[len(z) // 2] ^= 0x55
     try:
         assert ctx.debug_inflate(bytes(z)) != text

@@ -105,6 +105,14 @@ def test_refusals(emu, tmp_path, text):
     assert p.returncode != 0 or out != text
     p, _ = run_emu(emu, tmp_path, b"plain text, not gzip at all\n")
     assert p.returncode != 0
+    z = bytearray(gzip.compress(text, 6))
+    z[-6] ^= 0x01                                                                     # the trailer's CRC-32
+    p, _ = run_emu(emu, tmp_path, bytes(z), (8192, 8))
+    assert p.returncode != 0 and "CRC" in p.stderr
+    z = bytearray(gzip.compress(text[:500000], 0))                                    # stored blocks: a flipped payload byte changes nothing but the CRC
+    z[len(z) // 2] ^= 0x20
+    p, _ = run_emu(emu, tmp_path, bytes(z), (8192, 8))
+    assert p.returncode != 0 and "CRC" in p.stderr
 
 
 @pytest.mark.parametrize("every", [1, 3])
