@@ -90,6 +90,23 @@ int main(int argc, char** argv) {
     // `zcat <file> | java ...` (CIB:644-662) becomes: one inflate thread per input, each feeding the device through eqp_chunk_feed as the
     // text comes out of zlib, so inflating, the host-to-device copies and (for the later inputs) each other overlap.  The context is not
     // thread-safe: feed calls are serialised by a mutex (they only copy into a page-locked staging buffer and queue an async copy).
+    eqp_counts C; bool counted = false;
+    // Three `.gz` inputs: read them whole and let eqp_count_chunk_gz inflate them side by side on the device.
+    { const std::string* paths[3] = {&tPath, &jPath, &gPath}; auto p_count_gz = (decltype(&::eqp_count_chunk_gz))dlsym(lib, "eqp_count_chunk_gz");
+      bool allGz = p_count_gz && !getenv("EQP_HOST_INFLATE");
+      for (int f = 0; f < 3; f++) allGz = allGz && paths[f]->size() > 3 && !paths[f]->compare(paths[f]->size() - 3, 3, ".gz");
+      if (allGz) {
+        std::vector<uint8_t> z[3]; bool readOk[3] = {true, true, true}; std::vector<std::thread> rd;
+        for (int f = 0; f < 3; f++) rd.emplace_back([&, f] {
+          FILE* fp = fopen(paths[f]->c_str(), "rb"); if (!fp) { readOk[f] = false; return; }
+          uint8_t buf[1 << 16]; size_t n; while ((n = fread(buf, 1, sizeof buf, fp)) > 0) z[f].insert(z[f].end(), buf, buf + n); fclose(fp); });
+        for (auto& t : rd) t.join();
+        for (int f = 0; f < 3; f++) if (!readOk[f]) { fprintf(stderr, "ERROR: cannot open %s\n", paths[f]->c_str()); return 1; }
+        const int rc = p_count_gz(ctx, &P, z[0].data(), z[0].size(), z[1].data(), z[1].size(), z[2].data(), z[2].size(), &C);
+        if (rc == EQP_OK) counted = true;
+        else if (rc != EQP_ERR_UNSUPPORTED) { fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(ctx)); return 1; }
+      } }
+    if (!counted) {
     if (p_eqp_chunk_begin(ctx, 0, 0, 0)) { fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(ctx)); return 1; }
     // A `.gz` input goes to the device COMPRESSED and is inflated there (eqp_chunk_feed_gz); a file that decoder does not take (several gzip
     // members, BGZF) or EQP_HOST_INFLATE=1 leaves it to the zlib thread below.
@@ -116,8 +133,8 @@ int main(int argc, char** argv) {
       });
       for (auto& t : th) t.join();
       if (!failed.empty()) { fprintf(stderr, "ERROR: %s\n", failed.c_str()); return 1; } }
-    eqp_counts C;
     if (p_eqp_chunk_end(ctx, &P, &C)) { fprintf(stderr, "ERROR: %s\n", p_eqp_last_error(ctx)); return 1; }
+    }
     printf("NUMBER_MAPPED_READS=%lld\n", (long long)C.number_mapped_reads);                      // ConvertSamBed.java:266, CIB:975-976
     const char* names[3] = {"gene", "exon", "junction"}; const double* vec[3] = {C.gene, C.exon, C.junction};
     const uint64_t* fx[3] = {C.gene_fixed, C.exon_fixed, C.junction_fixed};
