@@ -288,6 +288,9 @@ InflateInfo device_inflate(const uint8_t* zHost, const uint8_t* zDev, uint64_t z
     // ---- counting pass over every segment with a start, then the chain walk (a chain member that passed a claimed start proves it bogus)
     std::vector<DecodeItem> items; std::vector<uint32_t> itemOf(nSeg, 0xFFFFFFFFu);
     for (uint32_t i = 0; i < nSeg; i++) if (start[i] != ZF_NONE) { itemOf[i] = (uint32_t)items.size(); items.push_back(DecodeItem{0, 0, i, 0}); }
+    // A large member in which the search finds next to nothing (stored blocks, binary content: the search only recognises blocks that start with
+    // text) would be decoded by a handful of threads for minutes: leave such a file to the host.
+    if (nSeg >= 4096 && items.size() < nSeg / 64) throw InflateError{"no parallelism to be found in this member (" + std::to_string(items.size()) + " block starts in " + std::to_string(nSeg) + " segments: stored blocks or binary content)", true};
     std::vector<SegOut> res(items.size());
     ZF_CUDA(cudaMemcpyAsync(dList, items.data(), items.size() * sizeof(DecodeItem), cudaMemcpyHostToDevice, st));
     timed(info.msDecode, [&] { k_zf_decode<false><<<((uint32_t)items.size() + ZF_THREADS - 1) / ZF_THREADS, ZF_THREADS, ZF_SMEM, st>>>(w, nWords, totalBits, dStart, dBogus, nSeg, dList, (uint32_t)items.size(), nullptr, dRes, dSym); });

@@ -175,8 +175,8 @@ int  eqp_chunk_end(eqp_ctx* ctx, const eqp_params* params, eqp_counts* out);
  * eqp_count_chunk_gz = begin + three members (their copies overlap the inflate of the one before) + end.  Checked: header, block chain
  * (every accepted block start is landed on exactly by the decoder in front of it), ISIZE and the trailer's CRC-32 (computed on the device
  * over the inflated text; EQP_INFLATE_NO_CRC=1 skips it).
- * EQP_ERR_UNSUPPORTED: a valid file this decoder does not take — several members / BGZF — inflate such a file on the host and use
- * eqp_chunk_feed.  EQP_ERR_FORMAT: not gzip / corrupt.
+ * EQP_ERR_UNSUPPORTED: a valid file this decoder does not take — several members / BGZF, or a large member without dynamic blocks that
+ * start with text (stored blocks, binary content) — inflate such a file on the host and use eqp_chunk_feed.  EQP_ERR_FORMAT: not gzip / corrupt.
  * Tunables (environment): EQP_INFLATE_SEG (bytes of compressed data per decoder thread, default 16384), EQP_INFLATE_SCRATCH_GB
  * (16-bit symbol scratch, default 24, at most half of the free device memory; a larger text is written in several waves). */
 typedef struct eqp_inflate_info {

@@ -1,7 +1,8 @@
 // Host emulation of the device inflate (eqp-cluster_b200/csrc/eqp_inflate.h): the same per-thread functions, the kernels' loops run one
 // "thread" after the other, the host driver's chain walk and waves restated.  Test infrastructure (tests/test_inflate.py compares the
 // output with zlib's); never linked into the library.
-//   inflate_emu <in.gz> <out> [segBytes ratio segsPerWave bogusEvery]      bogusEvery = k: every k-th found start is moved one bit on (made wrong)
+//   inflate_emu <in.gz> <out> [segBytes ratio segsPerWave bogusEvery maxGroups]      bogusEvery = k: every k-th found start is moved one bit on
+//   (made wrong); maxGroups: CTAs of the group-parallel window resolve (default 296)
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -20,7 +21,7 @@ static int fail(const char* m) { fprintf(stderr, "ERROR: %s\n", m); return 1; }
 int main(int argc, char** argv) {
   if (argc < 3) return fail("usage: inflate_emu <in.gz> <out> [segBytes ratio segsPerWave]");
   const uint64_t segBytes = argc > 3 ? strtoull(argv[3], 0, 10) : 32768, ratio = argc > 4 ? strtoull(argv[4], 0, 10) : 8;
-  const uint32_t perWave = argc > 5 ? (uint32_t)strtoul(argv[5], 0, 10) : 1u << 30, bogusEvery = argc > 6 ? (uint32_t)strtoul(argv[6], 0, 10) : 0;
+  const uint32_t perWave = argc > 5 ? (uint32_t)strtoul(argv[5], 0, 10) : 1u << 30, bogusEvery = argc > 6 ? (uint32_t)strtoul(argv[6], 0, 10) : 0, maxGroups = argc > 7 ? (uint32_t)strtoul(argv[7], 0, 10) : 296;
   FILE* f = fopen(argv[1], "rb"); if (!f) return fail("cannot open input");
   std::vector<uint8_t> z; { uint8_t buf[1 << 16]; size_t n; while ((n = fread(buf, 1, sizeof buf, f)) > 0) z.insert(z.end(), buf, buf + n); } fclose(f);
   const uint64_t zLen = z.size();
@@ -77,17 +78,41 @@ int main(int argc, char** argv) {
       if (r.status == ZF_NOWINDOW || r.status == ZF_BAD) return fail("invalid deflate data (distance)");
       if (r.status != res[chainSeg[c]].status || r.outLen != chain[c].len) return fail("the two passes disagree");
     }
-    for (uint32_t c = c0; c < c1; c++) {                                 // k_zf_resolve
-      const Chain& cs = chain[c];
-      const uint32_t Tn = cs.len < ZF_WINDOW ? (uint32_t)cs.len : ZF_WINDOW; uint16_t* tail = scratch.data() + cs.sym + (cs.len - Tn); const uint64_t absTail = cs.abs + (cs.len - Tn);
-      std::vector<uint8_t> r(Tn);
-      for (uint32_t k = 0; k < Tn; k++) { uint16_t v = tail[k]; if (v & 0x8000u) { uint64_t a = cs.abs - ZF_WINDOW + (v & 0x7FFFu); if (cs.abs < ZF_WINDOW && (v & 0x7FFFu) < ZF_WINDOW - cs.abs) return fail("distance in front of the stream"); v = win[a & (ZF_WINDOW - 1)]; tail[k] = v; } r[k] = (uint8_t)v; }
-      for (uint32_t k = 0; k < Tn; k++) win[(absTail + k) & (ZF_WINDOW - 1)] = r[k];
+    // k_zf_resolve_groups: per group of consecutive segments a window of 16-bit entries (a byte, or 0x8000|k = byte k of the window in front of the GROUP)
+    const uint32_t n = c1 - c0, nGroups = std::min<uint32_t>(n, std::max<uint32_t>(maxGroups, 1)), perGroup = (n + nGroups - 1) / nGroups, usedGroups = (n + perGroup - 1) / perGroup;
+    std::vector<std::vector<uint16_t>> F(usedGroups, std::vector<uint16_t>(ZF_WINDOW)); std::vector<std::vector<uint8_t>> init(usedGroups, std::vector<uint8_t>(ZF_WINDOW));
+    for (uint32_t g = 0; g < usedGroups; g++) {
+      const uint32_t g0 = c0 + g * perGroup, g1 = std::min(c1, g0 + perGroup); const uint64_t absG = chain[g0].abs; uint64_t absEnd = absG;
+      std::vector<uint16_t> w16(ZF_WINDOW);
+      for (uint32_t k = 0; k < ZF_WINDOW; k++) w16[(absG - ZF_WINDOW + k) & (ZF_WINDOW - 1)] = (uint16_t)(0x8000u | k);
+      for (uint32_t c = g0; c < g1; c++) {
+        const Chain& cs = chain[c];
+        const uint32_t Tn = cs.len < ZF_WINDOW ? (uint32_t)cs.len : ZF_WINDOW; uint16_t* tail = scratch.data() + cs.sym + (cs.len - Tn); const uint64_t absTail = cs.abs + (cs.len - Tn);
+        std::vector<uint16_t> r(Tn);
+        for (uint32_t k = 0; k < Tn; k++) { uint16_t v = tail[k]; if (v & 0x8000u) { v = w16[(cs.abs - ZF_WINDOW + (v & 0x7FFFu)) & (ZF_WINDOW - 1)]; tail[k] = v; } r[k] = v; }
+        for (uint32_t k = 0; k < Tn; k++) w16[(absTail + k) & (ZF_WINDOW - 1)] = r[k];
+        absEnd = cs.abs + cs.len;
+      }
+      for (uint32_t k = 0; k < ZF_WINDOW; k++) F[g][k] = w16[(absEnd - ZF_WINDOW + k) & (ZF_WINDOW - 1)];
+    }
+    // k_zf_chain_windows: win = the 32 K bytes in front of the wave (byte k = position start - 32768 + k), one step per group
+    for (uint32_t g = 0; g < usedGroups; g++) {
+      init[g] = win; std::vector<uint8_t> nw(ZF_WINDOW);
+      for (uint32_t k = 0; k < ZF_WINDOW; k++) { const uint16_t e = F[g][k]; nw[k] = (e & 0x8000u) ? win[e & 0x7FFFu] : (uint8_t)e; }
+      win = nw;
     }
     for (int pass = 0; pass < 2; pass++) for (uint32_t c = c0; c < c1; c++) {  // k_zf_emit
-      const Chain& cs = chain[c];
+      const Chain& cs = chain[c]; const uint32_t g = (c - c0) / perGroup; const uint64_t absG = chain[c0 + g * perGroup].abs;
       const uint64_t Tn = cs.len < ZF_WINDOW ? cs.len : ZF_WINDOW, hd = cs.len - Tn; const uint64_t k0 = pass == 0 ? hd : 0, k1 = pass == 0 ? cs.len : hd;
-      for (uint64_t k = k0; k < k1; k++) { uint16_t v = scratch[cs.sym + k]; if (v & 0x8000u) v = text[cs.abs - ZF_WINDOW + (v & 0x7FFFu)]; text[cs.abs + k] = (uint8_t)v; }
+      for (uint64_t k = k0; k < k1; k++) {
+        uint16_t v = scratch[cs.sym + k];
+        if (v & 0x8000u) {
+          const uint32_t wv = v & 0x7FFFu;
+          if (pass == 0) { if (absG < ZF_WINDOW && wv < ZF_WINDOW - absG) return fail("distance in front of the stream"); v = init[g][wv]; }
+          else { if (cs.abs < ZF_WINDOW && wv < ZF_WINDOW - cs.abs) return fail("distance in front of the stream"); v = text[cs.abs - ZF_WINDOW + wv]; }
+        }
+        text[cs.abs + k] = (uint8_t)v;
+      }
     }
     c0 = c1;
   }

@@ -123,3 +123,12 @@ def test_wrong_block_starts_are_dropped_by_the_chain_walk(emu, tmp_path, text, e
     assert p.returncode == 0, p.stderr
     assert out == text
     assert "bogus 0" not in p.stdout
+
+
+@pytest.mark.parametrize("groups", [1, 3, 7])
+def test_window_resolve_by_groups(emu, tmp_path, text, groups):
+    """The markers in every segment's last 32 K symbols are resolved per group of segments against a window of 16-bit entries, the groups'
+    windows are then composed in order: any group size (and several scratch waves, 9 segments each) must give zlib's bytes."""
+    p, out = run_emu(emu, tmp_path, gzip.compress(text, 6), (8192, 8, 9, 0, groups))
+    assert p.returncode == 0, p.stderr
+    assert out == text
