@@ -132,3 +132,38 @@ def test_window_resolve_by_groups(emu, tmp_path, text, groups):
     p, out = run_emu(emu, tmp_path, gzip.compress(text, 6), (8192, 8, 9, 0, groups))
     assert p.returncode == 0, p.stderr
     assert out == text
+
+
+def test_fuzz_against_zlib(emu, tmp_path, text):
+    """Seeded sweep over content kinds, sizes, levels, strategies (fixed / Huffman-only / RLE blocks), memLevels, flush points, segment sizes down to
+    512 bytes, scratch waves, forced wrong starts and resolve group sizes (1100 such cases were run once by hand; 60 stay in the suite)."""
+    rng = random.Random(7)
+
+    def content(kind, n):
+        if kind == 0:
+            o = rng.randrange(0, max(1, len(text) - n))
+            return text[o:o + n]
+        if kind == 1:
+            return bytes(rng.choice(b"ACGT\t\n") for _ in range(n))
+        if kind == 2:
+            return (b"@SQ\tSN:chr%d\tLN:1000\n" % rng.randrange(99)) * (n // 24 + 1)
+        if kind == 3:
+            return bytes(rng.randrange(32, 127) for _ in range(n))
+        return b"A" * n
+    for it in range(60):
+        n = rng.choice([0, 1, 2, 5, 100, 1000, 5000, 70000, 300000])
+        data = content(rng.randrange(5), n)[:n]
+        c = zlib.compressobj(rng.choice([1, 3, 6, 9]), zlib.DEFLATED, 31, rng.choice([1, 4, 8, 9]),
+                             rng.choice([zlib.Z_DEFAULT_STRATEGY, zlib.Z_FILTERED, zlib.Z_HUFFMAN_ONLY, zlib.Z_RLE, zlib.Z_FIXED]))
+        z, i = b"", 0
+        while i < len(data):
+            k = rng.choice([len(data), 1000, 50000])
+            z += c.compress(data[i:i + k])
+            i += k
+            if rng.random() < 0.2:
+                z += c.flush(rng.choice([zlib.Z_SYNC_FLUSH, zlib.Z_FULL_FLUSH]))
+        z += c.flush()
+        args = (rng.choice([512, 4096, 8192, 65536]), 8, rng.choice([1, 3, 50, 1 << 20]), rng.choice([0, 0, 0, 2, 5]), rng.choice([1, 4, 296]))
+        p, out = run_emu(emu, tmp_path, z, args)
+        assert p.returncode == 0, (it, args, p.stderr)
+        assert out == data, (it, args, len(data))
