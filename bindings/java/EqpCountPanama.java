@@ -16,6 +16,9 @@ public final class EqpCountPanama {
   static final MethodHandle BEGIN = fn("eqp_chunk_begin", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG, JAVA_LONG, JAVA_LONG));
   static final MethodHandle FEED = fn("eqp_chunk_feed", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, JAVA_LONG));
   static final MethodHandle END = fn("eqp_chunk_end", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+  // one complete .sam.gz member (a mapped or direct segment), inflated on the device; returns EQP_ERR_UNSUPPORTED (-5) for files to inflate on the host
+  static final MethodHandle FEED_GZ = fn("eqp_chunk_feed_gz", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, JAVA_LONG));
+  static final MethodHandle COUNT_GZ = fn("eqp_count_chunk_gz", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, JAVA_LONG, ADDRESS, JAVA_LONG, ADDRESS));
   static final MethodHandle ACCUMULATE = fn("eqp_accumulate", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
   static final MethodHandle COMM_ID = fn("eqp_comm_id", FunctionDescriptor.of(JAVA_INT, ADDRESS));
   static final MethodHandle COMM_INIT = fn("eqp_comm_init", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT));
